@@ -1,0 +1,529 @@
+/*
+ * h2ref.c -- plain-C CPU restatement of the halo2 MSM + NTT hot path on BN254.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+ * `--impl reference` leg may load this library; the product (libh2b200.so) never links or calls it.
+ *
+ * PARITY UNPINNED (see oracle/pyref.py header and DESIGN.md): the arithmetic the reference executes
+ * lives in the third-party crate halo2curves 0.6.0 (halo2_backend/Cargo.toml:31), not vendored under
+ * /root/reference and not buildable here (no Rust toolchain).  This file restates that crate's
+ * published algorithms and anchors on the reference's call sites:
+ *   best_multiexp  <- halo2_middleware/src/zal.rs:136-138         (chunk-per-thread Booth Pippenger)
+ *   best_fft       <- halo2_backend/src/poly/domain.rs:238,344    (bit-reverse + radix-2 DIT, twiddle table)
+ *   ifft / distribute_powers_zeta / lagrange_to_coeff / coeff_to_extended / extended_to_coeff /
+ *   divide_by_vanishing_poly <- halo2_backend/src/poly/domain.rs:216-351
+ *   commit / commit_lagrange <- halo2_backend/src/poly/kzg/commitment.rs:305-317,354-366
+ * It is validated against oracle/pyref.py (python big ints) in tests/test_oracle.py.
+ *
+ * Layouts: Fr/Fq = 4 x u64 little-endian limbs, Montgomery form (R = 2^256);
+ * G1Affine = (x,y) 64 B with identity (0,0); G1 = Jacobian (x,y,z) 96 B with identity z = 0.
+ *
+ * Build: gcc -O3 -fopenmp -shared -fPIC -o oracle/libh2ref.so oracle/h2ref.c
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+typedef unsigned __int128 u128;
+typedef struct { uint64_t l[4]; } fe;             /* field element, Montgomery form */
+typedef struct { uint64_t p[4]; uint64_t inv; fe r; fe r2; } field_t;
+
+/* ------------------------------------------------------------------ field constants */
+static const field_t FR = {
+    {0x43e1f593f0000001ULL, 0x2833e84879b97091ULL, 0xb85045b68181585dULL, 0x30644e72e131a029ULL},
+    0xc2e1f593efffffffULL,
+    {{0xac96341c4ffffffbULL, 0x36fc76959f60cd29ULL, 0x666ea36f7879462eULL, 0x0e0a77c19a07df2fULL}},
+    {{0x1bb8e645ae216da7ULL, 0x53fe3ab1e35c59e3ULL, 0x8c49833d53bb8085ULL, 0x0216d0b17f4e44a5ULL}}};
+static const field_t FQ = {
+    {0x3c208c16d87cfd47ULL, 0x97816a916871ca8dULL, 0xb85045b68181585dULL, 0x30644e72e131a029ULL},
+    0x87d20782e4866389ULL,
+    {{0xd35d438dc58f0d9dULL, 0x0a78eb28f5c70b3dULL, 0x666ea36f7879462cULL, 0x0e0a77c19a07df2fULL}},
+    {{0xf32cfc5b538afa89ULL, 0xb5e71911d44501fbULL, 0x47ab1eff0a417ff6ULL, 0x06d89f71cab8351fULL}}};
+
+/* ------------------------------------------------------------------ generic Montgomery arithmetic */
+static inline int fe_is_zero(const fe *a) { return (a->l[0] | a->l[1] | a->l[2] | a->l[3]) == 0; }
+static inline int fe_eq(const fe *a, const fe *b) {
+    return ((a->l[0] ^ b->l[0]) | (a->l[1] ^ b->l[1]) | (a->l[2] ^ b->l[2]) | (a->l[3] ^ b->l[3])) == 0;
+}
+static inline int geq_p(const uint64_t t[4], const uint64_t p[4]) {
+    for (int i = 3; i >= 0; i--) { if (t[i] > p[i]) return 1; if (t[i] < p[i]) return 0; }
+    return 1;
+}
+static inline void sub_p(uint64_t t[4], const uint64_t p[4]) {
+    u128 b = 0;
+    for (int i = 0; i < 4; i++) { u128 d = (u128)t[i] - p[i] - (uint64_t)b; t[i] = (uint64_t)d; b = (d >> 64) & 1; }
+}
+static inline void fe_add(fe *o, const fe *a, const fe *b, const field_t *F) {
+    u128 c = 0; uint64_t t[4];
+    for (int i = 0; i < 4; i++) { c += (u128)a->l[i] + b->l[i]; t[i] = (uint64_t)c; c >>= 64; }
+    if (geq_p(t, F->p)) sub_p(t, F->p);          /* p < 2^254 so no carry out */
+    memcpy(o->l, t, 32);
+}
+static inline void fe_sub(fe *o, const fe *a, const fe *b, const field_t *F) {
+    u128 br = 0; uint64_t t[4];
+    for (int i = 0; i < 4; i++) { u128 d = (u128)a->l[i] - b->l[i] - (uint64_t)br; t[i] = (uint64_t)d; br = (d >> 64) & 1; }
+    if (br) { u128 c = 0; for (int i = 0; i < 4; i++) { c += (u128)t[i] + F->p[i]; t[i] = (uint64_t)c; c >>= 64; } }
+    memcpy(o->l, t, 32);
+}
+static inline void fe_neg(fe *o, const fe *a, const field_t *F) {
+    fe z = {{0, 0, 0, 0}};
+    fe_sub(o, &z, a, F);
+}
+static inline void fe_dbl(fe *o, const fe *a, const field_t *F) { fe_add(o, a, a, F); }
+
+/* CIOS Montgomery multiplication, 4 x 64-bit limbs */
+static inline void fe_mul(fe *o, const fe *a, const fe *b, const field_t *F) {
+    uint64_t t[6] = {0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < 4; i++) {
+        u128 c = 0;
+        for (int j = 0; j < 4; j++) { c += (u128)a->l[j] * b->l[i] + t[j]; t[j] = (uint64_t)c; c >>= 64; }
+        c += t[4]; t[4] = (uint64_t)c; t[5] = (uint64_t)(c >> 64);
+        uint64_t m = t[0] * F->inv;
+        c = (u128)m * F->p[0] + t[0]; c >>= 64;
+        for (int j = 1; j < 4; j++) { c += (u128)m * F->p[j] + t[j]; t[j - 1] = (uint64_t)c; c >>= 64; }
+        c += t[4]; t[3] = (uint64_t)c; t[4] = t[5] + (uint64_t)(c >> 64);
+    }
+    if (t[4] || geq_p(t, F->p)) sub_p(t, F->p);
+    memcpy(o->l, t, 32);
+}
+static inline void fe_sqr(fe *o, const fe *a, const field_t *F) { fe_mul(o, a, a, F); }
+static void fe_from_u64(fe *o, uint64_t v, const field_t *F) {
+    fe t = {{v, 0, 0, 0}};
+    fe_mul(o, &t, &F->r2, F);
+}
+/* Montgomery -> canonical integer limbs (halo2curves to_repr) */
+static inline void fe_to_canonical(uint64_t out[4], const fe *a, const field_t *F) {
+    fe one = {{1, 0, 0, 0}}, t;
+    fe_mul(&t, a, &one, F);
+    memcpy(out, t.l, 32);
+}
+static void fe_pow(fe *o, const fe *a, const uint64_t e[4], const field_t *F) {
+    fe acc = F->r;
+    for (int i = 255; i >= 0; i--) {
+        fe_sqr(&acc, &acc, F);
+        if ((e[i / 64] >> (i % 64)) & 1) fe_mul(&acc, &acc, a, F);
+    }
+    *o = acc;
+}
+static void fe_inv(fe *o, const fe *a, const field_t *F) {       /* Fermat; 0 -> 0 */
+    uint64_t e[4] = {F->p[0] - 2, F->p[1], F->p[2], F->p[3]};
+    fe_pow(o, a, e, F);
+}
+
+/* ------------------------------------------------------------------ G1: y^2 = x^3 + 3 */
+typedef struct { fe x, y; } g1a;          /* affine, identity = (0,0) */
+typedef struct { fe x, y, z; } g1j;       /* Jacobian, identity z = 0 */
+
+static inline int g1a_is_identity(const g1a *p) { return fe_is_zero(&p->x) && fe_is_zero(&p->y); }
+static inline void g1j_set_identity(g1j *p) { memset(p, 0, sizeof *p); p->y = FQ.r; }
+static inline int g1j_is_identity(const g1j *p) { return fe_is_zero(&p->z); }
+
+static void g1j_double(g1j *o, const g1j *p) {                    /* dbl-2009-l */
+    if (g1j_is_identity(p)) { *o = *p; return; }
+    const field_t *F = &FQ;
+    fe a, b, c, d, e, f, t, x3, y3, z3;
+    fe_sqr(&a, &p->x, F); fe_sqr(&b, &p->y, F); fe_sqr(&c, &b, F);
+    fe_add(&t, &p->x, &b, F); fe_sqr(&t, &t, F); fe_sub(&t, &t, &a, F); fe_sub(&t, &t, &c, F); fe_dbl(&d, &t, F);
+    fe_dbl(&e, &a, F); fe_add(&e, &e, &a, F);
+    fe_sqr(&f, &e, F);
+    fe_dbl(&t, &d, F); fe_sub(&x3, &f, &t, F);
+    fe_mul(&z3, &p->y, &p->z, F); fe_dbl(&z3, &z3, F);
+    fe_sub(&t, &d, &x3, F); fe_mul(&y3, &e, &t, F);
+    fe_dbl(&c, &c, F); fe_dbl(&c, &c, F); fe_dbl(&c, &c, F); fe_sub(&y3, &y3, &c, F);
+    o->x = x3; o->y = y3; o->z = z3;
+}
+static void g1j_add_affine(g1j *o, const g1j *p, const g1a *q) {  /* madd-2007-bl */
+    const field_t *F = &FQ;
+    if (g1a_is_identity(q)) { *o = *p; return; }
+    if (g1j_is_identity(p)) { o->x = q->x; o->y = q->y; o->z = F->r; return; }
+    fe z1z1, u2, s2, h, hh, i, j, r, v, t, x3, y3, z3;
+    fe_sqr(&z1z1, &p->z, F);
+    fe_mul(&u2, &q->x, &z1z1, F);
+    fe_mul(&s2, &q->y, &p->z, F); fe_mul(&s2, &s2, &z1z1, F);
+    if (fe_eq(&u2, &p->x)) {
+        if (fe_eq(&s2, &p->y)) { g1j_double(o, p); return; }
+        g1j_set_identity(o); return;
+    }
+    fe_sub(&h, &u2, &p->x, F);
+    fe_sqr(&hh, &h, F);
+    fe_dbl(&i, &hh, F); fe_dbl(&i, &i, F);
+    fe_mul(&j, &h, &i, F);
+    fe_sub(&r, &s2, &p->y, F); fe_dbl(&r, &r, F);
+    fe_mul(&v, &p->x, &i, F);
+    fe_sqr(&x3, &r, F); fe_sub(&x3, &x3, &j, F); fe_dbl(&t, &v, F); fe_sub(&x3, &x3, &t, F);
+    fe_sub(&t, &v, &x3, F); fe_mul(&y3, &r, &t, F); fe_mul(&t, &p->y, &j, F); fe_dbl(&t, &t, F); fe_sub(&y3, &y3, &t, F);
+    fe_add(&z3, &p->z, &h, F); fe_sqr(&z3, &z3, F); fe_sub(&z3, &z3, &z1z1, F); fe_sub(&z3, &z3, &hh, F);
+    o->x = x3; o->y = y3; o->z = z3;
+}
+static void g1j_add(g1j *o, const g1j *p, const g1j *q) {         /* add-2007-bl */
+    const field_t *F = &FQ;
+    if (g1j_is_identity(q)) { *o = *p; return; }
+    if (g1j_is_identity(p)) { *o = *q; return; }
+    fe z1z1, z2z2, u1, u2, s1, s2, h, i, j, r, v, t, x3, y3, z3;
+    fe_sqr(&z1z1, &p->z, F); fe_sqr(&z2z2, &q->z, F);
+    fe_mul(&u1, &p->x, &z2z2, F); fe_mul(&u2, &q->x, &z1z1, F);
+    fe_mul(&s1, &p->y, &q->z, F); fe_mul(&s1, &s1, &z2z2, F);
+    fe_mul(&s2, &q->y, &p->z, F); fe_mul(&s2, &s2, &z1z1, F);
+    if (fe_eq(&u1, &u2)) {
+        if (fe_eq(&s1, &s2)) { g1j_double(o, p); return; }
+        g1j_set_identity(o); return;
+    }
+    fe_sub(&h, &u2, &u1, F);
+    fe_dbl(&i, &h, F); fe_sqr(&i, &i, F);
+    fe_mul(&j, &h, &i, F);
+    fe_sub(&r, &s2, &s1, F); fe_dbl(&r, &r, F);
+    fe_mul(&v, &u1, &i, F);
+    fe_sqr(&x3, &r, F); fe_sub(&x3, &x3, &j, F); fe_dbl(&t, &v, F); fe_sub(&x3, &x3, &t, F);
+    fe_sub(&t, &v, &x3, F); fe_mul(&y3, &r, &t, F); fe_mul(&t, &s1, &j, F); fe_dbl(&t, &t, F); fe_sub(&y3, &y3, &t, F);
+    fe_add(&z3, &p->z, &q->z, F); fe_sqr(&z3, &z3, F); fe_sub(&z3, &z3, &z1z1, F); fe_sub(&z3, &z3, &z2z2, F);
+    fe_mul(&z3, &z3, &h, F);
+    o->x = x3; o->y = y3; o->z = z3;
+}
+static void g1j_to_affine(g1a *o, const g1j *p) {
+    const field_t *F = &FQ;
+    if (g1j_is_identity(p)) { memset(o, 0, sizeof *o); return; }
+    fe zi, zi2, zi3;
+    fe_inv(&zi, &p->z, F); fe_sqr(&zi2, &zi, F); fe_mul(&zi3, &zi2, &zi, F);
+    fe_mul(&o->x, &p->x, &zi2, F); fe_mul(&o->y, &p->y, &zi3, F);
+}
+/* Curve::batch_normalize: Montgomery's trick, identity -> (0,0) */
+static void g1_batch_normalize(g1a *out, const g1j *in, size_t n) {
+    const field_t *F = &FQ;
+    fe *pre = (fe *)malloc(sizeof(fe) * (n ? n : 1));
+    fe acc = F->r;
+    for (size_t i = 0; i < n; i++) { pre[i] = acc; if (!g1j_is_identity(&in[i])) fe_mul(&acc, &acc, &in[i].z, F); }
+    fe inv; fe_inv(&inv, &acc, F);
+    for (size_t i = n; i-- > 0;) {
+        if (g1j_is_identity(&in[i])) { memset(&out[i], 0, sizeof(g1a)); continue; }
+        fe zi, zi2, zi3;
+        fe_mul(&zi, &inv, &pre[i], F);
+        fe_mul(&inv, &inv, &in[i].z, F);
+        fe_sqr(&zi2, &zi, F); fe_mul(&zi3, &zi2, &zi, F);
+        fe_mul(&out[i].x, &in[i].x, &zi2, F); fe_mul(&out[i].y, &in[i].y, &zi3, F);
+    }
+    free(pre);
+}
+static void g1_mul_canonical(g1j *o, const g1a *p, const uint64_t k[4]) {
+    g1j acc; g1j_set_identity(&acc);
+    for (int i = 255; i >= 0; i--) {
+        g1j_double(&acc, &acc);
+        if ((k[i / 64] >> (i % 64)) & 1) g1j_add_affine(&acc, &acc, p);
+    }
+    *o = acc;
+}
+
+/* ------------------------------------------------------------------ MSM: halo2curves 0.6 best_multiexp */
+/* Booth window recoding of the little-endian canonical scalar bytes (halo2curves msm.rs get_booth_index). */
+static int32_t booth_index(size_t window_index, size_t c, const uint8_t *el) {
+    size_t skip_bits = window_index * c; skip_bits = skip_bits ? skip_bits - 1 : 0;
+    size_t skip_bytes = skip_bits / 8;
+    uint8_t v[4] = {0, 0, 0, 0};
+    for (size_t i = 0; i < 4 && skip_bytes + i < 32; i++) v[i] = el[skip_bytes + i];
+    uint32_t tmp = (uint32_t)v[0] | ((uint32_t)v[1] << 8) | ((uint32_t)v[2] << 16) | ((uint32_t)v[3] << 24);
+    if (window_index == 0) tmp <<= 1;
+    tmp >>= skip_bits - skip_bytes * 8;
+    tmp &= (1u << (c + 1)) - 1;
+    int sign = (tmp & (1u << c)) == 0;
+    tmp = (tmp + 1) >> 1;
+    if (sign) return (int32_t)tmp;
+    return -(int32_t)((~(tmp - 1)) & ((1u << c) - 1));
+}
+
+typedef struct { int kind; g1a a; g1j j; } bucket_t;   /* 0 None, 1 Affine, 2 Projective */
+
+static void multiexp_serial(const fe *coeffs, const g1a *bases, size_t n, g1j *acc) {
+    uint8_t *repr = (uint8_t *)malloc(32 * (n ? n : 1));
+    for (size_t i = 0; i < n; i++) { uint64_t t[4]; fe_to_canonical(t, &coeffs[i], &FR); memcpy(repr + 32 * i, t, 32); }
+    size_t c;
+    if (n < 4) c = 1; else if (n < 32) c = 3; else c = (size_t)ceil(log((double)n));
+    size_t number_of_windows = 254 / c + 1;            /* Fr::NUM_BITS = 254 */
+    size_t nb = (size_t)1 << (c - 1);
+    bucket_t *buckets = (bucket_t *)malloc(sizeof(bucket_t) * nb);
+    for (size_t w = number_of_windows; w-- > 0;) {
+        for (size_t i = 0; i < c; i++) g1j_double(acc, acc);
+        for (size_t b = 0; b < nb; b++) buckets[b].kind = 0;
+        for (size_t i = 0; i < n; i++) {
+            int32_t d = booth_index(w, c, repr + 32 * i);
+            if (d == 0) continue;
+            g1a base = bases[i];
+            size_t idx;
+            if (d > 0) idx = (size_t)d - 1; else { idx = (size_t)(-d) - 1; fe_neg(&base.y, &base.y, &FQ); }
+            bucket_t *bk = &buckets[idx];
+            if (bk->kind == 0) { bk->kind = 1; bk->a = base; }
+            else if (bk->kind == 1) {
+                g1j t;
+                if (g1a_is_identity(&bk->a)) g1j_set_identity(&t); else { t.x = bk->a.x; t.y = bk->a.y; t.z = FQ.r; }
+                g1j_add_affine(&bk->j, &t, &base); bk->kind = 2;
+            } else g1j_add_affine(&bk->j, &bk->j, &base);
+        }
+        g1j running; g1j_set_identity(&running);
+        for (size_t b = nb; b-- > 0;) {
+            if (buckets[b].kind == 1) g1j_add_affine(&running, &running, &buckets[b].a);
+            else if (buckets[b].kind == 2) g1j_add(&running, &running, &buckets[b].j);
+            g1j_add(acc, acc, &running);
+        }
+    }
+    free(buckets); free(repr);
+}
+
+static int ref_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+/* coeffs: n x 32 B Montgomery Fr; bases: n x 64 B affine; out: 96 B Jacobian (not normalised) */
+void h2ref_best_multiexp(const void *coeffs_, const void *bases_, size_t n, void *out96) {
+    const fe *coeffs = (const fe *)coeffs_; const g1a *bases = (const g1a *)bases_;
+    size_t threads = (size_t)ref_threads();
+    g1j total; g1j_set_identity(&total);
+    if (n > threads) {
+        size_t chunk = n / threads;
+        size_t num_chunks = (n + chunk - 1) / chunk;
+        g1j *results = (g1j *)malloc(sizeof(g1j) * num_chunks);
+        #pragma omp parallel for schedule(dynamic, 1)
+        for (long ci = 0; ci < (long)num_chunks; ci++) {
+            size_t lo = (size_t)ci * chunk, hi = lo + chunk > n ? n : lo + chunk;
+            g1j_set_identity(&results[ci]);
+            multiexp_serial(coeffs + lo, bases + lo, hi - lo, &results[ci]);
+        }
+        for (size_t ci = 0; ci < num_chunks; ci++) g1j_add(&total, &total, &results[ci]);
+        free(results);
+    } else {
+        multiexp_serial(coeffs, bases, n, &total);
+    }
+    memcpy(out96, &total, 96);
+}
+
+/* naive double-and-add MSM (ground truth for small n) */
+void h2ref_msm_naive(const void *coeffs_, const void *bases_, size_t n, void *out96) {
+    const fe *coeffs = (const fe *)coeffs_; const g1a *bases = (const g1a *)bases_;
+    g1j total; g1j_set_identity(&total);
+    for (size_t i = 0; i < n; i++) {
+        uint64_t k[4]; fe_to_canonical(k, &coeffs[i], &FR);
+        g1j t; g1_mul_canonical(&t, &bases[i], k);
+        g1j_add(&total, &total, &t);
+    }
+    memcpy(out96, &total, 96);
+}
+
+/* Jacobian (96 B) -> affine (64 B), identity -> (0,0)   [Curve::to_affine] */
+void h2ref_to_affine(const void *in96, void *out64) {
+    g1j p; memcpy(&p, in96, 96);
+    g1a a; g1j_to_affine(&a, &p);
+    memcpy(out64, &a, 64);
+}
+int h2ref_is_on_curve(const void *in64) {
+    g1a p; memcpy(&p, in64, 64);
+    if (g1a_is_identity(&p)) return 1;
+    fe y2, x3, b;
+    fe_sqr(&y2, &p.y, &FQ); fe_sqr(&x3, &p.x, &FQ); fe_mul(&x3, &x3, &p.x, &FQ);
+    fe_from_u64(&b, 3, &FQ); fe_add(&x3, &x3, &b, &FQ);
+    return fe_eq(&y2, &x3);
+}
+/* out = a + b on affine points (64 B each) -> affine */
+void h2ref_affine_add(const void *a64, const void *b64, void *out64) {
+    g1a a, b; memcpy(&a, a64, 64); memcpy(&b, b64, 64);
+    g1j t;
+    if (g1a_is_identity(&a)) g1j_set_identity(&t); else { t.x = a.x; t.y = a.y; t.z = FQ.r; }
+    g1j_add_affine(&t, &t, &b);
+    g1a o; g1j_to_affine(&o, &t); memcpy(out64, &o, 64);
+}
+/* out = [k]P, k = Montgomery Fr (32 B), P affine -> affine */
+void h2ref_affine_mul(const void *p64, const void *k32, void *out64) {
+    g1a p; memcpy(&p, p64, 64); fe k; memcpy(&k, k32, 32);
+    uint64_t kc[4]; fe_to_canonical(kc, &k, &FR);
+    g1j t; g1_mul_canonical(&t, &p, kc);
+    g1a o; g1j_to_affine(&o, &t); memcpy(out64, &o, 64);
+}
+
+/* ------------------------------------------------------------------ NTT: halo2curves 0.6 best_fft */
+static inline size_t bitreverse(size_t n, unsigned l) {
+    size_t r = 0;
+    for (unsigned i = 0; i < l; i++) { r = (r << 1) | (n & 1); n >>= 1; }
+    return r;
+}
+static void recursive_butterfly(fe *a, size_t n, size_t twiddle_chunk, const fe *tw, int depth) {
+    const field_t *F = &FR;
+    if (n == 2) {
+        fe t = a[1]; a[1] = a[0]; fe_add(&a[0], &a[0], &t, F); fe_sub(&a[1], &a[1], &t, F);
+        return;
+    }
+    fe *left = a, *right = a + n / 2;
+    if (depth > 0) {
+        #pragma omp task
+        recursive_butterfly(left, n / 2, twiddle_chunk * 2, tw, depth - 1);
+        #pragma omp task
+        recursive_butterfly(right, n / 2, twiddle_chunk * 2, tw, depth - 1);
+        #pragma omp taskwait
+    } else {
+        recursive_butterfly(left, n / 2, twiddle_chunk * 2, tw, 0);
+        recursive_butterfly(right, n / 2, twiddle_chunk * 2, tw, 0);
+    }
+    { fe t = right[0]; right[0] = left[0]; fe_add(&left[0], &left[0], &t, F); fe_sub(&right[0], &right[0], &t, F); }
+    for (size_t i = 1; i < n / 2; i++) {
+        fe t; fe_mul(&t, &right[i], &tw[i * twiddle_chunk], F);
+        right[i] = left[i]; fe_add(&left[i], &left[i], &t, F); fe_sub(&right[i], &right[i], &t, F);
+    }
+}
+/* a: n = 2^log_n Montgomery Fr, in place; omega: 32 B Montgomery Fr */
+void h2ref_best_fft(void *a_, const void *omega_, uint32_t log_n) {
+    const field_t *F = &FR;
+    fe *a = (fe *)a_; fe omega; memcpy(&omega, omega_, 32);
+    size_t n = (size_t)1 << log_n;
+    for (size_t k = 0; k < n; k++) { size_t rk = bitreverse(k, log_n); if (k < rk) { fe t = a[rk]; a[rk] = a[k]; a[k] = t; } }
+    if (log_n == 0) return;
+    size_t half = n / 2 ? n / 2 : 1;
+    fe *tw = (fe *)malloc(sizeof(fe) * half);
+    fe w = F->r;
+    for (size_t i = 0; i < n / 2; i++) { tw[i] = w; fe_mul(&w, &w, &omega, F); }   /* serial scan, as in 0.6.0 */
+    int threads = ref_threads(), log_threads = 0;
+    while ((1 << (log_threads + 1)) <= threads) log_threads++;
+    if ((int)log_n <= log_threads) {
+        size_t chunk = 2, twiddle_chunk = n / 2;
+        for (uint32_t s = 0; s < log_n; s++) {
+            for (size_t base = 0; base < n; base += chunk) {
+                fe *left = a + base, *right = a + base + chunk / 2;
+                { fe t = right[0]; right[0] = left[0]; fe_add(&left[0], &left[0], &t, F); fe_sub(&right[0], &right[0], &t, F); }
+                for (size_t i = 1; i < chunk / 2; i++) {
+                    fe t; fe_mul(&t, &right[i], &tw[i * twiddle_chunk], F);
+                    right[i] = left[i]; fe_add(&left[i], &left[i], &t, F); fe_sub(&right[i], &right[i], &t, F);
+                }
+            }
+            chunk *= 2; twiddle_chunk /= 2;
+        }
+    } else {
+        #pragma omp parallel
+        #pragma omp single
+        recursive_butterfly(a, n, 1, tw, log_threads + 2);
+    }
+    free(tw);
+}
+
+/* arithmetic.rs:124-172 `parallelize`: here a plain omp-for; chunking does not change the values */
+static void scale_all(fe *a, size_t n, const fe *s) {
+    #pragma omp parallel for schedule(static)
+    for (long i = 0; i < (long)n; i++) fe_mul(&a[i], &a[i], s, &FR);
+}
+/* domain.rs:343-351 */
+void h2ref_ifft(void *a_, const void *omega_inv, uint32_t log_n, const void *divisor_) {
+    fe d; memcpy(&d, divisor_, 32);
+    h2ref_best_fft(a_, omega_inv, log_n);
+    scale_all((fe *)a_, (size_t)1 << log_n, &d);
+}
+/* domain.rs:325-341; c1 multiplies index%3==1, c2 multiplies index%3==2 */
+void h2ref_distribute_powers_zeta(void *a_, size_t n, const void *c1_, const void *c2_) {
+    fe *a = (fe *)a_; fe c1, c2; memcpy(&c1, c1_, 32); memcpy(&c2, c2_, 32);
+    #pragma omp parallel for schedule(static)
+    for (long i = 0; i < (long)n; i++) {
+        int r = (int)(i % 3);
+        if (r == 1) fe_mul(&a[i], &a[i], &c1, &FR); else if (r == 2) fe_mul(&a[i], &a[i], &c2, &FR);
+    }
+}
+/* domain.rs:216-226 */
+void h2ref_lagrange_to_coeff(void *a, uint32_t k, const void *omega_inv, const void *ifft_divisor) {
+    h2ref_ifft(a, omega_inv, k, ifft_divisor);
+}
+/* domain.rs:230-244: in = n Fr (copied), out = 2^ext_k Fr */
+void h2ref_coeff_to_extended(const void *in_n, void *out_ne, uint32_t k, uint32_t ext_k,
+                             const void *ext_omega, const void *g_coset, const void *g_coset_inv) {
+    size_t n = (size_t)1 << k, ne = (size_t)1 << ext_k;
+    memcpy(out_ne, in_n, 32 * n);
+    h2ref_distribute_powers_zeta(out_ne, n, g_coset, g_coset_inv);
+    memset((uint8_t *)out_ne + 32 * n, 0, 32 * (ne - n));
+    h2ref_best_fft(out_ne, ext_omega, ext_k);
+}
+/* domain.rs:271-293: in place on 2^ext_k Fr; the caller truncates to out_len */
+void h2ref_extended_to_coeff(void *a_ne, uint32_t ext_k, const void *ext_omega_inv, const void *ext_ifft_divisor,
+                             const void *g_coset, const void *g_coset_inv) {
+    h2ref_ifft(a_ne, ext_omega_inv, ext_k, ext_ifft_divisor);
+    h2ref_distribute_powers_zeta(a_ne, (size_t)1 << ext_k, g_coset_inv, g_coset);
+}
+/* domain.rs:297-316 */
+void h2ref_divide_by_vanishing_poly(void *a_, size_t len, const void *t_evals_, size_t e) {
+    fe *a = (fe *)a_; const fe *t = (const fe *)t_evals_;
+    #pragma omp parallel for schedule(static)
+    for (long i = 0; i < (long)len; i++) fe_mul(&a[i], &a[i], &t[(size_t)i % e], &FR);
+}
+
+/* ------------------------------------------------------------------ scalar helpers for the python side */
+void h2ref_fr_mul(const void *a, const void *b, void *o) { fe x, y, z; memcpy(&x, a, 32); memcpy(&y, b, 32); fe_mul(&z, &x, &y, &FR); memcpy(o, &z, 32); }
+void h2ref_fq_mul(const void *a, const void *b, void *o) { fe x, y, z; memcpy(&x, a, 32); memcpy(&y, b, 32); fe_mul(&z, &x, &y, &FQ); memcpy(o, &z, 32); }
+void h2ref_fr_add(const void *a, const void *b, void *o) { fe x, y, z; memcpy(&x, a, 32); memcpy(&y, b, 32); fe_add(&z, &x, &y, &FR); memcpy(o, &z, 32); }
+void h2ref_fr_sub(const void *a, const void *b, void *o) { fe x, y, z; memcpy(&x, a, 32); memcpy(&y, b, 32); fe_sub(&z, &x, &y, &FR); memcpy(o, &z, 32); }
+void h2ref_fr_inv(const void *a, void *o) { fe x, z; memcpy(&x, a, 32); fe_inv(&z, &x, &FR); memcpy(o, &z, 32); }
+
+/* ------------------------------------------------------------------ synthetic inputs (same stream as pyref.random_fr) */
+static inline uint64_t splitmix64(uint64_t *st) {
+    uint64_t z = (*st += 0x9E3779B97F4A7C15ULL);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+/* n uniform-ish Fr in Montgomery form: 256-bit word stream value reduced mod r, then x R */
+void h2ref_random_fr(void *out_, size_t n, uint64_t seed) {
+    fe *out = (fe *)out_;
+    uint64_t st = seed;
+    for (size_t i = 0; i < n; i++) {
+        uint64_t t[4];
+        for (int l = 0; l < 4; l++) t[l] = splitmix64(&st);
+        /* value < 2^256 < 6r : subtract r until canonical */
+        while (geq_p(t, FR.p)) sub_p(t, FR.p);
+        fe v; memcpy(v.l, t, 32);
+        fe_mul(&out[i], &v, &FR.r2, &FR);
+    }
+}
+/* n distinct affine bases P_i = [t0 + i]G, G = (1,2): incremental adds + batch normalisation */
+void h2ref_gen_bases(void *out_, size_t n, uint64_t t0) {
+    g1a *out = (g1a *)out_;
+    g1a G; fe_from_u64(&G.x, 1, &FQ); fe_from_u64(&G.y, 2, &FQ);
+    int T = ref_threads();
+    #pragma omp parallel for schedule(static, 1)
+    for (int t = 0; t < T; t++) {
+        size_t lo = n * (size_t)t / (size_t)T, hi = n * (size_t)(t + 1) / (size_t)T;
+        if (lo >= hi) continue;
+        uint64_t k[4] = {t0 + lo, 0, 0, 0};
+        g1j cur; g1_mul_canonical(&cur, &G, k);
+        const size_t B = 4096;
+        g1j *buf = (g1j *)malloc(sizeof(g1j) * B);
+        for (size_t s = lo; s < hi; s += B) {
+            size_t m = hi - s < B ? hi - s : B;
+            for (size_t i = 0; i < m; i++) { buf[i] = cur; g1j_add_affine(&cur, &cur, &G); }
+            g1_batch_normalize(out + s, buf, m);
+        }
+        free(buf);
+    }
+}
+/* KZG SRS with a known secret s (Montgomery Fr, 32 B): kzg/commitment.rs:64-131.
+ * g[i] = [s^i]G ; g_lagrange[i] = [ (s^n - 1)/n * w^i / (s - w^i) ]G, w = omega (32 B) */
+void h2ref_kzg_setup(uint32_t k, const void *s_, const void *omega_, void *g_out, void *g_lagrange_out) {
+    size_t n = (size_t)1 << k;
+    fe s, omega; memcpy(&s, s_, 32); memcpy(&omega, omega_, 32);
+    g1a G; fe_from_u64(&G.x, 1, &FQ); fe_from_u64(&G.y, 2, &FQ);
+    fe *sc_g = (fe *)malloc(sizeof(fe) * n), *sc_l = (fe *)malloc(sizeof(fe) * n);
+    fe sp = FR.r, wp = FR.r, sn, n_fe, n_inv, mult, one = FR.r;
+    for (size_t i = 0; i < n; i++) { sc_g[i] = sp; fe_mul(&sp, &sp, &s, &FR); }
+    sn = sp;                                              /* s^n */
+    fe_from_u64(&n_fe, (uint64_t)n, &FR); fe_inv(&n_inv, &n_fe, &FR);
+    fe_sub(&mult, &sn, &one, &FR); fe_mul(&mult, &mult, &n_inv, &FR);
+    for (size_t i = 0; i < n; i++) {
+        fe d, di; fe_sub(&d, &s, &wp, &FR); fe_inv(&di, &d, &FR);
+        fe_mul(&sc_l[i], &mult, &wp, &FR); fe_mul(&sc_l[i], &sc_l[i], &di, &FR);
+        fe_mul(&wp, &wp, &omega, &FR);
+    }
+    g1j *pj = (g1j *)malloc(sizeof(g1j) * n);
+    for (int pass = 0; pass < 2; pass++) {
+        const fe *sc = pass ? sc_l : sc_g;
+        #pragma omp parallel for schedule(dynamic, 64)
+        for (long i = 0; i < (long)n; i++) { uint64_t kc[4]; fe_to_canonical(kc, &sc[i], &FR); g1_mul_canonical(&pj[i], &G, kc); }
+        g1_batch_normalize((g1a *)(pass ? g_lagrange_out : g_out), pj, n);
+    }
+    free(pj); free(sc_g); free(sc_l);
+}
+int h2ref_num_threads(void) { return ref_threads(); }
