@@ -1,0 +1,112 @@
+// host_check.cpp -- unit-test shim: compiles field.cuh / curve.cuh for the HOST (carry-flag PTX ops
+// emulated in C) so the exact limb-level algorithms the kernels run are checked on the CPU against the
+// oracle (tests/test_field_host.py).  Not part of the product path: libh2b200.so never links this.
+#include <cstring>
+#include "curve.cuh"
+using namespace h2b;
+
+template <class F> static F ld(const void* p) { F f; std::memcpy(&f, p, 32); return f; }
+template <class F> static void st(void* p, const F& f) { std::memcpy(p, &f, 32); }
+
+extern "C" {
+void hc_fr_mul(const void* a, const void* b, void* o) { st(o, fe_mul(ld<Fr>(a), ld<Fr>(b))); }
+void hc_fq_mul(const void* a, const void* b, void* o) { st(o, fe_mul(ld<Fq>(a), ld<Fq>(b))); }
+void hc_fr_add(const void* a, const void* b, void* o) { st(o, fe_add(ld<Fr>(a), ld<Fr>(b))); }
+void hc_fr_sub(const void* a, const void* b, void* o) { st(o, fe_sub(ld<Fr>(a), ld<Fr>(b))); }
+void hc_fq_add(const void* a, const void* b, void* o) { st(o, fe_add(ld<Fq>(a), ld<Fq>(b))); }
+void hc_fq_sub(const void* a, const void* b, void* o) { st(o, fe_sub(ld<Fq>(a), ld<Fq>(b))); }
+void hc_fr_neg(const void* a, void* o) { st(o, fe_neg(ld<Fr>(a))); }
+void hc_fr_inv(const void* a, void* o) { st(o, fe_inv(ld<Fr>(a))); }
+void hc_fr_from_mont(const void* a, void* o) { st(o, fe_from_mont(ld<Fr>(a))); }
+void hc_fr_to_mont(const void* a, void* o) { st(o, fe_to_mont(ld<Fr>(a))); }
+
+// acc = sum_i (+/-) pts[i] through xyzz_madd, returned affine (64 B)
+void hc_madd_chain(const void* pts, const uint8_t* neg, size_t n, void* out64) {
+    Xyzz acc = Xyzz::identity();
+    for (size_t i = 0; i < n; i++) {
+        Affine p; std::memcpy(&p, (const uint8_t*)pts + 64 * i, 64);
+        if (p.is_identity()) continue;
+        xyzz_madd(acc, p.x, p.y, neg[i] != 0);
+    }
+    Affine r = xyzz_to_affine(acc);
+    std::memcpy(out64, &r, 64);
+}
+// tree-sum of affine points through xyzz_add (exercises add / double / cancellation), returned affine
+void hc_add_tree(const void* pts, size_t n, void* out64) {
+    Xyzz* v = new Xyzz[n ? n : 1];
+    for (size_t i = 0; i < n; i++) { Affine p; std::memcpy(&p, (const uint8_t*)pts + 64 * i, 64); v[i] = Xyzz::from_affine(p); }
+    // give the operands non-trivial ZZ by doubling+subtracting: P = 2P + (-P)
+    for (size_t i = 0; i < n; i++) v[i] = xyzz_add(xyzz_double(v[i]), xyzz_neg(v[i]));
+    for (size_t s = 1; s < n; s <<= 1)
+        for (size_t i = 0; i + s < n; i += 2 * s) v[i] = xyzz_add(v[i], v[i + s]);
+    Affine r = n ? xyzz_to_affine(v[0]) : xyzz_to_affine(Xyzz::identity());
+    std::memcpy(out64, &r, 64);
+    delete[] v;
+}
+}
+
+// ------------------------------------------------------------------------------------------------
+// NTT: run the very same per-thread level code (ntt.cuh) tile by tile, thread by thread.
+// ------------------------------------------------------------------------------------------------
+#include <vector>
+#include "ntt_plan.hpp"
+
+template <int LOG_S, bool ROW>
+static void run_pass_host(const NttPass& P, uint64_t tiles, const Fr* in, Fr* out) {
+    constexpr int S = 1 << LOG_S;
+    constexpr int NLEV = detail::lev_count(LOG_S);
+    std::vector<U4> slo((size_t)S * NTT_PITCH), shi((size_t)S * NTT_PITCH);
+    const uint32_t threads = S < 32 ? 32 : S;
+    for (uint64_t tile = 0; tile < tiles; tile++) {
+        for (uint32_t t = 0; t < threads; t++) ntt_level<LOG_S, 0, ROW>(P, t, tile, in, out, slo.data(), shi.data(), P.tw_s, 0);
+        if constexpr (NLEV > 1)
+            for (uint32_t t = 0; t < threads; t++) ntt_level<LOG_S, 1, ROW>(P, t, tile, in, out, slo.data(), shi.data(), P.tw_s, 0);
+        if constexpr (NLEV > 2)
+            for (uint32_t t = 0; t < threads; t++) ntt_level<LOG_S, 2, ROW>(P, t, tile, in, out, slo.data(), shi.data(), P.tw_s, 0);
+    }
+}
+template <bool ROW>
+static void run_pass_dispatch(const NttPass& P, uint64_t tiles, const Fr* in, Fr* out) {
+    switch (P.log_s) {
+        case 1: run_pass_host<1, ROW>(P, tiles, in, out); break;
+        case 2: run_pass_host<2, ROW>(P, tiles, in, out); break;
+        case 3: run_pass_host<3, ROW>(P, tiles, in, out); break;
+        case 4: run_pass_host<4, ROW>(P, tiles, in, out); break;
+        case 5: run_pass_host<5, ROW>(P, tiles, in, out); break;
+        case 6: run_pass_host<6, ROW>(P, tiles, in, out); break;
+        case 7: run_pass_host<7, ROW>(P, tiles, in, out); break;
+        case 8: run_pass_host<8, ROW>(P, tiles, in, out); break;
+        case 9: run_pass_host<9, ROW>(P, tiles, in, out); break;
+    }
+}
+
+extern "C" int hc_ntt(const void* in_, uint64_t in_len, void* out_, uint64_t out_len, uint32_t log_n, const void* omega_,
+                      const void* scale_or_null, const void* in_pat_or_null, const void* out_pat_or_null) {
+    if (log_n == 0) { std::memcpy(out_, in_, 32); return 0; }
+    Fr omega = ld<Fr>(omega_);
+    Fr scale; if (scale_or_null) scale = ld<Fr>(scale_or_null);
+    NttPlan pl = ntt_make_plan(log_n, omega, scale_or_null ? &scale : nullptr);
+    std::vector<Fr> tables(pl.table_elems);
+    for (auto& seg : pl.segments) {
+        Fr acc = seg.first;
+        for (uint32_t i = 0; i < seg.count; i++) { tables[seg.offset + i] = acc; acc = fe_mul(acc, seg.root); }
+    }
+    NttFused fz; fz.in_len = in_len; fz.out_len = out_len;
+    Fr ip[2], op[2];
+    if (in_pat_or_null) { std::memcpy(ip, in_pat_or_null, 64); fz.in_pat = ip; }
+    if (out_pat_or_null) { std::memcpy(op, out_pat_or_null, 64); fz.out_pat = op; }
+    NttPass passes[4];
+    ntt_build_passes(pl, tables.data(), scale_or_null ? &scale : nullptr, fz, passes);
+    const Fr* in = (const Fr*)in_;
+    Fr* out = (Fr*)out_;
+    std::vector<Fr> tmp(pl.n_pass > 1 ? (size_t)1 << log_n : 0);
+    for (int j = 0; j < pl.n_pass; j++) {
+        bool last = j == pl.n_pass - 1;
+        const Fr* src = j == 0 ? in : tmp.data();
+        Fr* dst = last ? out : tmp.data();
+        uint64_t tiles = ntt_pass_tiles(pl, j);
+        if (last) run_pass_dispatch<true>(passes[j], tiles, src, dst);
+        else run_pass_dispatch<false>(passes[j], tiles, src, dst);
+    }
+    return pl.n_pass;
+}

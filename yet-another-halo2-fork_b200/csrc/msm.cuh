@@ -1,0 +1,317 @@
+// msm.cuh -- bucket (Pippenger) multi-scalar multiplication over BN254 G1: the GPU side of
+// MsmAccel::msm / best_multiexp (reference halo2_middleware/src/zal.rs:57-58,136-138) behind
+// ParamsKZG::commit / commit_lagrange (halo2_backend/src/poly/kzg/commitment.rs:305-317,354-366).
+//
+// Unlike the reference's chunk-per-thread CPU Pippenger (which replicates the bucket set per thread) the
+// GPU pipeline keeps ONE bucket set per window and bins all n*W signed digits with a counting sort:
+//   1. digits+count   : scalar Montgomery -> canonical, signed base-2^c digits, histogram per (window,bucket)
+//   2. scan           : exclusive prefix sum -> bucket segment offsets
+//   3. scatter        : point index (+ sign bit) written into its bucket segment
+//   4. order          : buckets ordered by population so that the 32 lanes of a warp run equal trip counts
+//   5. accumulate     : one thread per bucket, XYZZ mixed additions (8M+2S) over its segment;
+//                       oversized buckets are split into block-cooperative chunks (tree-reduced)
+//   6. reduce         : per window sum_b b*B_b by chunked running sums + block tree reduction
+//   7. window combine : Horner over the W window sums (host, 64-bit limbs) -> affine
+// All curve arithmetic runs on the integer-multiply pipe (IMAD.WIDE carry chains, field.cuh).
+#pragma once
+#include "curve.cuh"
+
+namespace h2b {
+
+struct MsmGeom {
+    uint32_t c;          // window bits
+    uint32_t windows;    // W = ceil(255 / c)
+    uint32_t nb;         // buckets per window = 2^(c-1)
+    uint32_t n;          // number of (scalar, base) pairs
+};
+
+H2B_HD constexpr uint32_t msm_windows(uint32_t c) { return (255u + c - 1u) / c; }
+
+// Signed window digits of a canonical (non-Montgomery) scalar: value = sum_j d_j * 2^(c*j),
+// d_j in [-2^(c-1)+1, 2^(c-1)].  Calls f(j, d_j) for each window.
+template <class F>
+H2B_HD void msm_signed_digits(const Fr& canon, uint32_t c, uint32_t windows, F f) {
+    uint32_t carry = 0;
+    const uint32_t mask = (1u << c) - 1u, half = 1u << (c - 1);
+    for (uint32_t j = 0; j < windows; j++) {
+        uint32_t bit = j * c, word = bit >> 5, off = bit & 31u;
+        uint32_t v = 0;
+        if (word < 8) {
+            v = canon.l[word] >> off;
+            if (off && word + 1 < 8) v |= canon.l[word + 1] << (32u - off);
+        }
+        v = (v & mask) + carry;
+        int32_t d;
+        if (v > half) { d = (int32_t)v - (int32_t)(1u << c); carry = 1; }
+        else { d = (int32_t)v; carry = 0; }
+        f(j, d);
+    }
+}
+
+// Running-sum reduction of `len` consecutive buckets holding values v0, v0+1, ..., v0+len-1:
+// returns sum_v v * B_v  (chunked summation by parts + one small scalar multiplication).
+H2B_HD Xyzz msm_reduce_chunk(const Xyzz* buckets, uint32_t len, uint32_t v0) {
+    Xyzz run = Xyzz::identity(), acc = Xyzz::identity();
+    for (uint32_t i = len; i-- > 0;) {
+        run = xyzz_add(run, xyzz_load(buckets + i));
+        acc = xyzz_add(acc, run);
+    }
+    // acc = sum (v - v0 + 1) B_v ;  add (v0 - 1) * run
+    uint32_t k = v0 - 1;
+    if (k) {
+        Xyzz m = Xyzz::identity();
+        for (int bit = 31; bit >= 0; bit--) {
+            m = xyzz_double(m);
+            if ((k >> bit) & 1u) m = xyzz_add(m, run);
+        }
+        acc = xyzz_add(acc, m);
+    }
+    return acc;
+}
+
+#if defined(__CUDACC__)
+// ------------------------------------------------------------------------------------------------
+// kernels
+// ------------------------------------------------------------------------------------------------
+// 1. histogram of (window, |digit|) keys.  counts has windows*nb entries.
+__global__ void msm_count_kernel(MsmGeom g, const Fr* __restrict__ scalars, uint32_t* __restrict__ counts) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n) return;
+    Fr canon = fe_from_mont(fe_load(scalars + i));
+    msm_signed_digits(canon, g.c, g.windows, [&](uint32_t j, int32_t d) {
+        if (d != 0) {
+            uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
+            atomicAdd(counts + (size_t)j * g.nb + (mag - 1), 1u);
+        }
+    });
+}
+
+// 3. scatter point indices into bucket segments; cursor starts as a copy of the segment offsets.
+__global__ void msm_scatter_kernel(MsmGeom g, const Fr* __restrict__ scalars, uint32_t* __restrict__ cursor,
+                                   uint32_t* __restrict__ entries) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= g.n) return;
+    Fr canon = fe_from_mont(fe_load(scalars + i));
+    msm_signed_digits(canon, g.c, g.windows, [&](uint32_t j, int32_t d) {
+        if (d != 0) {
+            uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
+            uint32_t pos = atomicAdd(cursor + (size_t)j * g.nb + (mag - 1), 1u);
+            entries[pos] = i | (d < 0 ? 0x80000000u : 0u);
+        }
+    });
+}
+
+// ---- exclusive scan over uint32 (three small kernels; sizes up to a few million) ----------------
+constexpr int SCAN_BLOCK = 1024;
+__global__ void scan_block_sums_kernel(const uint32_t* __restrict__ in, uint32_t n, uint32_t* __restrict__ block_sums) {
+    __shared__ uint32_t sh[32];
+    uint32_t i = blockIdx.x * SCAN_BLOCK + threadIdx.x;
+    uint32_t v = i < n ? in[i] : 0u;
+    for (int o = 16; o; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        v = sh[threadIdx.x];
+        for (int o = 16; o; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+        if (threadIdx.x == 0) block_sums[blockIdx.x] = v;
+    }
+}
+// in-place exclusive scan of `m` values by ONE block (m up to ~1e5); total written to *total
+__global__ void scan_single_block_kernel(uint32_t* data, uint32_t m, uint32_t* total) {
+    __shared__ uint32_t sh[SCAN_BLOCK];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < m; base += SCAN_BLOCK) {
+        uint32_t i = base + threadIdx.x;
+        uint32_t v = i < m ? data[i] : 0u;
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int o = 1; o < SCAN_BLOCK; o <<= 1) {
+            uint32_t t = threadIdx.x >= (uint32_t)o ? sh[threadIdx.x - o] : 0u;
+            __syncthreads();
+            sh[threadIdx.x] += t;
+            __syncthreads();
+        }
+        uint32_t incl = sh[threadIdx.x];
+        if (i < m) data[i] = carry + incl - v;
+        __syncthreads();
+        if (threadIdx.x == SCAN_BLOCK - 1) carry += incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && total) *total = carry;
+}
+// out[i] = exclusive prefix of in within the block + block_offsets[block]; out2 (optional) gets a copy
+__global__ void scan_apply_kernel(const uint32_t* __restrict__ in, uint32_t n, const uint32_t* __restrict__ block_offsets,
+                                  uint32_t* __restrict__ out, uint32_t* __restrict__ out2) {
+    __shared__ uint32_t sh[SCAN_BLOCK];
+    uint32_t i = blockIdx.x * SCAN_BLOCK + threadIdx.x;
+    uint32_t v = i < n ? in[i] : 0u;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < SCAN_BLOCK; o <<= 1) {
+        uint32_t t = threadIdx.x >= (uint32_t)o ? sh[threadIdx.x - o] : 0u;
+        __syncthreads();
+        sh[threadIdx.x] += t;
+        __syncthreads();
+    }
+    if (i < n) {
+        uint32_t e = block_offsets[blockIdx.x] + sh[threadIdx.x] - v;
+        out[i] = e;
+        if (out2) out2[i] = e;
+    }
+}
+
+// ---- 4. order buckets by population (descending), and list the oversized ones --------------------
+constexpr uint32_t MSM_SIZE_BINS = 4096;
+// size_hist[MSM_SIZE_BINS]: bin = min(size, BINS-1); stored reversed so that an ascending scan gives descending size
+__global__ void msm_size_hist_kernel(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends, uint32_t nkeys,
+                                     uint32_t* __restrict__ size_hist) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nkeys) return;
+    uint32_t s = ends[k] - offsets[k];
+    uint32_t bin = s < MSM_SIZE_BINS - 1 ? s : MSM_SIZE_BINS - 1;
+    atomicAdd(size_hist + (MSM_SIZE_BINS - 1 - bin), 1u);
+}
+__global__ void msm_size_scatter_kernel(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends, uint32_t nkeys,
+                                        uint32_t* __restrict__ size_cursor, uint32_t* __restrict__ order) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nkeys) return;
+    uint32_t s = ends[k] - offsets[k];
+    uint32_t bin = s < MSM_SIZE_BINS - 1 ? s : MSM_SIZE_BINS - 1;
+    uint32_t pos = atomicAdd(size_cursor + (MSM_SIZE_BINS - 1 - bin), 1u);
+    order[pos] = k;
+}
+
+// ---- 5. bucket accumulation: one thread per bucket, in population order --------------------------
+// Buckets larger than `long_threshold` are left to msm_accumulate_long_kernel.
+__global__ void __launch_bounds__(128)
+msm_accumulate_kernel(const Affine* __restrict__ bases, const uint32_t* __restrict__ entries,
+                      const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends,
+                      const uint32_t* __restrict__ order, uint32_t nkeys, uint32_t long_threshold,
+                      Xyzz* __restrict__ buckets) {
+    uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= nkeys) return;
+    uint32_t key = order[tid];
+    uint32_t e = offsets[key], end = ends[key];
+    if (end - e > long_threshold) return;
+    Xyzz acc = Xyzz::identity();
+    if (e < end) {
+        uint32_t ent = entries[e];
+        Affine p = affine_load(bases + (ent & 0x7fffffffu));
+        while (true) {
+            uint32_t e1 = e + 1;
+            uint32_t ent_n = 0;
+            Affine pn;
+            bool more = e1 < end;
+            if (more) {                                   // prefetch the next point under the current addition
+                ent_n = entries[e1];
+                pn = affine_load(bases + (ent_n & 0x7fffffffu));
+            }
+            if (!p.is_identity()) xyzz_madd(acc, p.x, p.y, (ent >> 31) != 0);
+            if (!more) break;
+            p = pn; ent = ent_n; e = e1;
+        }
+    }
+    xyzz_store(buckets + key, acc);
+}
+
+// Oversized buckets (skewed scalars: selector-like columns put most points into one bucket) are cut into
+// chunks of MSM_LONG_CHUNK entries; one block per chunk strides over its entries and tree-reduces through
+// shared memory; a second kernel sums the chunk partials of each oversized bucket.
+constexpr int MSM_LONG_THREADS = 128;
+constexpr uint32_t MSM_LONG_CHUNK = 4096;
+struct MsmLongInfo { uint32_t key, task_base, ntasks, pad; };
+struct MsmLongTask { uint32_t key, chunk; };
+
+__global__ void msm_long_list_kernel(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends, uint32_t nkeys,
+                                     uint32_t long_threshold, MsmLongInfo* __restrict__ long_info,
+                                     MsmLongTask* __restrict__ tasks, uint32_t* __restrict__ counters /* [0]=#long, [1]=#tasks */) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nkeys) return;
+    uint32_t s = ends[k] - offsets[k];
+    if (s > long_threshold) {
+        uint32_t nt = (s + MSM_LONG_CHUNK - 1) / MSM_LONG_CHUNK;
+        uint32_t li = atomicAdd(counters + 0, 1u);
+        uint32_t base = atomicAdd(counters + 1, nt);
+        MsmLongInfo info; info.key = k; info.task_base = base; info.ntasks = nt; info.pad = 0;
+        long_info[li] = info;
+        for (uint32_t t = 0; t < nt; t++) { MsmLongTask tk; tk.key = k; tk.chunk = t; tasks[base + t] = tk; }
+    }
+}
+__global__ void __launch_bounds__(MSM_LONG_THREADS)
+msm_accumulate_long_kernel(const Affine* __restrict__ bases, const uint32_t* __restrict__ entries,
+                           const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends,
+                           const MsmLongTask* __restrict__ tasks, const uint32_t* __restrict__ counters,
+                           Xyzz* __restrict__ partials) {
+    __shared__ Xyzz sh[MSM_LONG_THREADS];
+    uint32_t total = counters[1];
+    for (uint32_t task = blockIdx.x; task < total; task += gridDim.x) {
+        MsmLongTask tk = tasks[task];
+        uint32_t lo = offsets[tk.key] + tk.chunk * MSM_LONG_CHUNK, end = ends[tk.key];
+        uint32_t hi = lo + MSM_LONG_CHUNK < end ? lo + MSM_LONG_CHUNK : end;
+        Xyzz acc = Xyzz::identity();
+        for (uint32_t e = lo + threadIdx.x; e < hi; e += MSM_LONG_THREADS) {
+            uint32_t ent = entries[e];
+            Affine p = affine_load(bases + (ent & 0x7fffffffu));
+            if (!p.is_identity()) xyzz_madd(acc, p.x, p.y, (ent >> 31) != 0);
+        }
+        sh[threadIdx.x] = acc;
+        __syncthreads();
+        for (int s = MSM_LONG_THREADS / 2; s > 0; s >>= 1) {
+            if (threadIdx.x < (uint32_t)s) sh[threadIdx.x] = xyzz_add(sh[threadIdx.x], sh[threadIdx.x + s]);
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) xyzz_store(partials + task, sh[0]);
+        __syncthreads();
+    }
+}
+__global__ void __launch_bounds__(MSM_LONG_THREADS)
+msm_long_combine_kernel(const MsmLongInfo* __restrict__ long_info, const uint32_t* __restrict__ counters,
+                        const Xyzz* __restrict__ partials, Xyzz* __restrict__ buckets) {
+    __shared__ Xyzz sh[MSM_LONG_THREADS];
+    uint32_t nlong = counters[0];
+    for (uint32_t li = blockIdx.x; li < nlong; li += gridDim.x) {
+        MsmLongInfo info = long_info[li];
+        Xyzz acc = Xyzz::identity();
+        for (uint32_t t = threadIdx.x; t < info.ntasks; t += MSM_LONG_THREADS)
+            acc = xyzz_add(acc, xyzz_load(partials + info.task_base + t));
+        sh[threadIdx.x] = acc;
+        __syncthreads();
+        for (int s = MSM_LONG_THREADS / 2; s > 0; s >>= 1) {
+            if (threadIdx.x < (uint32_t)s) sh[threadIdx.x] = xyzz_add(sh[threadIdx.x], sh[threadIdx.x + s]);
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) xyzz_store(buckets + info.key, sh[0]);
+        __syncthreads();
+    }
+}
+
+// ---- 6. bucket reduction --------------------------------------------------------------------------
+// grid = (slices, windows); block = MSM_REDUCE_THREADS.  Block (s, j) reduces buckets
+// [s*nb/slices, (s+1)*nb/slices) of window j to one point: sum_v v*B_v over its value range.
+constexpr int MSM_REDUCE_THREADS = 128;
+__global__ void __launch_bounds__(MSM_REDUCE_THREADS)
+msm_reduce_kernel(MsmGeom g, const Xyzz* __restrict__ buckets, uint32_t slices, Xyzz* __restrict__ window_partials) {
+    __shared__ Xyzz sh[MSM_REDUCE_THREADS];
+    uint32_t j = blockIdx.y, s = blockIdx.x;
+    uint32_t per_slice = g.nb / slices;                       // power of two, >= MSM_REDUCE_THREADS
+    uint32_t per_thread = per_slice / MSM_REDUCE_THREADS;
+    uint32_t first = s * per_slice + threadIdx.x * per_thread;     // bucket index (value = index + 1)
+    sh[threadIdx.x] = msm_reduce_chunk(buckets + (size_t)j * g.nb + first, per_thread, first + 1);
+    __syncthreads();
+    for (int st = MSM_REDUCE_THREADS / 2; st > 0; st >>= 1) {
+        if (threadIdx.x < (uint32_t)st) sh[threadIdx.x] = xyzz_add(sh[threadIdx.x], sh[threadIdx.x + st]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) xyzz_store(window_partials + (size_t)j * slices + s, sh[0]);
+}
+// small-window fallback: nb < MSM_REDUCE_THREADS -> one thread per window does the whole running sum
+__global__ void msm_reduce_small_kernel(MsmGeom g, const Xyzz* __restrict__ buckets, Xyzz* __restrict__ window_partials) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.windows) return;
+    xyzz_store(window_partials + j, msm_reduce_chunk(buckets + (size_t)j * g.nb, g.nb, 1));
+}
+#endif  // __CUDACC__
+
+}  // namespace h2b
