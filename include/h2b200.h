@@ -1,0 +1,143 @@
+/*
+ * h2b200.h -- C ABI of libh2b200.so: B200-native (sm_100a) MSM and NTT for the halo2 KZG prover on BN254.
+ *
+ * This is the drop-in boundary for the two data-parallel kernels of the reference
+ * (yetanotherco/yet-another-halo2-fork, paths below are under /root/reference):
+ *
+ *   MSM   halo2_middleware/src/zal.rs:57-103     trait MsmAccel<C> { msm, get_*_descriptor, msm_with_cached_* }
+ *         halo2_middleware/src/zal.rs:136-138    H2cEngine::msm -> halo2curves::msm::best_multiexp
+ *         halo2_backend/src/poly/kzg/commitment.rs:305-317,354-366   ParamsKZG::commit_lagrange / commit
+ *   NTT   halo2_backend/src/poly/domain.rs:216   EvaluationDomain::lagrange_to_coeff
+ *         halo2_backend/src/poly/domain.rs:230   EvaluationDomain::coeff_to_extended
+ *         halo2_backend/src/poly/domain.rs:271   EvaluationDomain::extended_to_coeff
+ *         halo2_backend/src/poly/domain.rs:297   EvaluationDomain::divide_by_vanishing_poly (fusable)
+ *         halo2_backend/src/poly/domain.rs:343   ifft = best_fft + scale  (halo2curves::fft::best_fft)
+ *
+ * Data layouts are the reference's in-memory layouts (halo2curves 0.6 bn256), so Rust slices are passed
+ * as-is with no conversion:
+ *   Fr, Fq      32 B  = [u64; 4] little-endian limbs, Montgomery form (R = 2^256), fully reduced
+ *   G1Affine    64 B  = (x, y), identity encoded as (0, 0)
+ *   G1          96 B  = Jacobian (x, y, z), identity z = 0.  Results are returned NORMALISED (z = 1, or
+ *                       (0, 1, 0) for the identity), i.e. the canonical representative Curve::to_affine /
+ *                       batch_normalize would produce, so results are bit-identical whatever the bucket order.
+ *
+ * Conventions: every function returns 0 on success and a negative H2B_E_* code on failure (the reason is
+ * kept per context: h2b_last_error).  Host pointers are borrowed for the duration of the call only.  All
+ * calls are synchronous on return and serialised per context (one context may be shared by threads).
+ * Nothing throws across this boundary.  There is no CPU fallback: without a usable sm_100 device
+ * h2b_init fails.
+ *
+ * INTEGRATION.md shows the Rust binding (`impl MsmAccel<G1Affine> for B200Engine`, EvaluationDomain patch).
+ */
+#ifndef H2B200_H
+#define H2B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct h2b_ctx h2b_ctx;
+
+enum {
+    H2B_OK = 0,
+    H2B_E_INVALID = -1,   /* bad argument (null pointer, length mismatch, log_n out of range, unknown handle) */
+    H2B_E_CUDA = -2,      /* CUDA runtime / launch failure */
+    H2B_E_NOMEM = -3,     /* device or host allocation failed */
+    H2B_E_NODEVICE = -4   /* no usable GPU */
+};
+
+/* ---- context ------------------------------------------------------------------------------------------
+ * Replaces the engine object of zal.rs:182-243 (PlonkEngine { msm_backend }): one context owns the devices,
+ * streams, resident bases and twiddle tables.  device_ids == NULL, n_devices == 0 selects device 0.
+ * With n_devices > 1 the MSM is sharded by contiguous point range and batched NTT columns are dealt
+ * round-robin (a single NTT stays on device_ids[0]). */
+int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices);
+void h2b_destroy(h2b_ctx* ctx);
+const char* h2b_last_error(const h2b_ctx* ctx);
+int h2b_device_count(void);
+const char* h2b_version(void);
+
+/* ---- MSM: MsmAccel<G1Affine> ---------------------------------------------------------------------------
+ * h2b_bases_register     = MsmAccel::get_base_descriptor (zal.rs:82): copy n affine bases to the device(s)
+ *                          once (ParamsKZG::g / g_lagrange stay resident across commits).
+ * h2b_bases_register_device: same, adopting a buffer that already lives on device 0 (not copied, not freed).
+ * h2b_bases_release      = Drop of the descriptor (zal.rs:47-50).
+ * h2b_msm                = MsmAccel::msm_with_cached_base (zal.rs:90): uses bases[0..n) of the handle; n may
+ *                          be smaller than the registered count (commit on a shorter polynomial,
+ *                          commitment.rs:313-316) but never larger -> H2B_E_INVALID (the reference asserts).
+ * h2b_msm_raw            = MsmAccel::msm (zal.rs:58): uncached bases, copied for this call only.
+ * h2b_msm_device         = same as h2b_msm with the scalars already resident on device 0 (descriptor path,
+ *                          MsmAccel::msm_with_cached_inputs, zal.rs:96).
+ * out96: G1 Jacobian, normalised. */
+int h2b_bases_register(h2b_ctx* ctx, const void* bases, size_t n, uint64_t* handle_out);
+int h2b_bases_register_device(h2b_ctx* ctx, const void* d_bases, size_t n, uint64_t* handle_out);
+int h2b_bases_release(h2b_ctx* ctx, uint64_t handle);
+int h2b_msm(h2b_ctx* ctx, uint64_t bases_handle, const void* scalars, size_t n, void* out96);
+int h2b_msm_raw(h2b_ctx* ctx, const void* bases, const void* scalars, size_t n, void* out96);
+int h2b_msm_device(h2b_ctx* ctx, uint64_t bases_handle, const void* d_scalars, size_t n, void* out96);
+
+/* Multi-process sharding (one process per GPU, point-range partition): each rank computes the per-window
+ * bucket sums of its own range, the ranks exchange H2B_MSM_WINDOW_BYTES * windows bytes (a tiny all-gather),
+ * and any rank folds them.  Window size c is a pure function of n_total so that all ranks agree.
+ *   h2b_msm_windows : out_windows receives `*windows_out` points of H2B_MSM_WINDOW_BYTES each.
+ *   h2b_msm_combine : host-only; parts = n_parts consecutive window arrays. */
+#define H2B_MSM_WINDOW_BYTES 128
+#define H2B_MSM_MAX_WINDOWS 64
+int h2b_msm_windows(h2b_ctx* ctx, uint64_t bases_handle, const void* scalars, int scalars_on_device, size_t n,
+                    size_t n_total, void* out_windows, uint32_t* c_out, uint32_t* windows_out);
+int h2b_msm_combine(const void* parts, uint32_t n_parts, uint32_t c, uint32_t windows, void* out96);
+
+/* ---- NTT: EvaluationDomain ----------------------------------------------------------------------------
+ * All roots / divisors / coset constants are the fields of the reference's EvaluationDomain (domain.rs:18-33)
+ * passed in as 32-byte Montgomery Fr; nothing is re-derived on this side.
+ *
+ * h2b_ntt               best_fft(a, omega, log_n) in place; if scale32 != NULL every output is multiplied by
+ *                       it (ifft, domain.rs:343-351: omega = omega_inv, scale = ifft_divisor)
+ *                       -> lagrange_to_coeff(a) = h2b_ntt(a, k, omega_inv, ifft_divisor).
+ * h2b_coeff_to_extended domain.rs:230-244: out[0..2^ext_k) = best_fft(zero_extend(a[i] * {1,g_coset,g_coset_inv}[i%3])).
+ * h2b_extended_to_coeff domain.rs:271-293: ifft with ext_omega_inv / ext_ifft_divisor, then
+ *                       a[i] *= {1,g_coset_inv,g_coset}[i%3], truncated to out_len (= n * quotient_poly_degree).
+ *                       If t_evals32 != NULL (e = n_t entries, domain.rs:297-316) the input is first divided by
+ *                       the vanishing polynomial: a[i] *= t_evals[i % n_t]  (divide_by_vanishing_poly fused).
+ * *_device variants take device pointers (device 0) and leave the result on the device.
+ * h2b_ntt_batch         n_cols independent transforms of the same shape (the per-column coset NTTs of
+ *                       evaluate_h, plonk/evaluation.rs:344-361); columns are dealt across the context's devices. */
+int h2b_ntt(h2b_ctx* ctx, void* a, uint32_t log_n, const void* omega32, const void* scale32_or_null);
+int h2b_ntt_device(h2b_ctx* ctx, void* d_a, uint32_t log_n, const void* omega32, const void* scale32_or_null);
+int h2b_coeff_to_extended(h2b_ctx* ctx, const void* in_n, void* out_ne, uint32_t k, uint32_t ext_k,
+                          const void* ext_omega32, const void* g_coset32, const void* g_coset_inv32);
+int h2b_coeff_to_extended_device(h2b_ctx* ctx, const void* d_in_n, void* d_out_ne, uint32_t k, uint32_t ext_k,
+                                 const void* ext_omega32, const void* g_coset32, const void* g_coset_inv32);
+int h2b_extended_to_coeff(h2b_ctx* ctx, const void* a_ne, void* out, uint32_t ext_k, const void* ext_omega_inv32,
+                          const void* ext_ifft_divisor32, const void* g_coset32, const void* g_coset_inv32,
+                          size_t out_len, const void* t_evals32_or_null, size_t n_t);
+int h2b_extended_to_coeff_device(h2b_ctx* ctx, const void* d_a_ne, void* d_out, uint32_t ext_k,
+                                 const void* ext_omega_inv32, const void* ext_ifft_divisor32, const void* g_coset32,
+                                 const void* g_coset_inv32, size_t out_len, const void* t_evals32_or_null, size_t n_t);
+int h2b_ntt_batch(h2b_ctx* ctx, void* const* cols, size_t n_cols, uint32_t log_n, const void* omega32,
+                  const void* scale32_or_null);
+int h2b_coeff_to_extended_batch(h2b_ctx* ctx, const void* const* in_cols, void* const* out_cols, size_t n_cols,
+                                uint32_t k, uint32_t ext_k, const void* ext_omega32, const void* g_coset32,
+                                const void* g_coset_inv32);
+
+/* ---- measurement hooks (bench.py / profiles) -----------------------------------------------------------
+ * h2b_last_call_ms: device time of the most recent call on this context, CUDA events on the launching
+ *                   stream from the first to the last enqueued operation (copies included if the call copied).
+ * h2b_profile: when enabled every kernel launch is bracketed by events; h2b_profile_read writes a JSON object
+ *              {"kernel": {"ms": total, "launches": count}, ...} (and resets the counters). */
+double h2b_last_call_ms(const h2b_ctx* ctx);
+int h2b_profile_enable(h2b_ctx* ctx, int on);
+int h2b_profile_read(h2b_ctx* ctx, char* json_out, size_t cap);
+uint64_t h2b_launch_count(const h2b_ctx* ctx);   /* kernels launched by this context since h2b_init */
+
+/* integer-multiply pipe calibration: runs a dependent-free IMAD.WIDE loop on every SM and returns the
+ * sustained rate in units of 32x32->64 multiply-adds per second (the MSM / NTT roofline denominator). */
+int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* H2B200_H */

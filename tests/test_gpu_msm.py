@@ -1,0 +1,164 @@
+"""GPU parity: the CUDA MSM (through the C ABI / MsmAccel mirror) against the CPU oracle.
+Bit-exact: the normalised result must equal the oracle's affine point limb for limb."""
+import ctypes
+
+import numpy as np
+import pytest
+
+from oracle import cref as C
+from oracle import pyref as R
+
+pytestmark = pytest.mark.gpu
+
+ONE_Q = C.limbs_from_int((1 << 256) % R.Q_MOD)
+
+
+def check(out12, exp_affine):
+    if not exp_affine.any():
+        assert not out12[:4].any() and not out12[8:].any() and np.array_equal(out12[4:8], ONE_Q)
+    else:
+        assert np.array_equal(out12[8:], ONE_Q), "result must be normalised (z = 1)"
+        assert np.array_equal(out12[:8], exp_affine)
+
+
+def oracle_affine(s, b):
+    return C.to_affine(C.best_multiexp(s, b))
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 31, 32, 33, 100, 1 << 10, (1 << 12) + 5, 1 << 14, 1 << 16])
+def test_msm_matches_oracle(engine, n):
+    """zal.rs:262-349 test_msm_zal restated: engine.msm == best_multiexp == msm_with_cached_base."""
+    s = C.random_fr(n, 10 + n)
+    b = C.gen_bases(n, 3)
+    exp = oracle_affine(s, b)
+    check(engine.msm(s, b), exp)
+    desc = engine.get_base_descriptor(b)
+    check(engine.msm_with_cached_base(s, desc), exp)
+    cdesc = engine.get_coeffs_descriptor(s)
+    check(engine.msm_with_cached_inputs(cdesc, desc), exp)
+    check(engine.msm_with_cached_scalars(cdesc, b), exp)
+    desc.release()
+
+
+@pytest.mark.parametrize("c", [2, 3, 5, 8, 11, 13, 16, 18, 20])
+def test_window_sizes(engine, c, monkeypatch):
+    monkeypatch.setenv("H2B_MSM_C", str(c))
+    n = 3000
+    s = C.random_fr(n, c)
+    b = C.gen_bases(n, 9)
+    check(engine.msm(s, b), oracle_affine(s, b))
+
+
+def test_edge_scalars_and_bases(engine):
+    n = 600
+    s = C.random_fr(n, 5)
+    b = C.gen_bases(n, 1)
+    s[0] = 0
+    s[1] = C.mont_from_int(1, R.R_MOD)
+    s[2] = C.mont_from_int(R.R_MOD - 1, R.R_MOD)
+    s[3] = C.mont_from_int((1 << 253) + 12345, R.R_MOD)
+    b[4] = 0                                  # identity base (0,0)
+    b[6] = b[5]; s[6] = s[5]                  # repeated (P, k), (P, k): doubling inside a bucket
+    b[8] = b[7]; s[8] = C.mont_from_int((-C.int_from_mont(s[7], R.R_MOD)) % R.R_MOD, R.R_MOD)   # P, -k: cancellation
+    check(engine.msm(s, b), oracle_affine(s, b))
+    # empty, all-zero scalars, all-identity bases -> identity
+    check(engine.msm(np.zeros((0, 4), dtype=np.uint64), np.zeros((0, 8), dtype=np.uint64)), np.zeros(8, dtype=np.uint64))
+    check(engine.msm(np.zeros((50, 4), dtype=np.uint64), C.gen_bases(50, 2)), np.zeros(8, dtype=np.uint64))
+    check(engine.msm(C.random_fr(50, 1), np.zeros((50, 8), dtype=np.uint64)), np.zeros(8, dtype=np.uint64))
+    # single generator times k
+    k = C.random_fr(1, 4)
+    g = C.gen_bases(1, 1)
+    check(engine.msm(k, g), C.affine_mul(g[0], k[0]))
+
+
+def test_skewed_scalars_long_buckets(engine):
+    """Columns of a real circuit are mostly 0/1/small values (SURVEY.md §7 hard parts): one bucket holds
+    most of the points, which exercises the block-cooperative oversized-bucket path."""
+    n = 1 << 15
+    s = C.random_fr(n, 21)
+    one = C.mont_from_int(1, R.R_MOD)
+    rng = np.random.default_rng(3)
+    sel = rng.random(n)
+    s[sel < 0.45] = 0
+    s[(sel >= 0.45) & (sel < 0.9)] = one
+    small = np.where(sel >= 0.97)[0]
+    for i in small:
+        s[i] = C.mont_from_int(int(rng.integers(0, 1 << 16)), R.R_MOD)
+    b = C.gen_bases(n, 5)
+    check(engine.msm(s, b), oracle_affine(s, b))
+    # every scalar identical -> every window has exactly one (huge) bucket
+    s2 = np.tile(C.random_fr(1, 8), (n, 1))
+    check(engine.msm(s2, b), oracle_affine(s2, b))
+
+
+def test_length_mismatch_and_short_commit(engine):
+    s = C.random_fr(10, 1)
+    b = C.gen_bases(8, 1)
+    with pytest.raises(ValueError):
+        engine.msm(s, b)
+    desc = engine.get_base_descriptor(b)
+    with pytest.raises(ValueError):
+        engine.msm_with_cached_base(s, desc)
+    # fewer scalars than cached bases uses the prefix (commitment.rs:313-316)
+    check(engine.msm_with_cached_base(s[:5], desc), oracle_affine(s[:5], b[:5]))
+
+
+def test_commit_lagrange_identity(engine, ctx):
+    """kzg/commitment.rs:381-408 test_commit_lagrange restated with a known secret:
+    commit(lagrange_to_coeff(a)) == commit_lagrange(a), and both equal [p(s)]G."""
+    import h2b200
+    k = 6
+    s_secret = 0x1234567890ABCDEF1234567890ABCDEF
+    ref_dom = R.EvaluationDomain(1, k)
+    g, gl = C.kzg_setup(k, C.mont_from_int(s_secret, R.R_MOD), C.mont_from_int(ref_dom.omega, R.R_MOD))
+    params = h2b200.ParamsKZG(k, g, gl, engine)
+    dom = h2b200.EvaluationDomain(1, k, ctx)
+    a = C.fr_array_from_ints(list(range(1 << k)), R.R_MOD)           # a[i] = i, as in the reference test
+    coeffs = dom.lagrange_to_coeff(a.copy())
+    c1 = params.commit(engine, coeffs)
+    c2 = params.commit_lagrange(engine, a)
+    assert np.array_equal(c1, c2)
+    p_at_s = R.eval_polynomial(C.ints_from_fr_array(coeffs, R.R_MOD), s_secret)
+    exp = R.g1_mul(R.G1_GEN, p_at_s)
+    assert h2b200.fields.jacobian_to_affine_ints(c1) == exp
+
+
+def test_sharded_windows_combine(engine):
+    """Point-range sharding (multi-GPU path): per-shard window sums + h2b_msm_combine == whole MSM."""
+    n = 5000
+    s = C.random_fr(n, 31)
+    b = C.gen_bases(n, 7)
+    parts = []
+    cs = set()
+    for lo, hi in [(0, 1200), (1200, 1201), (1201, 5000)]:
+        desc = engine.get_base_descriptor(b[lo:hi])
+        w, c = engine.msm_windows(np.ascontiguousarray(s[lo:hi]), desc, n)
+        parts.append(w)
+        cs.add(c)
+        desc.release()
+    assert len(cs) == 1
+    out = engine.msm_combine(np.stack(parts), cs.pop())
+    check(out, oracle_affine(s, b))
+
+
+def test_linearity_full_size(engine):
+    """BASELINE size 2^24 via size-independent properties: MSM(s, B) + MSM(t, B) == MSM(s + t, B) and a
+    concatenation split, all on device-resident inputs."""
+    import torch
+    n = 1 << 24
+    b = C.gen_bases(n, 1)
+    s = C.random_fr(n, 1)
+    desc = engine.get_base_descriptor(b)
+    ds = torch.from_numpy(s.view(np.int64)).cuda()
+    whole = engine.msm_with_cached_base(ds, desc)
+    half = n // 2
+    lo = engine.msm_with_cached_base(ds[:half], desc)
+    d_hi = engine.get_base_descriptor(b[half:])
+    hi = engine.msm_with_cached_base(ds[half:].contiguous(), d_hi)
+    assert np.array_equal(C.affine_add(lo[:8], hi[:8]), whole[:8])
+    assert C.is_on_curve(whole[:8])
+    # scalar all-ones: MSM == sum of bases == [sum_{i} (1+i)]G
+    ones = torch.from_numpy(np.tile(C.mont_from_int(1, R.R_MOD), (n, 1)).view(np.int64)).cuda()
+    tot = engine.msm_with_cached_base(ones, desc)
+    k = (n * (n + 1) // 2) % R.R_MOD
+    assert np.array_equal(tot[:8], C.affine_mul(C.gen_bases(1, 1)[0], C.mont_from_int(k, R.R_MOD)))

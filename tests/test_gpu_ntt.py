@@ -1,0 +1,165 @@
+"""GPU parity: the CUDA NTT path (through the C ABI / EvaluationDomain mirror) against the CPU oracle.
+Bit-exact comparison (integer arithmetic): every output limb must be equal."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from oracle import cref as C
+from oracle import pyref as R
+
+pytestmark = pytest.mark.gpu
+
+
+def m(x):
+    return C.mont_from_int(x, R.R_MOD)
+
+
+def omega_for(k):
+    return pow(R.ROOT_OF_UNITY, 1 << (28 - k), R.R_MOD)
+
+
+def gpu_ntt(ctx, a, k, omega, scale=None):
+    a = np.ascontiguousarray(a).copy()
+    sp = None if scale is None else scale.ctypes.data_as(ctypes.c_void_p)
+    ctx.check(ctx.lib.h2b_ntt(ctx.handle, a.ctypes.data_as(ctypes.c_void_p), k, omega.ctypes.data_as(ctypes.c_void_p), sp))
+    return a
+
+
+@pytest.mark.parametrize("k", list(range(1, 19)))
+def test_best_fft_matches_oracle(ctx, k):
+    a = C.random_fr(1 << k, 1000 + k)
+    w = m(omega_for(k))
+    out = gpu_ntt(ctx, a, k, w)
+    exp = C.best_fft(a, w, k)
+    assert np.array_equal(out, exp)
+
+
+@pytest.mark.parametrize("k", [19, 20, 22])
+def test_best_fft_three_pass(ctx, k):
+    a = C.random_fr(1 << k, 2000 + k)
+    w = m(omega_for(k))
+    assert np.array_equal(gpu_ntt(ctx, a, k, w), C.best_fft(a, w, k))
+
+
+@pytest.mark.parametrize("k,split", [(12, "4,4,4"), (12, "3,3,3,3"), (16, "8,8"), (18, "9,9"), (15, "7,8"), (13, "9,4"), (14, "5,9")])
+def test_split_overrides(ctx, k, split):
+    os.environ["H2B_NTT_SPLIT"] = split
+    try:
+        a = C.random_fr(1 << k, 3000 + k)
+        w = m(omega_for(k))
+        assert np.array_equal(gpu_ntt(ctx, a, k, w), C.best_fft(a, w, k))
+    finally:
+        os.environ.pop("H2B_NTT_SPLIT", None)
+
+
+def test_edge_inputs(ctx):
+    k = 10
+    w = m(omega_for(k))
+    zero = np.zeros((1 << k, 4), dtype=np.uint64)
+    assert np.array_equal(gpu_ntt(ctx, zero, k, w), zero)
+    # delta at 0 -> all ones; all (r-1) values
+    d = zero.copy(); d[0] = m(1)
+    assert np.array_equal(gpu_ntt(ctx, d, k, w), np.tile(m(1), (1 << k, 1)))
+    top = np.tile(m(R.R_MOD - 1), (1 << k, 1))
+    assert np.array_equal(gpu_ntt(ctx, top, k, w), C.best_fft(top, w, k))
+
+
+def test_invalid_arguments(ctx):
+    import h2b200
+    a = np.zeros((2, 4), dtype=np.uint64)
+    w = m(1)
+    for bad_k in (0, 29):
+        with pytest.raises(h2b200.H2bError):
+            ctx.check(ctx.lib.h2b_ntt(ctx.handle, a.ctypes.data_as(ctypes.c_void_p), bad_k, w.ctypes.data_as(ctypes.c_void_p), None))
+    with pytest.raises(h2b200.H2bError):
+        ctx.check(ctx.lib.h2b_ntt(ctx.handle, None, 4, w.ctypes.data_as(ctypes.c_void_p), None))
+
+
+@pytest.mark.parametrize("j,k", [(2, 3), (5, 3), (3, 4), (5, 6), (9, 8), (5, 10), (4, 11), (6, 12), (5, 14), (5, 16), (9, 17)])
+def test_domain_transforms_match_oracle(ctx, j, k):
+    import h2b200
+    dom = h2b200.EvaluationDomain(j, k, ctx)
+    ref = R.EvaluationDomain(j, k)
+    # host constants of the mirror == restated domain.rs constants
+    for name in ("omega", "omega_inv", "extended_omega", "extended_omega_inv", "g_coset", "g_coset_inv",
+                 "ifft_divisor", "extended_ifft_divisor", "extended_k", "t_evaluations"):
+        assert getattr(dom, name) == getattr(ref, name)
+    n, ek = 1 << k, ref.extended_k
+    a = C.random_fr(n, 77 * k + j)
+    coeff = dom.lagrange_to_coeff(a.copy())
+    assert np.array_equal(coeff, C.lagrange_to_coeff(a, k, m(ref.omega_inv), m(ref.ifft_divisor)))
+    ext = dom.coeff_to_extended(coeff)
+    exp_ext = C.coeff_to_extended(coeff, k, ek, m(ref.extended_omega), m(ref.g_coset), m(ref.g_coset_inv))
+    assert np.array_equal(ext, exp_ext)
+    out_len = n * (j - 1)
+    back = dom.extended_to_coeff(ext)
+    exp_back = C.extended_to_coeff(exp_ext, ek, m(ref.extended_omega_inv), m(ref.extended_ifft_divisor), m(ref.g_coset),
+                                   m(ref.g_coset_inv), out_len)
+    assert back.shape[0] == out_len and np.array_equal(back, exp_back)
+    assert np.array_equal(back[:min(n, out_len)], coeff[:min(n, out_len)])
+    # fused divide_by_vanishing_poly (domain.rs:297-316) + extended_to_coeff
+    h = C.random_fr(1 << ek, 5 * k + j)
+    t_evals = C.fr_array_from_ints(ref.t_evaluations, R.R_MOD)
+    exp_q = C.extended_to_coeff(C.divide_by_vanishing_poly(h, t_evals), ek, m(ref.extended_omega_inv),
+                                m(ref.extended_ifft_divisor), m(ref.g_coset), m(ref.g_coset_inv), out_len)
+    assert np.array_equal(dom.extended_to_coeff(h, divide_by_vanishing=True), exp_q)
+
+
+def test_wrong_length_panics(ctx):
+    import h2b200
+    dom = h2b200.EvaluationDomain(3, 5, ctx)
+    with pytest.raises(AssertionError):
+        dom.lagrange_to_coeff(np.zeros((31, 4), dtype=np.uint64))
+    with pytest.raises(AssertionError):
+        dom.coeff_to_extended(np.zeros((64, 4), dtype=np.uint64))
+    with pytest.raises(AssertionError):
+        dom.extended_to_coeff(np.zeros((32, 4), dtype=np.uint64))
+
+
+def test_rotation_orientation(ctx):
+    """domain.rs:478-517 test_rotate restated: rotating Lagrange values by +1 evaluates poly at omega*x."""
+    import h2b200
+    k = 3
+    dom = h2b200.EvaluationDomain(1, k, ctx)
+    vals = R.random_fr(1 << k, 5)
+    poly = C.ints_from_fr_array(dom.lagrange_to_coeff(C.fr_array_from_ints(vals, R.R_MOD)), R.R_MOD)
+    rot = vals[1:] + vals[:1]
+    poly_rot = C.ints_from_fr_array(dom.lagrange_to_coeff(C.fr_array_from_ints(rot, R.R_MOD)), R.R_MOD)
+    x = 0x1234567
+    assert R.eval_polynomial(poly, dom.rotate_omega(x, 1)) == R.eval_polynomial(poly_rot, x)
+    assert [R.eval_polynomial(poly, pow(dom.omega, i, R.R_MOD)) for i in range(1 << k)] == vals
+
+
+def test_batch_matches_single(ctx):
+    import h2b200
+    dom = h2b200.EvaluationDomain(5, 9, ctx)
+    cols = [C.random_fr(1 << 9, 40 + i) for i in range(5)]
+    singles = [dom.coeff_to_extended(c) for c in cols]
+    batch = dom.coeff_to_extended_batch(cols)
+    for s, b in zip(singles, batch):
+        assert np.array_equal(s, b)
+    lag = dom.lagrange_to_coeff_batch([c.copy() for c in cols])
+    for c, l in zip(cols, lag):
+        assert np.array_equal(l, dom.lagrange_to_coeff(c.copy()))
+
+
+def test_device_resident_round_trip_full_size(ctx):
+    """BASELINE size (2^24) through size-independent properties: iNTT(NTT(a)) == a and linearity at a sampled index."""
+    import torch
+    import h2b200
+    k = 24
+    dom = h2b200.EvaluationDomain(1, k, ctx)
+    a = C.random_fr(1 << k, 99)
+    d = torch.from_numpy(a.view(np.int64)).cuda()
+    dom.coeff_to_lagrange(d)
+    # spot check X[i] = sum_j a_j w^(ij) for i = 0: sum of inputs
+    x0 = d[0].cpu().numpy().view(np.uint64)
+    s = 0
+    ints = a.astype(object)
+    tot = [int(ints[:, i].sum()) for i in range(4)]
+    raw = sum(t << (64 * i) for i, t in enumerate(tot)) % R.R_MOD      # sum of Montgomery residues is the Montgomery sum
+    assert C.int_from_limbs(x0) == raw
+    dom.lagrange_to_coeff(d)
+    assert np.array_equal(d.cpu().numpy().view(np.uint64), a)

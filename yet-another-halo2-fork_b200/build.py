@@ -1,0 +1,53 @@
+"""In-tree build of libh2b200.so (sm_100a only) and the host unit-test shim."""
+from __future__ import annotations
+
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libh2b200.so")
+HOSTCHECK = os.path.join(HERE, "libh2b200_hostcheck.so")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+    "-Xcompiler", "-fPIC", "-shared",
+]
+
+
+def _newer(target: str, sources) -> bool:
+    if not os.path.exists(target):
+        return False
+    t = os.path.getmtime(target)
+    return all(os.path.getmtime(s) <= t for s in sources)
+
+
+def _sources():
+    out = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))]
+    out.append(os.path.join(HERE, "..", "include", "h2b200.h"))
+    return out
+
+
+def build_lib(force: bool = False, verbose: bool = False) -> str:
+    if not force and _newer(LIB, _sources()):
+        return LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, os.path.join(CSRC, "h2b200.cu")]
+    subprocess.check_call(cmd, cwd=HERE)
+    return LIB
+
+
+def build_hostcheck(force: bool = False) -> str:
+    if not force and _newer(HOSTCHECK, _sources()):
+        return HOSTCHECK
+    cmd = ["g++", "-O2", "-x", "c++", "-std=c++17", "-shared", "-fPIC", "-Wno-unknown-pragmas",
+           "-DH2B_HOST_EMULATE_PTX", "-o", HOSTCHECK, os.path.join(CSRC, "host_check.cpp")]
+    subprocess.check_call(cmd, cwd=HERE)
+    return HOSTCHECK
+
+
+if __name__ == "__main__":
+    import sys
+    build_lib(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    build_hostcheck(force="--force" in sys.argv)
+    print(LIB)

@@ -1,0 +1,879 @@
+// h2b200.cu -- libh2b200.so: context, resident data, kernel orchestration and the C ABI (include/h2b200.h).
+//
+// One `h2b_ctx` owns, per device: a compute stream, grow-only scratch buffers, resident MSM bases and cached
+// NTT twiddle tables.  Every entry point enqueues its whole pipeline on that stream with no host round trip
+// in the middle, then synchronises once and finishes on the host (window combine / normalisation).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/h2b200.h"
+#include "msm.cuh"
+#include "ntt.cuh"
+#include "ntt_plan.hpp"
+
+using namespace h2b;
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// small utilities
+// ------------------------------------------------------------------------------------------------
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = (bytes + 255) & ~(size_t)255;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct ProfRec { const char* name; cudaEvent_t a, b; };
+
+struct NttPlanDev {
+    NttPlan plan;
+    Fr* tables = nullptr;
+    bool has_scale = false;
+    Fr scale;
+};
+
+struct Dev {
+    int id = 0;
+    int sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_first = nullptr, ev_last = nullptr;
+    DevBuf ntt_a, ntt_b, ntt_tab;
+    DevBuf m_scalars, m_counts, m_offsets, m_ends, m_entries, m_order, m_buckets, m_wpart, m_blocksums,
+        m_sizehist, m_long_info, m_long_tasks, m_long_partials, m_counters, m_tmp_bases;
+    void* pinned = nullptr;
+    size_t pinned_cap = 0;
+    std::map<std::string, NttPlanDev> plans;
+    bool prof = false;
+    std::vector<ProfRec> recs;
+    std::vector<cudaEvent_t> ev_pool;
+    uint64_t launches = 0;
+
+    cudaEvent_t get_event() {
+        if (!ev_pool.empty()) { cudaEvent_t e = ev_pool.back(); ev_pool.pop_back(); return e; }
+        cudaEvent_t e; cudaEventCreate(&e); return e;
+    }
+    void prof_begin(const char* name) {
+        if (!prof) return;
+        ProfRec r; r.name = name; r.a = get_event(); r.b = get_event();
+        cudaEventRecord(r.a, stream);
+        recs.push_back(r);
+    }
+    void prof_end() {
+        if (!prof) return;
+        cudaEventRecord(recs.back().b, stream);
+    }
+    cudaError_t reserve_pinned(size_t bytes) {
+        if (bytes <= pinned_cap) return cudaSuccess;
+        if (pinned) cudaFreeHost(pinned);
+        pinned = nullptr; pinned_cap = 0;
+        cudaError_t e = cudaMallocHost(&pinned, bytes);
+        if (e == cudaSuccess) pinned_cap = bytes;
+        return e;
+    }
+};
+
+struct BasesShard { void* d = nullptr; size_t start = 0, count = 0; bool owned = true; };
+struct Bases { size_t n = 0; std::vector<BasesShard> shard; };
+
+}  // namespace
+
+struct h2b_ctx {
+    std::vector<Dev> devs;
+    std::mutex mu;
+    std::string err;
+    std::map<uint64_t, Bases> bases;
+    uint64_t next_handle = 1;
+    double last_ms = 0.0;
+    int fail(int code, const std::string& msg) { err = msg; return code; }
+};
+
+namespace {
+
+thread_local std::string g_init_error;
+
+#define H2B_CK(expr)                                                                                         \
+    do {                                                                                                     \
+        cudaError_t e__ = (expr);                                                                            \
+        if (e__ != cudaSuccess)                                                                              \
+            return ctx->fail(e__ == cudaErrorMemoryAllocation ? H2B_E_NOMEM : H2B_E_CUDA,                     \
+                             std::string(#expr) + ": " + cudaGetErrorString(e__));                           \
+    } while (0)
+
+#define H2B_LAUNCH(dev, name, kern, grid, block, smem, ...)                                                  \
+    do {                                                                                                     \
+        (dev).prof_begin(name);                                                                              \
+        kern<<<(grid), (block), (smem), (dev).stream>>>(__VA_ARGS__);                                        \
+        (dev).prof_end();                                                                                    \
+        (dev).launches++;                                                                                    \
+    } while (0)
+
+inline Fr fr_from_bytes(const void* p) { Fr f; std::memcpy(&f, p, 32); return f; }
+
+// ------------------------------------------------------------------------------------------------
+// NTT
+// ------------------------------------------------------------------------------------------------
+typedef void (*ntt_kernel_t)(const NttPass, const Fr*, Fr*, uint64_t, uint64_t);
+
+template <int LOG_S>
+void ntt_kernel_entry(ntt_kernel_t tab[10][2], size_t smem[10]) {
+    tab[LOG_S][0] = ntt_pass_kernel<LOG_S, false>;
+    tab[LOG_S][1] = ntt_pass_kernel<LOG_S, true>;
+    smem[LOG_S] = NttSmem<LOG_S>::bytes;
+}
+struct NttKernels {
+    ntt_kernel_t tab[10][2];
+    size_t smem[10];
+    NttKernels() {
+        std::memset(tab, 0, sizeof(tab));
+        std::memset(smem, 0, sizeof(smem));
+        ntt_kernel_entry<1>(tab, smem); ntt_kernel_entry<2>(tab, smem); ntt_kernel_entry<3>(tab, smem);
+        ntt_kernel_entry<4>(tab, smem); ntt_kernel_entry<5>(tab, smem); ntt_kernel_entry<6>(tab, smem);
+        ntt_kernel_entry<7>(tab, smem); ntt_kernel_entry<8>(tab, smem); ntt_kernel_entry<9>(tab, smem);
+    }
+};
+const NttKernels& ntt_kernels() { static NttKernels k; return k; }
+
+int ntt_prepare_device(h2b_ctx* ctx) {
+    const NttKernels& K = ntt_kernels();
+    for (int s = 1; s <= 9; s++)
+        for (int r = 0; r < 2; r++)
+            H2B_CK(cudaFuncSetAttribute((const void*)K.tab[s][r], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K.smem[s]));
+    return H2B_OK;
+}
+
+int ntt_get_plan(h2b_ctx* ctx, Dev& d, uint32_t log_n, const Fr& omega, const Fr* scale, NttPlanDev** out) {
+    std::string key((const char*)&log_n, 4);
+    key.append((const char*)&omega, 32);
+    if (scale) key.append((const char*)scale, 32);
+    if (const char* env = std::getenv("H2B_NTT_SPLIT")) key.append(env);
+    auto it = d.plans.find(key);
+    if (it != d.plans.end()) { *out = &it->second; return H2B_OK; }
+    NttPlanDev pd;
+    pd.plan = ntt_make_plan(log_n, omega, scale);
+    pd.has_scale = scale != nullptr;
+    if (scale) pd.scale = *scale;
+    H2B_CK(cudaMalloc((void**)&pd.tables, pd.plan.table_elems * sizeof(Fr)));
+    for (const auto& seg : pd.plan.segments) {
+        H2B_LAUNCH(d, "ntt_gen_powers", ntt_gen_powers_kernel, (seg.count + 127) / 128, 128, 0,
+                   pd.tables + seg.offset, seg.root, seg.first, seg.count);
+    }
+    H2B_CK(cudaGetLastError());
+    auto ins = d.plans.emplace(key, std::move(pd));
+    *out = &ins.first->second;
+    return H2B_OK;
+}
+
+// Enqueue a (batched) transform: in -> out, `tmp` holds 2^log_n elements per column for the intermediate
+// passes (unused for single-pass sizes).  in/tmp/out may be the same buffer only as documented at the call sites.
+int ntt_enqueue(h2b_ctx* ctx, Dev& d, const Fr* in, uint64_t in_stride, Fr* tmp, uint64_t tmp_stride, Fr* out,
+                uint64_t out_stride, uint32_t batch, uint32_t log_n, const Fr& omega, const Fr* scale, const NttFused& fz) {
+    if (log_n == 0) {   // size-1 transform: identity (times scale / patterns are no-ops at index 0 except scale)
+        return ctx->fail(H2B_E_INVALID, "ntt: log_n must be >= 1");
+    }
+    NttPlanDev* pd = nullptr;
+    int rc = ntt_get_plan(ctx, d, log_n, omega, scale, &pd);
+    if (rc) return rc;
+    NttPass passes[4];
+    ntt_build_passes(pd->plan, pd->tables, scale, fz, passes);
+    const NttKernels& K = ntt_kernels();
+    for (int j = 0; j < pd->plan.n_pass; j++) {
+        bool last = j == pd->plan.n_pass - 1;
+        const Fr* src = j == 0 ? in : tmp;
+        uint64_t src_stride = j == 0 ? in_stride : tmp_stride;
+        Fr* dst = last ? out : tmp;
+        uint64_t dst_stride = last ? out_stride : tmp_stride;
+        uint32_t s = passes[j].log_s;
+        uint64_t tiles = ntt_pass_tiles(pd->plan, j);
+        dim3 grid((unsigned)tiles, batch, 1);
+        unsigned threads = (1u << s) < 32u ? 32u : (1u << s);
+        ntt_kernel_t kern = K.tab[s][last ? 1 : 0];
+        H2B_LAUNCH(d, last ? "ntt_row_pass" : "ntt_column_pass", kern, grid, threads, K.smem[s], passes[j], src, dst,
+                   src_stride, dst_stride);
+    }
+    H2B_CK(cudaGetLastError());
+    return H2B_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// MSM
+// ------------------------------------------------------------------------------------------------
+uint32_t msm_choose_c(size_t n_total) {
+    if (const char* env = std::getenv("H2B_MSM_C")) {
+        int v = std::atoi(env);
+        if (v >= 2 && v <= 24) return (uint32_t)v;
+    }
+    uint32_t lg = 0;
+    while (((size_t)1 << (lg + 1)) <= n_total) lg++;
+    int c = (int)lg - 4;
+    if (c < 4) c = 4;
+    if (c > 16) c = 16;
+    return (uint32_t)c;
+}
+
+struct MsmLaunchInfo { uint32_t c, windows, slices; };
+
+// Enqueue the whole bucket pipeline for `n` resident (scalar, base) pairs on device d; the per-window partial
+// sums (windows * slices XYZZ points) are copied asynchronously into d.pinned.
+int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, uint32_t n, uint32_t c, MsmLaunchInfo* info) {
+    MsmGeom g;
+    g.c = c; g.windows = msm_windows(c); g.nb = 1u << (c - 1); g.n = n;
+    const uint32_t nkeys = g.windows * g.nb;
+    const uint64_t max_entries = (uint64_t)n * g.windows;
+    if (max_entries >= 0xffffffffull) return ctx->fail(H2B_E_INVALID, "msm: n * windows exceeds 2^32 (shard the MSM)");
+    uint32_t mean = n / g.nb;
+    uint32_t long_threshold = std::max<uint32_t>(256u, 16u * std::max<uint32_t>(mean, 1u));
+    uint32_t max_long = (uint32_t)(max_entries / long_threshold) + 1;
+    uint32_t max_tasks = (uint32_t)(max_entries / MSM_LONG_CHUNK) + max_long + 1;
+    uint32_t slices = 1;
+    if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
+        slices = g.nb / (MSM_REDUCE_THREADS * 16);
+        if (slices < 1) slices = 1;
+    }
+    const uint32_t nblk = (nkeys + SCAN_BLOCK - 1) / SCAN_BLOCK;
+
+    H2B_CK(d.m_counts.reserve((size_t)nkeys * 4));
+    H2B_CK(d.m_offsets.reserve((size_t)nkeys * 4));
+    H2B_CK(d.m_ends.reserve((size_t)nkeys * 4));
+    H2B_CK(d.m_order.reserve((size_t)nkeys * 4));
+    H2B_CK(d.m_entries.reserve(std::max<size_t>((size_t)max_entries * 4, 256)));
+    H2B_CK(d.m_buckets.reserve((size_t)nkeys * sizeof(Xyzz)));
+    H2B_CK(d.m_wpart.reserve((size_t)g.windows * slices * sizeof(Xyzz)));
+    H2B_CK(d.m_blocksums.reserve((size_t)nblk * 4 + 256));
+    H2B_CK(d.m_sizehist.reserve((size_t)MSM_SIZE_BINS * 4));
+    H2B_CK(d.m_long_info.reserve((size_t)max_long * sizeof(MsmLongInfo)));
+    H2B_CK(d.m_long_tasks.reserve((size_t)max_tasks * sizeof(MsmLongTask)));
+    H2B_CK(d.m_long_partials.reserve((size_t)max_tasks * sizeof(Xyzz)));
+    H2B_CK(d.m_counters.reserve(256));
+    H2B_CK(d.reserve_pinned(std::max<size_t>((size_t)g.windows * slices * sizeof(Xyzz), 4096)));
+
+    uint32_t* counts = d.m_counts.as<uint32_t>();
+    uint32_t* offsets = d.m_offsets.as<uint32_t>();
+    uint32_t* ends = d.m_ends.as<uint32_t>();
+    uint32_t* order = d.m_order.as<uint32_t>();
+    uint32_t* entries = d.m_entries.as<uint32_t>();
+    uint32_t* blocksums = d.m_blocksums.as<uint32_t>();
+    uint32_t* sizehist = d.m_sizehist.as<uint32_t>();
+    uint32_t* counters = d.m_counters.as<uint32_t>();
+    Xyzz* buckets = d.m_buckets.as<Xyzz>();
+    Xyzz* wpart = d.m_wpart.as<Xyzz>();
+
+    H2B_CK(cudaMemsetAsync(counts, 0, (size_t)nkeys * 4, d.stream));
+    H2B_CK(cudaMemsetAsync(sizehist, 0, (size_t)MSM_SIZE_BINS * 4, d.stream));
+    H2B_CK(cudaMemsetAsync(counters, 0, 256, d.stream));
+    const uint32_t tb = 256;
+    if (n) H2B_LAUNCH(d, "msm_count", msm_count_kernel, (n + tb - 1) / tb, tb, 0, g, scalars, counts);
+    H2B_LAUNCH(d, "msm_scan", scan_block_sums_kernel, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums);
+    H2B_LAUNCH(d, "msm_scan", scan_single_block_kernel, 1, SCAN_BLOCK, 0, blocksums, nblk, (uint32_t*)nullptr);
+    H2B_LAUNCH(d, "msm_scan", scan_apply_kernel, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums, offsets, ends);
+    if (n) H2B_LAUNCH(d, "msm_scatter", msm_scatter_kernel, (n + tb - 1) / tb, tb, 0, g, scalars, ends, entries);
+    H2B_LAUNCH(d, "msm_order", msm_size_hist_kernel, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist);
+    H2B_LAUNCH(d, "msm_order", scan_single_block_kernel, 1, SCAN_BLOCK, 0, sizehist, MSM_SIZE_BINS, (uint32_t*)nullptr);
+    H2B_LAUNCH(d, "msm_order", msm_size_scatter_kernel, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist, order);
+    H2B_LAUNCH(d, "msm_order", msm_long_list_kernel, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, long_threshold,
+               d.m_long_info.as<MsmLongInfo>(), d.m_long_tasks.as<MsmLongTask>(), counters);
+    H2B_LAUNCH(d, "msm_accumulate", msm_accumulate_kernel, (nkeys + 127) / 128, 128, 0, bases, entries, offsets, ends, order,
+               nkeys, long_threshold, buckets);
+    H2B_LAUNCH(d, "msm_accumulate_long", msm_accumulate_long_kernel, (unsigned)(d.sms * 8), MSM_LONG_THREADS, 0, bases, entries,
+               offsets, ends, d.m_long_tasks.as<MsmLongTask>(), counters, d.m_long_partials.as<Xyzz>());
+    H2B_LAUNCH(d, "msm_accumulate_long", msm_long_combine_kernel, (unsigned)d.sms, MSM_LONG_THREADS, 0,
+               d.m_long_info.as<MsmLongInfo>(), counters, d.m_long_partials.as<Xyzz>(), buckets);
+    if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
+        dim3 grid(slices, g.windows, 1);
+        H2B_LAUNCH(d, "msm_reduce", msm_reduce_kernel, grid, MSM_REDUCE_THREADS, 0, g, buckets, slices, wpart);
+    } else {
+        H2B_LAUNCH(d, "msm_reduce", msm_reduce_small_kernel, (g.windows + 31) / 32, 32, 0, g, buckets, wpart);
+    }
+    H2B_CK(cudaGetLastError());
+    H2B_CK(cudaMemcpyAsync(d.pinned, wpart, (size_t)g.windows * slices * sizeof(Xyzz), cudaMemcpyDeviceToHost, d.stream));
+    info->c = c; info->windows = g.windows; info->slices = slices;
+    return H2B_OK;
+}
+
+// host: fold the slices of each window (after the stream has been synchronised)
+void msm_fold_slices(const Dev& d, const MsmLaunchInfo& info, Xyzz* windows /* accumulated into */) {
+    const Xyzz* part = reinterpret_cast<const Xyzz*>(d.pinned);
+    for (uint32_t j = 0; j < info.windows; j++)
+        for (uint32_t s = 0; s < info.slices; s++) windows[j] = xyzz_add(windows[j], part[(size_t)j * info.slices + s]);
+}
+
+void begin_call(Dev& d) { cudaEventRecord(d.ev_first, d.stream); }
+int end_call(h2b_ctx* ctx, Dev& d) {
+    H2B_CK(cudaEventRecord(d.ev_last, d.stream));
+    H2B_CK(cudaStreamSynchronize(d.stream));
+    float ms = 0.f;
+    H2B_CK(cudaEventElapsedTime(&ms, d.ev_first, d.ev_last));
+    ctx->last_ms = ms;
+    return H2B_OK;
+}
+
+// MSM over all devices of the context.  scalars: host pointer, or device-0 pointer when on_device.
+int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, size_t n, size_t n_total,
+            Xyzz* windows_out, uint32_t* c_out, uint32_t* windows_count) {
+    if (n > B.n) return ctx->fail(H2B_E_INVALID, "msm: more scalars than registered bases");
+    uint32_t c = msm_choose_c(n_total);
+    uint32_t nw = msm_windows(c);
+    for (uint32_t j = 0; j < nw; j++) windows_out[j] = Xyzz::identity();
+    *c_out = c; *windows_count = nw;
+    if (n == 0) { ctx->last_ms = 0; return H2B_OK; }
+    if (n >= ((size_t)1 << 31)) return ctx->fail(H2B_E_INVALID, "msm: n too large");
+    std::vector<MsmLaunchInfo> infos(B.shard.size());
+    std::vector<int> used;
+    double max_ms = 0;
+    for (size_t di = 0; di < B.shard.size(); di++) {
+        const BasesShard& sh = B.shard[di];
+        if (sh.start >= n || sh.count == 0) continue;
+        size_t cnt = std::min(sh.count, n - sh.start);
+        Dev& d = ctx->devs[di];
+        H2B_CK(cudaSetDevice(d.id));
+        begin_call(d);
+        const Fr* d_scalars;
+        if (on_device && di == 0) {
+            d_scalars = reinterpret_cast<const Fr*>(scalars) + sh.start;
+        } else {
+            H2B_CK(d.m_scalars.reserve(cnt * 32));
+            H2B_CK(cudaMemcpyAsync(d.m_scalars.p, reinterpret_cast<const uint8_t*>(scalars) + sh.start * 32, cnt * 32,
+                                   on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, d.stream));
+            d_scalars = d.m_scalars.as<Fr>();
+        }
+        int rc = msm_enqueue(ctx, d, reinterpret_cast<const Affine*>(sh.d), d_scalars, (uint32_t)cnt, c, &infos[di]);
+        if (rc) return rc;
+        H2B_CK(cudaEventRecord(d.ev_last, d.stream));
+        used.push_back((int)di);
+    }
+    for (int di : used) {
+        Dev& d = ctx->devs[di];
+        H2B_CK(cudaSetDevice(d.id));
+        H2B_CK(cudaStreamSynchronize(d.stream));
+        float ms = 0.f;
+        H2B_CK(cudaEventElapsedTime(&ms, d.ev_first, d.ev_last));
+        max_ms = std::max(max_ms, (double)ms);
+        msm_fold_slices(d, infos[di], windows_out);
+    }
+    ctx->last_ms = max_ms;
+    return H2B_OK;
+}
+
+int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, uint64_t* handle_out) {
+    Bases B;
+    B.n = n;
+    size_t nd = on_device ? 1 : ctx->devs.size();
+    B.shard.resize(ctx->devs.size());
+    size_t per = (n + nd - 1) / nd;
+    for (size_t di = 0; di < nd; di++) {
+        BasesShard& sh = B.shard[di];
+        sh.start = std::min(n, di * per);
+        sh.count = std::min(per, n - sh.start);
+        if (on_device) { sh.d = const_cast<void*>(bases); sh.owned = false; continue; }
+        if (sh.count == 0) continue;
+        Dev& d = ctx->devs[di];
+        H2B_CK(cudaSetDevice(d.id));
+        H2B_CK(cudaMalloc(&sh.d, sh.count * 64));
+        H2B_CK(cudaMemcpyAsync(sh.d, reinterpret_cast<const uint8_t*>(bases) + sh.start * 64, sh.count * 64,
+                               cudaMemcpyHostToDevice, d.stream));
+        H2B_CK(cudaStreamSynchronize(d.stream));
+    }
+    uint64_t h = ctx->next_handle++;
+    ctx->bases.emplace(h, std::move(B));
+    *handle_out = h;
+    return H2B_OK;
+}
+
+void release_bases(h2b_ctx* ctx, Bases& B) {
+    for (size_t di = 0; di < B.shard.size(); di++)
+        if (B.shard[di].d && B.shard[di].owned) { cudaSetDevice(ctx->devs[di].id); cudaFree(B.shard[di].d); }
+}
+
+// ------------------------------------------------------------------------------------------------
+// integer-pipe calibration kernels
+// ------------------------------------------------------------------------------------------------
+__global__ void imad_wide_peak_kernel(uint32_t seed, uint32_t iters, unsigned long long* sink) {
+    uint32_t a = seed + threadIdx.x, b = seed * 3u + blockIdx.x;
+    unsigned long long acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) acc[i] = (unsigned long long)i * 0x9E3779B97F4A7C15ull + a;
+    for (uint32_t it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++)
+            asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a + (uint32_t)i), "r"(b));
+    }
+    unsigned long long s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s ^= acc[i];
+    if (s == 0x1234567ull) *sink = s;
+}
+__global__ void field_mul_peak_kernel(uint32_t iters, Fq* sink) {
+    Fq x = Fq::one(), y = Fq::r2();
+    x.l[0] += threadIdx.x; y.l[1] += blockIdx.x;
+    Fq a = x, b = y;
+    for (uint32_t it = 0; it < iters; it++) {
+        a = fe_mul(a, x);
+        b = fe_mul(b, y);
+    }
+    Fq r = fe_add(a, b);
+    if (r.l[0] == 0x12345u && r.l[7] == 0x54321u) *sink = r;
+}
+
+}  // namespace
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+extern "C" {
+
+const char* h2b_version(void) { return "h2b200 0.1 (sm_100a)"; }
+
+int h2b_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
+    if (!out) return H2B_E_INVALID;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        g_init_error = std::string("no CUDA device: ") + cudaGetErrorString(e);
+        return H2B_E_NODEVICE;
+    }
+    std::vector<int> ids;
+    if (!device_ids || n_devices <= 0) ids.push_back(0);
+    else ids.assign(device_ids, device_ids + n_devices);
+    h2b_ctx* ctx = new h2b_ctx();
+    ctx->devs.resize(ids.size());
+    for (size_t i = 0; i < ids.size(); i++) {
+        Dev& d = ctx->devs[i];
+        d.id = ids[i];
+        if (d.id < 0 || d.id >= count) { g_init_error = "bad device id"; delete ctx; return H2B_E_INVALID; }
+        cudaDeviceProp prop;
+        if (cudaSetDevice(d.id) != cudaSuccess || cudaGetDeviceProperties(&prop, d.id) != cudaSuccess) {
+            g_init_error = "cudaSetDevice failed"; delete ctx; return H2B_E_CUDA;
+        }
+        if (prop.major != 10) {
+            g_init_error = "device is not sm_100 (this library is built for B200 only)"; delete ctx; return H2B_E_NODEVICE;
+        }
+        d.sms = prop.multiProcessorCount;
+        if (cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreate(&d.ev_first) != cudaSuccess || cudaEventCreate(&d.ev_last) != cudaSuccess) {
+            g_init_error = "stream/event creation failed"; delete ctx; return H2B_E_CUDA;
+        }
+        int rc = ntt_prepare_device(ctx);
+        if (rc) { g_init_error = ctx->err; delete ctx; return rc; }
+    }
+    cudaSetDevice(ctx->devs[0].id);
+    *out = ctx;
+    return H2B_OK;
+}
+
+void h2b_destroy(h2b_ctx* ctx) {
+    if (!ctx) return;
+    for (auto& kv : ctx->bases) release_bases(ctx, kv.second);
+    for (Dev& d : ctx->devs) {
+        cudaSetDevice(d.id);
+        cudaStreamSynchronize(d.stream);
+        for (auto& kv : d.plans) cudaFree(kv.second.tables);
+        DevBuf* bufs[] = {&d.ntt_a, &d.ntt_b, &d.ntt_tab, &d.m_scalars, &d.m_counts, &d.m_offsets, &d.m_ends, &d.m_entries,
+                          &d.m_order, &d.m_buckets, &d.m_wpart, &d.m_blocksums, &d.m_sizehist, &d.m_long_info,
+                          &d.m_long_tasks, &d.m_long_partials, &d.m_counters, &d.m_tmp_bases};
+        for (DevBuf* b : bufs) b->release();
+        if (d.pinned) cudaFreeHost(d.pinned);
+        for (auto& r : d.recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+        for (auto ev : d.ev_pool) cudaEventDestroy(ev);
+        cudaEventDestroy(d.ev_first); cudaEventDestroy(d.ev_last);
+        cudaStreamDestroy(d.stream);
+    }
+    delete ctx;
+}
+
+const char* h2b_last_error(const h2b_ctx* ctx) { return ctx ? ctx->err.c_str() : g_init_error.c_str(); }
+
+// ---- MSM -----------------------------------------------------------------------------------------
+int h2b_bases_register(h2b_ctx* ctx, const void* bases, size_t n, uint64_t* handle_out) {
+    if (!ctx || !handle_out || (!bases && n)) return ctx ? ctx->fail(H2B_E_INVALID, "bases_register: null argument") : H2B_E_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return register_bases(ctx, bases, false, n, handle_out);
+}
+int h2b_bases_register_device(h2b_ctx* ctx, const void* d_bases, size_t n, uint64_t* handle_out) {
+    if (!ctx || !handle_out || (!d_bases && n)) return ctx ? ctx->fail(H2B_E_INVALID, "bases_register_device: null argument") : H2B_E_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return register_bases(ctx, d_bases, true, n, handle_out);
+}
+int h2b_bases_release(h2b_ctx* ctx, uint64_t handle) {
+    if (!ctx) return H2B_E_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->bases.find(handle);
+    if (it == ctx->bases.end()) return ctx->fail(H2B_E_INVALID, "bases_release: unknown handle");
+    release_bases(ctx, it->second);
+    ctx->bases.erase(it);
+    return H2B_OK;
+}
+
+static int msm_common(h2b_ctx* ctx, uint64_t handle, const void* scalars, bool on_device, size_t n, void* out96) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!out96 || (!scalars && n)) return ctx->fail(H2B_E_INVALID, "msm: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->bases.find(handle);
+    if (it == ctx->bases.end()) return ctx->fail(H2B_E_INVALID, "msm: unknown bases handle");
+    Xyzz windows[H2B_MSM_MAX_WINDOWS];
+    uint32_t c = 0, nw = 0;
+    int rc = msm_run(ctx, it->second, scalars, on_device, n, n, windows, &c, &nw);
+    if (rc) return rc;
+    msm_finish(windows, nw, c, out96);
+    return H2B_OK;
+}
+int h2b_msm(h2b_ctx* ctx, uint64_t handle, const void* scalars, size_t n, void* out96) {
+    return msm_common(ctx, handle, scalars, false, n, out96);
+}
+int h2b_msm_device(h2b_ctx* ctx, uint64_t handle, const void* d_scalars, size_t n, void* out96) {
+    return msm_common(ctx, handle, d_scalars, true, n, out96);
+}
+int h2b_msm_raw(h2b_ctx* ctx, const void* bases, const void* scalars, size_t n, void* out96) {
+    if (!ctx) return H2B_E_INVALID;
+    uint64_t h = 0;
+    int rc = h2b_bases_register(ctx, bases, n, &h);
+    if (rc) return rc;
+    rc = h2b_msm(ctx, h, scalars, n, out96);
+    int rc2 = h2b_bases_release(ctx, h);
+    return rc ? rc : rc2;
+}
+int h2b_msm_windows(h2b_ctx* ctx, uint64_t handle, const void* scalars, int scalars_on_device, size_t n, size_t n_total,
+                    void* out_windows, uint32_t* c_out, uint32_t* windows_out) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!out_windows || !c_out || !windows_out || (!scalars && n)) return ctx->fail(H2B_E_INVALID, "msm_windows: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->bases.find(handle);
+    if (it == ctx->bases.end()) return ctx->fail(H2B_E_INVALID, "msm_windows: unknown bases handle");
+    Xyzz windows[H2B_MSM_MAX_WINDOWS];
+    int rc = msm_run(ctx, it->second, scalars, scalars_on_device != 0, n, n_total, windows, c_out, windows_out);
+    if (rc) return rc;
+    std::memcpy(out_windows, windows, (size_t)*windows_out * sizeof(Xyzz));
+    return H2B_OK;
+}
+int h2b_msm_combine(const void* parts, uint32_t n_parts, uint32_t c, uint32_t windows, void* out96) {
+    if (!parts || !out96 || windows == 0 || windows > H2B_MSM_MAX_WINDOWS || c == 0 || c > 31) return H2B_E_INVALID;
+    Xyzz acc[H2B_MSM_MAX_WINDOWS];
+    const Xyzz* p = reinterpret_cast<const Xyzz*>(parts);
+    for (uint32_t j = 0; j < windows; j++) {
+        acc[j] = Xyzz::identity();
+        for (uint32_t r = 0; r < n_parts; r++) {
+            Xyzz t;
+            std::memcpy(&t, p + (size_t)r * windows + j, sizeof(Xyzz));
+            acc[j] = xyzz_add(acc[j], t);
+        }
+    }
+    msm_finish(acc, windows, c, out96);
+    return H2B_OK;
+}
+
+// ---- NTT -----------------------------------------------------------------------------------------
+static int ntt_args_ok(h2b_ctx* ctx, uint32_t log_n) {
+    if (log_n < 1 || log_n > 28) return ctx->fail(H2B_E_INVALID, "ntt: log_n out of range [1, 28] (Fr::S = 28, domain.rs:54)");
+    return H2B_OK;
+}
+
+int h2b_ntt_device(h2b_ctx* ctx, void* d_a, uint32_t log_n, const void* omega32, const void* scale32) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!d_a || !omega32) return ctx->fail(H2B_E_INVALID, "ntt: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = ntt_args_ok(ctx, log_n);
+    if (rc) return rc;
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    size_t N = (size_t)1 << log_n;
+    H2B_CK(d.ntt_b.reserve(N * 32));
+    Fr omega = fr_from_bytes(omega32), scale;
+    if (scale32) scale = fr_from_bytes(scale32);
+    begin_call(d);
+    NttFused fz;
+    // a -> (column passes) -> b -> (row pass) -> a ; single-pass sizes run a -> a inside one tile
+    rc = ntt_enqueue(ctx, d, (Fr*)d_a, 0, d.ntt_b.as<Fr>(), 0, (Fr*)d_a, 0, 1, log_n, omega, scale32 ? &scale : nullptr, fz);
+    if (rc) return rc;
+    return end_call(ctx, d);
+}
+
+int h2b_ntt(h2b_ctx* ctx, void* a, uint32_t log_n, const void* omega32, const void* scale32) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!a || !omega32) return ctx->fail(H2B_E_INVALID, "ntt: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = ntt_args_ok(ctx, log_n);
+    if (rc) return rc;
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    size_t N = (size_t)1 << log_n;
+    H2B_CK(d.ntt_a.reserve(N * 32));
+    H2B_CK(d.ntt_b.reserve(N * 32));
+    Fr omega = fr_from_bytes(omega32), scale;
+    if (scale32) scale = fr_from_bytes(scale32);
+    begin_call(d);
+    H2B_CK(cudaMemcpyAsync(d.ntt_a.p, a, N * 32, cudaMemcpyHostToDevice, d.stream));
+    NttFused fz;
+    rc = ntt_enqueue(ctx, d, d.ntt_a.as<Fr>(), 0, d.ntt_b.as<Fr>(), 0, d.ntt_a.as<Fr>(), 0, 1, log_n, omega,
+                     scale32 ? &scale : nullptr, fz);
+    if (rc) return rc;
+    H2B_CK(cudaMemcpyAsync(a, d.ntt_a.p, N * 32, cudaMemcpyDeviceToHost, d.stream));
+    return end_call(ctx, d);
+}
+
+static int c2e_impl(h2b_ctx* ctx, const void* in_n, void* out_ne, bool on_device, uint32_t k, uint32_t ext_k,
+                    const void* ext_omega32, const void* g_coset32, const void* g_coset_inv32) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!in_n || !out_ne || !ext_omega32 || !g_coset32 || !g_coset_inv32) return ctx->fail(H2B_E_INVALID, "coeff_to_extended: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = ntt_args_ok(ctx, ext_k);
+    if (rc) return rc;
+    if (k > ext_k) return ctx->fail(H2B_E_INVALID, "coeff_to_extended: k > extended_k");
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    size_t n = (size_t)1 << k, N = (size_t)1 << ext_k;
+    Fr omega = fr_from_bytes(ext_omega32);
+    Fr pat[2] = {fr_from_bytes(g_coset32), fr_from_bytes(g_coset_inv32)};
+    NttFused fz;
+    fz.in_len = n;
+    fz.in_pat = pat;
+    H2B_CK(d.ntt_b.reserve(N * 32));
+    begin_call(d);
+    const Fr* src;
+    Fr* dst;
+    if (on_device) { src = (const Fr*)in_n; dst = (Fr*)out_ne; }
+    else {
+        H2B_CK(d.ntt_a.reserve(N * 32));
+        // stage the n inputs at the END of ntt_a's N slots?  No: the row pass writes `dst` while reading `tmp` only,
+        // and the first pass has consumed `src` by then, so src may alias dst.
+        H2B_CK(cudaMemcpyAsync(d.ntt_a.p, in_n, n * 32, cudaMemcpyHostToDevice, d.stream));
+        src = d.ntt_a.as<Fr>(); dst = d.ntt_a.as<Fr>();
+    }
+    rc = ntt_enqueue(ctx, d, src, 0, d.ntt_b.as<Fr>(), 0, dst, 0, 1, ext_k, omega, nullptr, fz);
+    if (rc) return rc;
+    if (!on_device) H2B_CK(cudaMemcpyAsync(out_ne, dst, N * 32, cudaMemcpyDeviceToHost, d.stream));
+    return end_call(ctx, d);
+}
+int h2b_coeff_to_extended(h2b_ctx* ctx, const void* in_n, void* out_ne, uint32_t k, uint32_t ext_k, const void* ext_omega32,
+                          const void* g_coset32, const void* g_coset_inv32) {
+    return c2e_impl(ctx, in_n, out_ne, false, k, ext_k, ext_omega32, g_coset32, g_coset_inv32);
+}
+int h2b_coeff_to_extended_device(h2b_ctx* ctx, const void* d_in_n, void* d_out_ne, uint32_t k, uint32_t ext_k,
+                                 const void* ext_omega32, const void* g_coset32, const void* g_coset_inv32) {
+    return c2e_impl(ctx, d_in_n, d_out_ne, true, k, ext_k, ext_omega32, g_coset32, g_coset_inv32);
+}
+
+static int e2c_impl(h2b_ctx* ctx, const void* a_ne, void* out, bool on_device, uint32_t ext_k, const void* ext_omega_inv32,
+                    const void* ext_ifft_divisor32, const void* g_coset32, const void* g_coset_inv32, size_t out_len,
+                    const void* t_evals32, size_t n_t) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!a_ne || !out || !ext_omega_inv32 || !ext_ifft_divisor32 || !g_coset32 || !g_coset_inv32)
+        return ctx->fail(H2B_E_INVALID, "extended_to_coeff: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = ntt_args_ok(ctx, ext_k);
+    if (rc) return rc;
+    size_t N = (size_t)1 << ext_k;
+    if (out_len > N) return ctx->fail(H2B_E_INVALID, "extended_to_coeff: out_len exceeds the extended domain");
+    if (t_evals32 && (n_t == 0 || (n_t & (n_t - 1)) != 0 || n_t > N)) return ctx->fail(H2B_E_INVALID, "extended_to_coeff: t_evals length must be a power of two");
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    Fr omega = fr_from_bytes(ext_omega_inv32), scale = fr_from_bytes(ext_ifft_divisor32);
+    Fr pat[2] = {fr_from_bytes(g_coset_inv32), fr_from_bytes(g_coset32)};   // out of the coset: [1, zeta^2, zeta]
+    NttFused fz;
+    fz.out_len = out_len;
+    fz.out_pat = pat;
+    H2B_CK(d.ntt_b.reserve(N * 32));
+    begin_call(d);
+    if (t_evals32) {
+        H2B_CK(d.ntt_tab.reserve(n_t * 32));
+        H2B_CK(cudaMemcpyAsync(d.ntt_tab.p, t_evals32, n_t * 32, cudaMemcpyHostToDevice, d.stream));
+        fz.in_tab = d.ntt_tab.as<Fr>();
+        fz.in_tab_mask = (uint32_t)(n_t - 1);
+    }
+    const Fr* src;
+    Fr* dst;
+    if (on_device) { src = (const Fr*)a_ne; dst = (Fr*)out; }
+    else {
+        H2B_CK(d.ntt_a.reserve(N * 32));
+        H2B_CK(cudaMemcpyAsync(d.ntt_a.p, a_ne, N * 32, cudaMemcpyHostToDevice, d.stream));
+        src = d.ntt_a.as<Fr>(); dst = d.ntt_a.as<Fr>();
+    }
+    rc = ntt_enqueue(ctx, d, src, 0, d.ntt_b.as<Fr>(), 0, dst, 0, 1, ext_k, omega, &scale, fz);
+    if (rc) return rc;
+    if (!on_device) H2B_CK(cudaMemcpyAsync(out, dst, out_len * 32, cudaMemcpyDeviceToHost, d.stream));
+    return end_call(ctx, d);
+}
+int h2b_extended_to_coeff(h2b_ctx* ctx, const void* a_ne, void* out, uint32_t ext_k, const void* ext_omega_inv32,
+                          const void* ext_ifft_divisor32, const void* g_coset32, const void* g_coset_inv32, size_t out_len,
+                          const void* t_evals32, size_t n_t) {
+    return e2c_impl(ctx, a_ne, out, false, ext_k, ext_omega_inv32, ext_ifft_divisor32, g_coset32, g_coset_inv32, out_len, t_evals32, n_t);
+}
+int h2b_extended_to_coeff_device(h2b_ctx* ctx, const void* d_a_ne, void* d_out, uint32_t ext_k, const void* ext_omega_inv32,
+                                 const void* ext_ifft_divisor32, const void* g_coset32, const void* g_coset_inv32,
+                                 size_t out_len, const void* t_evals32, size_t n_t) {
+    return e2c_impl(ctx, d_a_ne, d_out, true, ext_k, ext_omega_inv32, ext_ifft_divisor32, g_coset32, g_coset_inv32, out_len, t_evals32, n_t);
+}
+
+// Batched transforms over host columns: columns are dealt round-robin over the devices; on each device the
+// columns are staged contiguously and transformed by ONE launch per pass (grid.y = column).
+static int batch_impl(h2b_ctx* ctx, const void* const* in_cols, void* const* out_cols, size_t n_cols, uint32_t log_in,
+                      uint32_t log_n, const Fr& omega, const Fr* scale, const NttFused& fz) {
+    size_t nin = (size_t)1 << log_in, N = (size_t)1 << log_n;
+    size_t nd = ctx->devs.size();
+    double max_ms = 0;
+    // bound the staging footprint: process in rounds of at most `chunk` columns per device
+    size_t chunk = std::max<size_t>(1, ((size_t)8 << 30) / (N * 32));
+    for (size_t base = 0; base < n_cols; base += chunk * nd) {
+        std::vector<std::vector<size_t>> mine(nd);
+        for (size_t c = base; c < std::min(n_cols, base + chunk * nd); c++) mine[(c - base) % nd].push_back(c);
+        for (size_t di = 0; di < nd; di++) {
+            if (mine[di].empty()) continue;
+            Dev& d = ctx->devs[di];
+            size_t m = mine[di].size();
+            H2B_CK(cudaSetDevice(d.id));
+            H2B_CK(d.ntt_a.reserve(m * N * 32));
+            H2B_CK(d.ntt_b.reserve(m * N * 32));
+            begin_call(d);
+            for (size_t i = 0; i < m; i++)
+                H2B_CK(cudaMemcpyAsync(d.ntt_a.as<Fr>() + i * N, in_cols[mine[di][i]], nin * 32, cudaMemcpyHostToDevice, d.stream));
+            int rc = ntt_enqueue(ctx, d, d.ntt_a.as<Fr>(), N, d.ntt_b.as<Fr>(), N, d.ntt_a.as<Fr>(), N, (uint32_t)m, log_n, omega, scale, fz);
+            if (rc) return rc;
+            for (size_t i = 0; i < m; i++)
+                H2B_CK(cudaMemcpyAsync(out_cols[mine[di][i]], d.ntt_a.as<Fr>() + i * N, N * 32, cudaMemcpyDeviceToHost, d.stream));
+            H2B_CK(cudaEventRecord(d.ev_last, d.stream));
+        }
+        for (size_t di = 0; di < nd; di++) {
+            if (mine[di].empty()) continue;
+            Dev& d = ctx->devs[di];
+            H2B_CK(cudaSetDevice(d.id));
+            H2B_CK(cudaStreamSynchronize(d.stream));
+            float ms = 0.f;
+            H2B_CK(cudaEventElapsedTime(&ms, d.ev_first, d.ev_last));
+            max_ms = std::max(max_ms, (double)ms);
+        }
+    }
+    ctx->last_ms = max_ms;
+    return H2B_OK;
+}
+int h2b_ntt_batch(h2b_ctx* ctx, void* const* cols, size_t n_cols, uint32_t log_n, const void* omega32, const void* scale32) {
+    if (!ctx) return H2B_E_INVALID;
+    if ((!cols && n_cols) || !omega32) return ctx->fail(H2B_E_INVALID, "ntt_batch: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = ntt_args_ok(ctx, log_n);
+    if (rc) return rc;
+    Fr omega = fr_from_bytes(omega32), scale;
+    if (scale32) scale = fr_from_bytes(scale32);
+    NttFused fz;
+    return batch_impl(ctx, (const void* const*)cols, cols, n_cols, log_n, log_n, omega, scale32 ? &scale : nullptr, fz);
+}
+int h2b_coeff_to_extended_batch(h2b_ctx* ctx, const void* const* in_cols, void* const* out_cols, size_t n_cols, uint32_t k,
+                                uint32_t ext_k, const void* ext_omega32, const void* g_coset32, const void* g_coset_inv32) {
+    if (!ctx) return H2B_E_INVALID;
+    if ((n_cols && (!in_cols || !out_cols)) || !ext_omega32 || !g_coset32 || !g_coset_inv32)
+        return ctx->fail(H2B_E_INVALID, "coeff_to_extended_batch: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = ntt_args_ok(ctx, ext_k);
+    if (rc) return rc;
+    if (k > ext_k) return ctx->fail(H2B_E_INVALID, "coeff_to_extended_batch: k > extended_k");
+    Fr omega = fr_from_bytes(ext_omega32);
+    Fr pat[2] = {fr_from_bytes(g_coset32), fr_from_bytes(g_coset_inv32)};
+    NttFused fz;
+    fz.in_len = (uint64_t)1 << k;
+    fz.in_pat = pat;
+    return batch_impl(ctx, in_cols, out_cols, n_cols, k, ext_k, omega, nullptr, fz);
+}
+
+// ---- measurement ---------------------------------------------------------------------------------
+double h2b_last_call_ms(const h2b_ctx* ctx) { return ctx ? ctx->last_ms : 0.0; }
+
+int h2b_profile_enable(h2b_ctx* ctx, int on) {
+    if (!ctx) return H2B_E_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    for (Dev& d : ctx->devs) d.prof = on != 0;
+    return H2B_OK;
+}
+
+int h2b_profile_read(h2b_ctx* ctx, char* json_out, size_t cap) {
+    if (!ctx || !json_out || cap < 3) return H2B_E_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    std::map<std::string, std::pair<double, uint64_t>> agg;
+    for (Dev& d : ctx->devs) {
+        cudaSetDevice(d.id);
+        cudaStreamSynchronize(d.stream);
+        for (auto& r : d.recs) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+                auto& a = agg[r.name];
+                a.first += ms; a.second += 1;
+            }
+            d.ev_pool.push_back(r.a); d.ev_pool.push_back(r.b);
+        }
+        d.recs.clear();
+    }
+    std::string s = "{";
+    bool first = true;
+    for (auto& kv : agg) {
+        char buf[256];
+        std::snprintf(buf, sizeof buf, "%s\"%s\": {\"ms\": %.6f, \"launches\": %llu}", first ? "" : ", ", kv.first.c_str(),
+                      kv.second.first, (unsigned long long)kv.second.second);
+        s += buf;
+        first = false;
+    }
+    s += "}";
+    if (s.size() + 1 > cap) return ctx->fail(H2B_E_INVALID, "profile_read: buffer too small");
+    std::memcpy(json_out, s.c_str(), s.size() + 1);
+    return H2B_OK;
+}
+
+uint64_t h2b_launch_count(const h2b_ctx* ctx) {
+    if (!ctx) return 0;
+    uint64_t t = 0;
+    for (const Dev& d : ctx->devs) t += d.launches;
+    return t;
+}
+
+int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_s) {
+    if (!ctx || !wide_mads_per_s || !field_muls_per_s) return H2B_E_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    H2B_CK(d.m_counters.reserve(256));
+    const unsigned blocks = (unsigned)d.sms * 8, threads = 256;
+    const uint32_t it1 = 4096, it2 = 512;
+    cudaEvent_t a = d.get_event(), b = d.get_event();
+    float ms = 0.f;
+    for (int rep = 0; rep < 3; rep++) {   // warm-up + 2 timed; keep the last
+        H2B_CK(cudaEventRecord(a, d.stream));
+        imad_wide_peak_kernel<<<blocks, threads, 0, d.stream>>>(12345u + rep, it1, (unsigned long long*)d.m_counters.p);
+        H2B_CK(cudaEventRecord(b, d.stream));
+        H2B_CK(cudaStreamSynchronize(d.stream));
+        H2B_CK(cudaEventElapsedTime(&ms, a, b));
+    }
+    *wide_mads_per_s = (double)blocks * threads * it1 * 8.0 / (ms * 1e-3);
+    for (int rep = 0; rep < 3; rep++) {
+        H2B_CK(cudaEventRecord(a, d.stream));
+        field_mul_peak_kernel<<<blocks, threads, 0, d.stream>>>(it2, (Fq*)d.m_counters.p);
+        H2B_CK(cudaEventRecord(b, d.stream));
+        H2B_CK(cudaStreamSynchronize(d.stream));
+        H2B_CK(cudaEventElapsedTime(&ms, a, b));
+    }
+    *field_muls_per_s = (double)blocks * threads * it2 * 2.0 / (ms * 1e-3);
+    d.launches += 6;
+    d.ev_pool.push_back(a); d.ev_pool.push_back(b);
+    H2B_CK(cudaGetLastError());
+    return H2B_OK;
+}
+
+}  // extern "C"

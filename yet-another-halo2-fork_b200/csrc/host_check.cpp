@@ -110,3 +110,42 @@ extern "C" int hc_ntt(const void* in_, uint64_t in_len, void* out_, uint64_t out
     }
     return pl.n_pass;
 }
+
+// ------------------------------------------------------------------------------------------------
+// MSM: the same digit recoding, bucket reduction chunking and window combine as the kernels, run serially.
+// ------------------------------------------------------------------------------------------------
+#include "msm.cuh"
+extern "C" void hc_msm(const void* scalars_, const void* bases_, uint32_t n, uint32_t c, uint32_t reduce_threads, void* out96) {
+    const Fr* scalars = (const Fr*)scalars_;
+    const Affine* bases = (const Affine*)bases_;
+    uint32_t W = msm_windows(c), nb = 1u << (c - 1);
+    std::vector<std::vector<uint32_t>> seg((size_t)W * nb);
+    for (uint32_t i = 0; i < n; i++) {
+        Fr canon = fe_from_mont(fe_load(scalars + i));
+        msm_signed_digits(canon, c, W, [&](uint32_t j, int32_t d) {
+            if (d != 0) {
+                uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
+                seg[(size_t)j * nb + mag - 1].push_back(i | (d < 0 ? 0x80000000u : 0u));
+            }
+        });
+    }
+    std::vector<Xyzz> buckets((size_t)W * nb);
+    for (size_t k = 0; k < buckets.size(); k++) {
+        Xyzz acc = Xyzz::identity();
+        for (uint32_t ent : seg[k]) {
+            Affine p = affine_load(bases + (ent & 0x7fffffffu));
+            if (!p.is_identity()) xyzz_madd(acc, p.x, p.y, (ent >> 31) != 0);
+        }
+        buckets[k] = acc;
+    }
+    std::vector<Xyzz> windows(W);
+    for (uint32_t j = 0; j < W; j++) {
+        Xyzz w = Xyzz::identity();
+        uint32_t threads = reduce_threads && nb >= reduce_threads ? reduce_threads : 1;
+        uint32_t per = nb / threads;
+        for (uint32_t t = 0; t < threads; t++)
+            w = xyzz_add(w, msm_reduce_chunk(buckets.data() + (size_t)j * nb + t * per, per, t * per + 1));
+        windows[j] = w;
+    }
+    msm_finish(windows.data(), W, c, out96);
+}

@@ -69,6 +69,22 @@ H2B_HD Xyzz msm_reduce_chunk(const Xyzz* buckets, uint32_t len, uint32_t v0) {
     return acc;
 }
 
+// host: Horner over the window sums (most significant last), normalise, and write the result as the
+// reference's G1 Jacobian layout: (x, y, 1), or (0, 1, 0) for the identity.
+inline void msm_finish(const Xyzz* windows, uint32_t nw, uint32_t c, void* out96) {
+    Xyzz acc = Xyzz::identity();
+    for (uint32_t j = nw; j-- > 0;) {
+        for (uint32_t i = 0; i < c; i++) acc = xyzz_double(acc);
+        acc = xyzz_add(acc, windows[j]);
+    }
+    Affine a = xyzz_to_affine(acc);
+    Fq out[3];
+    if (acc.is_identity()) { out[0] = Fq::zero(); out[1] = Fq::one(); out[2] = Fq::zero(); }
+    else { out[0] = a.x; out[1] = a.y; out[2] = Fq::one(); }
+    for (int i = 0; i < 3; i++)
+        for (int l = 0; l < 8; l++) reinterpret_cast<uint32_t*>(out96)[i * 8 + l] = out[i].l[l];
+}
+
 #if defined(__CUDACC__)
 // ------------------------------------------------------------------------------------------------
 // kernels

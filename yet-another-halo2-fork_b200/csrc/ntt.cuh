@@ -31,7 +31,7 @@ constexpr int NTT_LANES = 8;
 constexpr int NTT_PITCH = 9;          // shared-memory pitch (elements) per sub-NTT position
 constexpr int NTT_MAX_LOG_S = 9;
 
-enum : uint32_t { NTT_IN_PATTERN = 1u, NTT_OUT_PATTERN = 2u, NTT_OUT_SCALE = 4u };
+enum : uint32_t { NTT_IN_PATTERN = 1u, NTT_OUT_PATTERN = 2u, NTT_OUT_SCALE = 4u, NTT_IN_TABLE = 8u };
 
 struct NttPass {
     uint32_t log_s;        // sub-NTT size S = 2^log_s
@@ -41,12 +41,13 @@ struct NttPass {
     uint32_t prev_log[3];  // row pass: their log sizes, first pass first
     uint32_t tw_h;         // boundary twiddle = tw_lo[e & (2^h-1)] * tw_hi[e >> h]
     uint32_t flags;
-    uint32_t pad_;
+    uint32_t in_tab_mask;  // NTT_IN_TABLE: input[i] *= in_tab[i & in_tab_mask]  (divide_by_vanishing_poly, domain.rs:305-310)
     uint64_t in_len;       // inputs at natural index >= in_len read as zero (first pass only)
     uint64_t out_len;      // outputs at natural index >= out_len are not written (row pass only)
     const Fr* tw_s;        // S entries: (omega^(N/S))^e
     const Fr* tw_lo;
     const Fr* tw_hi;
+    const Fr* in_tab;
     Fr in_pat[2];          // multipliers for input index % 3 == 1, 2   (distribute_powers_zeta, domain.rs:325)
     Fr out_pat[2];         // multipliers for output index % 3 == 1, 2
     Fr out_scale;          // single-pass transforms only (multi-pass folds the scale into tw_hi)
@@ -207,6 +208,7 @@ H2B_HD void ntt_level(const NttPass& P, uint32_t t, uint64_t tile, const Fr* in,
                 uint64_t addr = ROW ? row_base + p : col_base + ((uint64_t)p << P.log_inner) + lane;
                 if (active && addr < P.in_len) {
                     x[a] = fe_load(in + addr);
+                    if (P.flags & NTT_IN_TABLE) x[a] = fe_mul(x[a], fe_load(P.in_tab + (addr & P.in_tab_mask)));
                     if (P.flags & NTT_IN_PATTERN) {
                         uint32_t m = mod3(addr);
                         if (m) x[a] = fe_mul(x[a], P.in_pat[m - 1]);
@@ -281,7 +283,6 @@ __global__ void __launch_bounds__((1 << LOG_S) < 32 ? 32 : (1 << LOG_S))
 ntt_pass_kernel(const __grid_constant__ NttPass P, const Fr* __restrict__ in, Fr* __restrict__ out,
                 uint64_t in_stride, uint64_t out_stride) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    constexpr int S = 1 << LOG_S;
     constexpr int NLEV = detail::lev_count(LOG_S);
     Fr* stw = reinterpret_cast<Fr*>(smem_raw);
     U4* slo = reinterpret_cast<U4*>(smem_raw + NttSmem<LOG_S>::tw_bytes);
@@ -307,11 +308,11 @@ ntt_pass_kernel(const __grid_constant__ NttPass P, const Fr* __restrict__ in, Fr
                      ::"r"(dst), "l"(P.tw_s), "r"(bytes), "r"(mbar) : "memory");
     }
     ntt_level<LOG_S, 0, ROW>(P, t, tile, in, out, slo, shi, stw, mbar);
-    if (NLEV > 1) {
+    if constexpr (NLEV > 1) {
         __syncthreads();
         ntt_level<LOG_S, 1, ROW>(P, t, tile, in, out, slo, shi, stw, mbar);
     }
-    if (NLEV > 2) {
+    if constexpr (NLEV > 2) {
         __syncthreads();
         ntt_level<LOG_S, 2, ROW>(P, t, tile, in, out, slo, shi, stw, mbar);
     }

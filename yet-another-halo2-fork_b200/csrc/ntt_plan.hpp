@@ -92,6 +92,8 @@ struct NttFused {            // the EvaluationDomain wrappers' extra work, fused
     uint64_t out_len = ~0ull;         // outputs beyond out_len are dropped (extended_to_coeff truncation)
     const Fr* in_pat = nullptr;       // [2]: multipliers for index%3 == 1, 2 on the way in
     const Fr* out_pat = nullptr;      // [2]: same on the way out
+    const Fr* in_tab = nullptr;       // table in the memory space of the kernel: input[i] *= in_tab[i & in_tab_mask]
+    uint32_t in_tab_mask = 0;
 };
 
 // Descriptors for all passes.  `tables` is the base of the generated table buffer (device or host).
@@ -122,6 +124,7 @@ inline void ntt_build_passes(const NttPlan& pl, const Fr* tables, const Fr* scal
         if (j == 0) {
             P.in_len = fz.in_len;
             if (fz.in_pat) { P.flags |= NTT_IN_PATTERN; P.in_pat[0] = fz.in_pat[0]; P.in_pat[1] = fz.in_pat[1]; }
+            if (fz.in_tab) { P.flags |= NTT_IN_TABLE; P.in_tab = fz.in_tab; P.in_tab_mask = fz.in_tab_mask; }
         }
         done += pl.log_s[j];
     }

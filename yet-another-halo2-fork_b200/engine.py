@@ -1,0 +1,244 @@
+"""B200Engine: the GPU implementation of the reference's ZK-acceleration-layer MSM trait.
+
+Mirrors `trait MsmAccel<C>` (halo2_middleware/src/zal.rs:57-103) method for method:
+
+    msm(coeffs, base)                      zal.rs:58
+    get_coeffs_descriptor(coeffs)          zal.rs:81
+    get_base_descriptor(base)              zal.rs:82
+    msm_with_cached_scalars(desc, base)    zal.rs:84
+    msm_with_cached_base(coeffs, desc)     zal.rs:90
+    msm_with_cached_inputs(desc, desc)     zal.rs:96
+
+Scalars are `n x 4` uint64 arrays (Montgomery Fr), bases `n x 8` uint64 (affine, identity = (0,0)); results are
+`uint64[12]` Jacobian, normalised.  Length mismatch raises (the reference `assert_eq!`s inside best_multiexp).
+Descriptors hold device memory and release it on drop, as zal.rs:47-50 asks.
+"""
+from __future__ import annotations
+
+import ctypes
+import json
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import H2bError
+
+
+def _is_torch_cuda(x) -> bool:
+    return hasattr(x, "is_cuda") and bool(x.is_cuda)
+
+
+def _host_ptr(a: np.ndarray, limbs: int):
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    if a.ndim != 2 or a.shape[1] != limbs:
+        raise ValueError(f"expected an (n, {limbs}) uint64 array, got {a.shape}")
+    return a, a.ctypes.data_as(ctypes.c_void_p), a.shape[0]
+
+
+class Context:
+    """Owns one `h2b_ctx` (devices, streams, resident bases, twiddle tables)."""
+
+    def __init__(self, device_ids: Optional[Sequence[int]] = None):
+        self.lib = _lib.load()
+        self._ctx = ctypes.c_void_p()
+        if device_ids is None:
+            rc = self.lib.h2b_init(ctypes.byref(self._ctx), None, 0)
+        else:
+            arr = (ctypes.c_int * len(device_ids))(*device_ids)
+            rc = self.lib.h2b_init(ctypes.byref(self._ctx), arr, len(device_ids))
+        if rc != 0:
+            msg = self.lib.h2b_last_error(None)
+            raise H2bError(rc, msg.decode() if msg else "h2b_init failed")
+
+    def check(self, rc: int):
+        if rc != 0:
+            msg = self.lib.h2b_last_error(self._ctx)
+            raise H2bError(rc, msg.decode() if msg else "?")
+
+    @property
+    def handle(self):
+        return self._ctx
+
+    def last_call_ms(self) -> float:
+        return float(self.lib.h2b_last_call_ms(self._ctx))
+
+    def launch_count(self) -> int:
+        return int(self.lib.h2b_launch_count(self._ctx))
+
+    def profile_enable(self, on: bool = True):
+        self.check(self.lib.h2b_profile_enable(self._ctx, 1 if on else 0))
+
+    def profile_read(self) -> dict:
+        buf = ctypes.create_string_buffer(1 << 16)
+        self.check(self.lib.h2b_profile_read(self._ctx, buf, len(buf)))
+        return json.loads(buf.value.decode())
+
+    def imad_peak(self):
+        a, b = ctypes.c_double(), ctypes.c_double()
+        self.check(self.lib.h2b_imad_peak(self._ctx, ctypes.byref(a), ctypes.byref(b)))
+        return a.value, b.value
+
+    def close(self):
+        if self._ctx:
+            self.lib.h2b_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class BaseDescriptor:
+    """`MsmAccel::BaseDescriptor`: bases resident on the device(s)."""
+
+    def __init__(self, ctx: Context, bases):
+        self.ctx = ctx
+        h = ctypes.c_uint64()
+        if _is_torch_cuda(bases):
+            self._keep = bases           # adopted, not copied
+            self.n = bases.numel() * bases.element_size() // 64
+            ctx.check(ctx.lib.h2b_bases_register_device(ctx.handle, ctypes.c_void_p(bases.data_ptr()), self.n, ctypes.byref(h)))
+        else:
+            a, p, self.n = _host_ptr(bases, 8)
+            ctx.check(ctx.lib.h2b_bases_register(ctx.handle, p, self.n, ctypes.byref(h)))
+        self.handle = h.value
+
+    def release(self):
+        if self.handle and self.ctx.handle:
+            self.ctx.lib.h2b_bases_release(self.ctx.handle, self.handle)
+        self.handle = 0
+
+    def __del__(self):
+        try:
+            self.release()
+        except Exception:
+            pass
+
+
+class CoeffsDescriptor:
+    """`MsmAccel::CoeffsDescriptor`: scalars staged once (a device tensor when torch is available)."""
+
+    def __init__(self, ctx: Context, coeffs):
+        self.ctx = ctx
+        if _is_torch_cuda(coeffs):
+            self.dev = coeffs
+            self.n = coeffs.numel() * coeffs.element_size() // 32
+        else:
+            import torch
+            a, _, self.n = _host_ptr(coeffs, 4)
+            self.dev = torch.from_numpy(a.view(np.int64)).to("cuda")
+
+
+class B200Engine:
+    """GPU `MsmAccel<G1Affine>` (replaces `H2cEngine`, zal.rs:119,135-177)."""
+
+    def __init__(self, ctx: Optional[Context] = None, device_ids: Optional[Sequence[int]] = None):
+        self.ctx = ctx if ctx is not None else Context(device_ids)
+
+    # --- zal.rs:58
+    def msm(self, coeffs, base) -> np.ndarray:
+        c, cp, n = _host_ptr(coeffs, 4)
+        b, bp, nb = _host_ptr(base, 8)
+        if n != nb:
+            raise ValueError(f"msm: coeffs.len() = {n} != base.len() = {nb}")
+        out = np.zeros(12, dtype=np.uint64)
+        self.ctx.check(self.ctx.lib.h2b_msm_raw(self.ctx.handle, bp, cp, n, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    # --- zal.rs:81-82
+    def get_coeffs_descriptor(self, coeffs) -> CoeffsDescriptor:
+        return CoeffsDescriptor(self.ctx, coeffs)
+
+    def get_base_descriptor(self, base) -> BaseDescriptor:
+        return BaseDescriptor(self.ctx, base)
+
+    # --- zal.rs:84
+    def msm_with_cached_scalars(self, coeffs: CoeffsDescriptor, base) -> np.ndarray:
+        desc = BaseDescriptor(self.ctx, base)
+        try:
+            return self.msm_with_cached_inputs(coeffs, desc)
+        finally:
+            desc.release()
+
+    # --- zal.rs:90
+    def msm_with_cached_base(self, coeffs, base: BaseDescriptor) -> np.ndarray:
+        out = np.zeros(12, dtype=np.uint64)
+        if _is_torch_cuda(coeffs):
+            n = coeffs.numel() * coeffs.element_size() // 32
+            self._check_len(n, base)
+            self.ctx.check(self.ctx.lib.h2b_msm_device(self.ctx.handle, base.handle, ctypes.c_void_p(coeffs.data_ptr()), n,
+                                                       out.ctypes.data_as(ctypes.c_void_p)))
+        else:
+            c, cp, n = _host_ptr(coeffs, 4)
+            self._check_len(n, base)
+            self.ctx.check(self.ctx.lib.h2b_msm(self.ctx.handle, base.handle, cp, n, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
+    # --- zal.rs:96
+    def msm_with_cached_inputs(self, coeffs: CoeffsDescriptor, base: BaseDescriptor) -> np.ndarray:
+        return self.msm_with_cached_base(coeffs.dev, base)
+
+    @staticmethod
+    def _check_len(n: int, base: BaseDescriptor):
+        if n > base.n:
+            raise ValueError(f"msm: {n} coefficients but only {base.n} cached bases")
+
+    # --- multi-process sharding helpers (h2b_msm_windows / h2b_msm_combine)
+    def msm_windows(self, coeffs, base: BaseDescriptor, n_total: int):
+        out = np.zeros((_lib.MSM_MAX_WINDOWS, 16), dtype=np.uint64)
+        c, w = ctypes.c_uint32(), ctypes.c_uint32()
+        if _is_torch_cuda(coeffs):
+            n = coeffs.numel() * coeffs.element_size() // 32
+            ptr, on_dev = ctypes.c_void_p(coeffs.data_ptr()), 1
+        else:
+            a, ptr, n = _host_ptr(coeffs, 4)
+            on_dev = 0
+        self._check_len(n, base)
+        self.ctx.check(self.ctx.lib.h2b_msm_windows(self.ctx.handle, base.handle, ptr, on_dev, n, n_total,
+                                                    out.ctypes.data_as(ctypes.c_void_p), ctypes.byref(c), ctypes.byref(w)))
+        return out[: w.value].copy(), c.value
+
+    @staticmethod
+    def msm_combine(parts: np.ndarray, c: int) -> np.ndarray:
+        """parts: (n_parts, windows, 16) uint64 -> normalised Jacobian."""
+        lib = _lib.load()
+        parts = np.ascontiguousarray(parts, dtype=np.uint64)
+        n_parts, windows = parts.shape[0], parts.shape[1]
+        out = np.zeros(12, dtype=np.uint64)
+        rc = lib.h2b_msm_combine(parts.ctypes.data_as(ctypes.c_void_p), n_parts, c, windows, out.ctypes.data_as(ctypes.c_void_p))
+        if rc != 0:
+            raise H2bError(rc, "h2b_msm_combine: invalid arguments")
+        return out
+
+
+class PlonkEngine:
+    """zal.rs:182-185: `PlonkEngine { msm_backend }`."""
+
+    def __init__(self, msm_backend: B200Engine):
+        self.msm_backend = msm_backend
+
+
+class PlonkEngineConfig:
+    """zal.rs:188-243 builder: PlonkEngineConfig().set_msm(engine).build()."""
+
+    def __init__(self):
+        self._msm = None
+
+    @staticmethod
+    def new():
+        return PlonkEngineConfig()
+
+    def set_curve(self, _curve=None):
+        return self
+
+    def set_msm(self, engine: B200Engine):
+        self._msm = engine
+        return self
+
+    def build(self) -> PlonkEngine:
+        if self._msm is None:
+            self._msm = B200Engine()
+        return PlonkEngine(self._msm)
