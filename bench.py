@@ -1,0 +1,337 @@
+#!/usr/bin/env python
+"""bench.py -- BN254 MSM 2^24 (headline) and Fr NTT 2^24 on B200, with the CPU restatement timed beside it.
+
+    python bench.py --gpus N --steps K --warmup W            this repo's CUDA path (one process per GPU under torchrun)
+    python bench.py --impl reference --gpus N --steps K ...  the reference's CPU algorithm (oracle port, host cores)
+
+A "step" is one 2^24-point MSM over resident bases (BASELINE.json configs[1]).  With N > 1 GPUs the MSM is sharded
+by contiguous point range (strong scaling): every rank reduces its own range to per-window sums, the ranks all-gather
+W x 128 bytes over NCCL, rank 0 folds them.  One JSON line is printed by rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+MSM_K = int(os.environ.get("H2B_BENCH_MSM_K", "24"))
+NTT_K = int(os.environ.get("H2B_BENCH_NTT_K", "24"))
+CPU_SAMPLE_K = int(os.environ.get("H2B_BENCH_CPU_K", "20"))
+# SURVEY.md §8(d) algorithmic work: XYZZ mixed additions for the best window size, 10 field multiplications each,
+# 128 IMAD.WIDE (32x32->64 multiply-add) per Montgomery multiplication (64 product + 64 reduction).
+MSM_ADDS = {16: 1.475e6, 18: 5.014e6, 20: 1.769e7, 22: 6.488e7, 24: 2.317e8, 26: 8.556e8}
+WIDE_PER_FIELD_MUL = 128
+MULS_PER_MADD = 10
+
+
+def workload_config(world: int) -> dict:
+    return {"workload": f"configs[1]: best_multiexp BN254 G1 MSM, 2^{MSM_K} points ([t0+i]G bases, uniform scalars), "
+                        f"sharded by point range over {world} GPU(s)",
+            "window_bits": int(os.environ.get("H2B_MSM_C", "0")) or "auto",
+            "l2": "inputs (1.5 GiB) exceed the 126 MB L2; no flush needed"}
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return float(d.get("hbm_gbs", 6650.0)), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for nm, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------
+# CPU restatement (oracle port): bounded sample, all host threads
+# ---------------------------------------------------------------------------------------------------------
+def cpu_msm_sample(sample_k: int, reps: int = 1):
+    """Times the C restatement of halo2curves best_multiexp (oracle/h2ref.c) on 2^sample_k points; returns
+    (ms for the sample, threads).  Same input generators as the GPU arm."""
+    from oracle import cref as C
+    n = 1 << sample_k
+    s, b = C.random_fr(n, 1), C.gen_bases(n, 1)
+    best = float("inf")
+    for _ in range(reps):
+        t = time.perf_counter()
+        C.best_multiexp(s, b)
+        best = min(best, (time.perf_counter() - t) * 1e3)
+    return best, C.num_threads()
+
+
+def cpu_ntt_sample(sample_k: int):
+    from oracle import cref as C
+    from oracle import pyref as R
+    a = C.random_fr(1 << sample_k, 2)
+    w = C.mont_from_int(pow(R.ROOT_OF_UNITY, 1 << (28 - sample_k), R.R_MOD), R.R_MOD)
+    t = time.perf_counter()
+    C.best_fft(a, w, sample_k)
+    return (time.perf_counter() - t) * 1e3
+
+
+def scale_to_full(ms: float, sample_k: int, full_k: int) -> float:
+    """Linear-in-n extrapolation of a sample to the full size (optimistic for the CPU: Pippenger's per-point cost
+    falls slowly with n, an NTT's rises with log n)."""
+    return ms * float(1 << (full_k - sample_k))
+
+
+def run_reference(args, rank: int, world: int):
+    if rank != 0:
+        return
+    from oracle import cref as C
+    for _ in range(max(0, args.warmup) and 1):       # one warm-up pass is enough for a CPU loop
+        cpu_msm_sample(min(CPU_SAMPLE_K, 16))
+    times = []
+    for _ in range(args.steps):
+        ms, threads = cpu_msm_sample(CPU_SAMPLE_K)
+        times.append(ms)
+    sample_ms = float(np.mean(times))
+    full_ms = scale_to_full(sample_ms, CPU_SAMPLE_K, MSM_K)
+    ntt_ms = cpu_ntt_sample(CPU_SAMPLE_K)
+    sample = (f"best_multiexp restatement on 2^{CPU_SAMPLE_K} points per step ({sample_ms:.1f} ms), scaled x{1 << (MSM_K - CPU_SAMPLE_K)} "
+              f"linearly to 2^{MSM_K}")
+    line = {
+        "impl": "reference", "metric": f"bn254_msm_2^{MSM_K}_ms", "value": full_ms, "unit": "ms", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": full_ms, "higher_is_better": False, "scaling": "strong",
+        "vs_baseline": None, "dtype": "u32x8 (254-bit Montgomery integers)", "data": "synthetic",
+        "config": workload_config(args.gpus),
+        "cpu_baseline": {"value": full_ms, "unit": "ms", "cores": C.num_threads(), "kind": "port", "sample": sample},
+        "e2e": {"value": full_ms, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "ntt": {"metric": f"fr_ntt_2^{NTT_K}_ms", "value": scale_to_full(ntt_ms, CPU_SAMPLE_K, NTT_K) * NTT_K / CPU_SAMPLE_K, "unit": "ms",
+                "sample": f"best_fft restatement on 2^{CPU_SAMPLE_K} ({ntt_ms:.1f} ms), scaled by n log n"},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------
+def run_gpu(args, rank: int, world: int, local_rank: int):
+    import ctypes
+    import torch
+    import torch.distributed as dist
+    import h2b200
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ctx = h2b200.Context([local_rank])
+    eng = h2b200.B200Engine(ctx)
+    F = h2b200.fields
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- inputs: this rank's contiguous point range ------------------------------------------------------
+    n_total = 1 << MSM_K
+    lo, hi = n_total * rank // world, n_total * (rank + 1) // world
+    n_loc = hi - lo
+    d_bases = h2b200.synth.device_bases(ctx, n_loc, 1 + lo)
+    desc = eng.get_base_descriptor(d_bases)
+    h_scalars = torch.from_numpy(h2b200.synth.random_scalars(n_loc, 1234 + rank).view(np.int64)).pin_memory()
+    d_scalars = h_scalars.cuda()
+
+    def msm_step(scalars):
+        """one whole MSM; returns the normalised result on rank 0 (None elsewhere)"""
+        if world == 1:
+            return eng.msm_with_cached_base(scalars, desc)
+        w, c = eng.msm_windows(scalars, desc, n_total)
+        mine = torch.from_numpy(w.view(np.int64)).cuda()
+        allw = torch.empty((world,) + tuple(mine.shape), dtype=mine.dtype, device="cuda")
+        dist.all_gather_into_tensor(allw, mine)
+        if rank == 0:
+            return eng.msm_combine(allw.cpu().numpy().view(np.uint64), c)
+        return None
+
+    for _ in range(args.warmup):
+        msm_step(d_scalars)
+    ctx.profile_enable(True)
+    ctx.profile_read()
+    sampler = ClockSampler(local_rank)
+    launches0 = ctx.launch_count()
+    barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res_dev = msm_step(d_scalars)
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop()
+    launches = ctx.launch_count() - launches0
+    prof = ctx.profile_read()
+    ctx.profile_enable(False)
+    ms_per_step = max_over_ranks(wall_ms / args.steps)
+
+    # ---- e2e: host (pinned) scalars in, 96-byte point out, through the same public call ----------------------
+    for _ in range(min(args.warmup, 2)):
+        msm_step(h_scalars.numpy().view(np.uint64))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res_e2e = msm_step(h_scalars.numpy().view(np.uint64))
+    barrier()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+    if rank == 0 and not np.array_equal(res_dev, res_e2e):
+        raise SystemExit("bench: device-resident and host-buffer MSM results differ")
+
+    # ---- NTT 2^24: device-resident, then host buffers in/out ----------------------------------------------
+    dom = h2b200.EvaluationDomain(1, NTT_K, ctx)
+    h_poly = torch.from_numpy(h2b200.synth.random_scalars(1 << NTT_K, 99 + rank).view(np.int64)).pin_memory()
+    d_poly = h_poly.cuda()
+    for _ in range(args.warmup):
+        dom.coeff_to_lagrange(d_poly)
+    ctx.profile_enable(True)
+    ctx.profile_read()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        dom.coeff_to_lagrange(d_poly)
+    barrier()
+    ntt_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+    ntt_prof = ctx.profile_read()
+    ctx.profile_enable(False)
+    hp = h_poly.numpy().view(np.uint64)
+    dom.coeff_to_lagrange(hp)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        dom.coeff_to_lagrange(hp)
+    barrier()
+    ntt_e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+
+    wide_peak, fmul_peak = ctx.imad_peak()
+    if rank != 0:
+        ctx.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (bucket accumulation), from CUDA events on the launching stream ---------
+    hbm_peak, peak_src = peaks()
+    acc = prof.get("msm_accumulate", {"ms": 0.0, "launches": 1})
+    acc_ms = acc["ms"] / max(1, acc["launches"])
+    kernel_ms = {k: v["ms"] / args.steps for k, v in prof.items()}
+    adds = MSM_ADDS.get(MSM_K, 0.0) / world                 # this rank's share of the SURVEY 8(d) addition count
+    alg_bytes = 96.0 * n_loc                                # 32 B scalar + 64 B base per point
+    imad_achieved = adds * MULS_PER_MADD * WIDE_PER_FIELD_MUL / (acc_ms * 1e-3) if acc_ms else 0.0
+    roofline = {
+        "kernel": "msm_accumulate_kernel", "bound": "hbm", "achieved": alg_bytes / (acc_ms * 1e-3) / 1e9 if acc_ms else 0.0,
+        "peak": hbm_peak, "unit": "GB/s", "peak_source": peak_src, "traffic": None,
+        "note": "integer-multiply bound, not HBM bound: the binding roofline is `imad` below (SURVEY.md 8d)",
+        "imad": {"achieved": imad_achieved, "peak": wide_peak, "unit": "IMAD.WIDE/s", "frac": imad_achieved / wide_peak if wide_peak else None,
+                 "peak_source": "h2b_imad_peak: IMAD.WIDE carry chains measured in this run", "field_muls_per_s_peak": fmul_peak,
+                 "algorithmic": f"{adds:.4g} XYZZ mixed adds x {MULS_PER_MADD} field muls x {WIDE_PER_FIELD_MUL} IMAD.WIDE"},
+        "kernel_ms_per_step": kernel_ms,
+    }
+    roofline["frac"] = roofline["achieved"] / hbm_peak
+    npass = sum(v["launches"] for v in ntt_prof.values()) // max(1, args.steps)
+    ntt_kernel_ms = sum(v["ms"] for v in ntt_prof.values()) / args.steps
+    ntt_bytes = 128.0 * (1 << NTT_K) if NTT_K > 21 else 64.0 * (1 << NTT_K)
+    ntt_muls = (1 << NTT_K) / 2 * NTT_K
+    ntt = {
+        "metric": f"fr_ntt_2^{NTT_K}_ms", "value": ntt_ms, "unit": "ms", "passes": npass, "aggregate_ntt_per_s": world * 1e3 / ntt_ms,
+        "e2e": {"value": ntt_e2e_ms, "unit": "ms", "h2d_bytes_per_step": 32 << NTT_K, "d2h_bytes_per_step": 32 << NTT_K},
+        "roofline": {"bound": "hbm", "achieved": ntt_bytes / (ntt_kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": ntt_bytes / (ntt_kernel_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None,
+                     "imad": {"achieved": ntt_muls * WIDE_PER_FIELD_MUL / (ntt_kernel_ms * 1e-3), "peak": wide_peak, "unit": "IMAD.WIDE/s",
+                              "frac": ntt_muls * WIDE_PER_FIELD_MUL / (ntt_kernel_ms * 1e-3) / wide_peak}},
+    }
+    line = {
+        "metric": f"bn254_msm_2^{MSM_K}_ms", "value": ms_per_step, "unit": "ms", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u32x8 (254-bit Montgomery integers)", "data": "synthetic",
+        "config": workload_config(world),
+        "e2e": {"value": e2e_ms, "unit": "ms", "h2d_bytes_per_step": 32 * n_total, "d2h_bytes_per_step": 96},
+        "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "ntt": ntt,
+        "msm_points_per_s": n_total / (ms_per_step * 1e-3),
+    }
+    if world == 1 and not args.no_cpu:
+        ms, threads = cpu_msm_sample(CPU_SAMPLE_K)
+        line["cpu_baseline"] = {"value": scale_to_full(ms, CPU_SAMPLE_K, MSM_K), "unit": "ms", "cores": threads, "kind": "port",
+                                "sample": f"C restatement of halo2curves 0.6 best_multiexp (rayon chunk-per-thread Booth Pippenger) on 2^{CPU_SAMPLE_K} "
+                                          f"points: {ms:.1f} ms, scaled x{1 << (MSM_K - CPU_SAMPLE_K)} linearly"}
+        nms = cpu_ntt_sample(CPU_SAMPLE_K)
+        ntt["cpu_baseline"] = {"value": scale_to_full(nms, CPU_SAMPLE_K, NTT_K) * NTT_K / CPU_SAMPLE_K, "unit": "ms", "cores": threads, "kind": "port",
+                               "sample": f"best_fft restatement on 2^{CPU_SAMPLE_K}: {nms:.1f} ms, scaled by n log n"}
+    print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if args.warmup < 3:
+        args.warmup = 3
+    run_gpu(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

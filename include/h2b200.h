@@ -133,6 +133,9 @@ int h2b_profile_enable(h2b_ctx* ctx, int on);
 int h2b_profile_read(h2b_ctx* ctx, char* json_out, size_t cap);
 uint64_t h2b_launch_count(const h2b_ctx* ctx);   /* kernels launched by this context since h2b_init */
 
+/* synthetic benchmark input: d_out[i] = [t0 + i]G as 64-byte affine points, on device 0. */
+int h2b_synth_bases(h2b_ctx* ctx, void* d_out, size_t n, uint64_t t0);
+
 /* integer-multiply pipe calibration: runs a dependent-free IMAD.WIDE loop on every SM and returns the
  * sustained rate in units of 32x32->64 multiply-adds per second (the MSM / NTT roofline denominator). */
 int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_s);

@@ -40,7 +40,7 @@ def test_msm_matches_oracle(engine, n):
     desc.release()
 
 
-@pytest.mark.parametrize("c", [2, 3, 5, 8, 11, 13, 16, 18, 20])
+@pytest.mark.parametrize("c", [4, 5, 7, 8, 11, 13, 16, 18, 20])
 def test_window_sizes(engine, c, monkeypatch):
     monkeypatch.setenv("H2B_MSM_C", str(c))
     n = 3000

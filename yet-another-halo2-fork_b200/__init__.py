@@ -3,11 +3,11 @@
 Importing this package does not touch the GPU; constructing a `Context` loads libh2b200.so and fails loudly
 if it is missing or no sm_100 device is present (there is no CPU fallback).
 """
-from . import fields
+from . import fields, synth
 from ._lib import H2bError, LIB_PATH, SYMBOLS, load
 from .domain import EvaluationDomain
 from .engine import B200Engine, BaseDescriptor, CoeffsDescriptor, Context, PlonkEngine, PlonkEngineConfig
 from .kzg import ParamsKZG
 
-__all__ = ["fields", "H2bError", "LIB_PATH", "SYMBOLS", "load", "EvaluationDomain", "B200Engine", "BaseDescriptor",
+__all__ = ["fields", "synth", "H2bError", "LIB_PATH", "SYMBOLS", "load", "EvaluationDomain", "B200Engine", "BaseDescriptor",
            "CoeffsDescriptor", "Context", "PlonkEngine", "PlonkEngineConfig", "ParamsKZG"]

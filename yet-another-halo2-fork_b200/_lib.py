@@ -42,6 +42,7 @@ SYMBOLS = {
     "h2b_profile_read": (_int, [_vp, ctypes.c_char_p, _sz]),
     "h2b_launch_count": (_u64, [_vp]),
     "h2b_imad_peak": (_int, [_vp, _pd, _pd]),
+    "h2b_synth_bases": (_int, [_vp, _vp, _sz, _u64]),
 }
 
 _lib = None

@@ -9,12 +9,6 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libh2b200.so")
 HOSTCHECK = os.path.join(HERE, "libh2b200_hostcheck.so")
 
-NVCC_FLAGS = [
-    "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared",
-]
-
-
 def _newer(target: str, sources) -> bool:
     if not os.path.exists(target):
         return False
@@ -29,11 +23,26 @@ def _sources():
 
 
 def build_lib(force: bool = False, verbose: bool = False) -> str:
+    """Compile every .cu under csrc/ for sm_100a (in parallel) and link libh2b200.so in-tree."""
     if not force and _newer(LIB, _sources()):
         return LIB
+    from concurrent.futures import ThreadPoolExecutor
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, os.path.join(CSRC, "h2b200.cu")]
-    subprocess.check_call(cmd, cwd=HERE)
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+    cus = sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+    cflags = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC"]
+    if verbose:
+        cflags += ["-Xptxas", "-v"]
+
+    def compile_one(f):
+        obj = os.path.join(objdir, f[:-3] + ".o")
+        subprocess.check_call([nvcc] + cflags + ["-c", "-o", obj, os.path.join(CSRC, f)], cwd=HERE)
+        return obj
+
+    with ThreadPoolExecutor(max_workers=min(8, len(cus))) as ex:
+        objs = list(ex.map(compile_one, cus))
+    subprocess.check_call([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs, cwd=HERE)
     return LIB
 
 

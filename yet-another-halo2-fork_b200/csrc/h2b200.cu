@@ -18,6 +18,7 @@
 #include "msm.cuh"
 #include "ntt.cuh"
 #include "ntt_plan.hpp"
+#include "ntt_kernels.hpp"
 
 using namespace h2b;
 
@@ -130,23 +131,16 @@ inline Fr fr_from_bytes(const void* p) { Fr f; std::memcpy(&f, p, 32); return f;
 // ------------------------------------------------------------------------------------------------
 // NTT
 // ------------------------------------------------------------------------------------------------
-typedef void (*ntt_kernel_t)(const NttPass, const Fr*, Fr*, uint64_t, uint64_t);
-
-template <int LOG_S>
-void ntt_kernel_entry(ntt_kernel_t tab[10][2], size_t smem[10]) {
-    tab[LOG_S][0] = ntt_pass_kernel<LOG_S, false>;
-    tab[LOG_S][1] = ntt_pass_kernel<LOG_S, true>;
-    smem[LOG_S] = NttSmem<LOG_S>::bytes;
-}
 struct NttKernels {
     ntt_kernel_t tab[10][2];
     size_t smem[10];
     NttKernels() {
         std::memset(tab, 0, sizeof(tab));
         std::memset(smem, 0, sizeof(smem));
-        ntt_kernel_entry<1>(tab, smem); ntt_kernel_entry<2>(tab, smem); ntt_kernel_entry<3>(tab, smem);
-        ntt_kernel_entry<4>(tab, smem); ntt_kernel_entry<5>(tab, smem); ntt_kernel_entry<6>(tab, smem);
-        ntt_kernel_entry<7>(tab, smem); ntt_kernel_entry<8>(tab, smem); ntt_kernel_entry<9>(tab, smem);
+        h2b_ntt_register_a(tab, smem);
+        h2b_ntt_register_b(tab, smem);
+        h2b_ntt_register_c(tab, smem);
+        h2b_ntt_register_d(tab, smem);
     }
 };
 const NttKernels& ntt_kernels() { static NttKernels k; return k; }
@@ -218,7 +212,7 @@ int ntt_enqueue(h2b_ctx* ctx, Dev& d, const Fr* in, uint64_t in_stride, Fr* tmp,
 uint32_t msm_choose_c(size_t n_total) {
     if (const char* env = std::getenv("H2B_MSM_C")) {
         int v = std::atoi(env);
-        if (v >= 2 && v <= 24) return (uint32_t)v;
+        if (v >= 4 && v <= 24) return (uint32_t)v;   // c >= 4 keeps windows <= H2B_MSM_MAX_WINDOWS
     }
     uint32_t lg = 0;
     while (((size_t)1 << (lg + 1)) <= n_total) lg++;
@@ -330,6 +324,7 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
     if (n > B.n) return ctx->fail(H2B_E_INVALID, "msm: more scalars than registered bases");
     uint32_t c = msm_choose_c(n_total);
     uint32_t nw = msm_windows(c);
+    if (nw > H2B_MSM_MAX_WINDOWS) return ctx->fail(H2B_E_INVALID, "msm: window size too small");
     for (uint32_t j = 0; j < nw; j++) windows_out[j] = Xyzz::identity();
     *c_out = c; *windows_count = nw;
     if (n == 0) { ctx->last_ms = 0; return H2B_OK; }
@@ -404,31 +399,68 @@ void release_bases(h2b_ctx* ctx, Bases& B) {
 // ------------------------------------------------------------------------------------------------
 // integer-pipe calibration kernels
 // ------------------------------------------------------------------------------------------------
+// IMAD.WIDE carry chains exactly as the field multiplier issues them (two interleaved chains of four
+// lo/hi pairs sharing one multiplier register; per-thread operands so nothing lands on the uniform datapath).
+// Counts one "wide mad" per IMAD.WIDE.U32(.X): 8 per iteration.
 __global__ void imad_wide_peak_kernel(uint32_t seed, uint32_t iters, unsigned long long* sink) {
-    uint32_t a = seed + threadIdx.x, b = seed * 3u + blockIdx.x;
-    unsigned long long acc[8];
+    uint32_t e[8], o[8], a[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++) acc[i] = (unsigned long long)i * 0x9E3779B97F4A7C15ull + a;
-    for (uint32_t it = 0; it < iters; it++) {
-#pragma unroll
-        for (int i = 0; i < 8; i++)
-            asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a + (uint32_t)i), "r"(b));
+    for (int i = 0; i < 8; i++) {
+        e[i] = seed * (i + 1) + threadIdx.x;
+        o[i] = e[i] * 3u + blockIdx.x;
+        a[i] = seed + 77u * i + blockIdx.x + threadIdx.x * 2654435761u;
     }
-    unsigned long long s = 0;
+    for (uint32_t it = 0; it < iters; it++) {
+        uint32_t bi = e[1] | 1u;
+        asm volatile(
+            "mad.lo.cc.u32 %0, %8, %12, %0;\n madc.hi.cc.u32 %1, %8, %12, %1;\n"
+            "madc.lo.cc.u32 %2, %9, %12, %2;\n madc.hi.cc.u32 %3, %9, %12, %3;\n"
+            "madc.lo.cc.u32 %4, %10, %12, %4;\n madc.hi.cc.u32 %5, %10, %12, %5;\n"
+            "madc.lo.cc.u32 %6, %11, %12, %6;\n madc.hi.u32 %7, %11, %12, %7;\n"
+            : "+r"(e[0]), "+r"(e[1]), "+r"(e[2]), "+r"(e[3]), "+r"(e[4]), "+r"(e[5]), "+r"(e[6]), "+r"(e[7])
+            : "r"(a[0]), "r"(a[2]), "r"(a[4]), "r"(a[6]), "r"(bi));
+        asm volatile(
+            "mad.lo.cc.u32 %0, %8, %12, %0;\n madc.hi.cc.u32 %1, %8, %12, %1;\n"
+            "madc.lo.cc.u32 %2, %9, %12, %2;\n madc.hi.cc.u32 %3, %9, %12, %3;\n"
+            "madc.lo.cc.u32 %4, %10, %12, %4;\n madc.hi.cc.u32 %5, %10, %12, %5;\n"
+            "madc.lo.cc.u32 %6, %11, %12, %6;\n madc.hi.u32 %7, %11, %12, %7;\n"
+            : "+r"(o[0]), "+r"(o[1]), "+r"(o[2]), "+r"(o[3]), "+r"(o[4]), "+r"(o[5]), "+r"(o[6]), "+r"(o[7])
+            : "r"(a[1]), "r"(a[3]), "r"(a[5]), "r"(a[7]), "r"(bi));
+    }
+    uint32_t s = 0;
 #pragma unroll
-    for (int i = 0; i < 8; i++) s ^= acc[i];
-    if (s == 0x1234567ull) *sink = s;
+    for (int i = 0; i < 8; i++) s ^= e[i] ^ o[i];
+    if (s == 0x1234567u) *sink = s;
 }
+// Two independent chains of dependent field multiplications per thread, all operands per-thread.
 __global__ void field_mul_peak_kernel(uint32_t iters, Fq* sink) {
     Fq x = Fq::one(), y = Fq::r2();
-    x.l[0] += threadIdx.x; y.l[1] += blockIdx.x;
+#pragma unroll
+    for (int i = 0; i < 7; i++) { x.l[i] ^= threadIdx.x * 2654435761u + i; y.l[i] ^= (threadIdx.x + 7u * blockIdx.x) * 40503u + i; }
     Fq a = x, b = y;
     for (uint32_t it = 0; it < iters; it++) {
-        a = fe_mul(a, x);
-        b = fe_mul(b, y);
+        a = fe_mul(a, y);
+        b = fe_mul(b, x);
+        x.l[0] ^= b.l[3] & 1u;          // keep the operands loop-variant
     }
     Fq r = fe_add(a, b);
     if (r.l[0] == 0x12345u && r.l[7] == 0x54321u) *sink = r;
+}
+
+// Synthetic benchmark bases: out[i] = [t0 + i] G, G = (1, 2), affine.
+__global__ void synth_bases_kernel(Affine* out, uint64_t n, uint64_t t0) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t k = t0 + i;
+    Fq gx = fe_from_u64<FqParams>(1), gy = fe_from_u64<FqParams>(2);
+    Xyzz acc = Xyzz::identity();
+    for (int bit = 63; bit >= 0; bit--) {
+        acc = xyzz_double(acc);
+        if ((k >> bit) & 1ull) xyzz_madd(acc, gx, gy, false);
+    }
+    Affine a = xyzz_to_affine(acc);
+    fe_store(&out[i].x, a.x);
+    fe_store(&out[i].y, a.y);
 }
 
 }  // namespace
@@ -844,6 +876,18 @@ uint64_t h2b_launch_count(const h2b_ctx* ctx) {
     return t;
 }
 
+int h2b_synth_bases(h2b_ctx* ctx, void* d_out, size_t n, uint64_t t0) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!d_out && n) return ctx->fail(H2B_E_INVALID, "synth_bases: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    begin_call(d);
+    if (n) H2B_LAUNCH(d, "synth_bases", synth_bases_kernel, (unsigned)((n + 127) / 128), 128, 0, (Affine*)d_out, (uint64_t)n, t0);
+    H2B_CK(cudaGetLastError());
+    return end_call(ctx, d);
+}
+
 int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_s) {
     if (!ctx || !wide_mads_per_s || !field_muls_per_s) return H2B_E_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);
@@ -861,7 +905,7 @@ int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_
         H2B_CK(cudaStreamSynchronize(d.stream));
         H2B_CK(cudaEventElapsedTime(&ms, a, b));
     }
-    *wide_mads_per_s = (double)blocks * threads * it1 * 8.0 / (ms * 1e-3);
+    *wide_mads_per_s = (double)blocks * threads * it1 * 8.0 / (ms * 1e-3);   // 8 IMAD.WIDE per iteration
     for (int rep = 0; rep < 3; rep++) {
         H2B_CK(cudaEventRecord(a, d.stream));
         field_mul_peak_kernel<<<blocks, threads, 0, d.stream>>>(it2, (Fq*)d.m_counters.p);

@@ -319,7 +319,7 @@ ntt_pass_kernel(const __grid_constant__ NttPass P, const Fr* __restrict__ in, Fr
 }
 
 // out[i] = first * root^i, i < count   (table generation; square-and-multiply on the bits of i)
-__global__ void ntt_gen_powers_kernel(Fr* out, Fr root, Fr first, uint32_t count) {
+static __global__ void ntt_gen_powers_kernel(Fr* out, Fr root, Fr first, uint32_t count) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
     Fr acc = first, base = root;
