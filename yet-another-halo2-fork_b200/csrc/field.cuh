@@ -281,6 +281,34 @@ H2B_HD Fe<P> fe_mul(const Fe<P>& a, const Fe<P>& b) {
 template <class P>
 H2B_HD Fe<P> fe_sqr(const Fe<P>& a) { return fe_mul(a, a); }
 
+// Out-of-line multiplier for kernels whose fully inlined body would not fit the instruction cache (the NTT
+// levels hold ~30 multiplications each).  Operands and result travel in registers (no stack); the ~20 extra
+// MOVs per call go to the ALU pipe, which is idle next to the saturated IMAD.WIDE pipe.
+template <class P>
+struct FePair { Fe<P> a, b; };
+#if defined(__CUDA_ARCH__)
+template <class P>
+__device__ __noinline__ Fe<P> fe_mul_call(Fe<P> a, Fe<P> b) { return fe_mul(a, b); }
+// two independent products per call: ptxas interleaves the four carry chains (2x the ILP of one product)
+template <class P>
+__device__ __noinline__ FePair<P> fe_mul2_call(Fe<P> a, Fe<P> b, Fe<P> c, Fe<P> d) {
+    FePair<P> r;
+    r.a = fe_mul(a, b);
+    r.b = fe_mul(c, d);
+    return r;
+}
+#else
+template <class P>
+inline Fe<P> fe_mul_call(const Fe<P>& a, const Fe<P>& b) { return fe_mul(a, b); }
+template <class P>
+inline FePair<P> fe_mul2_call(const Fe<P>& a, const Fe<P>& b, const Fe<P>& c, const Fe<P>& d) {
+    FePair<P> r;
+    r.a = fe_mul(a, b);
+    r.b = fe_mul(c, d);
+    return r;
+}
+#endif
+
 // Montgomery -> canonical integer (halo2curves to_repr): multiply by 1.
 template <class P>
 H2B_HD Fe<P> fe_from_mont(const Fe<P>& a) {

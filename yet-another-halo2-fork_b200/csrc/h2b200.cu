@@ -164,10 +164,23 @@ int ntt_get_plan(h2b_ctx* ctx, Dev& d, uint32_t log_n, const Fr& omega, const Fr
     pd.plan = ntt_make_plan(log_n, omega, scale);
     pd.has_scale = scale != nullptr;
     if (scale) pd.scale = *scale;
-    H2B_CK(cudaMalloc((void**)&pd.tables, pd.plan.table_elems * sizeof(Fr)));
+    H2B_CK(cudaMalloc((void**)&pd.tables, pd.plan.total_elems * sizeof(Fr)));
     for (const auto& seg : pd.plan.segments) {
         H2B_LAUNCH(d, "ntt_gen_powers", ntt_gen_powers_kernel, (seg.count + 127) / 128, 128, 0,
                    pd.tables + seg.offset, seg.root, seg.first, seg.count);
+    }
+    {
+        uint32_t done = 0;
+        for (int j = 0; j + 1 < pd.plan.n_pass; j++) {
+            if (pd.plan.full_count[j]) {
+                uint64_t cnt = pd.plan.full_count[j];
+                uint32_t log_inner = log_n - done - pd.plan.log_s[j];
+                const Fr* hi = pd.tables + (j == 0 ? pd.plan.off_hi_first : pd.plan.off_hi_rest);
+                H2B_LAUNCH(d, "ntt_gen_powers", ntt_gen_boundary_kernel, (unsigned)((cnt + 127) / 128), 128, 0,
+                           pd.tables + pd.plan.off_full[j], pd.tables + pd.plan.off_lo, hi, pd.plan.tw_h, log_inner, done, cnt);
+            }
+            done += pd.plan.log_s[j];
+        }
     }
     H2B_CK(cudaGetLastError());
     auto ins = d.plans.emplace(key, std::move(pd));

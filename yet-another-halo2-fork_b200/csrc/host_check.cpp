@@ -86,10 +86,24 @@ extern "C" int hc_ntt(const void* in_, uint64_t in_len, void* out_, uint64_t out
     Fr omega = ld<Fr>(omega_);
     Fr scale; if (scale_or_null) scale = ld<Fr>(scale_or_null);
     NttPlan pl = ntt_make_plan(log_n, omega, scale_or_null ? &scale : nullptr);
-    std::vector<Fr> tables(pl.table_elems);
+    std::vector<Fr> tables(pl.total_elems);
     for (auto& seg : pl.segments) {
         Fr acc = seg.first;
         for (uint32_t i = 0; i < seg.count; i++) { tables[seg.offset + i] = acc; acc = fe_mul(acc, seg.root); }
+    }
+    {   // full boundary tables, as ntt_gen_boundary_kernel fills them
+        uint32_t done = 0;
+        for (int j = 0; j + 1 < pl.n_pass; j++) {
+            if (pl.full_count[j]) {
+                uint32_t log_inner = log_n - done - pl.log_s[j];
+                const Fr* hi = tables.data() + (j == 0 ? pl.off_hi_first : pl.off_hi_rest);
+                for (uint64_t idx = 0; idx < pl.full_count[j]; idx++) {
+                    uint64_t k = idx >> log_inner, i = idx & ((1ull << log_inner) - 1), e = (i * k) << done;
+                    tables[pl.off_full[j] + idx] = fe_mul(tables[pl.off_lo + (e & ((1ull << pl.tw_h) - 1))], hi[e >> pl.tw_h]);
+                }
+            }
+            done += pl.log_s[j];
+        }
     }
     NttFused fz; fz.in_len = in_len; fz.out_len = out_len;
     Fr ip[2], op[2];

@@ -47,6 +47,7 @@ struct NttPass {
     const Fr* tw_s;        // S entries: (omega^(N/S))^e
     const Fr* tw_lo;
     const Fr* tw_hi;
+    const Fr* tw_full;     // optional full boundary table: tw_full[k * inner + i] = scale * omega^(outer * i * k)
     const Fr* in_tab;
     Fr in_pat[2];          // multipliers for input index % 3 == 1, 2   (distribute_powers_zeta, domain.rs:325)
     Fr out_pat[2];         // multipliers for output index % 3 == 1, 2
@@ -63,26 +64,32 @@ H2B_HD constexpr int lev_log_b(int s, int lev) { return s - 3 * lev; }
 template <int LOG_R>
 H2B_HD void butterflies(Fr x[8], const Fr& w1, const Fr& w2, const Fr& w3) {
     if (LOG_R == 3) {
+        Fr t[4];
 #pragma unroll
         for (int a = 0; a < 4; a++) {
-            Fr t = fe_sub(x[a], x[a + 4]);
+            t[a] = fe_sub(x[a], x[a + 4]);
             x[a] = fe_add(x[a], x[a + 4]);
-            x[a + 4] = a == 0 ? t : fe_mul(t, a == 1 ? w1 : (a == 2 ? w2 : w3));
         }
+        x[4] = t[0];
+        FePair<FrParams> pr = fe_mul2_call(t[1], w1, t[2], w2);
+        x[5] = pr.a; x[6] = pr.b;
+        x[7] = fe_mul_call(t[3], w3);
+        Fr u[2];
 #pragma unroll
         for (int h = 0; h < 8; h += 4) {
             Fr t0 = fe_sub(x[h], x[h + 2]);
             x[h] = fe_add(x[h], x[h + 2]);
             x[h + 2] = t0;
-            Fr t1 = fe_sub(x[h + 1], x[h + 3]);
+            u[h >> 2] = fe_sub(x[h + 1], x[h + 3]);
             x[h + 1] = fe_add(x[h + 1], x[h + 3]);
-            x[h + 3] = fe_mul(t1, w2);
         }
+        pr = fe_mul2_call(u[0], w2, u[1], w2);
+        x[3] = pr.a; x[7] = pr.b;
 #pragma unroll
         for (int h = 0; h < 8; h += 2) {
-            Fr t = fe_sub(x[h], x[h + 1]);
+            Fr tt = fe_sub(x[h], x[h + 1]);
             x[h] = fe_add(x[h], x[h + 1]);
-            x[h + 1] = t;
+            x[h + 1] = tt;
         }
     } else if (LOG_R == 2) {
         Fr t0 = fe_sub(x[0], x[2]);
@@ -90,7 +97,7 @@ H2B_HD void butterflies(Fr x[8], const Fr& w1, const Fr& w2, const Fr& w3) {
         x[2] = t0;
         Fr t1 = fe_sub(x[1], x[3]);
         x[1] = fe_add(x[1], x[3]);
-        x[3] = fe_mul(t1, w2);       // w2 = primitive 4th root
+        x[3] = fe_mul_call(t1, w2);       // w2 = primitive 4th root
         Fr t = fe_sub(x[0], x[1]);
         x[0] = fe_add(x[0], x[1]);
         x[1] = t;
@@ -208,10 +215,10 @@ H2B_HD void ntt_level(const NttPass& P, uint32_t t, uint64_t tile, const Fr* in,
                 uint64_t addr = ROW ? row_base + p : col_base + ((uint64_t)p << P.log_inner) + lane;
                 if (active && addr < P.in_len) {
                     x[a] = fe_load(in + addr);
-                    if (P.flags & NTT_IN_TABLE) x[a] = fe_mul(x[a], fe_load(P.in_tab + (addr & P.in_tab_mask)));
+                    if (P.flags & NTT_IN_TABLE) x[a] = fe_mul_call(x[a], fe_load(P.in_tab + (addr & P.in_tab_mask)));
                     if (P.flags & NTT_IN_PATTERN) {
                         uint32_t m = mod3(addr);
-                        if (m) x[a] = fe_mul(x[a], P.in_pat[m - 1]);
+                        if (m) x[a] = fe_mul_call(x[a], P.in_pat[m - 1]);
                     }
                 } else {
                     x[a] = Fr::zero();
@@ -234,29 +241,70 @@ H2B_HD void ntt_level(const NttPass& P, uint32_t t, uint64_t tile, const Fr* in,
         }
         // ---------------- level twiddles + store
         uint32_t kbase = LAST ? block_to_kbase<LOG_S>(blk) : 0;
+        if (!LAST) {
+            // level twiddles, two per out-of-line call
+#pragma unroll
+            for (int ka = 1; ka + 1 < R; ka += 2) {
+                FePair<FrParams> pr = fe_mul2_call(x[bitrev(ka, LOG_R)], fe_load(stw + ((b * (uint32_t)ka) << (LOG_S - LOG_B))),
+                                                   x[bitrev(ka + 1, LOG_R)], fe_load(stw + ((b * (uint32_t)(ka + 1)) << (LOG_S - LOG_B))));
+                x[bitrev(ka, LOG_R)] = pr.a;
+                x[bitrev(ka + 1, LOG_R)] = pr.b;
+            }
+            if (R >= 2) {
+                constexpr int kl = R - 1;
+                x[bitrev(kl, LOG_R)] = fe_mul_call(x[bitrev(kl, LOG_R)], fe_load(stw + ((b * (uint32_t)kl) << (LOG_S - LOG_B))));
+            }
+        }
+        if (LAST && !ROW) {
+            // column pass: boundary twiddle w^(outer*i*k), then store in place (row k, column i).
+            // Twiddles are fetched four at a time ahead of their multiplications (two products per call).
+            const uint64_t i = i0 + lane;
+            constexpr int HALF = R >= 4 ? 4 : R;
+#pragma unroll
+            for (int base = 0; base < R; base += HALF) {
+                Fr tw[HALF];
+#pragma unroll
+                for (int q2 = 0; q2 < HALF; q2++) {
+                    uint32_t k = kbase + ((uint32_t)(base + q2) << (LOG_S - LOG_R));
+                    if (P.tw_full) {
+                        tw[q2] = fe_load(P.tw_full + ((uint64_t)k << P.log_inner) + i);
+                    } else {
+                        uint64_t e = (i * k) << P.log_outer;
+                        tw[q2] = fe_mul_call(fe_load(P.tw_lo + (e & ((1ull << P.tw_h) - 1))), fe_load(P.tw_hi + (e >> P.tw_h)));
+                    }
+                }
+#pragma unroll
+                for (int q2 = 0; q2 < HALF; q2 += 2) {
+                    uint32_t k0 = kbase + ((uint32_t)(base + q2) << (LOG_S - LOG_R));
+                    if (q2 + 1 < HALF) {
+                        uint32_t k1 = kbase + ((uint32_t)(base + q2 + 1) << (LOG_S - LOG_R));
+                        FePair<FrParams> pr = fe_mul2_call(x[bitrev(base + q2, LOG_R)], tw[q2], x[bitrev(base + q2 + 1, LOG_R)], tw[q2 + 1 < HALF ? q2 + 1 : q2]);
+                        fe_store(out + col_base + ((uint64_t)k0 << P.log_inner) + lane, pr.a);
+                        fe_store(out + col_base + ((uint64_t)k1 << P.log_inner) + lane, pr.b);
+                    } else {
+                        fe_store(out + col_base + ((uint64_t)k0 << P.log_inner) + lane, fe_mul_call(x[bitrev(base + q2, LOG_R)], tw[q2]));
+                    }
+                }
+            }
+        }
 #pragma unroll
         for (int ka = 0; ka < R; ka++) {
             Fr v = x[bitrev(ka, LOG_R)];
             if (!LAST) {
-                if (ka > 0) v = fe_mul(v, fe_load(stw + ((b * (uint32_t)ka) << (LOG_S - LOG_B))));
                 uint32_t p = p0 + ((uint32_t)ka << LOG_Q);
                 uint32_t si = p * NTT_PITCH + lane;
                 fe_split(v, slo[si], shi[si]);
             } else {
                 uint32_t k = kbase + ((uint32_t)ka << (LOG_S - LOG_R));      // sub-NTT output index
                 if (!ROW) {
-                    uint64_t i = i0 + lane;
-                    uint64_t e = (i * k) << P.log_outer;
-                    Fr tw = fe_mul(fe_load(P.tw_lo + (e & ((1ull << P.tw_h) - 1))), fe_load(P.tw_hi + (e >> P.tw_h)));
-                    v = fe_mul(v, tw);
-                    fe_store(out + col_base + ((uint64_t)k << P.log_inner) + lane, v);
+                    // handled above
                 } else if (active) {
                     uint64_t idx = rev + ((uint64_t)k << P.log_outer);
                     if (idx < P.out_len) {
-                        if (P.flags & NTT_OUT_SCALE) v = fe_mul(v, P.out_scale);
+                        if (P.flags & NTT_OUT_SCALE) v = fe_mul_call(v, P.out_scale);
                         if (P.flags & NTT_OUT_PATTERN) {
                             uint32_t m = mod3(idx);
-                            if (m) v = fe_mul(v, P.out_pat[m - 1]);
+                            if (m) v = fe_mul_call(v, P.out_pat[m - 1]);
                         }
                         fe_store(out + idx, v);
                     }
@@ -279,7 +327,7 @@ struct NttSmem {
 };
 
 template <int LOG_S, bool ROW>
-__global__ void __launch_bounds__((1 << LOG_S) < 32 ? 32 : (1 << LOG_S))
+__global__ void __launch_bounds__((1 << LOG_S) < 32 ? 32 : (1 << LOG_S), (1 << LOG_S) < 32 ? 16 : 512 / (1 << LOG_S))
 ntt_pass_kernel(const __grid_constant__ NttPass P, const Fr* __restrict__ in, Fr* __restrict__ out,
                 uint64_t in_stride, uint64_t out_stride) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -328,6 +376,15 @@ static __global__ void ntt_gen_powers_kernel(Fr* out, Fr root, Fr first, uint32_
         base = fe_sqr(base);
     }
     fe_store(out + i, acc);
+}
+// full boundary table of a column pass: out[k * inner + i] = tw_lo[e & mask] * tw_hi[e >> h], e = (i * k) << log_outer
+static __global__ void ntt_gen_boundary_kernel(Fr* out, const Fr* tw_lo, const Fr* tw_hi, uint32_t tw_h, uint32_t log_inner,
+                                               uint32_t log_outer, uint64_t count) {
+    uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= count) return;
+    uint64_t k = idx >> log_inner, i = idx & ((1ull << log_inner) - 1);
+    uint64_t e = (i * k) << log_outer;
+    fe_store(out + idx, fe_mul(fe_load(tw_lo + (e & ((1ull << tw_h) - 1))), fe_load(tw_hi + (e >> tw_h))));
 }
 #endif  // __CUDACC__
 

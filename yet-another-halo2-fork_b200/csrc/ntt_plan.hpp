@@ -24,7 +24,10 @@ struct NttPlan {
     bool has_scale = false;
     size_t off_tw_s[4] = {0, 0, 0, 0};
     size_t off_lo = 0, off_hi_first = 0, off_hi_rest = 0;
-    size_t table_elems = 0;
+    size_t table_elems = 0;          // power segments
+    size_t off_full[4] = {0, 0, 0, 0};   // full boundary tables (0 = none), appended after the power segments
+    size_t full_count[4] = {0, 0, 0, 0};
+    size_t total_elems = 0;
     std::vector<NttPowerSegment> segments;
 };
 
@@ -84,6 +87,17 @@ inline NttPlan ntt_make_plan(uint32_t log_n, const Fr& omega, const Fr* scale) {
         }
     }
     pl.table_elems = off;
+    // Full boundary tables (one multiplication saved per element per column pass) while they stay affordable:
+    // pass j needs N / outer_j entries.  H2B_NTT_FULL_TABLE_MAX_LOG (default 26) caps the largest one.
+    uint32_t cap = 26;
+    if (const char* env = std::getenv("H2B_NTT_FULL_TABLE_MAX_LOG")) cap = (uint32_t)std::atoi(env);
+    uint32_t done = 0;
+    for (int j = 0; j + 1 < pl.n_pass; j++) {
+        uint32_t lg = log_n - done;
+        if (lg <= cap) { pl.off_full[j] = off; pl.full_count[j] = (size_t)1 << lg; off += (size_t)1 << lg; }
+        done += pl.log_s[j];
+    }
+    pl.total_elems = off;
     return pl;
 }
 
@@ -113,6 +127,7 @@ inline void ntt_build_passes(const NttPlan& pl, const Fr* tables, const Fr* scal
             P.log_inner = pl.log_n - done - pl.log_s[j];
             P.tw_lo = tables + pl.off_lo;
             P.tw_hi = tables + (j == 0 ? pl.off_hi_first : pl.off_hi_rest);
+            P.tw_full = pl.full_count[j] ? tables + pl.off_full[j] : nullptr;
         } else {
             P.log_outer = done;
             P.n_prev = (uint32_t)j;
