@@ -6,8 +6,9 @@ if it is missing or no sm_100 device is present (there is no CPU fallback).
 from . import fields, synth
 from ._lib import H2bError, LIB_PATH, SYMBOLS, load
 from .domain import EvaluationDomain
-from .engine import B200Engine, BaseDescriptor, CoeffsDescriptor, Context, PlonkEngine, PlonkEngineConfig
+from .engine import (B200Engine, BaseDescriptor, CoeffsDescriptor, Context, PlonkEngine, PlonkEngineConfig, shard_range,
+                     window_bits)
 from .kzg import ParamsKZG
 
 __all__ = ["fields", "synth", "H2bError", "LIB_PATH", "SYMBOLS", "load", "EvaluationDomain", "B200Engine", "BaseDescriptor",
-           "CoeffsDescriptor", "Context", "PlonkEngine", "PlonkEngineConfig", "ParamsKZG"]
+           "CoeffsDescriptor", "Context", "PlonkEngine", "PlonkEngineConfig", "ParamsKZG", "shard_range", "window_bits"]

@@ -129,7 +129,19 @@ extern "C" int hc_ntt(const void* in_, uint64_t in_len, void* out_, uint64_t out
 // MSM: the same digit recoding, bucket reduction chunking and window combine as the kernels, run serially.
 // ------------------------------------------------------------------------------------------------
 #include "msm.cuh"
+static void hc_msm_windows_impl(const void* scalars_, const void* bases_, uint32_t n, uint32_t c, uint32_t reduce_threads, std::vector<Xyzz>& windows);
 extern "C" void hc_msm(const void* scalars_, const void* bases_, uint32_t n, uint32_t c, uint32_t reduce_threads, void* out96) {
+    std::vector<Xyzz> windows;
+    hc_msm_windows_impl(scalars_, bases_, n, c, reduce_threads, windows);
+    msm_finish(windows.data(), msm_windows(c), c, out96);
+}
+// per-window sums of one point range (what h2b_msm_windows returns on the GPU): windows x 128 bytes
+extern "C" void hc_msm_windows(const void* scalars_, const void* bases_, uint32_t n, uint32_t c, void* out_windows) {
+    std::vector<Xyzz> windows;
+    hc_msm_windows_impl(scalars_, bases_, n, c, 0, windows);
+    std::memcpy(out_windows, windows.data(), windows.size() * sizeof(Xyzz));
+}
+static void hc_msm_windows_impl(const void* scalars_, const void* bases_, uint32_t n, uint32_t c, uint32_t reduce_threads, std::vector<Xyzz>& windows) {
     const Fr* scalars = (const Fr*)scalars_;
     const Affine* bases = (const Affine*)bases_;
     uint32_t W = msm_windows(c), nb = 1u << (c - 1);
@@ -152,7 +164,7 @@ extern "C" void hc_msm(const void* scalars_, const void* bases_, uint32_t n, uin
         }
         buckets[k] = acc;
     }
-    std::vector<Xyzz> windows(W);
+    windows.assign(W, Xyzz::identity());
     for (uint32_t j = 0; j < W; j++) {
         Xyzz w = Xyzz::identity();
         uint32_t threads = reduce_threads && nb >= reduce_threads ? reduce_threads : 1;
@@ -161,5 +173,4 @@ extern "C" void hc_msm(const void* scalars_, const void* bases_, uint32_t n, uin
             w = xyzz_add(w, msm_reduce_chunk(buckets.data() + (size_t)j * nb + t * per, per, t * per + 1));
         windows[j] = w;
     }
-    msm_finish(windows.data(), W, c, out96);
 }

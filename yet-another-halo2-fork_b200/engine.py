@@ -214,6 +214,21 @@ class B200Engine:
         return out
 
 
+def shard_range(n: int, rank: int, world: int):
+    """Contiguous point range [lo, hi) of rank `rank` out of `world` (MSM sharded by point range)."""
+    return n * rank // world, n * (rank + 1) // world
+
+
+def window_bits(n_total: int) -> int:
+    """The window size every shard of an n_total-point MSM uses (mirrors msm_choose_c in csrc/h2b200.cu)."""
+    import os
+    env = os.environ.get("H2B_MSM_C")
+    if env and 4 <= int(env) <= 24:
+        return int(env)
+    lg = max(n_total, 1).bit_length() - 1
+    return min(16, max(4, lg - 4))
+
+
 class PlonkEngine:
     """zal.rs:182-185: `PlonkEngine { msm_backend }`."""
 
