@@ -49,6 +49,18 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel_prefix: str, size_k: int):
+    """DRAM bytes per launch (read + write) from the committed `ncu` capture of the same kernel at the same size
+    (profiles/r1_full_size_dram_traffic.json, taken at 2^24); None when the size differs."""
+    path = os.path.join(ROOT, "profiles", "r1_full_size_dram_traffic.json")
+    if size_k != 24 or not os.path.exists(path):
+        return None
+    rows = [r for r in json.load(open(path)) if r["kernel"].startswith(kernel_prefix)]
+    if not rows:
+        return None
+    return float(np.mean([r["dram_read_bytes"] + r["dram_write_bytes"] for r in rows]))
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -118,6 +130,88 @@ def scale_to_full(ms: float, sample_k: int, full_k: int) -> float:
     """Linear-in-n extrapolation of a sample to the full size (optimistic for the CPU: Pippenger's per-point cost
     falls slowly with n, an NTT's rises with log n)."""
     return ms * float(1 << (full_k - sample_k))
+
+
+# ---------------------------------------------------------------------------------------------------------
+# k = 20 proof-shaped kernel sequence (BASELINE.json configs[3]): the MSM / NTT calls ONE create_proof makes for
+# the frontend_backend_split circuit at k = 20 (SURVEY.md 8d: 9 commit_lagrange + 8 commit MSMs of 2^20, 10 iNTTs of
+# 2^20, 10 coset NTTs 2^20 -> 2^23, 1 inverse coset NTT of 2^23), issued through the reference-facing interface with
+# HOST buffers.  It is the accelerated part of the prover, not a proof: witness synthesis, evaluate_h and the transcript
+# stay on the CPU in the reference integration and are not timed here.
+# ---------------------------------------------------------------------------------------------------------
+SEQ_K, SEQ_J = 20, 6
+SEQ_COUNTS = {"commit_lagrange_uniform": 4, "commit_lagrange_skewed": 5, "commit": 8, "lagrange_to_coeff": 10,
+              "coeff_to_extended": 10, "extended_to_coeff": 1}
+
+
+def skew(scalars: np.ndarray, one: np.ndarray, seed: int) -> np.ndarray:
+    """selector-like column: 45 % zeros, 45 % ones, 10 % uniform (SURVEY.md 8d non-uniform set (i))."""
+    rng = np.random.default_rng(seed)
+    u = rng.random(scalars.shape[0])
+    out = scalars.copy()
+    out[u < 0.45] = 0
+    out[(u >= 0.45) & (u < 0.9)] = one
+    return out
+
+
+def proof_sequence_gpu(ctx, eng):
+    import h2b200
+    n = 1 << SEQ_K
+    dom = h2b200.EvaluationDomain(SEQ_J, SEQ_K, ctx)
+    g = eng.get_base_descriptor(h2b200.synth.device_bases(ctx, n, 1))
+    gl = eng.get_base_descriptor(h2b200.synth.device_bases(ctx, n, 1 + n))
+    uni = h2b200.synth.random_scalars(n, 5)
+    skw = skew(uni, h2b200.fields.fr_mont(1), 6)
+    ext = np.empty((dom.extended_len(), 4), dtype=np.uint64)
+
+    def once():
+        for _ in range(SEQ_COUNTS["commit_lagrange_uniform"]):
+            eng.msm_with_cached_base(uni, gl)
+        for _ in range(SEQ_COUNTS["commit_lagrange_skewed"]):
+            eng.msm_with_cached_base(skw, gl)
+        for _ in range(SEQ_COUNTS["commit"]):
+            eng.msm_with_cached_base(uni, g)
+        for _ in range(SEQ_COUNTS["lagrange_to_coeff"]):
+            dom.lagrange_to_coeff(uni.copy())
+        for _ in range(SEQ_COUNTS["coeff_to_extended"]):
+            dom.coeff_to_extended(uni, out=ext)
+        for _ in range(SEQ_COUNTS["extended_to_coeff"]):
+            dom.extended_to_coeff(ext)
+
+    once()
+    l0 = ctx.launch_count()
+    t = time.perf_counter()
+    once()
+    ms = (time.perf_counter() - t) * 1e3
+    return ms, ctx.launch_count() - l0
+
+
+def proof_sequence_cpu():
+    """One call of each kind through the oracle port, scaled by SEQ_COUNTS (bounded sample)."""
+    from oracle import cref as C
+    from oracle import pyref as R
+    n = 1 << SEQ_K
+    d = R.EvaluationDomain(SEQ_J, SEQ_K)
+    m = lambda x: C.mont_from_int(x, R.R_MOD)
+    uni, bases = C.random_fr(n, 5), C.gen_bases(n, 1)
+    skw = skew(uni, m(1), 6)
+    parts = {}
+
+    def timed(name, fn):
+        t = time.perf_counter()
+        r = fn()
+        parts[name] = (time.perf_counter() - t) * 1e3
+        return r
+
+    timed("commit_lagrange_uniform", lambda: C.best_multiexp(uni, bases))
+    timed("commit_lagrange_skewed", lambda: C.best_multiexp(skw, bases))
+    parts["commit"] = parts["commit_lagrange_uniform"]
+    coeff = timed("lagrange_to_coeff", lambda: C.lagrange_to_coeff(uni, SEQ_K, m(d.omega_inv), m(d.ifft_divisor)))
+    ext = timed("coeff_to_extended", lambda: C.coeff_to_extended(coeff, SEQ_K, d.extended_k, m(d.extended_omega), m(d.g_coset), m(d.g_coset_inv)))
+    timed("extended_to_coeff", lambda: C.extended_to_coeff(ext, d.extended_k, m(d.extended_omega_inv), m(d.extended_ifft_divisor),
+                                                            m(d.g_coset), m(d.g_coset_inv), n * (SEQ_J - 1)))
+    total = sum(parts[k] * SEQ_COUNTS[k] for k in SEQ_COUNTS)
+    return total, parts, C.num_threads()
 
 
 def run_reference(args, rank: int, world: int):
@@ -271,7 +365,8 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
     imad_achieved = adds * MULS_PER_MADD * WIDE_PER_FIELD_MUL / (acc_ms * 1e-3) if acc_ms else 0.0
     roofline = {
         "kernel": "msm_accumulate_kernel", "bound": "hbm", "achieved": alg_bytes / (acc_ms * 1e-3) / 1e9 if acc_ms else 0.0,
-        "peak": hbm_peak, "unit": "GB/s", "peak_source": peak_src, "traffic": None,
+        "peak": hbm_peak, "unit": "GB/s", "peak_source": peak_src,
+        "traffic": (ncu_traffic("msm_accumulate_kernel", MSM_K) or 0) / world or None,
         "note": "integer-multiply bound, not HBM bound: the binding roofline is `imad` below (SURVEY.md 8d)",
         "imad": {"achieved": imad_achieved, "peak": wide_peak, "unit": "IMAD.WIDE/s", "frac": imad_achieved / wide_peak if wide_peak else None,
                  "peak_source": "h2b_imad_peak: IMAD.WIDE carry chains measured in this run", "field_muls_per_s_peak": fmul_peak,
@@ -287,7 +382,9 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
         "metric": f"fr_ntt_2^{NTT_K}_ms", "value": ntt_ms, "unit": "ms", "passes": npass, "aggregate_ntt_per_s": world * 1e3 / ntt_ms,
         "e2e": {"value": ntt_e2e_ms, "unit": "ms", "h2d_bytes_per_step": 32 << NTT_K, "d2h_bytes_per_step": 32 << NTT_K},
         "roofline": {"bound": "hbm", "achieved": ntt_bytes / (ntt_kernel_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": ntt_bytes / (ntt_kernel_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None,
+                     "frac": ntt_bytes / (ntt_kernel_ms * 1e-3) / 1e9 / hbm_peak,
+                     "traffic": (ncu_traffic("ntt_pass_kernel", NTT_K) or 0) * npass or None,
+                     "traffic_note": "sum over the passes of one transform (ncu dram__bytes_read+write)",
                      "imad": {"achieved": ntt_muls * WIDE_PER_FIELD_MUL / (ntt_kernel_ms * 1e-3), "peak": wide_peak, "unit": "IMAD.WIDE/s",
                               "frac": ntt_muls * WIDE_PER_FIELD_MUL / (ntt_kernel_ms * 1e-3) / wide_peak}},
     }
@@ -300,6 +397,15 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "ntt": ntt,
         "msm_points_per_s": n_total / (ms_per_step * 1e-3),
     }
+    if world == 1 and not args.no_seq:
+        seq_ms, seq_launches = proof_sequence_gpu(ctx, eng)
+        line["k20_kernel_sequence"] = {
+            "what": "MSM + NTT calls of one k=20 create_proof (SURVEY 8d counts), host buffers in/out, through MsmAccel / EvaluationDomain mirrors; not a proof",
+            "counts": SEQ_COUNTS, "value": seq_ms, "unit": "ms", "gpu_launches": seq_launches}
+        if not args.no_cpu:
+            cpu_total, cpu_parts, thr = proof_sequence_cpu()
+            line["k20_kernel_sequence"]["cpu_baseline"] = {"value": cpu_total, "unit": "ms", "cores": thr, "kind": "port",
+                                                           "sample": "one call of each kind timed, scaled by the counts", "per_call_ms": cpu_parts}
     if world == 1 and not args.no_cpu:
         ms, threads = cpu_msm_sample(CPU_SAMPLE_K)
         line["cpu_baseline"] = {"value": scale_to_full(ms, CPU_SAMPLE_K, MSM_K), "unit": "ms", "cores": threads, "kind": "port",
@@ -321,6 +427,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-seq", action="store_true", help="skip the k=20 proof-shaped kernel sequence")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -6,6 +6,7 @@
 // Formulas: EFD shortw/xyzz madd-2008-s, add-2008-s, dbl-2008-s-1, mdbl-2008-s-1 (a = 0).
 #pragma once
 #include "field.cuh"
+#include "field_wide.cuh"
 
 namespace h2b {
 
@@ -49,13 +50,13 @@ H2B_HD Xyzz xyzz_load(const Xyzz* p) {
 H2B_HD Xyzz xyzz_double_affine(const Fq& x1, const Fq& y1) {
     Xyzz r;
     Fq u = fe_dbl(y1);
-    Fq v = fe_sqr(u);
+    Fq v = fe_sqr_w(u);
     Fq w = fe_mul(u, v);
     Fq s = fe_mul(x1, v);
-    Fq xx = fe_sqr(x1);
+    Fq xx = fe_sqr_w(x1);
     Fq m = fe_add(fe_dbl(xx), xx);
-    r.x = fe_sub(fe_sqr(m), fe_dbl(s));
-    r.y = fe_sub(fe_mul(m, fe_sub(s, r.x)), fe_mul(w, y1));
+    r.x = fe_sub(fe_sqr_w(m), fe_dbl(s));
+    r.y = fe_mul_sub_mul(m, fe_sub(s, r.x), w, y1);
     r.zz = v;
     r.zzz = w;
     return r;
@@ -66,13 +67,13 @@ H2B_HD Xyzz xyzz_double(const Xyzz& p) {
     if (p.is_identity()) return p;
     Xyzz r;
     Fq u = fe_dbl(p.y);
-    Fq v = fe_sqr(u);
+    Fq v = fe_sqr_w(u);
     Fq w = fe_mul(u, v);
     Fq s = fe_mul(p.x, v);
-    Fq xx = fe_sqr(p.x);
+    Fq xx = fe_sqr_w(p.x);
     Fq m = fe_add(fe_dbl(xx), xx);
-    r.x = fe_sub(fe_sqr(m), fe_dbl(s));
-    r.y = fe_sub(fe_mul(m, fe_sub(s, r.x)), fe_mul(w, p.y));
+    r.x = fe_sub(fe_sqr_w(m), fe_dbl(s));
+    r.y = fe_mul_sub_mul(m, fe_sub(s, r.x), w, p.y);
     r.zz = fe_mul(v, p.zz);
     r.zzz = fe_mul(w, p.zzz);
     return r;
@@ -94,11 +95,11 @@ H2B_HD void xyzz_madd(Xyzz& acc, const Fq& x2, const Fq& y2_in, bool neg) {
         else acc = Xyzz::identity();
         return;
     }
-    Fq pp = fe_sqr(p);
+    Fq pp = fe_sqr_w(p);
     Fq ppp = fe_mul(p, pp);
     Fq q = fe_mul(acc.x, pp);
-    Fq x3 = fe_sub(fe_sub(fe_sqr(r), ppp), fe_dbl(q));
-    Fq y3 = fe_sub(fe_mul(r, fe_sub(q, x3)), fe_mul(acc.y, ppp));
+    Fq x3 = fe_sub(fe_sub(fe_sqr_w(r), ppp), fe_dbl(q));
+    Fq y3 = fe_mul_sub_mul(r, fe_sub(q, x3), acc.y, ppp);     // one reduction for r*(q-x3) - y1*ppp
     acc.x = x3;
     acc.y = y3;
     acc.zz = fe_mul(acc.zz, pp);
@@ -120,11 +121,11 @@ H2B_HD Xyzz xyzz_add(const Xyzz& a, const Xyzz& b) {
         return Xyzz::identity();
     }
     Xyzz o;
-    Fq pp = fe_sqr(p);
+    Fq pp = fe_sqr_w(p);
     Fq ppp = fe_mul(p, pp);
     Fq q = fe_mul(u1, pp);
-    o.x = fe_sub(fe_sub(fe_sqr(r), ppp), fe_dbl(q));
-    o.y = fe_sub(fe_mul(r, fe_sub(q, o.x)), fe_mul(s1, ppp));
+    o.x = fe_sub(fe_sub(fe_sqr_w(r), ppp), fe_dbl(q));
+    o.y = fe_mul_sub_mul(r, fe_sub(q, o.x), s1, ppp);
     o.zz = fe_mul(fe_mul(a.zz, b.zz), pp);
     o.zzz = fe_mul(fe_mul(a.zzz, b.zzz), ppp);
     return o;

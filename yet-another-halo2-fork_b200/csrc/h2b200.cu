@@ -235,6 +235,9 @@ uint32_t msm_choose_c(size_t n_total) {
     return (uint32_t)c;
 }
 
+#ifndef H2B_ACC_DEFAULT_VARIANT
+#define H2B_ACC_DEFAULT_VARIANT 1
+#endif
 struct MsmLaunchInfo { uint32_t c, windows, slices; };
 
 // Enqueue the whole bucket pipeline for `n` resident (scalar, base) pairs on device d; the per-window partial
@@ -296,8 +299,17 @@ int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, ui
     H2B_LAUNCH(d, "msm_order", msm_size_scatter_kernel, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist, order);
     H2B_LAUNCH(d, "msm_order", msm_long_list_kernel, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, long_threshold,
                d.m_long_info.as<MsmLongInfo>(), d.m_long_tasks.as<MsmLongTask>(), counters);
-    H2B_LAUNCH(d, "msm_accumulate", msm_accumulate_kernel, (nkeys + 127) / 128, 128, 0, bases, entries, offsets, ends, order,
-               nkeys, long_threshold, buckets);
+    {
+        typedef void (*acc_kernel_t)(const Affine*, const uint32_t*, const uint32_t*, const uint32_t*, const uint32_t*, uint32_t,
+                                     uint32_t, Xyzz*);
+        static const acc_kernel_t variants[4] = {msm_accumulate_kernel<4, false>, msm_accumulate_kernel<4, true>,
+                                                 msm_accumulate_kernel<5, true>, msm_accumulate_kernel<6, true>};
+        int v = H2B_ACC_DEFAULT_VARIANT;
+        if (const char* env = std::getenv("H2B_ACC_VARIANT")) { int t = std::atoi(env); if (t >= 0 && t < 4) v = t; }
+        acc_kernel_t kern = variants[v];
+        H2B_LAUNCH(d, "msm_accumulate", kern, (nkeys + 127) / 128, 128, 0, bases, entries, offsets, ends, order, nkeys,
+                   long_threshold, buckets);
+    }
     H2B_LAUNCH(d, "msm_accumulate_long", msm_accumulate_long_kernel, (unsigned)(d.sms * 8), MSM_LONG_THREADS, 0, bases, entries,
                offsets, ends, d.m_long_tasks.as<MsmLongTask>(), counters, d.m_long_partials.as<Xyzz>());
     H2B_LAUNCH(d, "msm_accumulate_long", msm_long_combine_kernel, (unsigned)d.sms, MSM_LONG_THREADS, 0,

@@ -3,6 +3,7 @@
 // oracle (tests/test_field_host.py).  Not part of the product path: libh2b200.so never links this.
 #include <cstring>
 #include "curve.cuh"
+#include "field_wide.cuh"
 using namespace h2b;
 
 template <class F> static F ld(const void* p) { F f; std::memcpy(&f, p, 32); return f; }
@@ -173,4 +174,17 @@ static void hc_msm_windows_impl(const void* scalars_, const void* bases_, uint32
             w = xyzz_add(w, msm_reduce_chunk(buckets.data() + (size_t)j * nb + t * per, per, t * per + 1));
         windows[j] = w;
     }
+}
+
+// split multiplier (field_wide.cuh)
+extern "C" {
+void hc_fq_mul_w(const void* a, const void* b, void* o) { st(o, fe_mul_w(ld<Fq>(a), ld<Fq>(b))); }
+void hc_fr_mul_w(const void* a, const void* b, void* o) { st(o, fe_mul_w(ld<Fr>(a), ld<Fr>(b))); }
+void hc_fq_sqr_w(const void* a, void* o) { st(o, fe_sqr_w(ld<Fq>(a))); }
+void hc_fr_sqr_w(const void* a, void* o) { st(o, fe_sqr_w(ld<Fr>(a))); }
+void hc_fq_mul_sub_mul(const void* a, const void* b, const void* c, const void* d, void* o) {
+    st(o, fe_mul_sub_mul(ld<Fq>(a), ld<Fq>(b), ld<Fq>(c), ld<Fq>(d)));
+}
+void hc_mul_wide(const void* a, const void* b, void* o64) { Fq x = ld<Fq>(a), y = ld<Fq>(b); Wide w = mul_wide(x.l, y.l); std::memcpy(o64, &w, 64); }
+void hc_sqr_wide(const void* a, void* o64) { Fq x = ld<Fq>(a); Wide w = sqr_wide(x.l); std::memcpy(o64, &w, 64); }
 }

@@ -201,7 +201,10 @@ __global__ void msm_size_scatter_kernel(const uint32_t* __restrict__ offsets, co
 
 // ---- 5. bucket accumulation: one thread per bucket, in population order --------------------------
 // Buckets larger than `long_threshold` are left to msm_accumulate_long_kernel.
-__global__ void __launch_bounds__(128)
+// MINB = resident 128-thread blocks per SM the register allocation must allow (4 -> 128 regs, 5 -> 96, 6 -> 80);
+// PF = pull the next point into L2 with prefetch.global.L2 instead of double-buffering it in registers.
+template <int MINB, bool PF>
+__global__ void __launch_bounds__(128, MINB)
 msm_accumulate_kernel(const Affine* __restrict__ bases, const uint32_t* __restrict__ entries,
                       const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends,
                       const uint32_t* __restrict__ order, uint32_t nkeys, uint32_t long_threshold,
@@ -212,7 +215,19 @@ msm_accumulate_kernel(const Affine* __restrict__ bases, const uint32_t* __restri
     uint32_t e = offsets[key], end = ends[key];
     if (end - e > long_threshold) return;
     Xyzz acc = Xyzz::identity();
-    if (e < end) {
+    if (PF) {
+    // No register double-buffer: the next point is pulled into L2 while the current addition runs, which frees
+    // ~16 registers for one more resident warp per scheduler.
+    uint32_t ent = e < end ? entries[e] : 0u;
+    while (e < end) {
+        uint32_t e1 = e + 1;
+        uint32_t ent_n = e1 < end ? entries[e1] : 0u;
+        if (e1 < end) asm volatile("prefetch.global.L2 [%0];" ::"l"(bases + (ent_n & 0x7fffffffu)));
+        Affine p = affine_load(bases + (ent & 0x7fffffffu));
+        if (!p.is_identity()) xyzz_madd(acc, p.x, p.y, (ent >> 31) != 0);
+        ent = ent_n; e = e1;
+    }
+    } else if (e < end) {
         uint32_t ent = entries[e];
         Affine p = affine_load(bases + (ent & 0x7fffffffu));
         while (true) {
