@@ -49,6 +49,30 @@ def test_window_sizes(engine, c, monkeypatch):
     check(engine.msm(s, b), oracle_affine(s, b))
 
 
+@pytest.mark.parametrize("pre_c", [4, 6, 9, 13, 16, 20])
+def test_precomputed_window_multiples(engine, pre_c, monkeypatch):
+    """Registered bases carry 2^(c*j) * P_i for every window (one shared bucket set); any c must give the same point,
+    also for a prefix of the registered bases and for identity bases / edge scalars."""
+    monkeypatch.setenv("H2B_MSM_PRE_C", str(pre_c))
+    n = 2500
+    s = C.random_fr(n, 100 + pre_c)
+    b = C.gen_bases(n, 13)
+    s[0] = 0; s[1] = C.mont_from_int(R.R_MOD - 1, R.R_MOD); s[2] = C.mont_from_int(1, R.R_MOD); b[3] = 0; b[5] = b[4]
+    desc = engine.get_base_descriptor(b)
+    check(engine.msm_with_cached_base(s, desc), oracle_affine(s, b))
+    check(engine.msm_with_cached_base(s[:777], desc), oracle_affine(s[:777], b[:777]))
+    desc.release()
+
+
+def test_precompute_can_be_disabled(engine, monkeypatch):
+    monkeypatch.setenv("H2B_MSM_PRECOMPUTE", "0")
+    n = 4000
+    s, b = C.random_fr(n, 5), C.gen_bases(n, 2)
+    desc = engine.get_base_descriptor(b)
+    check(engine.msm_with_cached_base(s, desc), oracle_affine(s, b))
+    desc.release()
+
+
 def test_edge_scalars_and_bases(engine):
     n = 600
     s = C.random_fr(n, 5)

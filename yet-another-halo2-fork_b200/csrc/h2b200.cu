@@ -91,7 +91,13 @@ struct Dev {
     }
 };
 
-struct BasesShard { void* d = nullptr; size_t start = 0, count = 0; bool owned = true; };
+struct BasesShard {
+    void* d = nullptr;            // count affine points as registered
+    size_t start = 0, count = 0;
+    bool owned = true;
+    void* pre = nullptr;          // optional: pre_w * count precomputed multiples 2^(pre_c*j) * P_i (window-major)
+    uint32_t pre_c = 0, pre_w = 0;
+};
 struct Bases { size_t n = 0; std::vector<BasesShard> shard; };
 
 }  // namespace
@@ -238,24 +244,28 @@ uint32_t msm_choose_c(size_t n_total) {
 #ifndef H2B_ACC_DEFAULT_VARIANT
 #define H2B_ACC_DEFAULT_VARIANT 1
 #endif
-struct MsmLaunchInfo { uint32_t c, windows, slices; };
+struct MsmLaunchInfo { uint32_t c, windows, slices; bool pre; };
 
 // Enqueue the whole bucket pipeline for `n` resident (scalar, base) pairs on device d; the per-window partial
 // sums (windows * slices XYZZ points) are copied asynchronously into d.pinned.
-int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, uint32_t n, uint32_t c, MsmLaunchInfo* info) {
+// pre_stride > 0: `bases` holds precomputed window multiples (see MsmGeom::pre_stride) and ONE bucket set is used.
+int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, uint32_t n, uint32_t c, uint32_t pre_stride,
+                MsmLaunchInfo* info) {
     MsmGeom g;
-    g.c = c; g.windows = msm_windows(c); g.nb = 1u << (c - 1); g.n = n;
-    const uint32_t nkeys = g.windows * g.nb;
+    g.c = c; g.windows = msm_windows(c); g.nb = 1u << (c - 1); g.n = n; g.pre_stride = pre_stride;
+    const uint32_t kw = pre_stride ? 1u : g.windows;          // bucket sets
+    const uint32_t nkeys = kw * g.nb;
     const uint64_t max_entries = (uint64_t)n * g.windows;
-    if (max_entries >= 0xffffffffull) return ctx->fail(H2B_E_INVALID, "msm: n * windows exceeds 2^32 (shard the MSM)");
-    uint32_t mean = n / g.nb;
+    if (max_entries >= 0x7fffffffull) return ctx->fail(H2B_E_INVALID, "msm: n * windows exceeds 2^31 (shard the MSM)");
+    uint32_t mean = (uint32_t)(max_entries / nkeys);
     uint32_t long_threshold = std::max<uint32_t>(256u, 16u * std::max<uint32_t>(mean, 1u));
     uint32_t max_long = (uint32_t)(max_entries / long_threshold) + 1;
     uint32_t max_tasks = (uint32_t)(max_entries / MSM_LONG_CHUNK) + max_long + 1;
-    uint32_t slices = 1;
+    // reduce geometry: 128 threads x L buckets per block, at most MSM_REDUCE_MAX_SLICES blocks per bucket set
+    uint32_t slices = 1, log_l = 0;
     if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
-        slices = g.nb / (MSM_REDUCE_THREADS * 16);
-        if (slices < 1) slices = 1;
+        slices = g.nb / MSM_REDUCE_THREADS;
+        while (slices > (uint32_t)MSM_REDUCE_MAX_SLICES) { slices >>= 1; log_l++; }
     }
     const uint32_t nblk = (nkeys + SCAN_BLOCK - 1) / SCAN_BLOCK;
 
@@ -265,14 +275,14 @@ int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, ui
     H2B_CK(d.m_order.reserve((size_t)nkeys * 4));
     H2B_CK(d.m_entries.reserve(std::max<size_t>((size_t)max_entries * 4, 256)));
     H2B_CK(d.m_buckets.reserve((size_t)nkeys * sizeof(Xyzz)));
-    H2B_CK(d.m_wpart.reserve((size_t)g.windows * slices * sizeof(Xyzz)));
+    H2B_CK(d.m_wpart.reserve(((size_t)kw * slices * 2 + kw) * sizeof(Xyzz)));
     H2B_CK(d.m_blocksums.reserve((size_t)nblk * 4 + 256));
     H2B_CK(d.m_sizehist.reserve((size_t)MSM_SIZE_BINS * 4));
     H2B_CK(d.m_long_info.reserve((size_t)max_long * sizeof(MsmLongInfo)));
     H2B_CK(d.m_long_tasks.reserve((size_t)max_tasks * sizeof(MsmLongTask)));
     H2B_CK(d.m_long_partials.reserve((size_t)max_tasks * sizeof(Xyzz)));
     H2B_CK(d.m_counters.reserve(256));
-    H2B_CK(d.reserve_pinned(std::max<size_t>((size_t)g.windows * slices * sizeof(Xyzz), 4096)));
+    H2B_CK(d.reserve_pinned(std::max<size_t>((size_t)kw * sizeof(Xyzz), 4096)));
 
     uint32_t* counts = d.m_counts.as<uint32_t>();
     uint32_t* offsets = d.m_offsets.as<uint32_t>();
@@ -314,21 +324,29 @@ int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, ui
                offsets, ends, d.m_long_tasks.as<MsmLongTask>(), counters, d.m_long_partials.as<Xyzz>());
     H2B_LAUNCH(d, "msm_accumulate_long", msm_long_combine_kernel, (unsigned)d.sms, MSM_LONG_THREADS, 0,
                d.m_long_info.as<MsmLongInfo>(), counters, d.m_long_partials.as<Xyzz>(), buckets);
+    MsmGeom gr = g;
+    gr.windows = kw;
+    Xyzz* block_p = wpart;
+    Xyzz* block_r = wpart + (size_t)kw * slices;
+    Xyzz* set_sums = wpart + (size_t)kw * slices * 2;
     if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
-        dim3 grid(slices, g.windows, 1);
-        H2B_LAUNCH(d, "msm_reduce", msm_reduce_kernel, grid, MSM_REDUCE_THREADS, 0, g, buckets, slices, wpart);
+        dim3 grid(slices, kw, 1);
+        H2B_LAUNCH(d, "msm_reduce", msm_reduce_kernel, grid, MSM_REDUCE_THREADS, 0, gr, buckets, slices, log_l, block_p, block_r);
+        H2B_LAUNCH(d, "msm_reduce", msm_reduce_final_kernel, kw, MSM_REDUCE_MAX_SLICES, 0, slices, log_l + 7u, block_p, block_r, set_sums);
     } else {
-        H2B_LAUNCH(d, "msm_reduce", msm_reduce_small_kernel, (g.windows + 31) / 32, 32, 0, g, buckets, wpart);
+        H2B_LAUNCH(d, "msm_reduce", msm_reduce_small_kernel, (kw + 31) / 32, 32, 0, gr, buckets, set_sums);
     }
     H2B_CK(cudaGetLastError());
-    H2B_CK(cudaMemcpyAsync(d.pinned, wpart, (size_t)g.windows * slices * sizeof(Xyzz), cudaMemcpyDeviceToHost, d.stream));
-    info->c = c; info->windows = g.windows; info->slices = slices;
+    H2B_CK(cudaMemcpyAsync(d.pinned, set_sums, (size_t)kw * sizeof(Xyzz), cudaMemcpyDeviceToHost, d.stream));
+    slices = 1;
+    info->c = c; info->windows = kw; info->slices = slices; info->pre = pre_stride != 0;
     return H2B_OK;
 }
 
 // host: fold the slices of each window (after the stream has been synchronised)
 void msm_fold_slices(const Dev& d, const MsmLaunchInfo& info, Xyzz* windows /* accumulated into */) {
     const Xyzz* part = reinterpret_cast<const Xyzz*>(d.pinned);
+    // (with precomputed multiples there is one bucket set whose sum already carries every window's weight: it joins window 0)
     for (uint32_t j = 0; j < info.windows; j++)
         for (uint32_t s = 0; s < info.slices; s++) windows[j] = xyzz_add(windows[j], part[(size_t)j * info.slices + s]);
 }
@@ -373,7 +391,9 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
                                    on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, d.stream));
             d_scalars = d.m_scalars.as<Fr>();
         }
-        int rc = msm_enqueue(ctx, d, reinterpret_cast<const Affine*>(sh.d), d_scalars, (uint32_t)cnt, c, &infos[di]);
+        int rc;
+        if (sh.pre) rc = msm_enqueue(ctx, d, reinterpret_cast<const Affine*>(sh.pre), d_scalars, (uint32_t)cnt, sh.pre_c, (uint32_t)sh.count, &infos[di]);
+        else rc = msm_enqueue(ctx, d, reinterpret_cast<const Affine*>(sh.d), d_scalars, (uint32_t)cnt, c, 0, &infos[di]);
         if (rc) return rc;
         H2B_CK(cudaEventRecord(d.ev_last, d.stream));
         used.push_back((int)di);
@@ -391,7 +411,44 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
     return H2B_OK;
 }
 
-int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, uint64_t* handle_out) {
+// Window size used with precomputed multiples (one shared bucket set, so larger windows stay cheap to reduce).
+uint32_t msm_choose_pre_c(size_t n) {
+    if (const char* env = std::getenv("H2B_MSM_PRE_C")) {
+        int v = std::atoi(env);
+        if (v >= 4 && v <= 24) return (uint32_t)v;
+    }
+    // Measured on B200 (profiles/README.md): c = 20 (13 windows, 2^19 buckets) wins from 2^19 points up, c = 17 from 2^16;
+    // below that one bucket set has too few buckets to fill the GPU and the classic per-window layout is used (0).
+    // Window sizes whose top window would hold only 1-2 scalar bits (18, 19, 21, 23) are avoided: every point would
+    // land in a handful of buckets of that window.
+    if (n >= ((size_t)1 << 19)) return 20;
+    if (n >= ((size_t)1 << 16)) return 17;
+    return 0;
+}
+
+// Registration = MsmAccel::get_base_descriptor's "expensive preprocessing" (zal.rs:71-77): besides making the bases
+// resident, store 2^(c*j) * P_i for every window j so that an MSM needs ONE bucket set instead of one per window.
+// Skipped (classic per-window buckets) for one-shot bases, tiny inputs, or when the multiples would not fit.
+int precompute_shard(h2b_ctx* ctx, Dev& d, BasesShard& sh) {
+    if (const char* env = std::getenv("H2B_MSM_PRECOMPUTE")) { if (std::atoi(env) == 0) return H2B_OK; }
+    if (sh.count < 256) return H2B_OK;
+    uint32_t c = msm_choose_pre_c(sh.count);
+    if (c == 0) return H2B_OK;
+    uint32_t w = msm_windows(c);
+    if ((uint64_t)sh.count * w >= 0x7fffffffull) return H2B_OK;
+    size_t bytes = (size_t)sh.count * w * 64, free_b = 0, total_b = 0;
+    H2B_CK(cudaMemGetInfo(&free_b, &total_b));
+    if (bytes > free_b / 2) return H2B_OK;
+    H2B_CK(cudaMalloc(&sh.pre, bytes));
+    H2B_LAUNCH(d, "msm_precompute", msm_precompute_kernel, (unsigned)((sh.count + 127) / 128), 128, 0, (const Affine*)sh.d,
+               (Affine*)sh.pre, (uint32_t)sh.count, (uint32_t)sh.count, c, w);
+    H2B_CK(cudaGetLastError());
+    H2B_CK(cudaStreamSynchronize(d.stream));
+    sh.pre_c = c; sh.pre_w = w;
+    return H2B_OK;
+}
+
+int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, bool allow_pre, uint64_t* handle_out) {
     Bases B;
     B.n = n;
     size_t nd = on_device ? 1 : ctx->devs.size();
@@ -401,14 +458,17 @@ int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, ui
         BasesShard& sh = B.shard[di];
         sh.start = std::min(n, di * per);
         sh.count = std::min(per, n - sh.start);
-        if (on_device) { sh.d = const_cast<void*>(bases); sh.owned = false; continue; }
         if (sh.count == 0) continue;
         Dev& d = ctx->devs[di];
         H2B_CK(cudaSetDevice(d.id));
-        H2B_CK(cudaMalloc(&sh.d, sh.count * 64));
-        H2B_CK(cudaMemcpyAsync(sh.d, reinterpret_cast<const uint8_t*>(bases) + sh.start * 64, sh.count * 64,
-                               cudaMemcpyHostToDevice, d.stream));
-        H2B_CK(cudaStreamSynchronize(d.stream));
+        if (on_device) { sh.d = const_cast<void*>(bases); sh.owned = false; }
+        else {
+            H2B_CK(cudaMalloc(&sh.d, sh.count * 64));
+            H2B_CK(cudaMemcpyAsync(sh.d, reinterpret_cast<const uint8_t*>(bases) + sh.start * 64, sh.count * 64,
+                                   cudaMemcpyHostToDevice, d.stream));
+            H2B_CK(cudaStreamSynchronize(d.stream));
+        }
+        if (allow_pre) { int rc = precompute_shard(ctx, d, sh); if (rc) return rc; }
     }
     uint64_t h = ctx->next_handle++;
     ctx->bases.emplace(h, std::move(B));
@@ -418,7 +478,11 @@ int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, ui
 
 void release_bases(h2b_ctx* ctx, Bases& B) {
     for (size_t di = 0; di < B.shard.size(); di++)
-        if (B.shard[di].d && B.shard[di].owned) { cudaSetDevice(ctx->devs[di].id); cudaFree(B.shard[di].d); }
+        {
+            cudaSetDevice(ctx->devs[di].id);
+            if (B.shard[di].d && B.shard[di].owned) cudaFree(B.shard[di].d);
+            if (B.shard[di].pre) cudaFree(B.shard[di].pre);
+        }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -567,12 +631,12 @@ const char* h2b_last_error(const h2b_ctx* ctx) { return ctx ? ctx->err.c_str() :
 int h2b_bases_register(h2b_ctx* ctx, const void* bases, size_t n, uint64_t* handle_out) {
     if (!ctx || !handle_out || (!bases && n)) return ctx ? ctx->fail(H2B_E_INVALID, "bases_register: null argument") : H2B_E_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);
-    return register_bases(ctx, bases, false, n, handle_out);
+    return register_bases(ctx, bases, false, n, true, handle_out);
 }
 int h2b_bases_register_device(h2b_ctx* ctx, const void* d_bases, size_t n, uint64_t* handle_out) {
     if (!ctx || !handle_out || (!d_bases && n)) return ctx ? ctx->fail(H2B_E_INVALID, "bases_register_device: null argument") : H2B_E_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);
-    return register_bases(ctx, d_bases, true, n, handle_out);
+    return register_bases(ctx, d_bases, true, n, true, handle_out);
 }
 int h2b_bases_release(h2b_ctx* ctx, uint64_t handle) {
     if (!ctx) return H2B_E_INVALID;
@@ -606,7 +670,12 @@ int h2b_msm_device(h2b_ctx* ctx, uint64_t handle, const void* d_scalars, size_t 
 int h2b_msm_raw(h2b_ctx* ctx, const void* bases, const void* scalars, size_t n, void* out96) {
     if (!ctx) return H2B_E_INVALID;
     uint64_t h = 0;
-    int rc = h2b_bases_register(ctx, bases, n, &h);
+    int rc;
+    if ((!bases && n)) return ctx->fail(H2B_E_INVALID, "msm_raw: null argument");
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        rc = register_bases(ctx, bases, false, n, false, &h);     // one-shot bases: no window precomputation
+    }
     if (rc) return rc;
     rc = h2b_msm(ctx, h, scalars, n, out96);
     int rc2 = h2b_bases_release(ctx, h);

@@ -167,12 +167,33 @@ static void hc_msm_windows_impl(const void* scalars_, const void* bases_, uint32
     }
     windows.assign(W, Xyzz::identity());
     for (uint32_t j = 0; j < W; j++) {
-        Xyzz w = Xyzz::identity();
-        uint32_t threads = reduce_threads && nb >= reduce_threads ? reduce_threads : 1;
-        uint32_t per = nb / threads;
-        for (uint32_t t = 0; t < threads; t++)
-            w = xyzz_add(w, msm_reduce_chunk(buckets.data() + (size_t)j * nb + t * per, per, t * per + 1));
-        windows[j] = w;
+        const Xyzz* bk = buckets.data() + (size_t)j * nb;
+        if (!reduce_threads || nb < reduce_threads) {
+            Xyzz run;
+            windows[j] = msm_chunk_sums(bk, nb, run);
+            continue;
+        }
+        // the kernels' hierarchy: blocks of `reduce_threads` threads x L buckets; P_b = A + L*T, R_b; then
+        // window = sum_b P_b + (threads * L) * sum_b b * R_b
+        uint32_t slices = nb / reduce_threads, log_l = 0;
+        while (slices > 4) { slices >>= 1; log_l++; }          // small cap so that several levels are exercised
+        uint32_t L = 1u << log_l;
+        Xyzz sumP = Xyzz::identity(), sumbR = Xyzz::identity();
+        for (uint32_t b = 0; b < slices; b++) {
+            Xyzz A = Xyzz::identity(), T = Xyzz::identity(), Rn = Xyzz::identity();
+            for (uint32_t t = 0; t < reduce_threads; t++) {
+                Xyzz run;
+                Xyzz acc = msm_chunk_sums(bk + (((size_t)b * reduce_threads + t) << log_l), L, run);
+                A = xyzz_add(A, acc);
+                for (uint32_t r = 0; r < t; r++) T = xyzz_add(T, run);      // t * run_t
+                Rn = xyzz_add(Rn, run);
+            }
+            Xyzz P = xyzz_add(A, xyzz_mul_pow2(T, log_l));
+            sumP = xyzz_add(sumP, P);
+            for (uint32_t r = 0; r < b; r++) sumbR = xyzz_add(sumbR, Rn);
+        }
+        uint32_t log_bb = log_l; { uint32_t rt = reduce_threads; while (rt > 1) { rt >>= 1; log_bb++; } }
+        windows[j] = xyzz_add(sumP, xyzz_mul_pow2(sumbR, log_bb));
     }
 }
 

@@ -23,6 +23,9 @@ struct MsmGeom {
     uint32_t windows;    // W = ceil(255 / c)
     uint32_t nb;         // buckets per window = 2^(c-1)
     uint32_t n;          // number of (scalar, base) pairs
+    uint32_t pre_stride; // 0: classic (one bucket set per window, bases[i]).  > 0: the bases buffer holds the
+                         // precomputed multiples pre[j * pre_stride + i] = 2^(c*j) * P_i, so all windows share ONE
+                         // bucket set: digit j of scalar i goes to bucket |d| with entry index j * pre_stride + i.
 };
 
 H2B_HD constexpr uint32_t msm_windows(uint32_t c) { return (255u + c - 1u) / c; }
@@ -69,6 +72,21 @@ H2B_HD Xyzz msm_reduce_chunk(const Xyzz* buckets, uint32_t len, uint32_t v0) {
     return acc;
 }
 
+// Summation by parts over `len` consecutive buckets: returns sum_{i<len} (i+1) * B_i and, in `run`, sum_i B_i.
+H2B_HD Xyzz msm_chunk_sums(const Xyzz* buckets, uint32_t len, Xyzz& run) {
+    run = Xyzz::identity();
+    Xyzz acc = Xyzz::identity();
+    for (uint32_t i = len; i-- > 0;) {
+        run = xyzz_add(run, xyzz_load(buckets + i));
+        acc = xyzz_add(acc, run);
+    }
+    return acc;
+}
+H2B_HD Xyzz xyzz_mul_pow2(Xyzz p, uint32_t log2k) {
+    for (uint32_t i = 0; i < log2k; i++) p = xyzz_double(p);
+    return p;
+}
+
 // host: Horner over the window sums (most significant last), normalise, and write the result as the
 // reference's G1 Jacobian layout: (x, y, 1), or (0, 1, 0) for the identity.
 inline void msm_finish(const Xyzz* windows, uint32_t nw, uint32_t c, void* out96) {
@@ -97,7 +115,7 @@ __global__ void msm_count_kernel(MsmGeom g, const Fr* __restrict__ scalars, uint
     msm_signed_digits(canon, g.c, g.windows, [&](uint32_t j, int32_t d) {
         if (d != 0) {
             uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
-            atomicAdd(counts + (size_t)j * g.nb + (mag - 1), 1u);
+            atomicAdd(counts + (g.pre_stride ? 0 : (size_t)j * g.nb) + (mag - 1), 1u);
         }
     });
 }
@@ -111,8 +129,8 @@ __global__ void msm_scatter_kernel(MsmGeom g, const Fr* __restrict__ scalars, ui
     msm_signed_digits(canon, g.c, g.windows, [&](uint32_t j, int32_t d) {
         if (d != 0) {
             uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
-            uint32_t pos = atomicAdd(cursor + (size_t)j * g.nb + (mag - 1), 1u);
-            entries[pos] = i | (d < 0 ? 0x80000000u : 0u);
+            uint32_t pos = atomicAdd(cursor + (g.pre_stride ? 0 : (size_t)j * g.nb) + (mag - 1), 1u);
+            entries[pos] = (g.pre_stride ? j * g.pre_stride + i : i) | (d < 0 ? 0x80000000u : 0u);
         }
     });
 }
@@ -175,6 +193,27 @@ __global__ void scan_apply_kernel(const uint32_t* __restrict__ in, uint32_t n, c
         uint32_t e = block_offsets[blockIdx.x] + sh[threadIdx.x] - v;
         out[i] = e;
         if (out2) out2[i] = e;
+    }
+}
+
+// ---- registration-time precomputation: out[j * stride + i] = 2^(c*j) * in[i], j < windows (affine) ------------
+// One thread per point; each multiple is normalised with its own inversion (a one-off cost per registered SRS).
+__global__ void __launch_bounds__(128)
+msm_precompute_kernel(const Affine* __restrict__ in, Affine* __restrict__ out, uint32_t n, uint32_t stride, uint32_t c,
+                      uint32_t windows) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Affine p = affine_load(in + i);
+    fe_store(&out[i].x, p.x);
+    fe_store(&out[i].y, p.y);
+    for (uint32_t j = 1; j < windows; j++) {
+        if (!p.is_identity()) {
+            Xyzz t = xyzz_double_affine(p.x, p.y);
+            for (uint32_t k = 1; k < c; k++) t = xyzz_double(t);
+            p = xyzz_to_affine(t);
+        }
+        fe_store(&out[(size_t)j * stride + i].x, p.x);
+        fe_store(&out[(size_t)j * stride + i].y, p.y);
     }
 }
 
@@ -319,23 +358,83 @@ msm_long_combine_kernel(const MsmLongInfo* __restrict__ long_info, const uint32_
 }
 
 // ---- 6. bucket reduction --------------------------------------------------------------------------
-// grid = (slices, windows); block = MSM_REDUCE_THREADS.  Block (s, j) reduces buckets
-// [s*nb/slices, (s+1)*nb/slices) of window j to one point: sum_v v*B_v over its value range.
+// sum_v v * B_v per bucket set, with no scalar multiplication other than by powers of two:
+//   level 1  grid = (slices, sets), 128 threads, L = 2^log_l buckets per thread.  Thread t: run_t = sum B,
+//            acc_t = sum (i+1) B over its L buckets.  Block: A = sum_t acc_t, T = sum_t t * run_t (suffix scan + tree),
+//            R = sum_t run_t.  Emits P = A + L * T (weights relative to the block's first bucket) and R.
+//   level 2  one block per set over the `slices` (<= 256) block results:
+//            sum_b P_b + (128 * L) * sum_b b * R_b      (same suffix-scan trick).
 constexpr int MSM_REDUCE_THREADS = 128;
-__global__ void __launch_bounds__(MSM_REDUCE_THREADS)
-msm_reduce_kernel(MsmGeom g, const Xyzz* __restrict__ buckets, uint32_t slices, Xyzz* __restrict__ window_partials) {
-    __shared__ Xyzz sh[MSM_REDUCE_THREADS];
-    uint32_t j = blockIdx.y, s = blockIdx.x;
-    uint32_t per_slice = g.nb / slices;                       // power of two, >= MSM_REDUCE_THREADS
-    uint32_t per_thread = per_slice / MSM_REDUCE_THREADS;
-    uint32_t first = s * per_slice + threadIdx.x * per_thread;     // bucket index (value = index + 1)
-    sh[threadIdx.x] = msm_reduce_chunk(buckets + (size_t)j * g.nb + first, per_thread, first + 1);
-    __syncthreads();
-    for (int st = MSM_REDUCE_THREADS / 2; st > 0; st >>= 1) {
-        if (threadIdx.x < (uint32_t)st) sh[threadIdx.x] = xyzz_add(sh[threadIdx.x], sh[threadIdx.x + st]);
+constexpr int MSM_REDUCE_MAX_SLICES = 256;
+
+// block-wide helpers on a shared array of n (power of two) points
+template <int N>
+H2B_D void block_suffix_scan(Xyzz* sh, uint32_t t) {       // sh[t] <- sum_{u >= t} sh[u]
+    for (int o = 1; o < N; o <<= 1) {
+        Xyzz v = Xyzz::identity();
+        bool take = t + (uint32_t)o < (uint32_t)N;
+        if (take) v = sh[t + o];
+        __syncthreads();
+        if (take) sh[t] = xyzz_add(sh[t], v);
         __syncthreads();
     }
-    if (threadIdx.x == 0) xyzz_store(window_partials + (size_t)j * slices + s, sh[0]);
+}
+template <int N>
+H2B_D void block_tree_sum(Xyzz* sh, uint32_t t) {          // sh[0] <- sum_t sh[t]
+    for (int st = N / 2; st > 0; st >>= 1) {
+        if (t < (uint32_t)st) sh[t] = xyzz_add(sh[t], sh[t + st]);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(MSM_REDUCE_THREADS)
+msm_reduce_kernel(MsmGeom g, const Xyzz* __restrict__ buckets, uint32_t slices, uint32_t log_l,
+                  Xyzz* __restrict__ block_p, Xyzz* __restrict__ block_r) {
+    __shared__ Xyzz sh[MSM_REDUCE_THREADS];
+    const uint32_t j = blockIdx.y, s = blockIdx.x, t = threadIdx.x;
+    const uint32_t L = 1u << log_l;
+    const uint32_t first = (s * MSM_REDUCE_THREADS + t) << log_l;       // bucket index within the set
+    Xyzz run;
+    Xyzz acc = msm_chunk_sums(buckets + (size_t)j * g.nb + first, L, run);
+    // A = sum acc_t
+    sh[t] = acc;
+    __syncthreads();
+    block_tree_sum<MSM_REDUCE_THREADS>(sh, t);
+    Xyzz A = sh[0];
+    __syncthreads();
+    // suffix sums of run_t: S_0 = R, sum_{t>=1} S_t = sum_t t * run_t
+    sh[t] = run;
+    __syncthreads();
+    block_suffix_scan<MSM_REDUCE_THREADS>(sh, t);
+    Xyzz R = sh[0];
+    __syncthreads();
+    if (t == 0) sh[0] = Xyzz::identity();
+    __syncthreads();
+    block_tree_sum<MSM_REDUCE_THREADS>(sh, t);
+    if (t == 0) {
+        Xyzz P = xyzz_add(A, xyzz_mul_pow2(sh[0], log_l));
+        xyzz_store(block_p + (size_t)j * slices + s, P);
+        xyzz_store(block_r + (size_t)j * slices + s, R);
+    }
+}
+__global__ void __launch_bounds__(MSM_REDUCE_MAX_SLICES)
+msm_reduce_final_kernel(uint32_t slices, uint32_t log_block_buckets, const Xyzz* __restrict__ block_p,
+                        const Xyzz* __restrict__ block_r, Xyzz* __restrict__ set_sums) {
+    __shared__ Xyzz sh[MSM_REDUCE_MAX_SLICES];
+    const uint32_t j = blockIdx.x, t = threadIdx.x;
+    sh[t] = t < slices ? xyzz_load(block_p + (size_t)j * slices + t) : Xyzz::identity();
+    __syncthreads();
+    block_tree_sum<MSM_REDUCE_MAX_SLICES>(sh, t);
+    Xyzz sumP = sh[0];
+    __syncthreads();
+    sh[t] = t < slices ? xyzz_load(block_r + (size_t)j * slices + t) : Xyzz::identity();
+    __syncthreads();
+    block_suffix_scan<MSM_REDUCE_MAX_SLICES>(sh, t);
+    __syncthreads();
+    if (t == 0) sh[0] = Xyzz::identity();
+    __syncthreads();
+    block_tree_sum<MSM_REDUCE_MAX_SLICES>(sh, t);
+    if (t == 0) xyzz_store(set_sums + j, xyzz_add(sumP, xyzz_mul_pow2(sh[0], log_block_buckets)));
 }
 // small-window fallback: nb < MSM_REDUCE_THREADS -> one thread per window does the whole running sum
 __global__ void msm_reduce_small_kernel(MsmGeom g, const Xyzz* __restrict__ buckets, Xyzz* __restrict__ window_partials) {
