@@ -73,6 +73,23 @@ def test_precompute_can_be_disabled(engine, monkeypatch):
     desc.release()
 
 
+@pytest.mark.parametrize("chunks,precompute", [(3, "1"), (5, "0"), (2, "1")])
+def test_streamed_scalar_chunks(engine, chunks, precompute, monkeypatch):
+    """Host scalars are streamed in chunks that add into the same buckets (copy / compute overlap): same point."""
+    monkeypatch.setenv("H2B_MSM_CHUNKS", str(chunks))
+    monkeypatch.setenv("H2B_MSM_PRECOMPUTE", precompute)
+    monkeypatch.setenv("H2B_MSM_PRE_C", "11")
+    n = 5001
+    s, b = C.random_fr(n, 60 + chunks), C.gen_bases(n, 4)
+    s[10:400] = C.mont_from_int(1, R.R_MOD)          # an oversized bucket that spans chunks
+    b[1700] = 0
+    desc = engine.get_base_descriptor(b)
+    exp = oracle_affine(s, b)
+    check(engine.msm_with_cached_base(s, desc), exp)
+    check(engine.msm_with_cached_base(s, desc), exp)      # scratch reuse across calls
+    desc.release()
+
+
 def test_edge_scalars_and_bases(engine):
     n = 600
     s = C.random_fr(n, 5)

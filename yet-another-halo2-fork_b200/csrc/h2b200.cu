@@ -54,8 +54,9 @@ struct NttPlanDev {
 struct Dev {
     int id = 0;
     int sms = 148;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
     cudaEvent_t ev_first = nullptr, ev_last = nullptr;
+    std::vector<cudaEvent_t> chunk_events;
     DevBuf ntt_a, ntt_b, ntt_tab;
     DevBuf m_scalars, m_counts, m_offsets, m_ends, m_entries, m_order, m_buckets, m_wpart, m_blocksums,
         m_sizehist, m_long_info, m_long_tasks, m_long_partials, m_counters, m_tmp_bases;
@@ -248,25 +249,33 @@ struct MsmLaunchInfo { uint32_t c, windows, slices; bool pre; };
 
 // Enqueue the whole bucket pipeline for `n` resident (scalar, base) pairs on device d; the per-window partial
 // sums (windows * slices XYZZ points) are copied asynchronously into d.pinned.
-// pre_stride > 0: `bases` holds precomputed window multiples (see MsmGeom::pre_stride) and ONE bucket set is used.
-int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, uint32_t n, uint32_t c, uint32_t pre_stride,
-                MsmLaunchInfo* info) {
-    MsmGeom g;
-    g.c = c; g.windows = msm_windows(c); g.nb = 1u << (c - 1); g.n = n; g.pre_stride = pre_stride;
-    const uint32_t kw = pre_stride ? 1u : g.windows;          // bucket sets
-    const uint32_t nkeys = kw * g.nb;
+// The bucket pipeline in two stages so that a host-resident scalar vector can be streamed in chunks: stage A
+// (count / scan / scatter / order / accumulate) runs per chunk and adds into the SAME bucket array; stage B (reduce +
+// copy-back of the per-set sums) runs once.  pre_stride > 0: `bases` holds precomputed window multiples (see
+// MsmGeom::pre_stride) and ONE bucket set is used.
+struct MsmShape { MsmGeom g; uint32_t kw, nkeys; };
+
+MsmShape msm_shape(uint32_t n, uint32_t c, uint32_t pre_stride, uint32_t idx_offset) {
+    MsmShape sp;
+    sp.g.c = c; sp.g.windows = msm_windows(c); sp.g.nb = 1u << (c - 1); sp.g.n = n; sp.g.pre_stride = pre_stride;
+    sp.g.idx_offset = idx_offset;
+    sp.kw = pre_stride ? 1u : sp.g.windows;
+    sp.nkeys = sp.kw * sp.g.nb;
+    return sp;
+}
+
+int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, uint32_t n, uint32_t idx_offset, uint32_t c,
+                         uint32_t pre_stride, bool add_to) {
+    MsmShape sp = msm_shape(n, c, pre_stride, idx_offset);
+    const MsmGeom& g = sp.g;
+    const uint32_t nkeys = sp.nkeys;
     const uint64_t max_entries = (uint64_t)n * g.windows;
-    if (max_entries >= 0x7fffffffull) return ctx->fail(H2B_E_INVALID, "msm: n * windows exceeds 2^31 (shard the MSM)");
+    if (max_entries >= 0x7fffffffull || (uint64_t)(idx_offset + n) * (pre_stride ? g.windows : 1) >= 0x7fffffffull)
+        return ctx->fail(H2B_E_INVALID, "msm: n * windows exceeds 2^31 (shard the MSM)");
     uint32_t mean = (uint32_t)(max_entries / nkeys);
     uint32_t long_threshold = std::max<uint32_t>(256u, 16u * std::max<uint32_t>(mean, 1u));
     uint32_t max_long = (uint32_t)(max_entries / long_threshold) + 1;
     uint32_t max_tasks = (uint32_t)(max_entries / MSM_LONG_CHUNK) + max_long + 1;
-    // reduce geometry: 128 threads x L buckets per block, at most MSM_REDUCE_MAX_SLICES blocks per bucket set
-    uint32_t slices = 1, log_l = 0;
-    if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
-        slices = g.nb / MSM_REDUCE_THREADS;
-        while (slices > (uint32_t)MSM_REDUCE_MAX_SLICES) { slices >>= 1; log_l++; }
-    }
     const uint32_t nblk = (nkeys + SCAN_BLOCK - 1) / SCAN_BLOCK;
 
     H2B_CK(d.m_counts.reserve((size_t)nkeys * 4));
@@ -275,14 +284,12 @@ int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, ui
     H2B_CK(d.m_order.reserve((size_t)nkeys * 4));
     H2B_CK(d.m_entries.reserve(std::max<size_t>((size_t)max_entries * 4, 256)));
     H2B_CK(d.m_buckets.reserve((size_t)nkeys * sizeof(Xyzz)));
-    H2B_CK(d.m_wpart.reserve(((size_t)kw * slices * 2 + kw) * sizeof(Xyzz)));
     H2B_CK(d.m_blocksums.reserve((size_t)nblk * 4 + 256));
     H2B_CK(d.m_sizehist.reserve((size_t)MSM_SIZE_BINS * 4));
     H2B_CK(d.m_long_info.reserve((size_t)max_long * sizeof(MsmLongInfo)));
     H2B_CK(d.m_long_tasks.reserve((size_t)max_tasks * sizeof(MsmLongTask)));
     H2B_CK(d.m_long_partials.reserve((size_t)max_tasks * sizeof(Xyzz)));
     H2B_CK(d.m_counters.reserve(256));
-    H2B_CK(d.reserve_pinned(std::max<size_t>((size_t)kw * sizeof(Xyzz), 4096)));
 
     uint32_t* counts = d.m_counts.as<uint32_t>();
     uint32_t* offsets = d.m_offsets.as<uint32_t>();
@@ -293,7 +300,6 @@ int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, ui
     uint32_t* sizehist = d.m_sizehist.as<uint32_t>();
     uint32_t* counters = d.m_counters.as<uint32_t>();
     Xyzz* buckets = d.m_buckets.as<Xyzz>();
-    Xyzz* wpart = d.m_wpart.as<Xyzz>();
 
     H2B_CK(cudaMemsetAsync(counts, 0, (size_t)nkeys * 4, d.stream));
     H2B_CK(cudaMemsetAsync(sizehist, 0, (size_t)MSM_SIZE_BINS * 4, d.stream));
@@ -311,19 +317,37 @@ int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, ui
                d.m_long_info.as<MsmLongInfo>(), d.m_long_tasks.as<MsmLongTask>(), counters);
     {
         typedef void (*acc_kernel_t)(const Affine*, const uint32_t*, const uint32_t*, const uint32_t*, const uint32_t*, uint32_t,
-                                     uint32_t, Xyzz*);
+                                     uint32_t, Xyzz*, uint32_t);
         static const acc_kernel_t variants[4] = {msm_accumulate_kernel<4, false>, msm_accumulate_kernel<4, true>,
                                                  msm_accumulate_kernel<5, true>, msm_accumulate_kernel<6, true>};
         int v = H2B_ACC_DEFAULT_VARIANT;
         if (const char* env = std::getenv("H2B_ACC_VARIANT")) { int t = std::atoi(env); if (t >= 0 && t < 4) v = t; }
         acc_kernel_t kern = variants[v];
         H2B_LAUNCH(d, "msm_accumulate", kern, (nkeys + 127) / 128, 128, 0, bases, entries, offsets, ends, order, nkeys,
-                   long_threshold, buckets);
+                   long_threshold, buckets, add_to ? 1u : 0u);
     }
     H2B_LAUNCH(d, "msm_accumulate_long", msm_accumulate_long_kernel, (unsigned)(d.sms * 8), MSM_LONG_THREADS, 0, bases, entries,
                offsets, ends, d.m_long_tasks.as<MsmLongTask>(), counters, d.m_long_partials.as<Xyzz>());
     H2B_LAUNCH(d, "msm_accumulate_long", msm_long_combine_kernel, (unsigned)d.sms, MSM_LONG_THREADS, 0,
-               d.m_long_info.as<MsmLongInfo>(), counters, d.m_long_partials.as<Xyzz>(), buckets);
+               d.m_long_info.as<MsmLongInfo>(), counters, d.m_long_partials.as<Xyzz>(), buckets, add_to ? 1u : 0u);
+    H2B_CK(cudaGetLastError());
+    return H2B_OK;
+}
+
+int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmLaunchInfo* info) {
+    MsmShape sp = msm_shape(0, c, pre_stride, 0);
+    const MsmGeom& g = sp.g;
+    const uint32_t kw = sp.kw;
+    // reduce geometry: 128 threads x L buckets per block, at most MSM_REDUCE_MAX_SLICES blocks per bucket set
+    uint32_t slices = 1, log_l = 0;
+    if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
+        slices = g.nb / MSM_REDUCE_THREADS;
+        while (slices > (uint32_t)MSM_REDUCE_MAX_SLICES) { slices >>= 1; log_l++; }
+    }
+    H2B_CK(d.m_wpart.reserve(((size_t)kw * slices * 2 + kw) * sizeof(Xyzz)));
+    H2B_CK(d.reserve_pinned(std::max<size_t>((size_t)kw * sizeof(Xyzz), 4096)));
+    Xyzz* buckets = d.m_buckets.as<Xyzz>();
+    Xyzz* wpart = d.m_wpart.as<Xyzz>();
     MsmGeom gr = g;
     gr.windows = kw;
     Xyzz* block_p = wpart;
@@ -338,8 +362,7 @@ int msm_enqueue(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, ui
     }
     H2B_CK(cudaGetLastError());
     H2B_CK(cudaMemcpyAsync(d.pinned, set_sums, (size_t)kw * sizeof(Xyzz), cudaMemcpyDeviceToHost, d.stream));
-    slices = 1;
-    info->c = c; info->windows = kw; info->slices = slices; info->pre = pre_stride != 0;
+    info->c = c; info->windows = kw; info->slices = 1; info->pre = pre_stride != 0;
     return H2B_OK;
 }
 
@@ -382,18 +405,37 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
         Dev& d = ctx->devs[di];
         H2B_CK(cudaSetDevice(d.id));
         begin_call(d);
-        const Fr* d_scalars;
+        const Affine* dev_bases = reinterpret_cast<const Affine*>(sh.pre ? sh.pre : sh.d);
+        const uint32_t use_c = sh.pre ? sh.pre_c : c;
+        const uint32_t stride = sh.pre ? (uint32_t)sh.count : 0u;
+        int rc = H2B_OK;
         if (on_device && di == 0) {
-            d_scalars = reinterpret_cast<const Fr*>(scalars) + sh.start;
+            rc = msm_stage_accumulate(ctx, d, dev_bases, reinterpret_cast<const Fr*>(scalars) + sh.start, (uint32_t)cnt, 0, use_c, stride, false);
         } else {
+            // Stream the scalars: chunk k+1 crosses PCIe on the copy stream while chunk k is binned and accumulated.
             H2B_CK(d.m_scalars.reserve(cnt * 32));
-            H2B_CK(cudaMemcpyAsync(d.m_scalars.p, reinterpret_cast<const uint8_t*>(scalars) + sh.start * 32, cnt * 32,
-                                   on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, d.stream));
-            d_scalars = d.m_scalars.as<Fr>();
+            size_t chunk = cnt;
+            if (!on_device && cnt >= ((size_t)1 << 23)) chunk = (cnt + 3) / 4;
+            if (const char* env = std::getenv("H2B_MSM_CHUNKS")) { int k = std::atoi(env); if (k >= 1 && k <= 64) chunk = (cnt + k - 1) / k; }
+            size_t nchunks = (cnt + chunk - 1) / chunk;
+            while (d.chunk_events.size() < nchunks) { cudaEvent_t e; H2B_CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); d.chunk_events.push_back(e); }
+            H2B_CK(cudaStreamWaitEvent(d.copy_stream, d.ev_first, 0));      // previous call's use of m_scalars is over
+            const uint8_t* src = reinterpret_cast<const uint8_t*>(scalars) + sh.start * 32;
+            for (size_t k = 0; k < nchunks; k++) {
+                size_t lo = k * chunk, len = std::min(chunk, cnt - lo);
+                H2B_CK(cudaMemcpyAsync(d.m_scalars.as<uint8_t>() + lo * 32, src + lo * 32, len * 32,
+                                       on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, d.copy_stream));
+                H2B_CK(cudaEventRecord(d.chunk_events[k], d.copy_stream));
+            }
+            for (size_t k = 0; k < nchunks && rc == H2B_OK; k++) {
+                size_t lo = k * chunk, len = std::min(chunk, cnt - lo);
+                H2B_CK(cudaStreamWaitEvent(d.stream, d.chunk_events[k], 0));
+                const Affine* b = stride ? dev_bases : dev_bases + lo;       // classic mode indexes bases relative to the chunk
+                rc = msm_stage_accumulate(ctx, d, b, d.m_scalars.as<Fr>() + lo, (uint32_t)len, stride ? (uint32_t)lo : 0u, use_c, stride, k > 0);
+            }
         }
-        int rc;
-        if (sh.pre) rc = msm_enqueue(ctx, d, reinterpret_cast<const Affine*>(sh.pre), d_scalars, (uint32_t)cnt, sh.pre_c, (uint32_t)sh.count, &infos[di]);
-        else rc = msm_enqueue(ctx, d, reinterpret_cast<const Affine*>(sh.d), d_scalars, (uint32_t)cnt, c, 0, &infos[di]);
+        if (rc) return rc;
+        rc = msm_stage_reduce(ctx, d, use_c, stride, &infos[di]);
         if (rc) return rc;
         H2B_CK(cudaEventRecord(d.ev_last, d.stream));
         used.push_back((int)di);
@@ -594,6 +636,7 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
         }
         d.sms = prop.multiProcessorCount;
         if (cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) != cudaSuccess ||
+            cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
             cudaEventCreate(&d.ev_first) != cudaSuccess || cudaEventCreate(&d.ev_last) != cudaSuccess) {
             g_init_error = "stream/event creation failed"; delete ctx; return H2B_E_CUDA;
         }
@@ -620,6 +663,8 @@ void h2b_destroy(h2b_ctx* ctx) {
         for (auto& r : d.recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         for (auto ev : d.ev_pool) cudaEventDestroy(ev);
         cudaEventDestroy(d.ev_first); cudaEventDestroy(d.ev_last);
+        for (auto ev : d.chunk_events) cudaEventDestroy(ev);
+        cudaStreamDestroy(d.copy_stream);
         cudaStreamDestroy(d.stream);
     }
     delete ctx;

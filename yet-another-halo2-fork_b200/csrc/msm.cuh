@@ -26,6 +26,7 @@ struct MsmGeom {
     uint32_t pre_stride; // 0: classic (one bucket set per window, bases[i]).  > 0: the bases buffer holds the
                          // precomputed multiples pre[j * pre_stride + i] = 2^(c*j) * P_i, so all windows share ONE
                          // bucket set: digit j of scalar i goes to bucket |d| with entry index j * pre_stride + i.
+    uint32_t idx_offset; // index of scalars[0] within the bases (an MSM streamed in chunks keeps global indices)
 };
 
 H2B_HD constexpr uint32_t msm_windows(uint32_t c) { return (255u + c - 1u) / c; }
@@ -130,7 +131,8 @@ __global__ void msm_scatter_kernel(MsmGeom g, const Fr* __restrict__ scalars, ui
         if (d != 0) {
             uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
             uint32_t pos = atomicAdd(cursor + (g.pre_stride ? 0 : (size_t)j * g.nb) + (mag - 1), 1u);
-            entries[pos] = (g.pre_stride ? j * g.pre_stride + i : i) | (d < 0 ? 0x80000000u : 0u);
+            uint32_t idx = i + g.idx_offset;
+            entries[pos] = (g.pre_stride ? j * g.pre_stride + idx : idx) | (d < 0 ? 0x80000000u : 0u);
         }
     });
 }
@@ -247,13 +249,14 @@ __global__ void __launch_bounds__(128, MINB)
 msm_accumulate_kernel(const Affine* __restrict__ bases, const uint32_t* __restrict__ entries,
                       const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends,
                       const uint32_t* __restrict__ order, uint32_t nkeys, uint32_t long_threshold,
-                      Xyzz* __restrict__ buckets) {
+                      Xyzz* __restrict__ buckets, uint32_t add_to) {
     uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= nkeys) return;
     uint32_t key = order[tid];
     uint32_t e = offsets[key], end = ends[key];
     if (end - e > long_threshold) return;
-    Xyzz acc = Xyzz::identity();
+    if (add_to && e == end) return;                        // later chunk of a streamed MSM, nothing new for this bucket
+    Xyzz acc = add_to ? xyzz_load(buckets + key) : Xyzz::identity();
     if (PF) {
     // No register double-buffer: the next point is pulled into L2 while the current addition runs, which frees
     // ~16 registers for one more resident warp per scheduler.
@@ -338,7 +341,7 @@ msm_accumulate_long_kernel(const Affine* __restrict__ bases, const uint32_t* __r
 }
 __global__ void __launch_bounds__(MSM_LONG_THREADS)
 msm_long_combine_kernel(const MsmLongInfo* __restrict__ long_info, const uint32_t* __restrict__ counters,
-                        const Xyzz* __restrict__ partials, Xyzz* __restrict__ buckets) {
+                        const Xyzz* __restrict__ partials, Xyzz* __restrict__ buckets, uint32_t add_to) {
     __shared__ Xyzz sh[MSM_LONG_THREADS];
     uint32_t nlong = counters[0];
     for (uint32_t li = blockIdx.x; li < nlong; li += gridDim.x) {
@@ -352,7 +355,7 @@ msm_long_combine_kernel(const MsmLongInfo* __restrict__ long_info, const uint32_
             if (threadIdx.x < (uint32_t)s) sh[threadIdx.x] = xyzz_add(sh[threadIdx.x], sh[threadIdx.x + s]);
             __syncthreads();
         }
-        if (threadIdx.x == 0) xyzz_store(buckets + info.key, sh[0]);
+        if (threadIdx.x == 0) xyzz_store(buckets + info.key, add_to ? xyzz_add(sh[0], xyzz_load(buckets + info.key)) : sh[0]);
         __syncthreads();
     }
 }
