@@ -203,3 +203,29 @@ def test_linearity_full_size(engine):
     tot = engine.msm_with_cached_base(ones, desc)
     k = (n * (n + 1) // 2) % R.R_MOD
     assert np.array_equal(tot[:8], C.affine_mul(C.gen_bases(1, 1)[0], C.mont_from_int(k, R.R_MOD)))
+
+
+def test_single_process_multi_device_context():
+    """h2b_init with several devices: bases sharded by point range, shards run concurrently, host folds the sums;
+    batched NTT columns are dealt round-robin.  Needs >= 2 GPUs (skipped otherwise)."""
+    import h2b200
+    ndev = h2b200.load().h2b_device_count()
+    if ndev < 2:
+        pytest.skip("needs >= 2 GPUs")
+    ctx2 = h2b200.Context(list(range(min(ndev, 4))))
+    eng2 = h2b200.B200Engine(ctx2)
+    for n in (1, 3, 1000, (1 << 17) + 11):
+        s, b = C.random_fr(n, 900 + n), C.gen_bases(n, 6)
+        exp = oracle_affine(s, b)
+        check(eng2.msm(s, b), exp)
+        desc = eng2.get_base_descriptor(b)
+        check(eng2.msm_with_cached_base(s, desc), exp)
+        check(eng2.msm_with_cached_base(s[: n // 2 + 1], desc), oracle_affine(s[: n // 2 + 1], b[: n // 2 + 1]))
+        desc.release()
+    dom = h2b200.EvaluationDomain(5, 10, ctx2)
+    cols = [C.random_fr(1 << 10, 70 + i) for i in range(7)]
+    ref = R.EvaluationDomain(5, 10)
+    m = lambda x: C.mont_from_int(x, R.R_MOD)
+    for c, o in zip(cols, dom.coeff_to_extended_batch(cols)):
+        assert np.array_equal(o, C.coeff_to_extended(c, 10, ref.extended_k, m(ref.extended_omega), m(ref.g_coset), m(ref.g_coset_inv)))
+    ctx2.close()
