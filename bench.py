@@ -240,7 +240,7 @@ def run_reference(args, rank: int, world: int):
                 "sample": f"best_fft restatement on 2^{CPU_SAMPLE_K} ({ntt_ms:.1f} ms), scaled by n log n"},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -254,6 +254,9 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
 
     torch.cuda.set_device(local_rank)
     if world > 1:
+        # NCCL_DEBUG=VERSION (set by some images) makes NCCL print a banner on stdout; the contract is ONE JSON line.
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = h2b200.Context([local_rank])
     eng = h2b200.B200Engine(ctx)
@@ -420,13 +423,34 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
         nms = cpu_ntt_sample(CPU_SAMPLE_K)
         ntt["cpu_baseline"] = {"value": scale_to_full(nms, CPU_SAMPLE_K, NTT_K) * NTT_K / CPU_SAMPLE_K, "unit": "ms", "cores": threads, "kind": "port",
                                "sample": f"best_fft restatement on 2^{CPU_SAMPLE_K}: {nms:.1f} ms, scaled by n log n"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def capture_stdout():
+    """The contract is ONE JSON line on stdout.  Native libraries (NCCL's version banner, CUDA warnings) write to fd 1
+    behind Python's back, so fd 1 is pointed at stderr for the whole run and the JSON line goes to the saved descriptor."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    capture_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
