@@ -35,8 +35,24 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
     if verbose:
         cflags += ["-Xptxas", "-v"]
 
+    def deps(path, seen=None):
+        """the file plus every quoted #include reachable from it (so touching msm.cuh does not rebuild the NTT objects)"""
+        seen = set() if seen is None else seen
+        path = os.path.normpath(path)
+        if path in seen or not os.path.exists(path):
+            return seen
+        seen.add(path)
+        with open(path) as fh:
+            for line in fh:
+                line = line.strip()
+                if line.startswith("#include \""):
+                    deps(os.path.join(os.path.dirname(path), line.split('"')[1]), seen)
+        return seen
+
     def compile_one(f):
         obj = os.path.join(objdir, f[:-3] + ".o")
+        if not force and not verbose and _newer(obj, deps(os.path.join(CSRC, f))):
+            return obj
         subprocess.check_call([nvcc] + cflags + ["-c", "-o", obj, os.path.join(CSRC, f)], cwd=HERE)
         return obj
 

@@ -15,7 +15,9 @@
 #include <vector>
 
 #include "../../include/h2b200.h"
+#define H2B_NO_KERNELS 1      // kernels live in msm_kernels.cu / ntt_kernels_*.cu; this unit is host orchestration only
 #include "msm.cuh"
+#include "msm_kernels.hpp"
 #include "ntt.cuh"
 #include "ntt_plan.hpp"
 #include "ntt_kernels.hpp"
@@ -51,15 +53,31 @@ struct NttPlanDev {
     Fr scale;
 };
 
+// Outputs of the binning stage of one MSM chunk (count / scan / scatter / order).  Two sets, so that chunk k+1 is binned
+// on the sort stream (memory / atomic bound) while chunk k is accumulated on the compute stream (multiplier bound).
+struct MsmSortSet {
+    DevBuf counts, offsets, ends, entries, order, blocksums, sizehist, long_info, long_tasks, counters;
+    cudaEvent_t sorted = nullptr, consumed = nullptr;
+    bool consumed_pending = false;
+    void release() {
+        DevBuf* bufs[] = {&counts, &offsets, &ends, &entries, &order, &blocksums, &sizehist, &long_info, &long_tasks, &counters};
+        for (DevBuf* b : bufs) b->release();
+        if (sorted) cudaEventDestroy(sorted);
+        if (consumed) cudaEventDestroy(consumed);
+        sorted = consumed = nullptr;
+    }
+};
+
 struct Dev {
     int id = 0;
     int sms = 148;
-    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr, sort_stream = nullptr;
+    cudaStream_t launch_stream = nullptr;         // where H2B_LAUNCH enqueues (stream, or sort_stream inside the binning stage)
     cudaEvent_t ev_first = nullptr, ev_last = nullptr;
     std::vector<cudaEvent_t> chunk_events;
     DevBuf ntt_a, ntt_b, ntt_tab;
-    DevBuf m_scalars, m_counts, m_offsets, m_ends, m_entries, m_order, m_buckets, m_wpart, m_blocksums,
-        m_sizehist, m_long_info, m_long_tasks, m_long_partials, m_counters, m_tmp_bases;
+    MsmSortSet ms[2];
+    DevBuf m_scalars, m_buckets, m_wpart, m_long_partials, m_counters, m_tmp_bases;
     void* pinned = nullptr;
     size_t pinned_cap = 0;
     std::map<std::string, NttPlanDev> plans;
@@ -75,12 +93,12 @@ struct Dev {
     void prof_begin(const char* name) {
         if (!prof) return;
         ProfRec r; r.name = name; r.a = get_event(); r.b = get_event();
-        cudaEventRecord(r.a, stream);
+        cudaEventRecord(r.a, launch_stream);
         recs.push_back(r);
     }
     void prof_end() {
         if (!prof) return;
-        cudaEventRecord(recs.back().b, stream);
+        cudaEventRecord(recs.back().b, launch_stream);
     }
     cudaError_t reserve_pinned(size_t bytes) {
         if (bytes <= pinned_cap) return cudaSuccess;
@@ -128,7 +146,7 @@ thread_local std::string g_init_error;
 #define H2B_LAUNCH(dev, name, kern, grid, block, smem, ...)                                                  \
     do {                                                                                                     \
         (dev).prof_begin(name);                                                                              \
-        kern<<<(grid), (block), (smem), (dev).stream>>>(__VA_ARGS__);                                        \
+        kern<<<(grid), (block), (smem), (dev).launch_stream>>>(__VA_ARGS__);                                        \
         (dev).prof_end();                                                                                    \
         (dev).launches++;                                                                                    \
     } while (0)
@@ -246,6 +264,7 @@ uint32_t msm_choose_c(size_t n_total) {
 #define H2B_ACC_DEFAULT_VARIANT 1
 #endif
 struct MsmLaunchInfo { uint32_t c, windows, slices; bool pre; };
+const MsmKernelTable& MK = msm_kernel_table();
 
 // Enqueue the whole bucket pipeline for `n` resident (scalar, base) pairs on device d; the per-window partial
 // sums (windows * slices XYZZ points) are copied asynchronously into d.pinned.
@@ -264,72 +283,94 @@ MsmShape msm_shape(uint32_t n, uint32_t c, uint32_t pre_stride, uint32_t idx_off
     return sp;
 }
 
-int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, const Affine* bases, const Fr* scalars, uint32_t n, uint32_t idx_offset, uint32_t c,
-                         uint32_t pre_stride, bool add_to) {
-    MsmShape sp = msm_shape(n, c, pre_stride, idx_offset);
-    const MsmGeom& g = sp.g;
-    const uint32_t nkeys = sp.nkeys;
+struct MsmChunkPlan { MsmShape sp; uint32_t long_threshold, max_long, max_tasks, nblk; };
+
+int msm_chunk_plan(h2b_ctx* ctx, uint32_t n, uint32_t idx_offset, uint32_t c, uint32_t pre_stride, MsmChunkPlan* out) {
+    MsmChunkPlan pl;
+    pl.sp = msm_shape(n, c, pre_stride, idx_offset);
+    const MsmGeom& g = pl.sp.g;
     const uint64_t max_entries = (uint64_t)n * g.windows;
     if (max_entries >= 0x7fffffffull || (uint64_t)(idx_offset + n) * (pre_stride ? g.windows : 1) >= 0x7fffffffull)
         return ctx->fail(H2B_E_INVALID, "msm: n * windows exceeds 2^31 (shard the MSM)");
-    uint32_t mean = (uint32_t)(max_entries / nkeys);
-    uint32_t long_threshold = std::max<uint32_t>(256u, 16u * std::max<uint32_t>(mean, 1u));
-    uint32_t max_long = (uint32_t)(max_entries / long_threshold) + 1;
-    uint32_t max_tasks = (uint32_t)(max_entries / MSM_LONG_CHUNK) + max_long + 1;
-    const uint32_t nblk = (nkeys + SCAN_BLOCK - 1) / SCAN_BLOCK;
+    uint32_t mean = (uint32_t)(max_entries / pl.sp.nkeys);
+    pl.long_threshold = std::max<uint32_t>(256u, 16u * std::max<uint32_t>(mean, 1u));
+    pl.max_long = (uint32_t)(max_entries / pl.long_threshold) + 1;
+    pl.max_tasks = (uint32_t)(max_entries / MSM_LONG_CHUNK) + pl.max_long + 1;
+    pl.nblk = (pl.sp.nkeys + SCAN_BLOCK - 1) / SCAN_BLOCK;
+    *out = pl;
+    return H2B_OK;
+}
 
-    H2B_CK(d.m_counts.reserve((size_t)nkeys * 4));
-    H2B_CK(d.m_offsets.reserve((size_t)nkeys * 4));
-    H2B_CK(d.m_ends.reserve((size_t)nkeys * 4));
-    H2B_CK(d.m_order.reserve((size_t)nkeys * 4));
-    H2B_CK(d.m_entries.reserve(std::max<size_t>((size_t)max_entries * 4, 256)));
-    H2B_CK(d.m_buckets.reserve((size_t)nkeys * sizeof(Xyzz)));
-    H2B_CK(d.m_blocksums.reserve((size_t)nblk * 4 + 256));
-    H2B_CK(d.m_sizehist.reserve((size_t)MSM_SIZE_BINS * 4));
-    H2B_CK(d.m_long_info.reserve((size_t)max_long * sizeof(MsmLongInfo)));
-    H2B_CK(d.m_long_tasks.reserve((size_t)max_tasks * sizeof(MsmLongTask)));
-    H2B_CK(d.m_long_partials.reserve((size_t)max_tasks * sizeof(Xyzz)));
-    H2B_CK(d.m_counters.reserve(256));
+// Binning stage of one chunk, enqueued on the SORT stream into sort set `S`: histogram, offsets, scatter, population order,
+// oversized-bucket task list.
+int msm_stage_sort(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, const Fr* scalars) {
+    const MsmGeom& g = pl.sp.g;
+    const uint32_t nkeys = pl.sp.nkeys, n = g.n, nblk = pl.nblk;
+    const uint64_t max_entries = (uint64_t)n * g.windows;
+    H2B_CK(S.counts.reserve((size_t)nkeys * 4));
+    H2B_CK(S.offsets.reserve((size_t)nkeys * 4));
+    H2B_CK(S.ends.reserve((size_t)nkeys * 4));
+    H2B_CK(S.order.reserve((size_t)nkeys * 4));
+    H2B_CK(S.entries.reserve(std::max<size_t>((size_t)max_entries * 4, 256)));
+    H2B_CK(S.blocksums.reserve((size_t)nblk * 4 + 256));
+    H2B_CK(S.sizehist.reserve((size_t)MSM_SIZE_BINS * 4));
+    H2B_CK(S.long_info.reserve((size_t)pl.max_long * sizeof(MsmLongInfo)));
+    H2B_CK(S.long_tasks.reserve((size_t)pl.max_tasks * sizeof(MsmLongTask)));
+    H2B_CK(S.counters.reserve(256));
+    uint32_t* counts = S.counts.as<uint32_t>();
+    uint32_t* offsets = S.offsets.as<uint32_t>();
+    uint32_t* ends = S.ends.as<uint32_t>();
+    uint32_t* order = S.order.as<uint32_t>();
+    uint32_t* entries = S.entries.as<uint32_t>();
+    uint32_t* blocksums = S.blocksums.as<uint32_t>();
+    uint32_t* sizehist = S.sizehist.as<uint32_t>();
+    uint32_t* counters = S.counters.as<uint32_t>();
 
-    uint32_t* counts = d.m_counts.as<uint32_t>();
-    uint32_t* offsets = d.m_offsets.as<uint32_t>();
-    uint32_t* ends = d.m_ends.as<uint32_t>();
-    uint32_t* order = d.m_order.as<uint32_t>();
-    uint32_t* entries = d.m_entries.as<uint32_t>();
-    uint32_t* blocksums = d.m_blocksums.as<uint32_t>();
-    uint32_t* sizehist = d.m_sizehist.as<uint32_t>();
-    uint32_t* counters = d.m_counters.as<uint32_t>();
-    Xyzz* buckets = d.m_buckets.as<Xyzz>();
-
-    H2B_CK(cudaMemsetAsync(counts, 0, (size_t)nkeys * 4, d.stream));
-    H2B_CK(cudaMemsetAsync(sizehist, 0, (size_t)MSM_SIZE_BINS * 4, d.stream));
-    H2B_CK(cudaMemsetAsync(counters, 0, 256, d.stream));
+    d.launch_stream = d.sort_stream;
+    cudaStream_t st = d.sort_stream;
+    cudaError_t e1 = cudaMemsetAsync(counts, 0, (size_t)nkeys * 4, st);
+    cudaError_t e2 = cudaMemsetAsync(sizehist, 0, (size_t)MSM_SIZE_BINS * 4, st);
+    cudaError_t e3 = cudaMemsetAsync(counters, 0, 256, st);
+    if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) { d.launch_stream = d.stream; H2B_CK(e1); H2B_CK(e2); H2B_CK(e3); }
     const uint32_t tb = 256;
-    if (n) H2B_LAUNCH(d, "msm_count", msm_count_kernel, (n + tb - 1) / tb, tb, 0, g, scalars, counts);
-    H2B_LAUNCH(d, "msm_scan", scan_block_sums_kernel, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums);
-    H2B_LAUNCH(d, "msm_scan", scan_single_block_kernel, 1, SCAN_BLOCK, 0, blocksums, nblk, (uint32_t*)nullptr);
-    H2B_LAUNCH(d, "msm_scan", scan_apply_kernel, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums, offsets, ends);
-    if (n) H2B_LAUNCH(d, "msm_scatter", msm_scatter_kernel, (n + tb - 1) / tb, tb, 0, g, scalars, ends, entries);
-    H2B_LAUNCH(d, "msm_order", msm_size_hist_kernel, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist);
-    H2B_LAUNCH(d, "msm_order", scan_single_block_kernel, 1, SCAN_BLOCK, 0, sizehist, MSM_SIZE_BINS, (uint32_t*)nullptr);
-    H2B_LAUNCH(d, "msm_order", msm_size_scatter_kernel, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist, order);
-    H2B_LAUNCH(d, "msm_order", msm_long_list_kernel, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, long_threshold,
-               d.m_long_info.as<MsmLongInfo>(), d.m_long_tasks.as<MsmLongTask>(), counters);
+    if (n) H2B_LAUNCH(d, "msm_count", MK.count, (n + tb - 1) / tb, tb, 0, g, scalars, counts);
+    H2B_LAUNCH(d, "msm_scan", MK.scan_block_sums, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums);
+    H2B_LAUNCH(d, "msm_scan", MK.scan_single_block, 1, SCAN_BLOCK, 0, blocksums, nblk, (uint32_t*)nullptr);
+    H2B_LAUNCH(d, "msm_scan", MK.scan_apply, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums, offsets, ends);
+    if (n) H2B_LAUNCH(d, "msm_scatter", MK.scatter, (n + tb - 1) / tb, tb, 0, g, scalars, ends, entries);
+    H2B_LAUNCH(d, "msm_order", MK.size_hist, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist);
+    H2B_LAUNCH(d, "msm_order", MK.scan_single_block, 1, SCAN_BLOCK, 0, sizehist, MSM_SIZE_BINS, (uint32_t*)nullptr);
+    H2B_LAUNCH(d, "msm_order", MK.size_scatter, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist, order);
+    H2B_LAUNCH(d, "msm_order", MK.long_list, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, pl.long_threshold,
+               S.long_info.as<MsmLongInfo>(), S.long_tasks.as<MsmLongTask>(), counters);
+    d.launch_stream = d.stream;
+    H2B_CK(cudaGetLastError());
+    return H2B_OK;
+}
+
+// Accumulation stage of one chunk, enqueued on the COMPUTE stream: every bucket of sort set `S` is summed into the shared
+// bucket array (add_to: on top of what earlier chunks left there).
+int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, const Affine* bases, bool add_to) {
+    const uint32_t nkeys = pl.sp.nkeys;
+    H2B_CK(d.m_buckets.reserve((size_t)nkeys * sizeof(Xyzz)));
+    H2B_CK(d.m_long_partials.reserve((size_t)pl.max_tasks * sizeof(Xyzz)));
+    const uint32_t* offsets = S.offsets.as<uint32_t>();
+    const uint32_t* ends = S.ends.as<uint32_t>();
+    const uint32_t* order = S.order.as<uint32_t>();
+    const uint32_t* entries = S.entries.as<uint32_t>();
+    const uint32_t* counters = S.counters.as<uint32_t>();
+    Xyzz* buckets = d.m_buckets.as<Xyzz>();
     {
-        typedef void (*acc_kernel_t)(const Affine*, const uint32_t*, const uint32_t*, const uint32_t*, const uint32_t*, uint32_t,
-                                     uint32_t, Xyzz*, uint32_t);
-        static const acc_kernel_t variants[4] = {msm_accumulate_kernel<4, false>, msm_accumulate_kernel<4, true>,
-                                                 msm_accumulate_kernel<5, true>, msm_accumulate_kernel<6, true>};
         int v = H2B_ACC_DEFAULT_VARIANT;
         if (const char* env = std::getenv("H2B_ACC_VARIANT")) { int t = std::atoi(env); if (t >= 0 && t < 4) v = t; }
-        acc_kernel_t kern = variants[v];
+        auto kern = MK.accumulate[v];
         H2B_LAUNCH(d, "msm_accumulate", kern, (nkeys + 127) / 128, 128, 0, bases, entries, offsets, ends, order, nkeys,
-                   long_threshold, buckets, add_to ? 1u : 0u);
+                   pl.long_threshold, buckets, add_to ? 1u : 0u);
     }
-    H2B_LAUNCH(d, "msm_accumulate_long", msm_accumulate_long_kernel, (unsigned)(d.sms * 8), MSM_LONG_THREADS, 0, bases, entries,
-               offsets, ends, d.m_long_tasks.as<MsmLongTask>(), counters, d.m_long_partials.as<Xyzz>());
-    H2B_LAUNCH(d, "msm_accumulate_long", msm_long_combine_kernel, (unsigned)d.sms, MSM_LONG_THREADS, 0,
-               d.m_long_info.as<MsmLongInfo>(), counters, d.m_long_partials.as<Xyzz>(), buckets, add_to ? 1u : 0u);
+    H2B_LAUNCH(d, "msm_accumulate_long", MK.accumulate_long, (unsigned)(d.sms * 8), MSM_LONG_THREADS, 0, bases, entries,
+               offsets, ends, S.long_tasks.as<MsmLongTask>(), counters, d.m_long_partials.as<Xyzz>());
+    H2B_LAUNCH(d, "msm_accumulate_long", MK.long_combine, (unsigned)d.sms, MSM_LONG_THREADS, 0,
+               S.long_info.as<MsmLongInfo>(), counters, d.m_long_partials.as<Xyzz>(), buckets, add_to ? 1u : 0u);
     H2B_CK(cudaGetLastError());
     return H2B_OK;
 }
@@ -355,10 +396,10 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
     Xyzz* set_sums = wpart + (size_t)kw * slices * 2;
     if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
         dim3 grid(slices, kw, 1);
-        H2B_LAUNCH(d, "msm_reduce", msm_reduce_kernel, grid, MSM_REDUCE_THREADS, 0, gr, buckets, slices, log_l, block_p, block_r);
-        H2B_LAUNCH(d, "msm_reduce", msm_reduce_final_kernel, kw, MSM_REDUCE_MAX_SLICES, 0, slices, log_l + 7u, block_p, block_r, set_sums);
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce, grid, MSM_REDUCE_THREADS, 0, gr, buckets, slices, log_l, block_p, block_r);
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce_final, kw, MSM_REDUCE_MAX_SLICES, 0, slices, log_l + 7u, block_p, block_r, set_sums);
     } else {
-        H2B_LAUNCH(d, "msm_reduce", msm_reduce_small_kernel, (kw + 31) / 32, 32, 0, gr, buckets, set_sums);
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce_small, (kw + 31) / 32, 32, 0, gr, buckets, set_sums);
     }
     H2B_CK(cudaGetLastError());
     H2B_CK(cudaMemcpyAsync(d.pinned, set_sums, (size_t)kw * sizeof(Xyzz), cudaMemcpyDeviceToHost, d.stream));
@@ -409,15 +450,19 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
         const uint32_t use_c = sh.pre ? sh.pre_c : c;
         const uint32_t stride = sh.pre ? (uint32_t)sh.count : 0u;
         int rc = H2B_OK;
-        if (on_device && di == 0) {
-            rc = msm_stage_accumulate(ctx, d, dev_bases, reinterpret_cast<const Fr*>(scalars) + sh.start, (uint32_t)cnt, 0, use_c, stride, false);
-        } else {
-            // Stream the scalars: chunk k+1 crosses PCIe on the copy stream while chunk k is binned and accumulated.
+        // The scalars are processed in chunks: chunk k+1 crosses PCIe on the copy stream (host scalars) and is binned on the
+        // sort stream while chunk k is accumulated on the compute stream; all chunks add into ONE bucket array.
+        const bool staged = !(on_device && di == 0);
+        size_t chunk = cnt;
+        if (cnt >= ((size_t)1 << 22)) {          // 2^21-point chunks, at most 8 (measured on B200: profiles/README.md)
+            size_t k = std::min<size_t>(8, cnt >> 21);
+            chunk = (cnt + k - 1) / k;
+        }
+        if (const char* env = std::getenv("H2B_MSM_CHUNKS")) { int k = std::atoi(env); if (k >= 1 && k <= 64) chunk = (cnt + k - 1) / k; }
+        size_t nchunks = (cnt + chunk - 1) / chunk;
+        const Fr* dev_scalars = reinterpret_cast<const Fr*>(scalars) + sh.start;
+        if (staged) {
             H2B_CK(d.m_scalars.reserve(cnt * 32));
-            size_t chunk = cnt;
-            if (!on_device && cnt >= ((size_t)1 << 23)) chunk = (cnt + 3) / 4;
-            if (const char* env = std::getenv("H2B_MSM_CHUNKS")) { int k = std::atoi(env); if (k >= 1 && k <= 64) chunk = (cnt + k - 1) / k; }
-            size_t nchunks = (cnt + chunk - 1) / chunk;
             while (d.chunk_events.size() < nchunks) { cudaEvent_t e; H2B_CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); d.chunk_events.push_back(e); }
             H2B_CK(cudaStreamWaitEvent(d.copy_stream, d.ev_first, 0));      // previous call's use of m_scalars is over
             const uint8_t* src = reinterpret_cast<const uint8_t*>(scalars) + sh.start * 32;
@@ -427,12 +472,26 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
                                        on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, d.copy_stream));
                 H2B_CK(cudaEventRecord(d.chunk_events[k], d.copy_stream));
             }
-            for (size_t k = 0; k < nchunks && rc == H2B_OK; k++) {
-                size_t lo = k * chunk, len = std::min(chunk, cnt - lo);
-                H2B_CK(cudaStreamWaitEvent(d.stream, d.chunk_events[k], 0));
-                const Affine* b = stride ? dev_bases : dev_bases + lo;       // classic mode indexes bases relative to the chunk
-                rc = msm_stage_accumulate(ctx, d, b, d.m_scalars.as<Fr>() + lo, (uint32_t)len, stride ? (uint32_t)lo : 0u, use_c, stride, k > 0);
-            }
+            dev_scalars = d.m_scalars.as<Fr>();
+        }
+        H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.ev_first, 0));
+        for (size_t k = 0; k < nchunks && rc == H2B_OK; k++) {
+            size_t lo = k * chunk, len = std::min(chunk, cnt - lo);
+            MsmSortSet& S = d.ms[k & 1];
+            MsmChunkPlan pl;
+            rc = msm_chunk_plan(ctx, (uint32_t)len, stride ? (uint32_t)lo : 0u, use_c, stride, &pl);
+            if (rc) break;
+            if (S.consumed_pending) { H2B_CK(cudaStreamWaitEvent(d.sort_stream, S.consumed, 0)); S.consumed_pending = false; }
+            if (staged) H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.chunk_events[k], 0));
+            rc = msm_stage_sort(ctx, d, S, pl, dev_scalars + lo);
+            if (rc) break;
+            H2B_CK(cudaEventRecord(S.sorted, d.sort_stream));
+            H2B_CK(cudaStreamWaitEvent(d.stream, S.sorted, 0));
+            const Affine* b = stride ? dev_bases : dev_bases + lo;           // classic mode indexes bases relative to the chunk
+            rc = msm_stage_accumulate(ctx, d, S, pl, b, k > 0);
+            if (rc) break;
+            H2B_CK(cudaEventRecord(S.consumed, d.stream));
+            S.consumed_pending = true;
         }
         if (rc) return rc;
         rc = msm_stage_reduce(ctx, d, use_c, stride, &infos[di]);
@@ -482,7 +541,7 @@ int precompute_shard(h2b_ctx* ctx, Dev& d, BasesShard& sh) {
     H2B_CK(cudaMemGetInfo(&free_b, &total_b));
     if (bytes > free_b / 2) return H2B_OK;
     H2B_CK(cudaMalloc(&sh.pre, bytes));
-    H2B_LAUNCH(d, "msm_precompute", msm_precompute_kernel, (unsigned)((sh.count + 127) / 128), 128, 0, (const Affine*)sh.d,
+    H2B_LAUNCH(d, "msm_precompute", MK.precompute, (unsigned)((sh.count + 127) / 128), 128, 0, (const Affine*)sh.d,
                (Affine*)sh.pre, (uint32_t)sh.count, (uint32_t)sh.count, c, w);
     H2B_CK(cudaGetLastError());
     H2B_CK(cudaStreamSynchronize(d.stream));
@@ -527,73 +586,6 @@ void release_bases(h2b_ctx* ctx, Bases& B) {
         }
 }
 
-// ------------------------------------------------------------------------------------------------
-// integer-pipe calibration kernels
-// ------------------------------------------------------------------------------------------------
-// IMAD.WIDE carry chains exactly as the field multiplier issues them (two interleaved chains of four
-// lo/hi pairs sharing one multiplier register; per-thread operands so nothing lands on the uniform datapath).
-// Counts one "wide mad" per IMAD.WIDE.U32(.X): 8 per iteration.
-__global__ void imad_wide_peak_kernel(uint32_t seed, uint32_t iters, unsigned long long* sink) {
-    uint32_t e[8], o[8], a[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) {
-        e[i] = seed * (i + 1) + threadIdx.x;
-        o[i] = e[i] * 3u + blockIdx.x;
-        a[i] = seed + 77u * i + blockIdx.x + threadIdx.x * 2654435761u;
-    }
-    for (uint32_t it = 0; it < iters; it++) {
-        uint32_t bi = e[1] | 1u;
-        asm volatile(
-            "mad.lo.cc.u32 %0, %8, %12, %0;\n madc.hi.cc.u32 %1, %8, %12, %1;\n"
-            "madc.lo.cc.u32 %2, %9, %12, %2;\n madc.hi.cc.u32 %3, %9, %12, %3;\n"
-            "madc.lo.cc.u32 %4, %10, %12, %4;\n madc.hi.cc.u32 %5, %10, %12, %5;\n"
-            "madc.lo.cc.u32 %6, %11, %12, %6;\n madc.hi.u32 %7, %11, %12, %7;\n"
-            : "+r"(e[0]), "+r"(e[1]), "+r"(e[2]), "+r"(e[3]), "+r"(e[4]), "+r"(e[5]), "+r"(e[6]), "+r"(e[7])
-            : "r"(a[0]), "r"(a[2]), "r"(a[4]), "r"(a[6]), "r"(bi));
-        asm volatile(
-            "mad.lo.cc.u32 %0, %8, %12, %0;\n madc.hi.cc.u32 %1, %8, %12, %1;\n"
-            "madc.lo.cc.u32 %2, %9, %12, %2;\n madc.hi.cc.u32 %3, %9, %12, %3;\n"
-            "madc.lo.cc.u32 %4, %10, %12, %4;\n madc.hi.cc.u32 %5, %10, %12, %5;\n"
-            "madc.lo.cc.u32 %6, %11, %12, %6;\n madc.hi.u32 %7, %11, %12, %7;\n"
-            : "+r"(o[0]), "+r"(o[1]), "+r"(o[2]), "+r"(o[3]), "+r"(o[4]), "+r"(o[5]), "+r"(o[6]), "+r"(o[7])
-            : "r"(a[1]), "r"(a[3]), "r"(a[5]), "r"(a[7]), "r"(bi));
-    }
-    uint32_t s = 0;
-#pragma unroll
-    for (int i = 0; i < 8; i++) s ^= e[i] ^ o[i];
-    if (s == 0x1234567u) *sink = s;
-}
-// Two independent chains of dependent field multiplications per thread, all operands per-thread.
-__global__ void field_mul_peak_kernel(uint32_t iters, Fq* sink) {
-    Fq x = Fq::one(), y = Fq::r2();
-#pragma unroll
-    for (int i = 0; i < 7; i++) { x.l[i] ^= threadIdx.x * 2654435761u + i; y.l[i] ^= (threadIdx.x + 7u * blockIdx.x) * 40503u + i; }
-    Fq a = x, b = y;
-    for (uint32_t it = 0; it < iters; it++) {
-        a = fe_mul(a, y);
-        b = fe_mul(b, x);
-        x.l[0] ^= b.l[3] & 1u;          // keep the operands loop-variant
-    }
-    Fq r = fe_add(a, b);
-    if (r.l[0] == 0x12345u && r.l[7] == 0x54321u) *sink = r;
-}
-
-// Synthetic benchmark bases: out[i] = [t0 + i] G, G = (1, 2), affine.
-__global__ void synth_bases_kernel(Affine* out, uint64_t n, uint64_t t0) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    uint64_t k = t0 + i;
-    Fq gx = fe_from_u64<FqParams>(1), gy = fe_from_u64<FqParams>(2);
-    Xyzz acc = Xyzz::identity();
-    for (int bit = 63; bit >= 0; bit--) {
-        acc = xyzz_double(acc);
-        if ((k >> bit) & 1ull) xyzz_madd(acc, gx, gy, false);
-    }
-    Affine a = xyzz_to_affine(acc);
-    fe_store(&out[i].x, a.x);
-    fe_store(&out[i].y, a.y);
-}
-
 }  // namespace
 
 // ================================================================================================
@@ -635,11 +627,19 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
             g_init_error = "device is not sm_100 (this library is built for B200 only)"; delete ctx; return H2B_E_NODEVICE;
         }
         d.sms = prop.multiProcessorCount;
-        if (cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking) != cudaSuccess ||
+        int prio_lo = 0, prio_hi = 0;
+        cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+        if (cudaStreamCreateWithPriority(&d.stream, cudaStreamNonBlocking, prio_lo) != cudaSuccess ||
             cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
-            cudaEventCreate(&d.ev_first) != cudaSuccess || cudaEventCreate(&d.ev_last) != cudaSuccess) {
+            cudaStreamCreateWithPriority(&d.sort_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
+            cudaEventCreate(&d.ev_first) != cudaSuccess || cudaEventCreate(&d.ev_last) != cudaSuccess ||
+            cudaEventCreateWithFlags(&d.ms[0].sorted, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&d.ms[0].consumed, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&d.ms[1].sorted, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&d.ms[1].consumed, cudaEventDisableTiming) != cudaSuccess) {
             g_init_error = "stream/event creation failed"; delete ctx; return H2B_E_CUDA;
         }
+        d.launch_stream = d.stream;
         int rc = ntt_prepare_device(ctx);
         if (rc) { g_init_error = ctx->err; delete ctx; return rc; }
     }
@@ -655,16 +655,18 @@ void h2b_destroy(h2b_ctx* ctx) {
         cudaSetDevice(d.id);
         cudaStreamSynchronize(d.stream);
         for (auto& kv : d.plans) cudaFree(kv.second.tables);
-        DevBuf* bufs[] = {&d.ntt_a, &d.ntt_b, &d.ntt_tab, &d.m_scalars, &d.m_counts, &d.m_offsets, &d.m_ends, &d.m_entries,
-                          &d.m_order, &d.m_buckets, &d.m_wpart, &d.m_blocksums, &d.m_sizehist, &d.m_long_info,
-                          &d.m_long_tasks, &d.m_long_partials, &d.m_counters, &d.m_tmp_bases};
+        cudaStreamSynchronize(d.sort_stream);
+        DevBuf* bufs[] = {&d.ntt_a, &d.ntt_b, &d.ntt_tab, &d.m_scalars, &d.m_buckets, &d.m_wpart, &d.m_long_partials, &d.m_counters,
+                          &d.m_tmp_bases};
         for (DevBuf* b : bufs) b->release();
+        d.ms[0].release(); d.ms[1].release();
         if (d.pinned) cudaFreeHost(d.pinned);
         for (auto& r : d.recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         for (auto ev : d.ev_pool) cudaEventDestroy(ev);
         cudaEventDestroy(d.ev_first); cudaEventDestroy(d.ev_last);
         for (auto ev : d.chunk_events) cudaEventDestroy(ev);
         cudaStreamDestroy(d.copy_stream);
+        cudaStreamDestroy(d.sort_stream);
         cudaStreamDestroy(d.stream);
     }
     delete ctx;
@@ -1022,7 +1024,7 @@ int h2b_synth_bases(h2b_ctx* ctx, void* d_out, size_t n, uint64_t t0) {
     Dev& d = ctx->devs[0];
     H2B_CK(cudaSetDevice(d.id));
     begin_call(d);
-    if (n) H2B_LAUNCH(d, "synth_bases", synth_bases_kernel, (unsigned)((n + 127) / 128), 128, 0, (Affine*)d_out, (uint64_t)n, t0);
+    if (n) H2B_LAUNCH(d, "synth_bases", MK.synth_bases, (unsigned)((n + 127) / 128), 128, 0, (Affine*)d_out, (uint64_t)n, t0);
     H2B_CK(cudaGetLastError());
     return end_call(ctx, d);
 }
@@ -1039,7 +1041,7 @@ int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_
     float ms = 0.f;
     for (int rep = 0; rep < 3; rep++) {   // warm-up + 2 timed; keep the last
         H2B_CK(cudaEventRecord(a, d.stream));
-        imad_wide_peak_kernel<<<blocks, threads, 0, d.stream>>>(12345u + rep, it1, (unsigned long long*)d.m_counters.p);
+        MK.imad_wide_peak<<<blocks, threads, 0, d.stream>>>(12345u + rep, it1, (unsigned long long*)d.m_counters.p);
         H2B_CK(cudaEventRecord(b, d.stream));
         H2B_CK(cudaStreamSynchronize(d.stream));
         H2B_CK(cudaEventElapsedTime(&ms, a, b));
@@ -1047,7 +1049,7 @@ int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_
     *wide_mads_per_s = (double)blocks * threads * it1 * 8.0 / (ms * 1e-3);   // 8 IMAD.WIDE per iteration
     for (int rep = 0; rep < 3; rep++) {
         H2B_CK(cudaEventRecord(a, d.stream));
-        field_mul_peak_kernel<<<blocks, threads, 0, d.stream>>>(it2, (Fq*)d.m_counters.p);
+        MK.field_mul_peak<<<blocks, threads, 0, d.stream>>>(it2, (Fq*)d.m_counters.p);
         H2B_CK(cudaEventRecord(b, d.stream));
         H2B_CK(cudaStreamSynchronize(d.stream));
         H2B_CK(cudaEventElapsedTime(&ms, a, b));

@@ -104,7 +104,17 @@ inline void msm_finish(const Xyzz* windows, uint32_t nw, uint32_t c, void* out96
         for (int l = 0; l < 8; l++) reinterpret_cast<uint32_t*>(out96)[i * 8 + l] = out[i].l[l];
 }
 
-#if defined(__CUDACC__)
+// launch geometry constants and small records shared by the kernels (msm_kernels.cu) and the host orchestration
+constexpr int SCAN_BLOCK = 1024;
+constexpr uint32_t MSM_SIZE_BINS = 4096;
+constexpr int MSM_LONG_THREADS = 128;
+constexpr uint32_t MSM_LONG_CHUNK = 4096;
+struct MsmLongInfo { uint32_t key, task_base, ntasks, pad; };
+struct MsmLongTask { uint32_t key, chunk; };
+constexpr int MSM_REDUCE_THREADS = 128;
+constexpr int MSM_REDUCE_MAX_SLICES = 256;
+
+#if defined(__CUDACC__) && !defined(H2B_NO_KERNELS)
 // ------------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------------
@@ -138,7 +148,6 @@ __global__ void msm_scatter_kernel(MsmGeom g, const Fr* __restrict__ scalars, ui
 }
 
 // ---- exclusive scan over uint32 (three small kernels; sizes up to a few million) ----------------
-constexpr int SCAN_BLOCK = 1024;
 __global__ void scan_block_sums_kernel(const uint32_t* __restrict__ in, uint32_t n, uint32_t* __restrict__ block_sums) {
     __shared__ uint32_t sh[32];
     uint32_t i = blockIdx.x * SCAN_BLOCK + threadIdx.x;
@@ -220,7 +229,6 @@ msm_precompute_kernel(const Affine* __restrict__ in, Affine* __restrict__ out, u
 }
 
 // ---- 4. order buckets by population (descending), and list the oversized ones --------------------
-constexpr uint32_t MSM_SIZE_BINS = 4096;
 // size_hist[MSM_SIZE_BINS]: bin = min(size, BINS-1); stored reversed so that an ascending scan gives descending size
 __global__ void msm_size_hist_kernel(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends, uint32_t nkeys,
                                      uint32_t* __restrict__ size_hist) {
@@ -292,11 +300,6 @@ msm_accumulate_kernel(const Affine* __restrict__ bases, const uint32_t* __restri
 // Oversized buckets (skewed scalars: selector-like columns put most points into one bucket) are cut into
 // chunks of MSM_LONG_CHUNK entries; one block per chunk strides over its entries and tree-reduces through
 // shared memory; a second kernel sums the chunk partials of each oversized bucket.
-constexpr int MSM_LONG_THREADS = 128;
-constexpr uint32_t MSM_LONG_CHUNK = 4096;
-struct MsmLongInfo { uint32_t key, task_base, ntasks, pad; };
-struct MsmLongTask { uint32_t key, chunk; };
-
 __global__ void msm_long_list_kernel(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends, uint32_t nkeys,
                                      uint32_t long_threshold, MsmLongInfo* __restrict__ long_info,
                                      MsmLongTask* __restrict__ tasks, uint32_t* __restrict__ counters /* [0]=#long, [1]=#tasks */) {
@@ -367,9 +370,6 @@ msm_long_combine_kernel(const MsmLongInfo* __restrict__ long_info, const uint32_
 //            R = sum_t run_t.  Emits P = A + L * T (weights relative to the block's first bucket) and R.
 //   level 2  one block per set over the `slices` (<= 256) block results:
 //            sum_b P_b + (128 * L) * sum_b b * R_b      (same suffix-scan trick).
-constexpr int MSM_REDUCE_THREADS = 128;
-constexpr int MSM_REDUCE_MAX_SLICES = 256;
-
 // block-wide helpers on a shared array of n (power of two) points
 template <int N>
 H2B_D void block_suffix_scan(Xyzz* sh, uint32_t t) {       // sh[t] <- sum_{u >= t} sh[u]
@@ -445,6 +445,6 @@ __global__ void msm_reduce_small_kernel(MsmGeom g, const Xyzz* __restrict__ buck
     if (j >= g.windows) return;
     xyzz_store(window_partials + j, msm_reduce_chunk(buckets + (size_t)j * g.nb, g.nb, 1));
 }
-#endif  // __CUDACC__
+#endif  // __CUDACC__ && !H2B_NO_KERNELS
 
 }  // namespace h2b
