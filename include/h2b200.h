@@ -127,6 +127,27 @@ int h2b_coeff_to_extended_batch(h2b_ctx* ctx, const void* const* in_cols, void* 
                                 uint32_t k, uint32_t ext_k, const void* ext_omega32, const void* g_coset32,
                                 const void* g_coset_inv32);
 
+/* ---- polynomial helpers between the accelerated steps ------------------------------------
+ * The serial O(n) loops of create_proof that sit between MSM and NTT calls, as tiled prefix computations.
+ * Elements are 32-byte Montgomery Fr.  *_device variants take device-0 pointers and leave results on the device.
+ *
+ * h2b_batch_invert   = ff::BatchInvert over a slice (permutation/prover.rs:124, lookup/prover.rs:225,
+ *                      shuffle/prover.rs:150): a[i] <- 1 / a[i] in place; zeros are left untouched.
+ * h2b_grand_product  = the running products of the Z polynomials (permutation/prover.rs:160-166,
+ *                      lookup/prover.rs:254-259, shuffle/prover.rs:161-166): z[0] = init, z[i] = z[i-1] * v[i-1],
+ *                      for i < out_len (out_len <= n + 1).  z may alias v.
+ * h2b_eval_polynomial = arithmetic.rs:56-82 eval_polynomial: out = sum_i poly[i] * point^i  (n = 0 -> 0).
+ * h2b_kate_division  = arithmetic.rs:99-120 kate_division: q (n - 1 entries) = a(X) / (X - b), remainder dropped;
+ *                      n = 0 is an error (the reference panics on `a.len() - 1`). */
+int h2b_batch_invert(h2b_ctx* ctx, void* a, size_t n);
+int h2b_batch_invert_device(h2b_ctx* ctx, void* d_a, size_t n);
+int h2b_grand_product(h2b_ctx* ctx, const void* v, size_t n, const void* init32, void* z, size_t out_len);
+int h2b_grand_product_device(h2b_ctx* ctx, const void* d_v, size_t n, const void* init32, void* d_z, size_t out_len);
+int h2b_eval_polynomial(h2b_ctx* ctx, const void* poly, size_t n, const void* point32, void* out32);
+int h2b_eval_polynomial_device(h2b_ctx* ctx, const void* d_poly, size_t n, const void* point32, void* out32);
+int h2b_kate_division(h2b_ctx* ctx, const void* a, size_t n, const void* b32, void* q);
+int h2b_kate_division_device(h2b_ctx* ctx, const void* d_a, size_t n, const void* b32, void* d_q);
+
 /* ---- measurement hooks (bench.py / profiles) -----------------------------------------------------------
  * h2b_last_call_ms: device time of the most recent call on this context, CUDA events on the launching
  *                   stream from the first to the last enqueued operation (copies included if the call copied).

@@ -47,6 +47,10 @@ def lib():
             "h2ref_coeff_to_extended": [vp, vp, u32, u32, vp, vp, vp],
             "h2ref_extended_to_coeff": [vp, u32, vp, vp, vp, vp],
             "h2ref_divide_by_vanishing_poly": [vp, sz, vp, sz],
+            "h2ref_eval_polynomial": [vp, sz, vp, vp],
+            "h2ref_kate_division": [vp, sz, vp, vp],
+            "h2ref_batch_invert": [vp, sz],
+            "h2ref_grand_product": [vp, sz, vp, vp, sz],
             "h2ref_fr_mul": [vp, vp, vp], "h2ref_fq_mul": [vp, vp, vp],
             "h2ref_fr_add": [vp, vp, vp], "h2ref_fr_sub": [vp, vp, vp], "h2ref_fr_inv": [vp, vp],
             "h2ref_random_fr": [vp, sz, u64],
@@ -148,6 +152,39 @@ def divide_by_vanishing_poly(a, t_evals) -> np.ndarray:
     t = np.ascontiguousarray(t_evals)
     lib().h2ref_divide_by_vanishing_poly(_p(a), a.shape[0], _p(t), t.shape[0])
     return a
+
+
+def eval_polynomial(poly: np.ndarray, point: np.ndarray) -> np.ndarray:
+    """arithmetic.rs:56-82; point and result are 4-limb Montgomery Fr."""
+    poly = np.ascontiguousarray(poly, dtype=np.uint64)
+    out = np.zeros(4, dtype=np.uint64)
+    lib().h2ref_eval_polynomial(_p(poly), poly.shape[0], _p(np.ascontiguousarray(point, dtype=np.uint64)), _p(out))
+    return out
+
+
+def kate_division(a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    """arithmetic.rs:99-120; returns len(a) - 1 coefficients."""
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    assert a.shape[0] >= 1
+    q = np.zeros((a.shape[0] - 1, 4), dtype=np.uint64)
+    scratch = q if a.shape[0] > 1 else np.zeros((1, 4), dtype=np.uint64)
+    lib().h2ref_kate_division(_p(a), a.shape[0], _p(np.ascontiguousarray(b, dtype=np.uint64)), _p(scratch))
+    return q
+
+
+def batch_invert(a: np.ndarray) -> np.ndarray:
+    """ff::BatchInvert on a copy: non-zero elements inverted, zeros untouched."""
+    a = np.array(a, dtype=np.uint64, copy=True, order="C")
+    lib().h2ref_batch_invert(_p(a), a.shape[0])
+    return a
+
+
+def grand_product(v: np.ndarray, init: np.ndarray, out_len: int) -> np.ndarray:
+    """z[0] = init, z[i] = z[i-1] * v[i-1] (permutation/prover.rs:160-166 and the lookup / shuffle analogues)."""
+    v = np.ascontiguousarray(v, dtype=np.uint64)
+    z = np.zeros((out_len, 4), dtype=np.uint64)
+    lib().h2ref_grand_product(_p(v), v.shape[0], _p(np.ascontiguousarray(init, dtype=np.uint64)), _p(z), out_len)
+    return z
 
 
 def kzg_setup(k: int, s: np.ndarray, omega: np.ndarray):

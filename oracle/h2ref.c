@@ -452,6 +452,49 @@ void h2ref_divide_by_vanishing_poly(void *a_, size_t len, const void *t_evals_, 
     for (long i = 0; i < (long)len; i++) fe_mul(&a[i], &a[i], &t[(size_t)i % e], &FR);
 }
 
+/* ------------------------------------------------------------------ O(n) polynomial helpers */
+/* arithmetic.rs:56-82 eval_polynomial: the reference folds Horner per thread chunk and recombines with point^start; the value
+ * is the same field element for every chunking, so the restatement is the plain fold of :58-60. */
+void h2ref_eval_polynomial(const void *poly_, size_t n, const void *point_, void *out32) {
+    const fe *poly = (const fe *)poly_; fe x, acc; memcpy(&x, point_, 32);
+    memset(&acc, 0, sizeof acc);
+    for (size_t i = n; i-- > 0;) { fe_mul(&acc, &acc, &x, &FR); fe_add(&acc, &acc, &poly[i], &FR); }
+    memcpy(out32, &acc, 32);
+}
+/* arithmetic.rs:99-120 kate_division: q has n - 1 entries */
+void h2ref_kate_division(const void *a_, size_t n, const void *b_, void *q_) {
+    const fe *a = (const fe *)a_; fe *q = (fe *)q_; fe b, nb, tmp, lead;
+    memcpy(&b, b_, 32);
+    fe_neg(&nb, &b, &FR);                              /* b = -b            (:103) */
+    memset(&tmp, 0, sizeof tmp);
+    for (size_t i = n - 1; i >= 1; i--) {             /* q.rev() zip a.rev() (:109): q[i-1] pairs with a[i] */
+        fe_sub(&lead, &a[i], &tmp, &FR);              /* lead_coeff = r - tmp */
+        q[i - 1] = lead;
+        fe_mul(&tmp, &lead, &nb, &FR);                /* tmp = lead_coeff * b */
+    }
+}
+/* ff::BatchInvert (ff 0.13 batch.rs): prefix products skipping zeros, one inversion, back-substitution; zeros untouched */
+void h2ref_batch_invert(void *a_, size_t n) {
+    fe *a = (fe *)a_;
+    fe *pre = (fe *)malloc(sizeof(fe) * (n ? n : 1));
+    fe acc = FR.r;                                     /* one */
+    for (size_t i = 0; i < n; i++) { pre[i] = acc; if (!fe_is_zero(&a[i])) fe_mul(&acc, &acc, &a[i], &FR); }
+    fe inv; fe_inv(&inv, &acc, &FR);
+    for (size_t i = n; i-- > 0;) {
+        if (fe_is_zero(&a[i])) continue;
+        fe t; fe_mul(&t, &inv, &pre[i], &FR);
+        fe_mul(&inv, &inv, &a[i], &FR);
+        a[i] = t;
+    }
+    free(pre);
+}
+/* the Z-polynomial running product: permutation/prover.rs:160-166 (z[0] = last_z; z[row] = z[row-1] * v[row-1]),
+ * lookup/prover.rs:254-259 and shuffle/prover.rs:161-166 (once(ONE).chain(product).scan(ONE, *)) */
+void h2ref_grand_product(const void *v_, size_t n, const void *init_, void *z_, size_t out_len) {
+    const fe *v = (const fe *)v_; fe *z = (fe *)z_; fe acc; memcpy(&acc, init_, 32);
+    for (size_t i = 0; i < out_len; i++) { z[i] = acc; if (i < n) fe_mul(&acc, &acc, &v[i], &FR); }
+}
+
 /* ------------------------------------------------------------------ scalar helpers for the python side */
 void h2ref_fr_mul(const void *a, const void *b, void *o) { fe x, y, z; memcpy(&x, a, 32); memcpy(&y, b, 32); fe_mul(&z, &x, &y, &FR); memcpy(o, &z, 32); }
 void h2ref_fq_mul(const void *a, const void *b, void *o) { fe x, y, z; memcpy(&x, a, 32); memcpy(&y, b, 32); fe_mul(&z, &x, &y, &FQ); memcpy(o, &z, 32); }

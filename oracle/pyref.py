@@ -326,6 +326,33 @@ def eval_polynomial(poly, point):
     return acc
 
 
+def kate_division(a, b):
+    """arithmetic.rs:99-120: a(X) / (X - b), remainder dropped (python ints)."""
+    b = (-b) % R_MOD
+    q = [0] * (len(a) - 1)
+    tmp = 0
+    for i in range(len(a) - 1, 0, -1):
+        lead = (a[i] - tmp) % R_MOD
+        q[i - 1] = lead
+        tmp = lead * b % R_MOD
+    return q
+
+
+def batch_invert(a):
+    """ff::BatchInvert semantics: zeros stay zero."""
+    return [fr_inv(x) if x % R_MOD else 0 for x in a]
+
+
+def grand_product(v, init, out_len):
+    """z[0] = init, z[i] = z[i-1] * v[i-1]  (permutation/prover.rs:160-166)."""
+    z, acc = [], init % R_MOD
+    for i in range(out_len):
+        z.append(acc)
+        if i < len(v):
+            acc = acc * v[i] % R_MOD
+    return z
+
+
 # ---------------------------------------------------------------------------------------------
 # KZG SRS with a known secret: kzg/commitment.rs:64-131
 # ---------------------------------------------------------------------------------------------

@@ -55,6 +55,10 @@ def test_field_ops(hc):
         hc.hc_fr_from_mont(p(A), p(o)); assert C.int_from_limbs(o) == a * pow(1 << 256, -1, R.R_MOD) % R.R_MOD
         hc.hc_fr_to_mont(p(A), p(o)); assert C.int_from_limbs(o) == (a << 256) % R.R_MOD
         hc.hc_fr_inv(p(m(a)), p(o)); assert C.int_from_mont(o, R.R_MOD) == (pow(a, -1, R.R_MOD) if a else 0)
+        # the windowed Fermat inversion the batch-inversion kernel uses (poly.cuh)
+        hc.hc_fr_inv_window(p(m(a)), p(o)); assert C.int_from_mont(o, R.R_MOD) == (pow(a, -1, R.R_MOD) if a else 0)
+        aq = a % R.Q_MOD
+        hc.hc_fq_inv_window(p(C.mont_from_int(aq, R.Q_MOD)), p(o)); assert C.int_from_mont(o, R.Q_MOD) == (pow(aq, -1, R.Q_MOD) if aq else 0)
 
 
 def test_curve_ops(hc):

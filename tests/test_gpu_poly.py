@@ -1,0 +1,122 @@
+"""GPU parity of the polynomial helpers (eval_polynomial, kate_division, batch inversion, grand products)
+through the C ABI / PolyOps mirror against the CPU oracle.  Bit-exact: every output limb must be equal."""
+import numpy as np
+import pytest
+
+from oracle import cref as C
+from oracle import pyref as R
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [1, 2, 7, 8, 9, 255, 256, 257, 2047, 2048, 2049, 4096 + 5, (1 << 16) + 3, 1 << 19, (1 << 19) + 4097]
+
+
+def m(x):
+    return C.mont_from_int(x, R.R_MOD)
+
+
+@pytest.fixture(scope="module")
+def ops(ctx):
+    import h2b200
+    return h2b200.PolyOps(ctx)
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_eval_polynomial(ops, n):
+    a = C.random_fr(n, 10 + n)
+    for pt in (0, 1, R.R_MOD - 1, 0x1234567890ABCDEF1234567890ABCDEF % R.R_MOD):
+        exp = C.int_from_mont(C.eval_polynomial(a, m(pt)), R.R_MOD)
+        assert ops.eval_polynomial(a, pt) == exp, (n, pt)
+
+
+def test_eval_polynomial_empty_and_pyref(ops):
+    assert ops.eval_polynomial(np.zeros((0, 4), dtype=np.uint64), 5) == 0
+    a = C.random_fr(300, 3)
+    assert ops.eval_polynomial(a, 77) == R.eval_polynomial(C.ints_from_fr_array(a, R.R_MOD), 77)
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_kate_division(ops, n):
+    a = C.random_fr(n, 20 + n)
+    for b in (0, 1, 0xDEADBEEFCAFEBABE1234 % R.R_MOD):
+        got = ops.kate_division(a, b)
+        assert got.shape[0] == n - 1
+        assert np.array_equal(got, C.kate_division(a, m(b))), (n, b)
+
+
+def test_kate_division_is_exact_division(ops):
+    """(X - b) * q + a(b) == a : the identity the SHPLONK / GWC openers rely on (shplonk/prover.rs, gwc/prover.rs)."""
+    n, b = 1000, 987654321
+    a = C.random_fr(n, 5)
+    ai = C.ints_from_fr_array(a, R.R_MOD)
+    q = C.ints_from_fr_array(ops.kate_division(a, b), R.R_MOD)
+    rem = ops.eval_polynomial(a, b)
+    rec = [0] * n
+    for i, c in enumerate(q):
+        rec[i + 1] = (rec[i + 1] + c) % R.R_MOD
+        rec[i] = (rec[i] - b * c) % R.R_MOD
+    rec[0] = (rec[0] + rem) % R.R_MOD
+    assert rec == ai
+    with pytest.raises(AssertionError):
+        ops.kate_division(np.zeros((0, 4), dtype=np.uint64), 1)
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_batch_invert(ops, n):
+    a = C.random_fr(n, 30 + n)
+    a[:: 5] = 0                      # ff::BatchInvert leaves zeros untouched
+    if n > 3:
+        a[3] = m(1)
+    got = ops.batch_invert(a.copy())
+    assert np.array_equal(got, C.batch_invert(a)), n
+
+
+def test_batch_invert_all_zero_and_involution(ops):
+    z = np.zeros((5000, 4), dtype=np.uint64)
+    assert not ops.batch_invert(z.copy()).any()
+    a = C.random_fr(70000, 4)
+    assert np.array_equal(ops.batch_invert(ops.batch_invert(a.copy())), a)
+
+
+@pytest.mark.parametrize("n", SIZES)
+def test_grand_product(ops, n):
+    v = C.random_fr(n, 40 + n)
+    for init, out_len in ((1, n), (12345, n + 1), (R.R_MOD - 1, max(n - 6, 0))):
+        got = ops.grand_product(v, init, out_len)
+        assert np.array_equal(got, C.grand_product(v, m(init), out_len)), (n, init, out_len)
+
+
+def test_grand_product_with_zero_and_empty(ops):
+    v = C.random_fr(5000, 8)
+    v[2500] = 0
+    got = ops.grand_product(v, 1, 5001)
+    assert np.array_equal(got, C.grand_product(v, m(1), 5001))
+    assert not got[2501:].any()
+    assert np.array_equal(ops.grand_product(np.zeros((0, 4), dtype=np.uint64), 9, 1), m(9).reshape(1, 4))
+
+
+def test_device_resident_variants(ops):
+    """torch CUDA tensors in, results stay on the device (the *_device entry points)."""
+    import torch
+    n = (1 << 17) + 11
+    a = C.random_fr(n, 77)
+    d = torch.from_numpy(a.view(np.int64)).cuda()
+    assert ops.eval_polynomial(d, 4242) == C.int_from_mont(C.eval_polynomial(a, m(4242)), R.R_MOD)
+    q = ops.kate_division(d, 4242)
+    assert np.array_equal(q.cpu().numpy().view(np.uint64), C.kate_division(a, m(4242)))
+    z = ops.grand_product(d, 3, n)
+    assert np.array_equal(z.cpu().numpy().view(np.uint64), C.grand_product(a, m(3), n))
+    inv = ops.batch_invert(d.clone())
+    assert np.array_equal(inv.cpu().numpy().view(np.uint64), C.batch_invert(a))
+
+
+def test_permutation_product_shape(ops):
+    """The sequence of permutation/prover.rs:118-166 on the GPU: denominators -> batch_invert -> numerators -> running product."""
+    n = 1 << 12
+    num, den = C.random_fr(n, 1), C.random_fr(n, 2)
+    inv = ops.batch_invert(den.copy())
+    frac = np.stack([C.fr_mul(num[i], inv[i]) for i in range(n)])
+    z = ops.grand_product(frac, 1, n)
+    ni, di = C.ints_from_fr_array(num, R.R_MOD), C.ints_from_fr_array(den, R.R_MOD)
+    exp = R.grand_product([a * pow(b, -1, R.R_MOD) % R.R_MOD for a, b in zip(ni, di)], 1, n)
+    assert C.ints_from_fr_array(z, R.R_MOD) == exp

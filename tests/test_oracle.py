@@ -177,3 +177,28 @@ def test_coset_extension_is_evaluation(j, k):
     for i in range(len(d.t_evaluations)):
         x = R.FR_ZETA * pow(d.extended_omega, i, R.R_MOD) % R.R_MOD
         assert d.t_evaluations[i] * (pow(x, 1 << k, R.R_MOD) - 1) % R.R_MOD == 1
+
+
+def test_poly_helpers_c_port_matches_python():
+    """SURVEY.md 8f N3 helpers: the C restatement (arithmetic.rs:56-120, ff::BatchInvert, the Z running products) against
+    python big ints, including the reference's own identity for kate_division: (X - b) q + a(b) = a."""
+    for n in (1, 2, 5, 64, 257):
+        a = C.random_fr(n, 900 + n)
+        ai = C.ints_from_fr_array(a, R.R_MOD)
+        for b in (0, 1, 5, R.R_MOD - 1, 0xABCDEF0123456789):
+            bm = C.mont_from_int(b, R.R_MOD)
+            assert C.int_from_mont(C.eval_polynomial(a, bm), R.R_MOD) == R.eval_polynomial(ai, b)
+            q = C.ints_from_fr_array(C.kate_division(a, bm), R.R_MOD)
+            assert q == R.kate_division(ai, b)
+            rec = [0] * n
+            for i, c in enumerate(q):
+                rec[i + 1] = (rec[i + 1] + c) % R.R_MOD
+                rec[i] = (rec[i] - b * c) % R.R_MOD
+            rec[0] = (rec[0] + R.eval_polynomial(ai, b)) % R.R_MOD
+            assert rec == ai
+        z = a.copy()
+        z[::3] = 0
+        assert C.ints_from_fr_array(C.batch_invert(z), R.R_MOD) == R.batch_invert(C.ints_from_fr_array(z, R.R_MOD))
+        for init, out_len in ((1, n), (7, n + 1), (3, max(n - 1, 0))):
+            got = C.ints_from_fr_array(C.grand_product(a, C.mont_from_int(init, R.R_MOD), out_len), R.R_MOD) if out_len else []
+            assert got == R.grand_product(ai, init, out_len)

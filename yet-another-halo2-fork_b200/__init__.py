@@ -5,10 +5,11 @@ if it is missing or no sm_100 device is present (there is no CPU fallback).
 """
 from . import fields, synth
 from ._lib import H2bError, LIB_PATH, SYMBOLS, load
+from .arithmetic import PolyOps
 from .domain import EvaluationDomain
 from .engine import (B200Engine, BaseDescriptor, CoeffsDescriptor, Context, PlonkEngine, PlonkEngineConfig, shard_range,
                      window_bits)
 from .kzg import ParamsKZG
 
 __all__ = ["fields", "synth", "H2bError", "LIB_PATH", "SYMBOLS", "load", "EvaluationDomain", "B200Engine", "BaseDescriptor",
-           "CoeffsDescriptor", "Context", "PlonkEngine", "PlonkEngineConfig", "ParamsKZG", "shard_range", "window_bits"]
+           "CoeffsDescriptor", "Context", "PlonkEngine", "PlonkEngineConfig", "ParamsKZG", "PolyOps", "shard_range", "window_bits"]

@@ -18,6 +18,7 @@
 #define H2B_NO_KERNELS 1      // kernels live in msm_kernels.cu / ntt_kernels_*.cu; this unit is host orchestration only
 #include "msm.cuh"
 #include "msm_kernels.hpp"
+#include "poly_kernels.hpp"
 #include "ntt.cuh"
 #include "ntt_plan.hpp"
 #include "ntt_kernels.hpp"
@@ -78,6 +79,7 @@ struct Dev {
     DevBuf ntt_a, ntt_b, ntt_tab;
     MsmSortSet ms[2];
     DevBuf m_scalars, m_buckets, m_wpart, m_long_partials, m_counters, m_tmp_bases;
+    DevBuf p_in, p_out, p_tiles;                  // polynomial helpers (poly.cuh): staged operands and per-tile summaries
     void* pinned = nullptr;
     size_t pinned_cap = 0;
     std::map<std::string, NttPlanDev> plans;
@@ -586,6 +588,46 @@ void release_bases(h2b_ctx* ctx, Bases& B) {
         }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// polynomial helpers (poly.cuh): three-phase tiled scans
+// ------------------------------------------------------------------------------------------------
+const PolyKernelTable& PK = poly_kernel_table();
+
+inline uint32_t poly_tiles(uint64_t n) { return (uint32_t)((n + POLY_TILE - 1) / POLY_TILE); }
+
+// z[i] = init * prod_{j < i} v[j], i < out_len (out_len <= n + 1); z may alias v
+int poly_grand_product_enqueue(h2b_ctx* ctx, Dev& d, const Fr* v, uint64_t n, const Fr& init, Fr* z, uint64_t out_len) {
+    if (out_len == 0) return H2B_OK;
+    const uint32_t tiles = poly_tiles(out_len);
+    H2B_CK(d.p_tiles.reserve((size_t)tiles * 32 + 64));
+    Fr* tt = d.p_tiles.as<Fr>();
+    H2B_LAUNCH(d, "poly_grand_product", PK.prod_tile_reduce, tiles, POLY_T, 0, v, n, tt);
+    H2B_LAUNCH(d, "poly_grand_product", PK.prod_scan_totals, 1, POLY_T, 0, tt, tiles, init);
+    H2B_LAUNCH(d, "poly_grand_product", PK.prod_tile_scan, tiles, POLY_T, 0, v, n, (const Fr*)tt, z, out_len);
+    H2B_CK(cudaGetLastError());
+    return H2B_OK;
+}
+int poly_batch_invert_enqueue(h2b_ctx* ctx, Dev& d, Fr* a, uint64_t n) {
+    if (n == 0) return H2B_OK;
+    H2B_LAUNCH(d, "poly_batch_invert", PK.batch_invert, poly_tiles(n), POLY_T, 0, a, n);
+    H2B_CK(cudaGetLastError());
+    return H2B_OK;
+}
+// Horner machinery: q (n - 1 entries) = a / (X - b) when q != nullptr; *d_final = sum a_i b^i when d_final != nullptr
+int poly_horner_enqueue(h2b_ctx* ctx, Dev& d, const Fr* a, uint64_t n, const Fr& b, Fr* q, Fr* d_final) {
+    const uint32_t tiles = poly_tiles(n);
+    const uint64_t pad = (uint64_t)tiles * POLY_TILE - n;
+    H2B_CK(d.p_tiles.reserve((size_t)tiles * 32 + 64));
+    Fr* tv = d.p_tiles.as<Fr>();
+    Fr bk = fe_pow_u64(b, (uint64_t)POLY_K), bt = fe_pow_u64(b, (uint64_t)POLY_TILE);
+    H2B_LAUNCH(d, "poly_horner", PK.horner_tile_reduce, tiles, POLY_T, 0, a, n, pad, b, bk, tv);
+    H2B_LAUNCH(d, "poly_horner", PK.horner_scan_totals, 1, POLY_T, 0, tv, tiles, bt, d_final);
+    if (q) H2B_LAUNCH(d, "poly_horner", PK.horner_tile_scan, tiles, POLY_T, 0, a, n, pad, b, bk, (const Fr*)tv, q);
+    H2B_CK(cudaGetLastError());
+    return H2B_OK;
+}
+
 }  // namespace
 
 // ================================================================================================
@@ -657,7 +699,7 @@ void h2b_destroy(h2b_ctx* ctx) {
         for (auto& kv : d.plans) cudaFree(kv.second.tables);
         cudaStreamSynchronize(d.sort_stream);
         DevBuf* bufs[] = {&d.ntt_a, &d.ntt_b, &d.ntt_tab, &d.m_scalars, &d.m_buckets, &d.m_wpart, &d.m_long_partials, &d.m_counters,
-                          &d.m_tmp_bases};
+                          &d.m_tmp_bases, &d.p_in, &d.p_out, &d.p_tiles};
         for (DevBuf* b : bufs) b->release();
         d.ms[0].release(); d.ms[1].release();
         if (d.pinned) cudaFreeHost(d.pinned);
@@ -966,6 +1008,100 @@ int h2b_coeff_to_extended_batch(h2b_ctx* ctx, const void* const* in_cols, void* 
     fz.in_len = (uint64_t)1 << k;
     fz.in_pat = pat;
     return batch_impl(ctx, in_cols, out_cols, n_cols, k, ext_k, omega, nullptr, fz);
+}
+
+// ---- polynomial helpers -----------------------------------------------------------
+static int batch_invert_impl(h2b_ctx* ctx, void* a, size_t n, bool on_device) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!a && n) return ctx->fail(H2B_E_INVALID, "batch_invert: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    begin_call(d);
+    Fr* buf = (Fr*)a;
+    if (!on_device && n) {
+        H2B_CK(d.p_in.reserve(n * 32));
+        buf = d.p_in.as<Fr>();
+        H2B_CK(cudaMemcpyAsync(buf, a, n * 32, cudaMemcpyHostToDevice, d.stream));
+    }
+    int rc = poly_batch_invert_enqueue(ctx, d, buf, n);
+    if (rc) return rc;
+    if (!on_device && n) H2B_CK(cudaMemcpyAsync(a, buf, n * 32, cudaMemcpyDeviceToHost, d.stream));
+    return end_call(ctx, d);
+}
+int h2b_batch_invert(h2b_ctx* ctx, void* a, size_t n) { return batch_invert_impl(ctx, a, n, false); }
+int h2b_batch_invert_device(h2b_ctx* ctx, void* d_a, size_t n) { return batch_invert_impl(ctx, d_a, n, true); }
+
+static int grand_product_impl(h2b_ctx* ctx, const void* v, size_t n, const void* init32, void* z, size_t out_len, bool on_device) {
+    if (!ctx) return H2B_E_INVALID;
+    if ((!v && n) || !init32 || (!z && out_len)) return ctx->fail(H2B_E_INVALID, "grand_product: null argument");
+    if (out_len > n + 1) return ctx->fail(H2B_E_INVALID, "grand_product: out_len exceeds n + 1");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    begin_call(d);
+    Fr init = fr_from_bytes(init32);
+    const Fr* src = (const Fr*)v;
+    Fr* dst = (Fr*)z;
+    if (!on_device) {
+        H2B_CK(d.p_in.reserve(std::max<size_t>(n, 1) * 32));
+        H2B_CK(d.p_out.reserve(std::max<size_t>(out_len, 1) * 32));
+        if (n) H2B_CK(cudaMemcpyAsync(d.p_in.p, v, n * 32, cudaMemcpyHostToDevice, d.stream));
+        src = d.p_in.as<Fr>(); dst = d.p_out.as<Fr>();
+    }
+    int rc = poly_grand_product_enqueue(ctx, d, src, n, init, dst, out_len);
+    if (rc) return rc;
+    if (!on_device && out_len) H2B_CK(cudaMemcpyAsync(z, dst, out_len * 32, cudaMemcpyDeviceToHost, d.stream));
+    return end_call(ctx, d);
+}
+int h2b_grand_product(h2b_ctx* ctx, const void* v, size_t n, const void* init32, void* z, size_t out_len) {
+    return grand_product_impl(ctx, v, n, init32, z, out_len, false);
+}
+int h2b_grand_product_device(h2b_ctx* ctx, const void* d_v, size_t n, const void* init32, void* d_z, size_t out_len) {
+    return grand_product_impl(ctx, d_v, n, init32, d_z, out_len, true);
+}
+
+static int horner_impl(h2b_ctx* ctx, const void* a, size_t n, const void* b32, void* q, void* out32, bool on_device, const char* what) {
+    if (!ctx) return H2B_E_INVALID;
+    if ((!a && n) || !b32 || (!q && !out32)) return ctx->fail(H2B_E_INVALID, std::string(what) + ": null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (q && n == 0) return ctx->fail(H2B_E_INVALID, "kate_division: empty polynomial (the reference panics on a.len() - 1)");
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    if (n == 0) { std::memset(out32, 0, 32); ctx->last_ms = 0; return H2B_OK; }          // empty sum
+    begin_call(d);
+    Fr b = fr_from_bytes(b32);
+    const Fr* src = (const Fr*)a;
+    Fr* dq = (Fr*)q;
+    H2B_CK(d.m_counters.reserve(256));
+    if (!on_device) {
+        H2B_CK(d.p_in.reserve(n * 32));
+        H2B_CK(cudaMemcpyAsync(d.p_in.p, a, n * 32, cudaMemcpyHostToDevice, d.stream));
+        src = d.p_in.as<Fr>();
+        if (q) { H2B_CK(d.p_out.reserve(std::max<size_t>(n - 1, 1) * 32)); dq = d.p_out.as<Fr>(); }
+    }
+    Fr* d_final = out32 ? d.m_counters.as<Fr>() : nullptr;
+    int rc = poly_horner_enqueue(ctx, d, src, n, b, q ? dq : nullptr, d_final);
+    if (rc) return rc;
+    if (!on_device && q && n > 1) H2B_CK(cudaMemcpyAsync(q, dq, (n - 1) * 32, cudaMemcpyDeviceToHost, d.stream));
+    if (out32) H2B_CK(cudaMemcpyAsync(out32, d_final, 32, cudaMemcpyDeviceToHost, d.stream));
+    return end_call(ctx, d);
+}
+int h2b_eval_polynomial(h2b_ctx* ctx, const void* poly, size_t n, const void* point32, void* out32) {
+    if (ctx && !out32) return ctx->fail(H2B_E_INVALID, "eval_polynomial: null argument");
+    return horner_impl(ctx, poly, n, point32, nullptr, out32, false, "eval_polynomial");
+}
+int h2b_eval_polynomial_device(h2b_ctx* ctx, const void* d_poly, size_t n, const void* point32, void* out32) {
+    if (ctx && !out32) return ctx->fail(H2B_E_INVALID, "eval_polynomial: null argument");
+    return horner_impl(ctx, d_poly, n, point32, nullptr, out32, true, "eval_polynomial");
+}
+int h2b_kate_division(h2b_ctx* ctx, const void* a, size_t n, const void* b32, void* q) {
+    if (ctx && !q) return ctx->fail(H2B_E_INVALID, "kate_division: null argument");
+    return horner_impl(ctx, a, n, b32, q, nullptr, false, "kate_division");
+}
+int h2b_kate_division_device(h2b_ctx* ctx, const void* d_a, size_t n, const void* b32, void* d_q) {
+    if (ctx && !d_q) return ctx->fail(H2B_E_INVALID, "kate_division: null argument");
+    return horner_impl(ctx, d_a, n, b32, d_q, nullptr, true, "kate_division");
 }
 
 // ---- measurement ---------------------------------------------------------------------------------

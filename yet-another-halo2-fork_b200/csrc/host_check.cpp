@@ -4,6 +4,7 @@
 #include <cstring>
 #include "curve.cuh"
 #include "field_wide.cuh"
+#include "poly.cuh"
 using namespace h2b;
 
 template <class F> static F ld(const void* p) { F f; std::memcpy(&f, p, 32); return f; }
@@ -18,6 +19,8 @@ void hc_fq_add(const void* a, const void* b, void* o) { st(o, fe_add(ld<Fq>(a), 
 void hc_fq_sub(const void* a, const void* b, void* o) { st(o, fe_sub(ld<Fq>(a), ld<Fq>(b))); }
 void hc_fr_neg(const void* a, void* o) { st(o, fe_neg(ld<Fr>(a))); }
 void hc_fr_inv(const void* a, void* o) { st(o, fe_inv(ld<Fr>(a))); }
+void hc_fr_inv_window(const void* a, void* o) { st(o, fe_inv_window(ld<Fr>(a))); }
+void hc_fq_inv_window(const void* a, void* o) { st(o, fe_inv_window(ld<Fq>(a))); }
 void hc_fr_from_mont(const void* a, void* o) { st(o, fe_from_mont(ld<Fr>(a))); }
 void hc_fr_to_mont(const void* a, void* o) { st(o, fe_to_mont(ld<Fr>(a))); }
 

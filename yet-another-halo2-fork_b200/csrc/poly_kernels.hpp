@@ -1,0 +1,16 @@
+// poly_kernels.hpp -- entry points of the scan-shaped polynomial kernels (poly.cuh), compiled in poly_kernels.cu.
+#pragma once
+#include "poly.cuh"
+
+namespace h2b {
+struct PolyKernelTable {
+    void (*prod_tile_reduce)(const Fr*, uint64_t, Fr*);
+    void (*prod_scan_totals)(Fr*, uint32_t, Fr);
+    void (*prod_tile_scan)(const Fr*, uint64_t, const Fr*, Fr*, uint64_t);
+    void (*batch_invert)(Fr*, uint64_t);
+    void (*horner_tile_reduce)(const Fr*, uint64_t, uint64_t, Fr, Fr, Fr*);
+    void (*horner_scan_totals)(Fr*, uint32_t, Fr, Fr*);
+    void (*horner_tile_scan)(const Fr*, uint64_t, uint64_t, Fr, Fr, const Fr*, Fr*);
+};
+const PolyKernelTable& poly_kernel_table();
+}  // namespace h2b
