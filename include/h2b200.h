@@ -148,6 +148,52 @@ int h2b_eval_polynomial_device(h2b_ctx* ctx, const void* d_poly, size_t n, const
 int h2b_kate_division(h2b_ctx* ctx, const void* a, size_t n, const void* b32, void* q);
 int h2b_kate_division_device(h2b_ctx* ctx, const void* d_a, size_t n, const void* b32, void* d_q);
 
+/* ---- quotient evaluation: the pointwise part of Evaluator::evaluate_h ----------------------
+ * Everything is device resident (device 0): the inputs are the extended-domain columns coeff_to_extended produced, the
+ * output feeds extended_to_coeff.  size = 2^ext_k rows; rotations are index offsets (idx + rot * 2^(ext_k-k)) mod size
+ * (plonk/evaluation.rs:21-24).
+ *
+ * h2b_graph             = the reference's GraphEvaluator (evaluation.rs:187-196) flattened: `constants`, `rotations`, and
+ *                         the `calculations` as 32-bit words.  A ValueSource (evaluation.rs:26-47) is two words,
+ *                         w0 = kind | rotation_index << 8 and w1 = index, with kind 0 Constant, 1 Intermediate, 2 Fixed,
+ *                         3 Advice, 4 Instance, 5 Challenge, 6 Beta, 7 Gamma, 8 Theta, 9 Y, 10 PreviousValue.  A Calculation
+ *                         (evaluation.rs:101-121) is [op, target, a.w0, a.w1, b.w0, b.w1] with op 0 Add, 1 Sub, 2 Mul,
+ *                         3 Square, 4 Double, 5 Negate, 7 Store, and Horner is [6, target, start.w0, start.w1, factor.w0,
+ *                         factor.w1, n_parts, part.w0, part.w1, ...].
+ * h2b_quotient_graph_device = GraphEvaluator::evaluate (evaluation.rs:789-834) for every row: out[idx] = value of the last
+ *                         calculation (0 if there is none); `d_prev` supplies PreviousValue per row (NULL = zero; may alias d_out).
+ *                         Indices are validated on the host; a malformed program is H2B_E_INVALID.
+ * h2b_quotient_permutation_device = evaluation.rs:397-493 in place on d_values.  d_sets: permutation_product_coset of each set;
+ *                         d_col_values / d_col_perms: the cosets of the permuted columns and pk.permutation.cosets, in
+ *                         p.columns order, cut into sets of chunk_len; delta_start = beta * ZETA, delta = Fr::DELTA,
+ *                         ext_omega = domain.get_extended_omega(); last_rotation = -(blinding_factors + 1).
+ * h2b_quotient_lookup_device = evaluation.rs:517-565 in place (d_table_values = the lookup GraphEvaluator's output).
+ * h2b_quotient_shuffle_device = evaluation.rs:573-620 in place (input / shuffle GraphEvaluator outputs). */
+typedef struct h2b_graph {
+    const uint32_t* program;  size_t n_words;
+    const void* constants32;  size_t n_constants;
+    const int32_t* rotations; size_t n_rotations;
+    uint32_t n_intermediates;
+} h2b_graph;
+int h2b_quotient_graph_device(h2b_ctx* ctx, const h2b_graph* g, const void* const* d_fixed, size_t n_fixed,
+                              const void* const* d_advice, size_t n_advice, const void* const* d_instance, size_t n_instance,
+                              const void* challenges32, size_t n_challenges, const void* beta32, const void* gamma32,
+                              const void* theta32, const void* y32, const void* d_prev_or_null, void* d_out, uint32_t k,
+                              uint32_t ext_k);
+int h2b_quotient_permutation_device(h2b_ctx* ctx, void* d_values, const void* const* d_sets, size_t n_sets,
+                                    const void* const* d_col_values, const void* const* d_col_perms, size_t n_cols,
+                                    size_t chunk_len, const void* d_l0, const void* d_l_last, const void* d_l_active,
+                                    const void* beta32, const void* gamma32, const void* y32, const void* delta_start32,
+                                    const void* delta32, const void* ext_omega32, int32_t last_rotation, uint32_t k,
+                                    uint32_t ext_k);
+int h2b_quotient_lookup_device(h2b_ctx* ctx, void* d_values, const void* d_table_values, const void* d_product,
+                               const void* d_permuted_input, const void* d_permuted_table, const void* d_l0,
+                               const void* d_l_last, const void* d_l_active, const void* beta32, const void* gamma32,
+                               const void* y32, uint32_t k, uint32_t ext_k);
+int h2b_quotient_shuffle_device(h2b_ctx* ctx, void* d_values, const void* d_input_values, const void* d_shuffle_values,
+                                const void* d_product, const void* d_l0, const void* d_l_last, const void* d_l_active,
+                                const void* y32, uint32_t k, uint32_t ext_k);
+
 /* ---- measurement hooks (bench.py / profiles) -----------------------------------------------------------
  * h2b_last_call_ms: device time of the most recent call on this context, CUDA events on the launching
  *                   stream from the first to the last enqueued operation (copies included if the call copied).

@@ -354,6 +354,137 @@ def grand_product(v, init, out_len):
 
 
 # ---------------------------------------------------------------------------------------------
+# quotient evaluation: plonk/evaluation.rs restated on python ints (small domains only)
+# ---------------------------------------------------------------------------------------------
+def get_rotation_idx(idx: int, rot: int, rot_scale: int, isize: int) -> int:
+    """evaluation.rs:21-24."""
+    return (idx + rot * rot_scale) % isize
+
+
+def _value_source(v, rot_idx, constants, inter, fixed, advice, instance, challenges, beta, gamma, theta, y, prev):
+    """ValueSource::get, evaluation.rs:58-96.  v = (kind, ...) with the variant order of evaluation.rs:26-47."""
+    kind = v[0]
+    if kind == 0: return constants[v[1]]
+    if kind == 1: return inter[v[1]]
+    if kind == 2: return fixed[v[1]][rot_idx[v[2]]]
+    if kind == 3: return advice[v[1]][rot_idx[v[2]]]
+    if kind == 4: return instance[v[1]][rot_idx[v[2]]]
+    if kind == 5: return challenges[v[1]]
+    return (beta, gamma, theta, y, prev)[kind - 6]
+
+
+def graph_evaluate(calculations, constants, rotations, fixed, advice, instance, challenges, beta, gamma, theta, y, previous,
+                   size: int, rot_scale: int):
+    """GraphEvaluator::evaluate (evaluation.rs:789-834) for every row; Calculation::evaluate is evaluation.rs:124-172.
+    calculations: [(calc, target)], calc = ("add", a, b) | ("sub", a, b) | ("mul", a, b) | ("square", a) | ("double", a)
+    | ("negate", a) | ("horner", start, parts, factor) | ("store", a).  previous: list or None (zero)."""
+    n_inter = 1 + max([t for _, t in calculations], default=-1)
+    out = []
+    for idx in range(size):
+        rot_idx = [get_rotation_idx(idx, r, rot_scale, size) for r in rotations]
+        inter = [0] * n_inter
+        prev = previous[idx] if previous is not None else 0
+        get = lambda v: _value_source(v, rot_idx, constants, inter, fixed, advice, instance, challenges, beta, gamma, theta, y, prev)
+        for calc, target in calculations:
+            op = calc[0]
+            if op == "add": r = get(calc[1]) + get(calc[2])
+            elif op == "sub": r = get(calc[1]) - get(calc[2])
+            elif op == "mul": r = get(calc[1]) * get(calc[2])
+            elif op == "square": r = get(calc[1]) ** 2
+            elif op == "double": r = 2 * get(calc[1])
+            elif op == "negate": r = -get(calc[1])
+            elif op == "horner":
+                factor, r = get(calc[3]), get(calc[1])
+                for part in calc[2]:
+                    r = (r * factor + get(part)) % R_MOD
+            else: r = get(calc[1])
+            inter[target] = r % R_MOD
+        out.append(inter[calculations[-1][1]] if calculations else 0)
+    return out
+
+
+def evaluate_expression(expr, idx, size, rot_scale, fixed, advice, instance, challenges):
+    """The direct evaluator of an ExpressionBack (evaluation.rs:837-880), used to check the graph compiler."""
+    tag = expr[0]
+    if tag == "const": return expr[1] % R_MOD
+    if tag == "query":
+        cols = {"fixed": fixed, "advice": advice, "instance": instance}[expr[1]]
+        return cols[expr[2]][get_rotation_idx(idx, expr[3], rot_scale, size)]
+    if tag == "challenge": return challenges[expr[1]]
+    ev = lambda e: evaluate_expression(e, idx, size, rot_scale, fixed, advice, instance, challenges)
+    if tag == "neg": return (-ev(expr[1])) % R_MOD
+    if tag == "sum": return (ev(expr[1]) + ev(expr[2])) % R_MOD
+    if tag == "prod": return ev(expr[1]) * ev(expr[2]) % R_MOD
+    raise ValueError(tag)
+
+
+def permutation_fold(values, sets, col_values, col_perms, chunk_len, l0, l_last, l_active, beta, gamma, y, zeta, delta,
+                     extended_omega, blinding_factors, size, rot_scale):
+    """evaluation.rs:397-493."""
+    if not sets:
+        return list(values)
+    out = []
+    last_rotation = -(blinding_factors + 1)
+    delta_start = beta * zeta % R_MOD
+    beta_term = 1
+    for idx in range(size):
+        v = values[idx]
+        r_next = get_rotation_idx(idx, 1, rot_scale, size)
+        r_last = get_rotation_idx(idx, last_rotation, rot_scale, size)
+        v = (v * y + (1 - sets[0][idx]) * l0[idx]) % R_MOD
+        zl = sets[-1][idx]
+        v = (v * y + (zl * zl - zl) * l_last[idx]) % R_MOD
+        for s in range(1, len(sets)):
+            v = (v * y + (sets[s][idx] - sets[s - 1][r_last]) * l0[idx]) % R_MOD
+        current_delta = delta_start * beta_term % R_MOD
+        for s, z in enumerate(sets):
+            cols = range(s * chunk_len, min((s + 1) * chunk_len, len(col_values)))
+            left = z[r_next]
+            for c in cols:
+                left = left * (col_values[c][idx] + beta * col_perms[c][idx] + gamma) % R_MOD
+            right = z[idx]
+            for c in cols:
+                right = right * (col_values[c][idx] + current_delta + gamma) % R_MOD
+                current_delta = current_delta * delta % R_MOD
+            v = (v * y + (left - right) * l_active[idx]) % R_MOD
+        out.append(v)
+        beta_term = beta_term * extended_omega % R_MOD
+    return out
+
+
+def lookup_fold(values, table_values, product, permuted_input, permuted_table, l0, l_last, l_active, beta, gamma, y, size, rot_scale):
+    """evaluation.rs:517-565."""
+    out = []
+    for idx in range(size):
+        v = values[idx]
+        r_next, r_prev = get_rotation_idx(idx, 1, rot_scale, size), get_rotation_idx(idx, -1, rot_scale, size)
+        a_minus_s = permuted_input[idx] - permuted_table[idx]
+        z = product[idx]
+        v = (v * y + (1 - z) * l0[idx]) % R_MOD
+        v = (v * y + (z * z - z) * l_last[idx]) % R_MOD
+        v = (v * y + (product[r_next] * (permuted_input[idx] + beta) * (permuted_table[idx] + gamma) - z * table_values[idx])
+             * l_active[idx]) % R_MOD
+        v = (v * y + a_minus_s * l0[idx]) % R_MOD
+        v = (v * y + a_minus_s * (permuted_input[idx] - permuted_input[r_prev]) * l_active[idx]) % R_MOD
+        out.append(v)
+    return out
+
+
+def shuffle_fold(values, input_values, shuffle_values, product, l0, l_last, l_active, y, size, rot_scale):
+    """evaluation.rs:573-620."""
+    out = []
+    for idx in range(size):
+        v = values[idx]
+        r_next = get_rotation_idx(idx, 1, rot_scale, size)
+        z = product[idx]
+        v = (v * y + (1 - z) * l0[idx]) % R_MOD
+        v = (v * y + (z * z - z) * l_last[idx]) % R_MOD
+        v = (v * y + l_active[idx] * (product[r_next] * shuffle_values[idx] - z * input_values[idx])) % R_MOD
+        out.append(v)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
 # KZG SRS with a known secret: kzg/commitment.rs:64-131
 # ---------------------------------------------------------------------------------------------
 class ParamsKZG:

@@ -45,6 +45,12 @@ SYMBOLS = {
     "h2b_eval_polynomial_device": (_int, [_vp, _vp, _sz, _vp, _vp]),
     "h2b_kate_division": (_int, [_vp, _vp, _sz, _vp, _vp]),
     "h2b_kate_division_device": (_int, [_vp, _vp, _sz, _vp, _vp]),
+    "h2b_quotient_graph_device": (_int, [_vp, _vp, ctypes.POINTER(_vp), _sz, ctypes.POINTER(_vp), _sz, ctypes.POINTER(_vp), _sz,
+                                         _vp, _sz, _vp, _vp, _vp, _vp, _vp, _vp, _u32, _u32]),
+    "h2b_quotient_permutation_device": (_int, [_vp, _vp, ctypes.POINTER(_vp), _sz, ctypes.POINTER(_vp), ctypes.POINTER(_vp), _sz, _sz,
+                                               _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, ctypes.c_int32, _u32, _u32]),
+    "h2b_quotient_lookup_device": (_int, [_vp] * 12 + [_u32, _u32]),
+    "h2b_quotient_shuffle_device": (_int, [_vp] * 9 + [_u32, _u32]),
     "h2b_last_call_ms": (ctypes.c_double, [_vp]),
     "h2b_profile_enable": (_int, [_vp, _int]),
     "h2b_profile_read": (_int, [_vp, ctypes.c_char_p, _sz]),
@@ -52,6 +58,14 @@ SYMBOLS = {
     "h2b_imad_peak": (_int, [_vp, _pd, _pd]),
     "h2b_synth_bases": (_int, [_vp, _vp, _sz, _u64]),
 }
+
+
+
+class Graph(ctypes.Structure):
+    """`h2b_graph` of include/h2b200.h."""
+    _fields_ = [("program", ctypes.POINTER(ctypes.c_uint32)), ("n_words", _sz), ("constants32", _vp), ("n_constants", _sz),
+                ("rotations", ctypes.POINTER(ctypes.c_int32)), ("n_rotations", _sz), ("n_intermediates", _u32)]
+
 
 _lib = None
 

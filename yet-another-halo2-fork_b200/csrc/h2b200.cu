@@ -19,6 +19,7 @@
 #include "msm.cuh"
 #include "msm_kernels.hpp"
 #include "poly_kernels.hpp"
+#include "quotient_kernels.hpp"
 #include "ntt.cuh"
 #include "ntt_plan.hpp"
 #include "ntt_kernels.hpp"
@@ -79,6 +80,7 @@ struct Dev {
     DevBuf ntt_a, ntt_b, ntt_tab;
     MsmSortSet ms[2];
     DevBuf m_scalars, m_buckets, m_wpart, m_long_partials, m_counters, m_tmp_bases;
+    DevBuf q_stage, q_scratch;                    // quotient evaluation: uploaded program / pointer tables, intermediates
     DevBuf p_in, p_out, p_tiles;                  // polynomial helpers (poly.cuh): staged operands and per-tile summaries
     void* pinned = nullptr;
     size_t pinned_cap = 0;
@@ -628,6 +630,65 @@ int poly_horner_enqueue(h2b_ctx* ctx, Dev& d, const Fr* a, uint64_t n, const Fr&
     return H2B_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// quotient evaluation (quotient.cuh)
+// ------------------------------------------------------------------------------------------------
+const QuotientKernelTable& QK = quotient_kernel_table();
+
+// Bump allocator over one staging buffer: everything a call needs on the device (program words, constants, pointer tables)
+// is packed on the host and uploaded with ONE copy.
+struct Stage {
+    std::vector<uint8_t> host;
+    size_t put(const void* src, size_t bytes) {
+        size_t off = (host.size() + 31) & ~(size_t)31;
+        host.resize(off + bytes);
+        if (bytes) std::memcpy(host.data() + off, src, bytes);
+        return off;
+    }
+};
+
+// Walk the program once on the host: every index must be in range (the kernel trusts it).
+int quotient_validate(h2b_ctx* ctx, const h2b_graph* g, size_t n_fixed, size_t n_advice, size_t n_instance, size_t n_challenges,
+                      uint32_t* last_target, bool* has_calcs) {
+    auto bad = [&](const char* what) { return ctx->fail(H2B_E_INVALID, std::string("quotient_graph: ") + what); };
+    if (g->n_rotations > Q_MAX_ROTATIONS) return bad("too many distinct rotations");
+    auto src_ok = [&](uint32_t w0, uint32_t w1) {
+        uint32_t kind = w0 & 0xffu, rot = w0 >> 8;
+        switch (kind) {
+            case QS_CONSTANT: return w1 < g->n_constants;
+            case QS_INTERMEDIATE: return w1 < g->n_intermediates;
+            case QS_FIXED: return w1 < n_fixed && rot < g->n_rotations;
+            case QS_ADVICE: return w1 < n_advice && rot < g->n_rotations;
+            case QS_INSTANCE: return w1 < n_instance && rot < g->n_rotations;
+            case QS_CHALLENGE: return w1 < n_challenges;
+            case QS_BETA: case QS_GAMMA: case QS_THETA: case QS_Y: case QS_PREVIOUS: return true;
+            default: return false;
+        }
+    };
+    size_t pc = 0;
+    *has_calcs = false;
+    while (pc < g->n_words) {
+        if (pc + 6 > g->n_words) return bad("truncated calculation");
+        const uint32_t* w = g->program + pc;
+        if (w[0] > QC_STORE) return bad("unknown calculation");
+        if (w[1] >= g->n_intermediates) return bad("target out of range");
+        if (!src_ok(w[2], w[3])) return bad("value source out of range");
+        if (w[0] == QC_HORNER) {
+            if (pc + 7 > g->n_words) return bad("truncated Horner");
+            size_t np = w[6];
+            if (!src_ok(w[4], w[5]) || pc + 7 + 2 * np > g->n_words) return bad("truncated Horner");
+            for (size_t i = 0; i < np; i++) if (!src_ok(w[7 + 2 * i], w[8 + 2 * i])) return bad("value source out of range");
+            pc += 7 + 2 * np;
+        } else {
+            if (w[0] <= QC_MUL && !src_ok(w[4], w[5])) return bad("value source out of range");
+            pc += 6;
+        }
+        *last_target = w[1];
+        *has_calcs = true;
+    }
+    return H2B_OK;
+}
 }  // namespace
 
 // ================================================================================================
@@ -699,7 +760,7 @@ void h2b_destroy(h2b_ctx* ctx) {
         for (auto& kv : d.plans) cudaFree(kv.second.tables);
         cudaStreamSynchronize(d.sort_stream);
         DevBuf* bufs[] = {&d.ntt_a, &d.ntt_b, &d.ntt_tab, &d.m_scalars, &d.m_buckets, &d.m_wpart, &d.m_long_partials, &d.m_counters,
-                          &d.m_tmp_bases, &d.p_in, &d.p_out, &d.p_tiles};
+                          &d.m_tmp_bases, &d.p_in, &d.p_out, &d.p_tiles, &d.q_stage, &d.q_scratch};
         for (DevBuf* b : bufs) b->release();
         d.ms[0].release(); d.ms[1].release();
         if (d.pinned) cudaFreeHost(d.pinned);
@@ -1102,6 +1163,138 @@ int h2b_kate_division(h2b_ctx* ctx, const void* a, size_t n, const void* b32, vo
 int h2b_kate_division_device(h2b_ctx* ctx, const void* d_a, size_t n, const void* b32, void* d_q) {
     if (ctx && !d_q) return ctx->fail(H2B_E_INVALID, "kate_division: null argument");
     return horner_impl(ctx, d_a, n, b32, d_q, nullptr, true, "kate_division");
+}
+
+// ---- quotient evaluation ---------------------------------------------------------
+int h2b_quotient_graph_device(h2b_ctx* ctx, const h2b_graph* g, const void* const* d_fixed, size_t n_fixed,
+                              const void* const* d_advice, size_t n_advice, const void* const* d_instance, size_t n_instance,
+                              const void* challenges32, size_t n_challenges, const void* beta32, const void* gamma32,
+                              const void* theta32, const void* y32, const void* d_prev, void* d_out, uint32_t k, uint32_t ext_k) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!g || !d_out || !beta32 || !gamma32 || !theta32 || !y32 || (g->n_words && !g->program) || (g->n_constants && !g->constants32) ||
+        (g->n_rotations && !g->rotations) || (n_fixed && !d_fixed) || (n_advice && !d_advice) || (n_instance && !d_instance) ||
+        (n_challenges && !challenges32))
+        return ctx->fail(H2B_E_INVALID, "quotient_graph: null argument");
+    if (k > ext_k || ext_k > 28) return ctx->fail(H2B_E_INVALID, "quotient_graph: bad domain sizes");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    uint32_t last_target = 0;
+    bool has_calcs = false;
+    int rc = quotient_validate(ctx, g, n_fixed, n_advice, n_instance, n_challenges, &last_target, &has_calcs);
+    if (rc) return rc;
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    const uint32_t size = 1u << ext_k;
+    const unsigned threads = 128;
+    unsigned blocks = std::min<unsigned>((size + threads - 1) / threads, (unsigned)d.sms * 8);
+    const size_t nthreads = (size_t)blocks * threads;
+    Stage st;
+    size_t o_prog = st.put(g->program, g->n_words * 4), o_const = st.put(g->constants32, g->n_constants * 32),
+           o_rot = st.put(g->rotations, g->n_rotations * 4), o_fixed = st.put(d_fixed, n_fixed * sizeof(void*)),
+           o_adv = st.put(d_advice, n_advice * sizeof(void*)), o_inst = st.put(d_instance, n_instance * sizeof(void*)),
+           o_chal = st.put(challenges32, n_challenges * 32);
+    H2B_CK(d.q_stage.reserve(st.host.size() + 64));
+    H2B_CK(d.q_scratch.reserve(std::max<size_t>((size_t)g->n_intermediates * nthreads * 32, 256)));
+    begin_call(d);
+    H2B_CK(cudaMemcpyAsync(d.q_stage.p, st.host.data(), st.host.size(), cudaMemcpyHostToDevice, d.stream));
+    uint8_t* base = d.q_stage.as<uint8_t>();
+    GraphArgs A;
+    A.prog = (const uint32_t*)(base + o_prog); A.n_words = (uint32_t)g->n_words; A.n_rot = (uint32_t)g->n_rotations;
+    A.n_inter = g->n_intermediates; A.last_target = last_target; A.has_calcs = has_calcs ? 1 : 0;
+    A.constants = (const Fr*)(base + o_const); A.rotations = (const int32_t*)(base + o_rot);
+    A.fixed = (const Fr* const*)(base + o_fixed); A.advice = (const Fr* const*)(base + o_adv); A.instance = (const Fr* const*)(base + o_inst);
+    A.challenges = (const Fr*)(base + o_chal);
+    A.beta = fr_from_bytes(beta32); A.gamma = fr_from_bytes(gamma32); A.theta = fr_from_bytes(theta32); A.y = fr_from_bytes(y32);
+    A.prev = (const Fr*)d_prev; A.out = (Fr*)d_out; A.scratch = d.q_scratch.as<Fr>();
+    A.size = size; A.rot_scale = 1u << (ext_k - k);
+    H2B_LAUNCH(d, "quotient_graph", QK.graph, blocks, threads, 0, A);
+    H2B_CK(cudaGetLastError());
+    return end_call(ctx, d);       // synchronises: the host staging vector may go out of scope
+}
+
+int h2b_quotient_permutation_device(h2b_ctx* ctx, void* d_values, const void* const* d_sets, size_t n_sets,
+                                    const void* const* d_col_values, const void* const* d_col_perms, size_t n_cols, size_t chunk_len,
+                                    const void* d_l0, const void* d_l_last, const void* d_l_active, const void* beta32,
+                                    const void* gamma32, const void* y32, const void* delta_start32, const void* delta32,
+                                    const void* ext_omega32, int32_t last_rotation, uint32_t k, uint32_t ext_k) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!d_values || !d_l0 || !d_l_last || !d_l_active || !beta32 || !gamma32 || !y32 || !delta_start32 || !delta32 || !ext_omega32 ||
+        (n_sets && !d_sets) || (n_cols && (!d_col_values || !d_col_perms)))
+        return ctx->fail(H2B_E_INVALID, "quotient_permutation: null argument");
+    if (k > ext_k || ext_k > 28) return ctx->fail(H2B_E_INVALID, "quotient_permutation: bad domain sizes");
+    if (n_sets == 0) { ctx->last_ms = 0; return H2B_OK; }                       // `if !sets.is_empty()` (evaluation.rs:397)
+    if (chunk_len == 0 || n_sets * chunk_len < n_cols || (n_sets - 1) * chunk_len >= std::max<size_t>(n_cols, 1))
+        return ctx->fail(H2B_E_INVALID, "quotient_permutation: n_sets does not match columns.chunks(chunk_len)");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    Stage st;
+    size_t o_sets = st.put(d_sets, n_sets * sizeof(void*)), o_cv = st.put(d_col_values, n_cols * sizeof(void*)),
+           o_cp = st.put(d_col_perms, n_cols * sizeof(void*));
+    H2B_CK(d.q_stage.reserve(st.host.size() + 64));
+    begin_call(d);
+    H2B_CK(cudaMemcpyAsync(d.q_stage.p, st.host.data(), st.host.size(), cudaMemcpyHostToDevice, d.stream));
+    uint8_t* base = d.q_stage.as<uint8_t>();
+    PermFoldArgs A;
+    A.values = (Fr*)d_values; A.sets = (const Fr* const*)(base + o_sets); A.col_values = (const Fr* const*)(base + o_cv);
+    A.col_perms = (const Fr* const*)(base + o_cp);
+    A.n_sets = (uint32_t)n_sets; A.n_cols = (uint32_t)n_cols; A.chunk_len = (uint32_t)chunk_len;
+    A.l0 = (const Fr*)d_l0; A.l_last = (const Fr*)d_l_last; A.l_active = (const Fr*)d_l_active;
+    A.beta = fr_from_bytes(beta32); A.gamma = fr_from_bytes(gamma32); A.y = fr_from_bytes(y32);
+    A.delta_start = fr_from_bytes(delta_start32); A.delta = fr_from_bytes(delta32); A.ext_omega = fr_from_bytes(ext_omega32);
+    A.one = Fr::one(); A.last_rotation = last_rotation; A.size = 1u << ext_k; A.rot_scale = 1u << (ext_k - k);
+    const unsigned threads = 128;
+    unsigned blocks = std::min<unsigned>((A.size + threads - 1) / threads, (unsigned)d.sms * 8);
+    H2B_LAUNCH(d, "quotient_permutation", QK.permutation, blocks, threads, 0, A);
+    H2B_CK(cudaGetLastError());
+    return end_call(ctx, d);
+}
+
+int h2b_quotient_lookup_device(h2b_ctx* ctx, void* d_values, const void* d_table_values, const void* d_product,
+                               const void* d_permuted_input, const void* d_permuted_table, const void* d_l0, const void* d_l_last,
+                               const void* d_l_active, const void* beta32, const void* gamma32, const void* y32, uint32_t k,
+                               uint32_t ext_k) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!d_values || !d_table_values || !d_product || !d_permuted_input || !d_permuted_table || !d_l0 || !d_l_last || !d_l_active ||
+        !beta32 || !gamma32 || !y32)
+        return ctx->fail(H2B_E_INVALID, "quotient_lookup: null argument");
+    if (k > ext_k || ext_k > 28) return ctx->fail(H2B_E_INVALID, "quotient_lookup: bad domain sizes");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    LookupFoldArgs A;
+    A.values = (Fr*)d_values; A.table_values = (const Fr*)d_table_values; A.product = (const Fr*)d_product;
+    A.permuted_input = (const Fr*)d_permuted_input; A.permuted_table = (const Fr*)d_permuted_table;
+    A.l0 = (const Fr*)d_l0; A.l_last = (const Fr*)d_l_last; A.l_active = (const Fr*)d_l_active;
+    A.beta = fr_from_bytes(beta32); A.gamma = fr_from_bytes(gamma32); A.y = fr_from_bytes(y32); A.one = Fr::one();
+    A.size = 1u << ext_k; A.rot_scale = 1u << (ext_k - k);
+    const unsigned threads = 128;
+    unsigned blocks = std::min<unsigned>((A.size + threads - 1) / threads, (unsigned)d.sms * 16);
+    begin_call(d);
+    H2B_LAUNCH(d, "quotient_lookup", QK.lookup, blocks, threads, 0, A);
+    H2B_CK(cudaGetLastError());
+    return end_call(ctx, d);
+}
+
+int h2b_quotient_shuffle_device(h2b_ctx* ctx, void* d_values, const void* d_input_values, const void* d_shuffle_values,
+                                const void* d_product, const void* d_l0, const void* d_l_last, const void* d_l_active,
+                                const void* y32, uint32_t k, uint32_t ext_k) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!d_values || !d_input_values || !d_shuffle_values || !d_product || !d_l0 || !d_l_last || !d_l_active || !y32)
+        return ctx->fail(H2B_E_INVALID, "quotient_shuffle: null argument");
+    if (k > ext_k || ext_k > 28) return ctx->fail(H2B_E_INVALID, "quotient_shuffle: bad domain sizes");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    ShuffleFoldArgs A;
+    A.values = (Fr*)d_values; A.input_values = (const Fr*)d_input_values; A.shuffle_values = (const Fr*)d_shuffle_values;
+    A.product = (const Fr*)d_product; A.l0 = (const Fr*)d_l0; A.l_last = (const Fr*)d_l_last; A.l_active = (const Fr*)d_l_active;
+    A.y = fr_from_bytes(y32); A.one = Fr::one(); A.size = 1u << ext_k; A.rot_scale = 1u << (ext_k - k);
+    const unsigned threads = 128;
+    unsigned blocks = std::min<unsigned>((A.size + threads - 1) / threads, (unsigned)d.sms * 16);
+    begin_call(d);
+    H2B_LAUNCH(d, "quotient_shuffle", QK.shuffle, blocks, threads, 0, A);
+    H2B_CK(cudaGetLastError());
+    return end_call(ctx, d);
 }
 
 // ---- measurement ---------------------------------------------------------------------------------
