@@ -186,6 +186,82 @@ def proof_sequence_gpu(ctx, eng):
     return ms, ctx.launch_count() - l0
 
 
+# The same prover, as the device-resident integration runs it: columns are uploaded once, every
+# commit / transform / quotient fold / opening helper consumes and produces device buffers, and only 96-byte points and 32-byte
+# evaluations come back.  Counts follow SURVEY.md 8(d) for the k = 20 frontend_backend_split circuit (A=4, F=8, I=1, L=1, S=1,
+# P=1, d=6 -> extended_k = 23): the MSM / NTT calls of SEQ_COUNTS plus 3 batch inversions + 3 running products (permutation,
+# lookup, shuffle Z polynomials), the custom-gate / permutation / lookup / shuffle folds over 2^23 rows, and the SHPLONK side
+# (32 polynomial evaluations, 2 quotient divisions).  Still not a proof: witness synthesis and the transcript are host work.
+RES_COUNTS = {"upload_columns": 6, "batch_invert": 3, "grand_product": 3, "eval_polynomial": 32, "kate_division": 2,
+              "graph_rows": 1 << 23, "graph_programs": 3, "permutation_fold": 1, "lookup_fold": 1, "shuffle_fold": 1}
+
+
+def proof_sequence_resident(ctx, eng):
+    import h2b200
+    import torch
+    from h2b200 import evaluation as E
+    n = 1 << SEQ_K
+    dom = h2b200.EvaluationDomain(SEQ_J, SEQ_K, ctx)
+    ops = h2b200.PolyOps(ctx)
+    ext_k = dom.extended_k
+    g = eng.get_base_descriptor(h2b200.synth.device_bases(ctx, n, 1))
+    gl = eng.get_base_descriptor(h2b200.synth.device_bases(ctx, n, 1 + n))
+    uni_h = torch.from_numpy(h2b200.synth.random_scalars(n, 5).view(np.int64)).pin_memory()
+    skw_h = torch.from_numpy(skew(uni_h.numpy().view(np.uint64), h2b200.fields.fr_mont(1), 6).view(np.int64)).pin_memory()
+    # a representative custom-gate program: three degree-3 gates over 4 advice / 2 fixed columns with rotations, folded with y
+    adv = lambda c, r=0: ("query", "advice", c, r)
+    fix = lambda c, r=0: ("query", "fixed", c, r)
+    gates = [("prod", fix(0), ("sum", ("prod", adv(0), adv(1, 1)), ("neg", adv(2)))),
+             ("prod", fix(1), ("sum", ("prod", ("prod", adv(3), adv(3)), adv(0, -1)), ("neg", adv(1)))),
+             ("prod", fix(0, 1), ("sum", adv(2, 1), ("neg", ("prod", adv(2), ("const", 3)))))]
+    custom = E.GraphEvaluator()
+    custom.add_calculation(("horner", (10,), tuple(custom.add_expression(e) for e in gates), (9,)))
+    lookup = E.GraphEvaluator()                       # evaluation.rs:233-262 shape with degree-2 inputs
+    lc_in = lookup.add_calculation(("horner", (0, 0), (lookup.add_expression(("prod", fix(0), adv(0))),), (8,)))
+    lc_tab = lookup.add_calculation(("horner", (0, 0), (lookup.add_expression(("prod", fix(1), adv(1))),), (8,)))
+    lookup.add_calculation(("mul", lookup.add_calculation(("add", lc_in, (6,))), lookup.add_calculation(("add", lc_tab, (7,)))))
+    shuf = E.GraphEvaluator()
+    shuf.add_calculation(("add", shuf.add_calculation(("horner", (0, 0), (shuf.add_expression(("prod", fix(0), adv(2))),), (8,))), (7,)))
+    beta, gamma, theta, y = 11, 13, 17, 19
+    delta = pow(7, 1 << 28, h2b200.fields.R_MOD)
+
+    def once():
+        cols = [uni_h.cuda(non_blocking=True) for _ in range(4)] + [skw_h.cuda(non_blocking=True) for _ in range(2)]   # witness upload
+        for i in range(SEQ_COUNTS["commit_lagrange_uniform"]):
+            eng.msm_with_cached_base(cols[i % 4], gl)
+        for i in range(SEQ_COUNTS["commit_lagrange_skewed"]):
+            eng.msm_with_cached_base(cols[4 + i % 2], gl)
+        for i in range(RES_COUNTS["batch_invert"]):
+            z = ops.grand_product(ops.batch_invert(cols[i].clone()), 1, n)
+        coeffs = [dom.lagrange_to_coeff(cols[i % 6].clone()) for i in range(SEQ_COUNTS["lagrange_to_coeff"])]
+        for i in range(SEQ_COUNTS["commit"]):
+            eng.msm_with_cached_base(coeffs[i % len(coeffs)], g)
+        ext = [dom.coeff_to_extended(c) for c in coeffs[: SEQ_COUNTS["coeff_to_extended"]]]
+        values = torch.zeros((1 << ext_k, 4), dtype=torch.int64, device="cuda")
+        custom.evaluate(ctx, ext[4:6], ext[0:4], [], [], beta, gamma, theta, y, SEQ_K, ext_k, previous=values, out=values)
+        E.permutation_fold(ctx, values, [ext[6]], ext[0:4], ext[4:8], 4, ext[8], ext[9], ext[9], beta, gamma, y, h2b200.fields.FR_ZETA,
+                           delta, dom.extended_omega, 5, SEQ_K, ext_k)
+        table_values = lookup.evaluate(ctx, ext[4:6], ext[0:4], [], [], beta, gamma, theta, y, SEQ_K, ext_k)
+        E.lookup_fold(ctx, values, table_values, ext[6], ext[7], ext[5], ext[8], ext[9], ext[9], beta, gamma, y, SEQ_K, ext_k)
+        sv = shuf.evaluate(ctx, ext[4:6], ext[0:4], [], [], beta, gamma, theta, y, SEQ_K, ext_k)
+        E.shuffle_fold(ctx, values, sv, table_values, ext[6], ext[8], ext[9], ext[9], y, SEQ_K, ext_k)
+        h = dom.extended_to_coeff(values, divide_by_vanishing=True)
+        for i in range(RES_COUNTS["eval_polynomial"]):
+            ops.eval_polynomial(coeffs[i % len(coeffs)], 123457 + i)
+        for i in range(RES_COUNTS["kate_division"]):
+            ops.kate_division(coeffs[i], 987 + i)
+        return h
+
+    once()
+    torch.cuda.synchronize()
+    l0 = ctx.launch_count()
+    t = time.perf_counter()
+    once()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t) * 1e3
+    return ms, ctx.launch_count() - l0
+
+
 def proof_sequence_cpu():
     """One call of each kind through the oracle port, scaled by SEQ_COUNTS (bounded sample)."""
     from oracle import cref as C
@@ -423,6 +499,11 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
         line["k20_kernel_sequence"] = {
             "what": "MSM + NTT calls of one k=20 create_proof (SURVEY 8d counts), host buffers in/out, through MsmAccel / EvaluationDomain mirrors; not a proof",
             "counts": SEQ_COUNTS, "value": seq_ms, "unit": "ms", "gpu_launches": seq_launches}
+        res_ms, res_launches = proof_sequence_resident(ctx, eng)
+        line["k20_kernel_sequence"]["device_resident"] = {
+            "what": "same MSM / NTT counts with device-resident columns, plus the Z-polynomial inversions / running products, the "
+                    "quotient folds over 2^23 rows and the opening helpers (SURVEY 8f N1-N3) on the device; witness upload included",
+            "extra_counts": RES_COUNTS, "value": res_ms, "unit": "ms", "gpu_launches": res_launches}
         if not args.no_cpu:
             cpu_total, cpu_parts, thr = proof_sequence_cpu()
             line["k20_kernel_sequence"]["cpu_baseline"] = {"value": cpu_total, "unit": "ms", "cores": thr, "kind": "port",

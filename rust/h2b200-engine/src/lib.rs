@@ -121,5 +121,52 @@ pub fn extended_to_coeff(e: &B200Engine, d: &DomainConsts, a: &[Fr], t_evals: Op
     unsafe { out.set_len(out_len) };
     out
 }
+
+// ---- the O(n) helpers between the accelerated steps -------------------------------------------------
+fn fr_ptr(x: &Fr) -> *const c_void { x as *const Fr as *const c_void }
+
+/// arithmetic.rs:56-82
+pub fn eval_polynomial(e: &B200Engine, poly: &[Fr], point: Fr) -> Fr {
+    let mut out = core::mem::MaybeUninit::<Fr>::uninit();
+    e.check(unsafe { sys::h2b_eval_polynomial(e.ctx, poly.as_ptr() as *const c_void, poly.len(), fr_ptr(&point), out.as_mut_ptr() as *mut c_void) });
+    unsafe { out.assume_init() }
+}
+/// arithmetic.rs:99-120
+pub fn kate_division(e: &B200Engine, a: &[Fr], b: Fr) -> Vec<Fr> {
+    let mut q: Vec<Fr> = Vec::with_capacity(a.len() - 1);           // panics on an empty slice, as the reference does
+    e.check(unsafe { sys::h2b_kate_division(e.ctx, a.as_ptr() as *const c_void, a.len(), fr_ptr(&b), q.as_mut_ptr() as *mut c_void) });
+    unsafe { q.set_len(a.len() - 1) };
+    q
+}
+/// `values.iter_mut().batch_invert()` (permutation/prover.rs:124, lookup/prover.rs:225, shuffle/prover.rs:150)
+pub fn batch_invert(e: &B200Engine, a: &mut [Fr]) {
+    e.check(unsafe { sys::h2b_batch_invert(e.ctx, a.as_mut_ptr() as *mut c_void, a.len()) });
+}
+/// z[0] = init; z[i] = z[i-1] * v[i-1]  (permutation/prover.rs:160-166, lookup/prover.rs:254-259, shuffle/prover.rs:161-166)
+pub fn grand_product(e: &B200Engine, v: &[Fr], init: Fr, out_len: usize) -> Vec<Fr> {
+    assert!(out_len <= v.len() + 1);
+    let mut z: Vec<Fr> = Vec::with_capacity(out_len);
+    e.check(unsafe { sys::h2b_grand_product(e.ctx, v.as_ptr() as *const c_void, v.len(), fr_ptr(&init), z.as_mut_ptr() as *mut c_void, out_len) });
+    unsafe { z.set_len(out_len) };
+    z
+}
+
+// ---- quotient evaluation --------------------------------------------------------------------------------
+/// Flat encoding of `GraphEvaluator` (plonk/evaluation.rs:187-196) as `h2b_graph` wants it.  In the reference fork this is built
+/// inside halo2_backend (the struct's fields are private): one `push_source` per `ValueSource`, one record per `CalculationInfo`.
+#[derive(Default)]
+pub struct GraphProgram { pub words: Vec<u32>, pub constants: Vec<Fr>, pub rotations: Vec<i32>, pub n_intermediates: u32 }
+impl GraphProgram {
+    /// kind: 0 Constant, 1 Intermediate, 2 Fixed, 3 Advice, 4 Instance, 5 Challenge, 6 Beta, 7 Gamma, 8 Theta, 9 Y, 10 PreviousValue
+    pub fn push_source(&mut self, kind: u32, index: u32, rotation_index: u32) { self.words.push(kind | (rotation_index << 8)); self.words.push(index); }
+    /// op: 0 Add, 1 Sub, 2 Mul, 3 Square, 4 Double, 5 Negate, 7 Store (two sources follow; unary ops repeat Constant(0)); 6 Horner
+    /// (start, factor, n_parts, parts...).
+    pub fn begin(&mut self, op: u32, target: u32) { self.words.push(op); self.words.push(target); }
+    pub fn as_raw(&self) -> sys::h2b_graph {
+        sys::h2b_graph { program: self.words.as_ptr(), n_words: self.words.len(), constants32: self.constants.as_ptr() as *const c_void,
+                         n_constants: self.constants.len(), rotations: self.rotations.as_ptr(), n_rotations: self.rotations.len(),
+                         n_intermediates: self.n_intermediates }
+    }
+}
 #[allow(dead_code)]
 fn _layout_witness(_: Fq) {}

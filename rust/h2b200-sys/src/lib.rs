@@ -12,6 +12,18 @@ pub const H2B_OK: c_int = 0;
 pub const H2B_MSM_WINDOW_BYTES: usize = 128;
 pub const H2B_MSM_MAX_WINDOWS: usize = 64;
 
+/// `h2b_graph` of include/h2b200.h: the reference's `GraphEvaluator` (plonk/evaluation.rs:187-196) flattened.
+#[repr(C)]
+pub struct h2b_graph {
+    pub program: *const u32,
+    pub n_words: usize,
+    pub constants32: *const c_void,
+    pub n_constants: usize,
+    pub rotations: *const i32,
+    pub n_rotations: usize,
+    pub n_intermediates: u32,
+}
+
 #[link(name = "h2b200")]
 extern "C" {
     pub fn h2b_init(out: *mut *mut h2b_ctx, device_ids: *const c_int, n_devices: c_int) -> c_int;
@@ -33,4 +45,41 @@ extern "C" {
     pub fn h2b_coeff_to_extended_batch(ctx: *mut h2b_ctx, in_cols: *const *const c_void, out_cols: *const *mut c_void, n_cols: usize,
                                        k: u32, ext_k: u32, ext_omega32: *const c_void, g_coset32: *const c_void,
                                        g_coset_inv32: *const c_void) -> c_int;
+    // device-resident variants (device-0 pointers; results stay on the device)
+    pub fn h2b_bases_register_device(ctx: *mut h2b_ctx, d_bases: *const c_void, n: usize, handle_out: *mut u64) -> c_int;
+    pub fn h2b_msm_device(ctx: *mut h2b_ctx, bases_handle: u64, d_scalars: *const c_void, n: usize, out96: *mut c_void) -> c_int;
+    pub fn h2b_ntt_device(ctx: *mut h2b_ctx, d_a: *mut c_void, log_n: u32, omega32: *const c_void, scale32_or_null: *const c_void) -> c_int;
+    pub fn h2b_coeff_to_extended_device(ctx: *mut h2b_ctx, d_in_n: *const c_void, d_out_ne: *mut c_void, k: u32, ext_k: u32,
+                                        ext_omega32: *const c_void, g_coset32: *const c_void, g_coset_inv32: *const c_void) -> c_int;
+    pub fn h2b_extended_to_coeff_device(ctx: *mut h2b_ctx, d_a_ne: *const c_void, d_out: *mut c_void, ext_k: u32,
+                                        ext_omega_inv32: *const c_void, ext_ifft_divisor32: *const c_void, g_coset32: *const c_void,
+                                        g_coset_inv32: *const c_void, out_len: usize, t_evals32_or_null: *const c_void, n_t: usize) -> c_int;
+    // polynomial helpers (arithmetic.rs:56-120, ff::BatchInvert, the Z running products)
+    pub fn h2b_batch_invert(ctx: *mut h2b_ctx, a: *mut c_void, n: usize) -> c_int;
+    pub fn h2b_batch_invert_device(ctx: *mut h2b_ctx, d_a: *mut c_void, n: usize) -> c_int;
+    pub fn h2b_grand_product(ctx: *mut h2b_ctx, v: *const c_void, n: usize, init32: *const c_void, z: *mut c_void, out_len: usize) -> c_int;
+    pub fn h2b_grand_product_device(ctx: *mut h2b_ctx, d_v: *const c_void, n: usize, init32: *const c_void, d_z: *mut c_void, out_len: usize) -> c_int;
+    pub fn h2b_eval_polynomial(ctx: *mut h2b_ctx, poly: *const c_void, n: usize, point32: *const c_void, out32: *mut c_void) -> c_int;
+    pub fn h2b_eval_polynomial_device(ctx: *mut h2b_ctx, d_poly: *const c_void, n: usize, point32: *const c_void, out32: *mut c_void) -> c_int;
+    pub fn h2b_kate_division(ctx: *mut h2b_ctx, a: *const c_void, n: usize, b32: *const c_void, q: *mut c_void) -> c_int;
+    pub fn h2b_kate_division_device(ctx: *mut h2b_ctx, d_a: *const c_void, n: usize, b32: *const c_void, d_q: *mut c_void) -> c_int;
+    // quotient evaluation (plonk/evaluation.rs:317-623), device resident
+    pub fn h2b_quotient_graph_device(ctx: *mut h2b_ctx, g: *const h2b_graph, d_fixed: *const *const c_void, n_fixed: usize,
+                                     d_advice: *const *const c_void, n_advice: usize, d_instance: *const *const c_void, n_instance: usize,
+                                     challenges32: *const c_void, n_challenges: usize, beta32: *const c_void, gamma32: *const c_void,
+                                     theta32: *const c_void, y32: *const c_void, d_prev_or_null: *const c_void, d_out: *mut c_void,
+                                     k: u32, ext_k: u32) -> c_int;
+    pub fn h2b_quotient_permutation_device(ctx: *mut h2b_ctx, d_values: *mut c_void, d_sets: *const *const c_void, n_sets: usize,
+                                           d_col_values: *const *const c_void, d_col_perms: *const *const c_void, n_cols: usize,
+                                           chunk_len: usize, d_l0: *const c_void, d_l_last: *const c_void, d_l_active: *const c_void,
+                                           beta32: *const c_void, gamma32: *const c_void, y32: *const c_void,
+                                           delta_start32: *const c_void, delta32: *const c_void, ext_omega32: *const c_void,
+                                           last_rotation: i32, k: u32, ext_k: u32) -> c_int;
+    pub fn h2b_quotient_lookup_device(ctx: *mut h2b_ctx, d_values: *mut c_void, d_table_values: *const c_void, d_product: *const c_void,
+                                      d_permuted_input: *const c_void, d_permuted_table: *const c_void, d_l0: *const c_void,
+                                      d_l_last: *const c_void, d_l_active: *const c_void, beta32: *const c_void, gamma32: *const c_void,
+                                      y32: *const c_void, k: u32, ext_k: u32) -> c_int;
+    pub fn h2b_quotient_shuffle_device(ctx: *mut h2b_ctx, d_values: *mut c_void, d_input_values: *const c_void,
+                                       d_shuffle_values: *const c_void, d_product: *const c_void, d_l0: *const c_void,
+                                       d_l_last: *const c_void, d_l_active: *const c_void, y32: *const c_void, k: u32, ext_k: u32) -> c_int;
 }

@@ -30,11 +30,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--msm", default="16,18,20,22,24")
     ap.add_argument("--ntt", default="16,18,20,22,24,26")
+    ap.add_argument("--poly", default="20,23")
     ap.add_argument("--reps", type=int, default=5)
     args = ap.parse_args()
     ctx = h2b200.Context([0])
     eng = h2b200.B200Engine(ctx)
-    out = {"msm": {}, "ntt": {}}
+    out = {"msm": {}, "ntt": {}, "poly": {}}
     for k in [int(x) for x in args.msm.split(",") if x]:
         n = 1 << k
         d_bases = h2b200.synth.device_bases(ctx, n, 1)
@@ -75,6 +76,30 @@ def main():
             del ext, small
         out["ntt"][k] = rec
         del d, h
+        torch.cuda.empty_cache()
+    ops = h2b200.PolyOps(ctx)
+    for k in [int(x) for x in args.poly.split(",") if x]:
+        n = 1 << k
+        d = torch.from_numpy(h2b200.synth.random_scalars(n, 7).view(np.int64)).cuda()
+        rec = {}
+        rec["batch_invert_ms"] = timed(lambda: ops.batch_invert(d), args.reps)
+        rec["grand_product_ms"] = timed(lambda: ops.grand_product(d, 1, n), args.reps)
+        rec["eval_polynomial_ms"] = timed(lambda: ops.eval_polynomial(d, 12345), args.reps)
+        rec["kate_division_ms"] = timed(lambda: ops.kate_division(d, 12345), args.reps)
+        # one degree-3 gate over the rows of this domain (4 loads, 3 multiplications + the y fold per row)
+        from h2b200 import evaluation as E
+        g = E.GraphEvaluator()
+        gate = ("prod", ("query", "fixed", 0, 0), ("sum", ("prod", ("query", "advice", 0, 0), ("query", "advice", 1, 1)),
+                                                   ("neg", ("query", "advice", 0, -1))))
+        g.add_calculation(("horner", (10,), (g.add_expression(gate),), (9,)))
+        vals = torch.zeros_like(d)
+        kk = max(k - 3, 1)
+        rec["graph_gate_ms"] = timed(lambda: g.evaluate(ctx, [d], [d, d], [], [], 3, 5, 7, 11, kk, k, previous=vals, out=vals), args.reps)
+        rec["lookup_fold_ms"] = timed(lambda: E.lookup_fold(ctx, vals, d, d, d, d, d, d, d, 3, 5, 7, kk, k), args.reps)
+        rec["permutation_fold_4cols_ms"] = timed(lambda: E.permutation_fold(ctx, vals, [d], [d, d, d, d], [d, d, d, d], 4, d, d, d, 3, 5, 7,
+                                                                            h2b200.fields.FR_ZETA, 9, 11, 5, kk, k), args.reps)
+        out["poly"][k] = rec
+        del d, vals
         torch.cuda.empty_cache()
     print(json.dumps(out))
     ctx.close()
