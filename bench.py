@@ -227,15 +227,19 @@ def proof_sequence_resident(ctx, eng):
 
     def once():
         cols = [uni_h.cuda(non_blocking=True) for _ in range(4)] + [skw_h.cuda(non_blocking=True) for _ in range(2)]   # witness upload
-        for i in range(SEQ_COUNTS["commit_lagrange_uniform"]):
-            eng.msm_with_cached_base(cols[i % 4], gl)
-        for i in range(SEQ_COUNTS["commit_lagrange_skewed"]):
+        # commits that the prover issues back to back with no challenge in between go through h2b_msm_batch:
+        # the 4 advice columns (plonk/prover.rs:436-440), the 2 permuted lookup columns (lookup/prover.rs:130-135); the three
+        # Z-polynomial commits each follow a fresh challenge and stay single calls.
+        eng.msm_batch(cols[0:4], gl)
+        eng.msm_batch(cols[4:6], gl)
+        for i in range(3):
             eng.msm_with_cached_base(cols[4 + i % 2], gl)
         for i in range(RES_COUNTS["batch_invert"]):
             z = ops.grand_product(ops.batch_invert(cols[i].clone()), 1, n)
         coeffs = [dom.lagrange_to_coeff(cols[i % 6].clone()) for i in range(SEQ_COUNTS["lagrange_to_coeff"])]
-        for i in range(SEQ_COUNTS["commit"]):
-            eng.msm_with_cached_base(coeffs[i % len(coeffs)], g)
+        eng.msm_batch(coeffs[0:5], g)                      # the h pieces (vanishing/prover.rs:136-140)
+        for i in range(3):                                 # random poly, SHPLONK h1, h2: one at a time
+            eng.msm_with_cached_base(coeffs[5 + i], g)
         ext = [dom.coeff_to_extended(c) for c in coeffs[: SEQ_COUNTS["coeff_to_extended"]]]
         values = torch.zeros((1 << ext_k, 4), dtype=torch.int64, device="cuda")
         custom.evaluate(ctx, ext[4:6], ext[0:4], [], [], beta, gamma, theta, y, SEQ_K, ext_k, previous=values, out=values)

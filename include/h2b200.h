@@ -93,6 +93,13 @@ int h2b_msm_device(h2b_ctx* ctx, uint64_t bases_handle, const void* d_scalars, s
 int h2b_msm_windows(h2b_ctx* ctx, uint64_t bases_handle, const void* scalars, int scalars_on_device, size_t n,
                     size_t n_total, void* out_windows, uint32_t* c_out, uint32_t* windows_out);
 int h2b_msm_combine(const void* parts, uint32_t n_parts, uint32_t c, uint32_t windows, void* out96);
+/* h2b_msm_batch: n_cols MSMs of n scalars each against bases[0..n) of ONE handle -- the per-column commits of a prover phase
+ * (plonk/prover.rs:436-440 `.iter().map(commit_lagrange)`, vanishing/prover.rs:136-140 the h pieces).  out96s receives
+ * n_cols x 96 bytes.  Same results as n_cols calls of h2b_msm; the columns share one pipeline (binning of column k+1 overlaps
+ * accumulation of column k, one reduction launch for all).  An API extension: the reference has no batched commit. */
+int h2b_msm_batch(h2b_ctx* ctx, uint64_t bases_handle, const void* const* scalars_cols, size_t n_cols, size_t n, void* out96s);
+int h2b_msm_batch_device(h2b_ctx* ctx, uint64_t bases_handle, const void* const* d_scalars_cols, size_t n_cols, size_t n,
+                         void* out96s);
 
 /* ---- NTT: EvaluationDomain ----------------------------------------------------------------------------
  * All roots / divisors / coset constants are the fields of the reference's EvaluationDomain (domain.rs:18-33)

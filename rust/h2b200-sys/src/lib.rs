@@ -33,6 +33,8 @@ extern "C" {
     pub fn h2b_bases_register(ctx: *mut h2b_ctx, bases: *const c_void, n: usize, handle_out: *mut u64) -> c_int;
     pub fn h2b_bases_release(ctx: *mut h2b_ctx, handle: u64) -> c_int;
     pub fn h2b_msm(ctx: *mut h2b_ctx, bases_handle: u64, scalars: *const c_void, n: usize, out96: *mut c_void) -> c_int;
+    pub fn h2b_msm_batch(ctx: *mut h2b_ctx, bases_handle: u64, scalars_cols: *const *const c_void, n_cols: usize, n: usize, out96s: *mut c_void) -> c_int;
+    pub fn h2b_msm_batch_device(ctx: *mut h2b_ctx, bases_handle: u64, d_scalars_cols: *const *const c_void, n_cols: usize, n: usize, out96s: *mut c_void) -> c_int;
     pub fn h2b_msm_raw(ctx: *mut h2b_ctx, bases: *const c_void, scalars: *const c_void, n: usize, out96: *mut c_void) -> c_int;
     pub fn h2b_ntt(ctx: *mut h2b_ctx, a: *mut c_void, log_n: u32, omega32: *const c_void, scale32_or_null: *const c_void) -> c_int;
     pub fn h2b_coeff_to_extended(ctx: *mut h2b_ctx, in_n: *const c_void, out_ne: *mut c_void, k: u32, ext_k: u32,

@@ -229,3 +229,29 @@ def test_single_process_multi_device_context():
     for c, o in zip(cols, dom.coeff_to_extended_batch(cols)):
         assert np.array_equal(o, C.coeff_to_extended(c, 10, ref.extended_k, m(ref.extended_omega), m(ref.g_coset), m(ref.g_coset_inv)))
     ctx2.close()
+
+
+@pytest.mark.parametrize("n", [5, 3000, (1 << 16) + 7, 1 << 18])
+def test_msm_batch_equals_column_by_column(engine, n):
+    """h2b_msm_batch (the per-column commits of one prover phase, plonk/prover.rs:436-440): one pipeline, same points.
+    n >= 2^16 takes the batched path (precomputed windows, one bucket set per column); small n the per-column fallback."""
+    import torch
+    b = C.gen_bases(n, 9)
+    desc = engine.get_base_descriptor(b)
+    cols = [C.random_fr(n, 500 + i) for i in range(5)]
+    cols[1][::2] = 0                                   # selector-like column: half zeros ...
+    cols[1][1::4] = C.mont_from_int(1, R.R_MOD)        # ... a quarter ones (one oversized bucket)
+    cols[2][:] = cols[0]                               # a repeated column
+    cols[3][:] = 0                                     # all zero -> identity
+    exp = [engine.msm_with_cached_base(c, desc) for c in cols]
+    for c, e in zip(cols[:3], exp[:3]):
+        check(e, oracle_affine(c, b))
+    got = engine.msm_batch(cols, desc)
+    for g, e in zip(got, exp):
+        assert np.array_equal(g, e)
+    dev = [torch.from_numpy(c.view(np.int64)).cuda() for c in cols]
+    got = engine.msm_batch(dev, desc)
+    for g, e in zip(got, exp):
+        assert np.array_equal(g, e)
+    assert engine.msm_batch([], desc).shape == (0, 12)
+    desc.release()

@@ -28,6 +28,8 @@ SYMBOLS = {
     "h2b_msm_raw": (_int, [_vp, _vp, _vp, _sz, _vp]),
     "h2b_msm_device": (_int, [_vp, _u64, _vp, _sz, _vp]),
     "h2b_msm_windows": (_int, [_vp, _u64, _vp, _int, _sz, _sz, _vp, _pu32, _pu32]),
+    "h2b_msm_batch": (_int, [_vp, _u64, ctypes.POINTER(_vp), _sz, _sz, _vp]),
+    "h2b_msm_batch_device": (_int, [_vp, _u64, ctypes.POINTER(_vp), _sz, _sz, _vp]),
     "h2b_msm_combine": (_int, [_vp, _u32, _u32, _u32, _vp]),
     "h2b_ntt": (_int, [_vp, _vp, _u32, _vp, _vp]),
     "h2b_ntt_device": (_int, [_vp, _vp, _u32, _vp, _vp]),

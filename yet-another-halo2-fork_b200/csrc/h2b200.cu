@@ -354,16 +354,17 @@ int msm_stage_sort(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, 
 
 // Accumulation stage of one chunk, enqueued on the COMPUTE stream: every bucket of sort set `S` is summed into the shared
 // bucket array (add_to: on top of what earlier chunks left there).
-int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, const Affine* bases, bool add_to) {
+int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, const Affine* bases, bool add_to,
+                         uint32_t set_index = 0, uint32_t n_sets = 1) {
     const uint32_t nkeys = pl.sp.nkeys;
-    H2B_CK(d.m_buckets.reserve((size_t)nkeys * sizeof(Xyzz)));
+    H2B_CK(d.m_buckets.reserve((size_t)nkeys * n_sets * sizeof(Xyzz)));
     H2B_CK(d.m_long_partials.reserve((size_t)pl.max_tasks * sizeof(Xyzz)));
     const uint32_t* offsets = S.offsets.as<uint32_t>();
     const uint32_t* ends = S.ends.as<uint32_t>();
     const uint32_t* order = S.order.as<uint32_t>();
     const uint32_t* entries = S.entries.as<uint32_t>();
     const uint32_t* counters = S.counters.as<uint32_t>();
-    Xyzz* buckets = d.m_buckets.as<Xyzz>();
+    Xyzz* buckets = d.m_buckets.as<Xyzz>() + (size_t)set_index * nkeys;
     {
         int v = H2B_ACC_DEFAULT_VARIANT;
         if (const char* env = std::getenv("H2B_ACC_VARIANT")) { int t = std::atoi(env); if (t >= 0 && t < 4) v = t; }
@@ -379,10 +380,10 @@ int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan
     return H2B_OK;
 }
 
-int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmLaunchInfo* info) {
+int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmLaunchInfo* info, uint32_t batch_sets = 0) {
     MsmShape sp = msm_shape(0, c, pre_stride, 0);
     const MsmGeom& g = sp.g;
-    const uint32_t kw = sp.kw;
+    const uint32_t kw = batch_sets ? batch_sets : sp.kw;      // a batch of MSMs: one shared-window bucket set per column
     // reduce geometry: 128 threads x L buckets per block, at most MSM_REDUCE_MAX_SLICES blocks per bucket set
     uint32_t slices = 1, log_l = 0;
     if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
@@ -516,6 +517,56 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
     return H2B_OK;
 }
 
+// A batch of MSMs against the SAME registered bases (the per-column commits of one prover phase, plonk/prover.rs:436-440):
+// column k is "chunk" k of the two-stream pipeline with its own bucket set, and ONE reduction launch handles every set, so the
+// binning of column k+1 hides behind the accumulation of column k and the reduction latency is paid once.
+// Needs the precomputed-window layout (one bucket set per MSM) on a single device; callers fall back to a loop otherwise.
+int msm_run_batch(h2b_ctx* ctx, const Bases& B, const void* const* cols, bool on_device, size_t m, size_t n, Xyzz* sums_out,
+                  uint32_t* c_out) {
+    const BasesShard& sh = B.shard[0];
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    begin_call(d);
+    const Affine* dev_bases = reinterpret_cast<const Affine*>(sh.pre);
+    const uint32_t use_c = sh.pre_c, stride = (uint32_t)sh.count;
+    if (!on_device) {
+        H2B_CK(d.m_scalars.reserve(m * n * 32));
+        while (d.chunk_events.size() < m) { cudaEvent_t e; H2B_CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); d.chunk_events.push_back(e); }
+        H2B_CK(cudaStreamWaitEvent(d.copy_stream, d.ev_first, 0));
+        for (size_t k = 0; k < m; k++) {
+            H2B_CK(cudaMemcpyAsync(d.m_scalars.as<uint8_t>() + k * n * 32, cols[k], n * 32, cudaMemcpyHostToDevice, d.copy_stream));
+            H2B_CK(cudaEventRecord(d.chunk_events[k], d.copy_stream));
+        }
+    }
+    H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.ev_first, 0));
+    for (size_t k = 0; k < m; k++) {
+        MsmSortSet& S = d.ms[k & 1];
+        MsmChunkPlan pl;
+        int rc = msm_chunk_plan(ctx, (uint32_t)n, 0u, use_c, stride, &pl);
+        if (rc) return rc;
+        if (S.consumed_pending) { H2B_CK(cudaStreamWaitEvent(d.sort_stream, S.consumed, 0)); S.consumed_pending = false; }
+        if (!on_device) H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.chunk_events[k], 0));
+        const Fr* sc = on_device ? reinterpret_cast<const Fr*>(cols[k]) : d.m_scalars.as<Fr>() + k * n;
+        rc = msm_stage_sort(ctx, d, S, pl, sc);
+        if (rc) return rc;
+        H2B_CK(cudaEventRecord(S.sorted, d.sort_stream));
+        H2B_CK(cudaStreamWaitEvent(d.stream, S.sorted, 0));
+        rc = msm_stage_accumulate(ctx, d, S, pl, dev_bases, false, (uint32_t)k, (uint32_t)m);
+        if (rc) return rc;
+        H2B_CK(cudaEventRecord(S.consumed, d.stream));
+        S.consumed_pending = true;
+    }
+    MsmLaunchInfo info;
+    int rc = msm_stage_reduce(ctx, d, use_c, stride, &info, (uint32_t)m);
+    if (rc) return rc;
+    rc = end_call(ctx, d);
+    if (rc) return rc;
+    const Xyzz* part = reinterpret_cast<const Xyzz*>(d.pinned);
+    for (size_t k = 0; k < m; k++) sums_out[k] = part[k];
+    *c_out = use_c;
+    return H2B_OK;
+}
+
 // Window size used with precomputed multiples (one shared bucket set, so larger windows stay cheap to reduce).
 uint32_t msm_choose_pre_c(size_t n) {
     if (const char* env = std::getenv("H2B_MSM_PRE_C")) {
@@ -604,7 +655,7 @@ int poly_grand_product_enqueue(h2b_ctx* ctx, Dev& d, const Fr* v, uint64_t n, co
     const uint32_t tiles = poly_tiles(out_len);
     H2B_CK(d.p_tiles.reserve((size_t)tiles * 32 + 64));
     Fr* tt = d.p_tiles.as<Fr>();
-    H2B_LAUNCH(d, "poly_grand_product", PK.prod_tile_reduce, tiles, POLY_T, 0, v, n, tt);
+    H2B_LAUNCH(d, "poly_grand_product", PK.prod_tile_reduce, tiles, POLY_T, 0, v, n, tt, 0u);
     H2B_LAUNCH(d, "poly_grand_product", PK.prod_scan_totals, 1, POLY_T, 0, tt, tiles, init);
     H2B_LAUNCH(d, "poly_grand_product", PK.prod_tile_scan, tiles, POLY_T, 0, v, n, (const Fr*)tt, z, out_len);
     H2B_CK(cudaGetLastError());
@@ -612,7 +663,12 @@ int poly_grand_product_enqueue(h2b_ctx* ctx, Dev& d, const Fr* v, uint64_t n, co
 }
 int poly_batch_invert_enqueue(h2b_ctx* ctx, Dev& d, Fr* a, uint64_t n) {
     if (n == 0) return H2B_OK;
-    H2B_LAUNCH(d, "poly_batch_invert", PK.batch_invert, poly_tiles(n), POLY_T, 0, a, n);
+    const uint32_t tiles = poly_tiles(n);
+    H2B_CK(d.p_tiles.reserve((size_t)tiles * 64 + 64));
+    Fr* tt = d.p_tiles.as<Fr>();
+    H2B_LAUNCH(d, "poly_batch_invert", PK.prod_tile_reduce, tiles, POLY_T, 0, (const Fr*)a, n, tt, 1u);
+    H2B_LAUNCH(d, "poly_batch_invert", PK.invert_totals, 1, POLY_T, 0, tt, tt + tiles, tiles);
+    H2B_LAUNCH(d, "poly_batch_invert", PK.batch_invert, tiles, POLY_T, 0, a, n, (const Fr*)tt);
     H2B_CK(cudaGetLastError());
     return H2B_OK;
 }
@@ -816,6 +872,42 @@ int h2b_msm(h2b_ctx* ctx, uint64_t handle, const void* scalars, size_t n, void* 
 }
 int h2b_msm_device(h2b_ctx* ctx, uint64_t handle, const void* d_scalars, size_t n, void* out96) {
     return msm_common(ctx, handle, d_scalars, true, n, out96);
+}
+static int msm_batch_common(h2b_ctx* ctx, uint64_t handle, const void* const* cols, bool on_device, size_t n_cols, size_t n, void* out96s) {
+    if (!ctx) return H2B_E_INVALID;
+    if (n_cols && (!cols || !out96s)) return ctx->fail(H2B_E_INVALID, "msm_batch: null argument");
+    for (size_t k = 0; k < n_cols; k++) if (!cols[k] && n) return ctx->fail(H2B_E_INVALID, "msm_batch: null column");
+    bool batched = false;
+    {
+        std::lock_guard<std::mutex> lk(ctx->mu);
+        auto it = ctx->bases.find(handle);
+        if (it == ctx->bases.end()) return ctx->fail(H2B_E_INVALID, "msm_batch: unknown bases handle");
+        const Bases& B = it->second;
+        if (n > B.n) return ctx->fail(H2B_E_INVALID, "msm_batch: more scalars than registered bases");
+        // one bucket set per column needs the precomputed-window layout on a single device; a 4 GiB cap on the bucket sets
+        batched = n_cols > 1 && n > 0 && ctx->devs.size() == 1 && B.shard[0].pre && B.shard[0].count >= n &&
+                  (size_t)n_cols * ((size_t)1 << (B.shard[0].pre_c - 1)) * sizeof(Xyzz) <= ((size_t)4 << 30) &&
+                  !std::getenv("H2B_MSM_NO_BATCH");
+        if (batched) {
+            std::vector<Xyzz> sums(n_cols);
+            uint32_t c = 0;
+            int rc = msm_run_batch(ctx, B, cols, on_device, n_cols, n, sums.data(), &c);
+            if (rc) return rc;
+            for (size_t k = 0; k < n_cols; k++) msm_finish(&sums[k], 1, c, reinterpret_cast<uint8_t*>(out96s) + 96 * k);
+            return H2B_OK;
+        }
+    }
+    for (size_t k = 0; k < n_cols; k++) {          // fallback: one MSM per column (classic layout, several devices, ...)
+        int rc = msm_common(ctx, handle, cols[k], on_device, n, reinterpret_cast<uint8_t*>(out96s) + 96 * k);
+        if (rc) return rc;
+    }
+    return H2B_OK;
+}
+int h2b_msm_batch(h2b_ctx* ctx, uint64_t handle, const void* const* scalars_cols, size_t n_cols, size_t n, void* out96s) {
+    return msm_batch_common(ctx, handle, scalars_cols, false, n_cols, n, out96s);
+}
+int h2b_msm_batch_device(h2b_ctx* ctx, uint64_t handle, const void* const* d_scalars_cols, size_t n_cols, size_t n, void* out96s) {
+    return msm_batch_common(ctx, handle, d_scalars_cols, true, n_cols, n, out96s);
 }
 int h2b_msm_raw(h2b_ctx* ctx, const void* bases, const void* scalars, size_t n, void* out96) {
     if (!ctx) return H2B_E_INVALID;

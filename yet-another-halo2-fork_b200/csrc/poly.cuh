@@ -16,7 +16,7 @@
 //   * Horner scan (kate_division / eval_polynomial): reading the coefficients from the top, s_j = b * s_{j-1} + r_j.
 //     A run of `len` elements acts on its carry-in as  x -> b^len * x + S;  runs of equal length compose with the
 //     fixed multipliers b^len, b^(2 len), b^(4 len), ... (a Hillis-Steele scan with one multiplication per step).
-//   * batch inversion: Montgomery's trick per tile (prefix and suffix products), one Fermat inversion per tile.
+//   * batch inversion: Montgomery's trick on two levels (tile products, then inside each tile) with ONE Fermat inversion per call.
 #pragma once
 #include "field.cuh"
 #include "field_wide.cuh"
@@ -102,15 +102,20 @@ H2B_D Fr block_scan_horner(Fr v, const Fr* pw, PolyShared& sh, uint32_t t, int& 
 
 // ---- product scan ------------------------------------------------------------------------------------------------
 // phase 1: tile_tot[tile] = product of the tile's elements (indices >= n count as 1)
+// zero_as_one: zeros are skipped (batch inversion leaves them untouched, ff::BatchInvert)
 __global__ void __launch_bounds__(POLY_T)
-poly_prod_tile_reduce_kernel(const Fr* __restrict__ v, uint64_t n, Fr* __restrict__ tile_tot) {
+poly_prod_tile_reduce_kernel(const Fr* __restrict__ v, uint64_t n, Fr* __restrict__ tile_tot, uint32_t zero_as_one) {
     __shared__ PolyShared sh;
     const uint32_t t = threadIdx.x;
     const uint64_t base = (uint64_t)blockIdx.x * POLY_TILE + (uint64_t)t * POLY_K;
     Fr p = Fr::one();
 #pragma unroll
     for (int k = 0; k < POLY_K; k++)
-        if (base + k < n) p = k == 0 ? fe_load(v + base) : fe_mul(p, fe_load(v + base + k));
+        if (base + k < n) {
+            Fr e = fe_load(v + base + k);
+            if (zero_as_one && e.is_zero()) e = Fr::one();
+            p = k == 0 ? e : fe_mul(p, e);
+        }
     int cur;
     Fr incl = block_scan_mul(p, sh, t, cur);
     if (t == POLY_T - 1) fe_store(tile_tot + blockIdx.x, incl);
@@ -157,11 +162,38 @@ poly_prod_tile_scan_kernel(const Fr* v, uint64_t n, const Fr* __restrict__ tile_
     }
 }
 
-// ---- batch inversion (Montgomery's trick per tile; zeros stay zero as in ff::BatchInvert) ------------------------------
+// ---- batch inversion (Montgomery's trick on two levels; zeros stay zero as in ff::BatchInvert) ---------------------------
+// level 1: tile products (poly_prod_tile_reduce_kernel, zeros skipped); level 2: ONE block inverts all tile products with a
+// single Fermat inversion (below); level 3: each tile inverts its elements from 1 / (tile product).
+// tot[i] <- 1 / tot[i] for i < ntiles; pre = scratch of ntiles elements.  Tile products are never zero.
 __global__ void __launch_bounds__(POLY_T)
-poly_batch_invert_kernel(Fr* a, uint64_t n) {
+poly_invert_totals_kernel(Fr* tot, Fr* pre, uint32_t ntiles) {
     __shared__ PolyShared sh;
     __shared__ Fr inv_total;
+    const uint32_t t = threadIdx.x;
+    const uint32_t m = (ntiles + POLY_T - 1) / POLY_T;          // consecutive tile products per thread
+    const uint32_t lo = t * m, hi = lo + m < ntiles ? lo + m : ntiles;
+    Fr p = Fr::one();
+    for (uint32_t i = lo; i < hi; i++) {                        // pre[i] = product of this thread's entries before i
+        fe_store(pre + i, p);
+        p = fe_mul(p, fe_load(tot + i));
+    }
+    int cur;
+    block_scan_mul(p, sh, t, cur);
+    Fr excl_pre = t ? fe_load(&sh.s[cur][t - 1]) : Fr::one();
+    if (t == 0) inv_total = fe_inv_window(fe_load(&sh.s[cur][POLY_T - 1]));
+    block_suffix_scan_mul(p, sh, t, cur);                      // (its leading barrier also publishes inv_total)
+    Fr excl_suf = t + 1 < (uint32_t)POLY_T ? fe_load(&sh.s[cur][t + 1]) : Fr::one();
+    Fr inv = fe_mul(fe_mul(inv_total, excl_pre), excl_suf);     // 1 / (this thread's product)
+    for (uint32_t i = hi; i-- > lo;) {
+        Fr ti = fe_load(tot + i);
+        fe_store(tot + i, fe_mul(inv, fe_load(pre + i)));
+        inv = fe_mul(inv, ti);
+    }
+}
+__global__ void __launch_bounds__(POLY_T)
+poly_batch_invert_kernel(Fr* a, uint64_t n, const Fr* __restrict__ tile_inv) {
+    __shared__ PolyShared sh;
     const uint32_t t = threadIdx.x;
     const uint64_t base = (uint64_t)blockIdx.x * POLY_TILE + (uint64_t)t * POLY_K;
     Fr e[POLY_K], pre[POLY_K];          // pre[k] = e[0] * ... * e[k] with zeros replaced by one
@@ -175,11 +207,10 @@ poly_batch_invert_kernel(Fr* a, uint64_t n) {
     int cur;
     block_scan_mul(pre[POLY_K - 1], sh, t, cur);
     Fr excl_pre = t ? fe_load(&sh.s[cur][t - 1]) : Fr::one();
-    if (t == 0) inv_total = fe_inv_window(fe_load(&sh.s[cur][POLY_T - 1]));
-    block_suffix_scan_mul(pre[POLY_K - 1], sh, t, cur);            // (its leading barrier also publishes inv_total)
+    block_suffix_scan_mul(pre[POLY_K - 1], sh, t, cur);
     Fr excl_suf = t + 1 < (uint32_t)POLY_T ? fe_load(&sh.s[cur][t + 1]) : Fr::one();
-    // 1 / (this thread's product) = 1/total * (product before) * (product after)
-    Fr inv = fe_mul(fe_mul(inv_total, excl_pre), excl_suf);
+    // 1 / (this thread's product) = 1/(tile product) * (product before) * (product after)
+    Fr inv = fe_mul(fe_mul(fe_load(tile_inv + blockIdx.x), excl_pre), excl_suf);
 #pragma unroll
     for (int k = POLY_K - 1; k >= 0; k--) {
         Fr r = k ? fe_mul(inv, pre[k - 1]) : inv;

@@ -4,10 +4,11 @@
 
 namespace h2b {
 struct PolyKernelTable {
-    void (*prod_tile_reduce)(const Fr*, uint64_t, Fr*);
+    void (*prod_tile_reduce)(const Fr*, uint64_t, Fr*, uint32_t);
     void (*prod_scan_totals)(Fr*, uint32_t, Fr);
     void (*prod_tile_scan)(const Fr*, uint64_t, const Fr*, Fr*, uint64_t);
-    void (*batch_invert)(Fr*, uint64_t);
+    void (*invert_totals)(Fr*, Fr*, uint32_t);
+    void (*batch_invert)(Fr*, uint64_t, const Fr*);
     void (*horner_tile_reduce)(const Fr*, uint64_t, uint64_t, Fr, Fr, Fr*);
     void (*horner_scan_totals)(Fr*, uint32_t, Fr, Fr*);
     void (*horner_tile_scan)(const Fr*, uint64_t, uint64_t, Fr, Fr, const Fr*, Fr*);

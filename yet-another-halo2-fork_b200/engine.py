@@ -177,6 +177,29 @@ class B200Engine:
             self.ctx.check(self.ctx.lib.h2b_msm(self.ctx.handle, base.handle, cp, n, out.ctypes.data_as(ctypes.c_void_p)))
         return out
 
+    def msm_batch(self, columns, base: BaseDescriptor) -> np.ndarray:
+        """Several scalar vectors of equal length against the same cached bases (the per-column commits of one prover phase,
+        plonk/prover.rs:436-440); returns (len(columns), 12) normalised Jacobian points, equal to msm_with_cached_base per column."""
+        columns = list(columns)
+        out = np.zeros((len(columns), 12), dtype=np.uint64)
+        if not columns:
+            return out
+        if all(_is_torch_cuda(c) for c in columns):
+            n = columns[0].numel() * columns[0].element_size() // 32
+            assert all(c.numel() * c.element_size() // 32 == n for c in columns), "msm_batch: columns differ in length"
+            self._check_len(n, base)
+            ptrs = (ctypes.c_void_p * len(columns))(*[c.data_ptr() for c in columns])
+            self.ctx.check(self.ctx.lib.h2b_msm_batch_device(self.ctx.handle, base.handle, ptrs, len(columns), n,
+                                                             out.ctypes.data_as(ctypes.c_void_p)))
+            return out
+        host = [_host_ptr(c, 4) for c in columns]
+        n = host[0][2]
+        assert all(h[2] == n for h in host), "msm_batch: columns differ in length"
+        self._check_len(n, base)
+        ptrs = (ctypes.c_void_p * len(columns))(*[h[0].ctypes.data for h in host])
+        self.ctx.check(self.ctx.lib.h2b_msm_batch(self.ctx.handle, base.handle, ptrs, len(columns), n, out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
     # --- zal.rs:96
     def msm_with_cached_inputs(self, coeffs: CoeffsDescriptor, base: BaseDescriptor) -> np.ndarray:
         return self.msm_with_cached_base(coeffs.dev, base)
