@@ -399,7 +399,21 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
     Xyzz* block_p = wpart;
     Xyzz* block_r = wpart + (size_t)kw * slices;
     Xyzz* set_sums = wpart + (size_t)kw * slices * 2;
-    if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
+    uint32_t lg_nb = 0;
+    while ((1u << (lg_nb + 1)) <= g.nb) lg_nb++;
+    const bool lines_path = g.nb >= (1u << 14) && !std::getenv("H2B_MSM_REDUCE_CLASSIC");
+    if (lines_path) {
+        // low-latency path: row / column sums, masked sums per index bit, Horner over the bits (msm.cuh 6b)
+        const uint32_t w = lg_nb / 2, h = lg_nb - w, H = 1u << h, W = 1u << w;
+        H2B_CK(d.m_wpart.reserve(((size_t)kw * (H + W) + (size_t)kw * (h + w + 1) + kw) * sizeof(Xyzz)));
+        wpart = d.m_wpart.as<Xyzz>();
+        Xyzz* lines = wpart;
+        Xyzz* terms = wpart + (size_t)kw * (H + W);
+        set_sums = terms + (size_t)kw * (h + w + 1);
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce_lines, dim3((H + W + 3) / 4, kw, 1), MSM_REDUCE_THREADS, 0, (const Xyzz*)buckets, g.nb, w, lines);
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce_masked, dim3(h + w + 1, kw, 1), MSM_REDUCE_THREADS, 0, (const Xyzz*)lines, h, w, terms);
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce_combine, kw, 64, 0, (const Xyzz*)terms, h, w, set_sums);
+    } else if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
         dim3 grid(slices, kw, 1);
         H2B_LAUNCH(d, "msm_reduce", MK.reduce, grid, MSM_REDUCE_THREADS, 0, gr, buckets, slices, log_l, block_p, block_r);
         H2B_LAUNCH(d, "msm_reduce", MK.reduce_final, kw, MSM_REDUCE_MAX_SLICES, 0, slices, log_l + 7u, block_p, block_r, set_sums);
@@ -459,9 +473,10 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
         // sort stream while chunk k is accumulated on the compute stream; all chunks add into ONE bucket array.
         const bool staged = !(on_device && di == 0);
         size_t chunk = cnt;
-        if (cnt >= ((size_t)1 << 22)) {          // 2^21-point chunks, at most 8 (measured on B200: profiles/README.md)
-            size_t k = std::min<size_t>(8, cnt >> 21);
-            chunk = (cnt + k - 1) / k;
+        {   // at most 8 chunks of >= 2^20 points (device scalars) or >= 2^18 (host scalars, where the chunks also hide the
+            // PCIe copy); measured on B200: profiles/README.md
+            size_t k = std::min<size_t>(8, cnt >> (staged && !on_device ? 18 : 20));
+            if (k > 1) chunk = (cnt + k - 1) / k;
         }
         if (const char* env = std::getenv("H2B_MSM_CHUNKS")) { int k = std::atoi(env); if (k >= 1 && k <= 64) chunk = (cnt + k - 1) / k; }
         size_t nchunks = (cnt + chunk - 1) / chunk;
@@ -786,6 +801,10 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
             g_init_error = "device is not sm_100 (this library is built for B200 only)"; delete ctx; return H2B_E_NODEVICE;
         }
         d.sms = prop.multiProcessorCount;
+        if (const char* env = std::getenv("H2B_L2_FETCH")) {      // experiment knob: L2 fetch granularity hint (32 / 64 / 128 bytes)
+            int v = std::atoi(env);
+            if (v == 32 || v == 64 || v == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v);
+        }
         int prio_lo = 0, prio_hi = 0;
         cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
         if (cudaStreamCreateWithPriority(&d.stream, cudaStreamNonBlocking, prio_lo) != cudaSuccess ||

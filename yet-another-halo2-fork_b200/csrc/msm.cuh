@@ -229,23 +229,44 @@ msm_precompute_kernel(const Affine* __restrict__ in, Affine* __restrict__ out, u
 }
 
 // ---- 4. order buckets by population (descending), and list the oversized ones --------------------
-// size_hist[MSM_SIZE_BINS]: bin = min(size, BINS-1); stored reversed so that an ascending scan gives descending size
-__global__ void msm_size_hist_kernel(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends, uint32_t nkeys,
-                                     uint32_t* __restrict__ size_hist) {
+// size_hist[MSM_SIZE_BINS]: bin = min(size, BINS-1); stored reversed so that an ascending scan gives descending size.
+// Uniform scalars put almost every bucket into the same two or three bins, so both kernels first combine their block's keys
+// in shared memory and touch each global bin once per block (global atomics on one address serialise: 100 us -> a few us).
+__global__ void __launch_bounds__(256)
+msm_size_hist_kernel(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends, uint32_t nkeys,
+                     uint32_t* __restrict__ size_hist) {
+    __shared__ uint32_t sh[MSM_SIZE_BINS];
+    for (uint32_t i = threadIdx.x; i < MSM_SIZE_BINS; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= nkeys) return;
-    uint32_t s = ends[k] - offsets[k];
-    uint32_t bin = s < MSM_SIZE_BINS - 1 ? s : MSM_SIZE_BINS - 1;
-    atomicAdd(size_hist + (MSM_SIZE_BINS - 1 - bin), 1u);
+    if (k < nkeys) {
+        uint32_t s = ends[k] - offsets[k];
+        uint32_t bin = s < MSM_SIZE_BINS - 1 ? s : MSM_SIZE_BINS - 1;
+        atomicAdd(&sh[MSM_SIZE_BINS - 1 - bin], 1u);
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < MSM_SIZE_BINS; i += blockDim.x)
+        if (sh[i]) atomicAdd(size_hist + i, sh[i]);
 }
-__global__ void msm_size_scatter_kernel(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends, uint32_t nkeys,
-                                        uint32_t* __restrict__ size_cursor, uint32_t* __restrict__ order) {
+__global__ void __launch_bounds__(256)
+msm_size_scatter_kernel(const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ ends, uint32_t nkeys,
+                        uint32_t* __restrict__ size_cursor, uint32_t* __restrict__ order) {
+    __shared__ uint32_t sh[MSM_SIZE_BINS];          // per-block count of each bin, then the block's base position in that bin
+    for (uint32_t i = threadIdx.x; i < MSM_SIZE_BINS; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= nkeys) return;
-    uint32_t s = ends[k] - offsets[k];
-    uint32_t bin = s < MSM_SIZE_BINS - 1 ? s : MSM_SIZE_BINS - 1;
-    uint32_t pos = atomicAdd(size_cursor + (MSM_SIZE_BINS - 1 - bin), 1u);
-    order[pos] = k;
+    uint32_t rbin = 0, rank = 0;
+    if (k < nkeys) {
+        uint32_t s = ends[k] - offsets[k];
+        uint32_t bin = s < MSM_SIZE_BINS - 1 ? s : MSM_SIZE_BINS - 1;
+        rbin = MSM_SIZE_BINS - 1 - bin;
+        rank = atomicAdd(&sh[rbin], 1u);
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < MSM_SIZE_BINS; i += blockDim.x)
+        if (sh[i]) sh[i] = atomicAdd(size_cursor + i, sh[i]);
+    __syncthreads();
+    if (k < nkeys) order[sh[rbin] + rank] = k;
 }
 
 // ---- 5. bucket accumulation: one thread per bucket, in population order --------------------------
@@ -439,6 +460,70 @@ msm_reduce_final_kernel(uint32_t slices, uint32_t log_block_buckets, const Xyzz*
     block_tree_sum<MSM_REDUCE_MAX_SLICES>(sh, t);
     if (t == 0) xyzz_store(set_sums + j, xyzz_add(sumP, xyzz_mul_pow2(sh[0], log_block_buckets)));
 }
+// ---- 6b. low-latency reduction for large bucket sets (nb >= 2^14) ----------------------------------------------------
+// sum_i (i + 1) B_i with i = hi * W + lo (W = 2^w columns, H = 2^h rows):
+//     = 2^w * sum_hi hi * D_hi  +  sum_hi D_hi  +  sum_lo lo * C_lo,     D = row sums, C = column sums.
+// Every step is a plain (unweighted) sum, so nothing is serial beyond log-depth trees:
+//   lines   grid ((H + W) / 4, sets): one warp per row / column: strided partial sums + a 5-step tree in shared memory
+//   masked  grid (h + w + 1, sets): S^D_b = sum of the D_hi whose index has bit b set (b < h), S^C_b likewise, and V = sum D_hi
+//   combine grid (sets), two warps: Horner over the bits, acc <- 2 acc + S_b  (h + w doublings and additions in total).
+// Same 2 additions per bucket as the running-sum kernel above, but a dependency depth of ~40 additions instead of ~100.
+__global__ void __launch_bounds__(MSM_REDUCE_THREADS)
+msm_reduce_lines_kernel(const Xyzz* __restrict__ buckets, uint32_t nb, uint32_t w, Xyzz* __restrict__ lines) {
+    // one WARP per row / column (no block barrier: the four warps of a block are independent lines); a lane sums count/32
+    // strided elements, then a 5-step tree through the warp's slice of shared memory.
+    __shared__ Xyzz sh[MSM_REDUCE_THREADS];
+    const uint32_t W = 1u << w, H = nb >> w, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, set = blockIdx.y;
+    const uint32_t job = blockIdx.x * (MSM_REDUCE_THREADS / 32) + warp;
+    if (job >= H + W) return;
+    const Xyzz* b = buckets + (size_t)set * nb;
+    uint32_t start, stride, count;
+    if (job < H) { start = job * W; stride = 1; count = W; }           // row job: D_hi
+    else { start = job - H; stride = W; count = H; }                   // column job: C_lo
+    Xyzz acc = Xyzz::identity();
+    for (uint32_t i = lane; i < count; i += 32) acc = xyzz_add(acc, xyzz_load(b + start + (size_t)i * stride));
+    Xyzz* ws = sh + warp * 32;
+    ws[lane] = acc;
+    __syncwarp();
+    for (uint32_t st = 16; st > 0; st >>= 1) {
+        if (lane < st) ws[lane] = xyzz_add(ws[lane], ws[lane + st]);
+        __syncwarp();
+    }
+    if (lane == 0) xyzz_store(lines + (size_t)set * (H + W) + job, ws[0]);
+}
+__global__ void __launch_bounds__(MSM_REDUCE_THREADS)
+msm_reduce_masked_kernel(const Xyzz* __restrict__ lines, uint32_t h, uint32_t w, Xyzz* __restrict__ terms) {
+    __shared__ Xyzz sh[MSM_REDUCE_THREADS];
+    const uint32_t H = 1u << h, W = 1u << w, t = threadIdx.x, job = blockIdx.x, set = blockIdx.y;
+    const Xyzz* D = lines + (size_t)set * (H + W);
+    const Xyzz* src = job < h ? D : (job < h + w ? D + H : D);
+    const uint32_t count = job < h ? H : (job < h + w ? W : H);
+    const uint32_t mask = job < h ? (1u << job) : (job < h + w ? (1u << (job - h)) : 0u);     // 0: plain sum (V)
+    Xyzz acc = Xyzz::identity();
+    for (uint32_t i = t; i < count; i += MSM_REDUCE_THREADS)
+        if (mask == 0 || (i & mask)) acc = xyzz_add(acc, xyzz_load(src + i));
+    sh[t] = acc;
+    __syncthreads();
+    block_tree_sum<MSM_REDUCE_THREADS>(sh, t);
+    if (t == 0) xyzz_store(terms + (size_t)set * (h + w + 1) + job, sh[0]);
+}
+__global__ void __launch_bounds__(64)
+msm_reduce_combine_kernel(const Xyzz* __restrict__ terms, uint32_t h, uint32_t w, Xyzz* __restrict__ set_sums) {
+    __shared__ Xyzz part;
+    const Xyzz* T = terms + (size_t)blockIdx.x * (h + w + 1);
+    Xyzz acc = Xyzz::identity();
+    if (threadIdx.x == 32) {            // warp 1: Y + V = sum_b 2^b S^C_b + V
+        for (uint32_t b = w; b-- > 0;) acc = xyzz_add(xyzz_double(acc), xyzz_load(T + h + b));
+        part = xyzz_add(acc, xyzz_load(T + h + w));
+    }
+    if (threadIdx.x == 0) {             // warp 0: 2^w * U, U = sum_b 2^b S^D_b
+        for (uint32_t b = h; b-- > 0;) acc = xyzz_add(xyzz_double(acc), xyzz_load(T + b));
+        acc = xyzz_mul_pow2(acc, w);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) xyzz_store(set_sums + blockIdx.x, xyzz_add(acc, part));
+}
+
 // small-window fallback: nb < MSM_REDUCE_THREADS -> one thread per window does the whole running sum
 __global__ void msm_reduce_small_kernel(MsmGeom g, const Xyzz* __restrict__ buckets, Xyzz* __restrict__ window_partials) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
