@@ -255,3 +255,37 @@ def test_msm_batch_equals_column_by_column(engine, n):
         assert np.array_equal(g, e)
     assert engine.msm_batch([], desc).shape == (0, 12)
     desc.release()
+
+
+def test_concurrent_callers_share_one_context(engine, ctx):
+    """The engine is borrowed immutably everywhere (`&self`, zal.rs:57-58) and EvaluationDomain methods are called from inside
+    `parallelize` in keygen (permutation/keygen.rs:188-205): entry points must be safe to call from several host threads."""
+    import threading
+    import h2b200
+    n = 1 << 13
+    b = C.gen_bases(n, 4)
+    desc = engine.get_base_descriptor(b)
+    scal = [C.random_fr(n, 700 + i) for i in range(4)]
+    exp_msm = [oracle_affine(s, b) for s in scal]
+    dom = h2b200.EvaluationDomain(5, 10, ctx)
+    ref = R.EvaluationDomain(5, 10)
+    mm = lambda x: C.mont_from_int(x, R.R_MOD)
+    polys = [C.random_fr(1 << 10, 800 + i) for i in range(4)]
+    exp_ntt = [C.lagrange_to_coeff(p, 10, mm(ref.omega_inv), mm(ref.ifft_divisor)) for p in polys]
+    errors = []
+
+    def worker(i):
+        try:
+            for _ in range(5):
+                check(engine.msm_with_cached_base(scal[i], desc), exp_msm[i])
+                assert np.array_equal(dom.lagrange_to_coeff(polys[i].copy()), exp_ntt[i])
+        except Exception as e:          # noqa: BLE001
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    desc.release()
