@@ -11,10 +11,12 @@
 #include <cstring>
 #include <map>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
 #include "../../include/h2b200.h"
+#include "hostcopy.hpp"
 #define H2B_NO_KERNELS 1      // kernels live in msm_kernels.cu / ntt_kernels_*.cu; this unit is host orchestration only
 #include "msm.cuh"
 #include "msm_kernels.hpp"
@@ -80,6 +82,7 @@ struct Dev {
     DevBuf ntt_a, ntt_b, ntt_tab;
     MsmSortSet ms[2];
     DevBuf m_scalars, m_buckets, m_wpart, m_long_partials, m_counters, m_tmp_bases;
+    StageRing ring;                               // pinned slots for pageable caller buffers (hostcopy.hpp)
     DevBuf q_stage, q_scratch;                    // quotient evaluation: uploaded program / pointer tables, intermediates
     DevBuf p_in, p_out, p_tiles;                  // polynomial helpers (poly.cuh): staged operands and per-tile summaries
     void* pinned = nullptr;
@@ -132,7 +135,8 @@ struct h2b_ctx {
     std::map<uint64_t, Bases> bases;
     uint64_t next_handle = 1;
     double last_ms = 0.0;
-    int fail(int code, const std::string& msg) { err = msg; return code; }
+    std::mutex err_mu;                 // `fail` may be reached from the per-device host threads of a multi-GPU call
+    int fail(int code, const std::string& msg) { std::lock_guard<std::mutex> lk(err_mu); err = msg; return code; }
 };
 
 namespace {
@@ -421,7 +425,7 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
         H2B_LAUNCH(d, "msm_reduce", MK.reduce_small, (kw + 31) / 32, 32, 0, gr, buckets, set_sums);
     }
     H2B_CK(cudaGetLastError());
-    H2B_CK(cudaMemcpyAsync(d.pinned, set_sums, (size_t)kw * sizeof(Xyzz), cudaMemcpyDeviceToHost, d.stream));
+    H2B_CK(d.ring.d2h(d.pinned, set_sums, (size_t)kw * sizeof(Xyzz), d.stream));
     info->c = c; info->windows = kw; info->slices = 1; info->pre = pre_stride != 0;
     return H2B_OK;
 }
@@ -458,9 +462,10 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
     std::vector<MsmLaunchInfo> infos(B.shard.size());
     std::vector<int> used;
     double max_ms = 0;
-    for (size_t di = 0; di < B.shard.size(); di++) {
+    // One host thread per device when several shards take part: the staged copies of pageable scalars block their caller, and
+    // the devices must not queue up behind one another.
+    auto run_shard = [&](size_t di) -> int {
         const BasesShard& sh = B.shard[di];
-        if (sh.start >= n || sh.count == 0) continue;
         size_t cnt = std::min(sh.count, n - sh.start);
         Dev& d = ctx->devs[di];
         H2B_CK(cudaSetDevice(d.id));
@@ -481,17 +486,11 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
         if (const char* env = std::getenv("H2B_MSM_CHUNKS")) { int k = std::atoi(env); if (k >= 1 && k <= 64) chunk = (cnt + k - 1) / k; }
         size_t nchunks = (cnt + chunk - 1) / chunk;
         const Fr* dev_scalars = reinterpret_cast<const Fr*>(scalars) + sh.start;
+        const uint8_t* host_src = reinterpret_cast<const uint8_t*>(scalars) + sh.start * 32;
         if (staged) {
             H2B_CK(d.m_scalars.reserve(cnt * 32));
             while (d.chunk_events.size() < nchunks) { cudaEvent_t e; H2B_CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); d.chunk_events.push_back(e); }
             H2B_CK(cudaStreamWaitEvent(d.copy_stream, d.ev_first, 0));      // previous call's use of m_scalars is over
-            const uint8_t* src = reinterpret_cast<const uint8_t*>(scalars) + sh.start * 32;
-            for (size_t k = 0; k < nchunks; k++) {
-                size_t lo = k * chunk, len = std::min(chunk, cnt - lo);
-                H2B_CK(cudaMemcpyAsync(d.m_scalars.as<uint8_t>() + lo * 32, src + lo * 32, len * 32,
-                                       on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, d.copy_stream));
-                H2B_CK(cudaEventRecord(d.chunk_events[k], d.copy_stream));
-            }
             dev_scalars = d.m_scalars.as<Fr>();
         }
         H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.ev_first, 0));
@@ -501,6 +500,13 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
             MsmChunkPlan pl;
             rc = msm_chunk_plan(ctx, (uint32_t)len, stride ? (uint32_t)lo : 0u, use_c, stride, &pl);
             if (rc) break;
+            if (staged) {
+                // chunk k crosses PCIe on the copy stream (pageable scalars: through the pinned ring, hostcopy.hpp) while the
+                // kernels of chunk k-1, enqueued a moment ago, run
+                if (on_device) H2B_CK(cudaMemcpyAsync(d.m_scalars.as<uint8_t>() + lo * 32, host_src + lo * 32, len * 32, cudaMemcpyDeviceToDevice, d.copy_stream));
+                else H2B_CK(d.ring.h2d(d.m_scalars.as<uint8_t>() + lo * 32, host_src + lo * 32, len * 32, d.copy_stream));
+                H2B_CK(cudaEventRecord(d.chunk_events[k], d.copy_stream));
+            }
             if (S.consumed_pending) { H2B_CK(cudaStreamWaitEvent(d.sort_stream, S.consumed, 0)); S.consumed_pending = false; }
             if (staged) H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.chunk_events[k], 0));
             rc = msm_stage_sort(ctx, d, S, pl, dev_scalars + lo);
@@ -517,7 +523,19 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
         rc = msm_stage_reduce(ctx, d, use_c, stride, &infos[di]);
         if (rc) return rc;
         H2B_CK(cudaEventRecord(d.ev_last, d.stream));
-        used.push_back((int)di);
+        return H2B_OK;
+    };
+    for (size_t di = 0; di < B.shard.size(); di++)
+        if (B.shard[di].start < n && B.shard[di].count != 0) used.push_back((int)di);
+    if (used.size() == 1) {
+        int rc = run_shard((size_t)used[0]);
+        if (rc) return rc;
+    } else {
+        std::vector<int> rcs(used.size(), H2B_OK);
+        std::vector<std::thread> th;
+        for (size_t u = 0; u < used.size(); u++) th.emplace_back([&, u] { rcs[u] = run_shard((size_t)used[u]); });
+        for (auto& t : th) t.join();
+        for (int rc : rcs) if (rc) return rc;
     }
     for (int di : used) {
         Dev& d = ctx->devs[di];
@@ -548,10 +566,6 @@ int msm_run_batch(h2b_ctx* ctx, const Bases& B, const void* const* cols, bool on
         H2B_CK(d.m_scalars.reserve(m * n * 32));
         while (d.chunk_events.size() < m) { cudaEvent_t e; H2B_CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); d.chunk_events.push_back(e); }
         H2B_CK(cudaStreamWaitEvent(d.copy_stream, d.ev_first, 0));
-        for (size_t k = 0; k < m; k++) {
-            H2B_CK(cudaMemcpyAsync(d.m_scalars.as<uint8_t>() + k * n * 32, cols[k], n * 32, cudaMemcpyHostToDevice, d.copy_stream));
-            H2B_CK(cudaEventRecord(d.chunk_events[k], d.copy_stream));
-        }
     }
     H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.ev_first, 0));
     for (size_t k = 0; k < m; k++) {
@@ -560,7 +574,11 @@ int msm_run_batch(h2b_ctx* ctx, const Bases& B, const void* const* cols, bool on
         int rc = msm_chunk_plan(ctx, (uint32_t)n, 0u, use_c, stride, &pl);
         if (rc) return rc;
         if (S.consumed_pending) { H2B_CK(cudaStreamWaitEvent(d.sort_stream, S.consumed, 0)); S.consumed_pending = false; }
-        if (!on_device) H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.chunk_events[k], 0));
+        if (!on_device) {
+            H2B_CK(d.ring.h2d(d.m_scalars.as<uint8_t>() + k * n * 32, cols[k], n * 32, d.copy_stream));
+            H2B_CK(cudaEventRecord(d.chunk_events[k], d.copy_stream));
+            H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.chunk_events[k], 0));
+        }
         const Fr* sc = on_device ? reinterpret_cast<const Fr*>(cols[k]) : d.m_scalars.as<Fr>() + k * n;
         rc = msm_stage_sort(ctx, d, S, pl, sc);
         if (rc) return rc;
@@ -635,8 +653,7 @@ int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, bo
         if (on_device) { sh.d = const_cast<void*>(bases); sh.owned = false; }
         else {
             H2B_CK(cudaMalloc(&sh.d, sh.count * 64));
-            H2B_CK(cudaMemcpyAsync(sh.d, reinterpret_cast<const uint8_t*>(bases) + sh.start * 64, sh.count * 64,
-                                   cudaMemcpyHostToDevice, d.stream));
+            H2B_CK(d.ring.h2d(sh.d, reinterpret_cast<const uint8_t*>(bases) + sh.start * 64, sh.count * 64, d.stream));
             H2B_CK(cudaStreamSynchronize(d.stream));
         }
         if (allow_pre) { int rc = precompute_shard(ctx, d, sh); if (rc) return rc; }
@@ -838,6 +855,7 @@ void h2b_destroy(h2b_ctx* ctx) {
                           &d.m_tmp_bases, &d.p_in, &d.p_out, &d.p_tiles, &d.q_stage, &d.q_scratch};
         for (DevBuf* b : bufs) b->release();
         d.ms[0].release(); d.ms[1].release();
+        d.ring.release();
         if (d.pinned) cudaFreeHost(d.pinned);
         for (auto& r : d.recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
         for (auto ev : d.ev_pool) cudaEventDestroy(ev);
@@ -1011,12 +1029,12 @@ int h2b_ntt(h2b_ctx* ctx, void* a, uint32_t log_n, const void* omega32, const vo
     Fr omega = fr_from_bytes(omega32), scale;
     if (scale32) scale = fr_from_bytes(scale32);
     begin_call(d);
-    H2B_CK(cudaMemcpyAsync(d.ntt_a.p, a, N * 32, cudaMemcpyHostToDevice, d.stream));
+    H2B_CK(d.ring.h2d(d.ntt_a.p, a, N * 32, d.stream));
     NttFused fz;
     rc = ntt_enqueue(ctx, d, d.ntt_a.as<Fr>(), 0, d.ntt_b.as<Fr>(), 0, d.ntt_a.as<Fr>(), 0, 1, log_n, omega,
                      scale32 ? &scale : nullptr, fz);
     if (rc) return rc;
-    H2B_CK(cudaMemcpyAsync(a, d.ntt_a.p, N * 32, cudaMemcpyDeviceToHost, d.stream));
+    H2B_CK(d.ring.d2h(a, d.ntt_a.p, N * 32, d.stream));
     return end_call(ctx, d);
 }
 
@@ -1045,12 +1063,12 @@ static int c2e_impl(h2b_ctx* ctx, const void* in_n, void* out_ne, bool on_device
         H2B_CK(d.ntt_a.reserve(N * 32));
         // stage the n inputs at the END of ntt_a's N slots?  No: the row pass writes `dst` while reading `tmp` only,
         // and the first pass has consumed `src` by then, so src may alias dst.
-        H2B_CK(cudaMemcpyAsync(d.ntt_a.p, in_n, n * 32, cudaMemcpyHostToDevice, d.stream));
+        H2B_CK(d.ring.h2d(d.ntt_a.p, in_n, n * 32, d.stream));
         src = d.ntt_a.as<Fr>(); dst = d.ntt_a.as<Fr>();
     }
     rc = ntt_enqueue(ctx, d, src, 0, d.ntt_b.as<Fr>(), 0, dst, 0, 1, ext_k, omega, nullptr, fz);
     if (rc) return rc;
-    if (!on_device) H2B_CK(cudaMemcpyAsync(out_ne, dst, N * 32, cudaMemcpyDeviceToHost, d.stream));
+    if (!on_device) H2B_CK(d.ring.d2h(out_ne, dst, N * 32, d.stream));
     return end_call(ctx, d);
 }
 int h2b_coeff_to_extended(h2b_ctx* ctx, const void* in_n, void* out_ne, uint32_t k, uint32_t ext_k, const void* ext_omega32,
@@ -1085,7 +1103,7 @@ static int e2c_impl(h2b_ctx* ctx, const void* a_ne, void* out, bool on_device, u
     begin_call(d);
     if (t_evals32) {
         H2B_CK(d.ntt_tab.reserve(n_t * 32));
-        H2B_CK(cudaMemcpyAsync(d.ntt_tab.p, t_evals32, n_t * 32, cudaMemcpyHostToDevice, d.stream));
+        H2B_CK(d.ring.h2d(d.ntt_tab.p, t_evals32, n_t * 32, d.stream));
         fz.in_tab = d.ntt_tab.as<Fr>();
         fz.in_tab_mask = (uint32_t)(n_t - 1);
     }
@@ -1094,12 +1112,12 @@ static int e2c_impl(h2b_ctx* ctx, const void* a_ne, void* out, bool on_device, u
     if (on_device) { src = (const Fr*)a_ne; dst = (Fr*)out; }
     else {
         H2B_CK(d.ntt_a.reserve(N * 32));
-        H2B_CK(cudaMemcpyAsync(d.ntt_a.p, a_ne, N * 32, cudaMemcpyHostToDevice, d.stream));
+        H2B_CK(d.ring.h2d(d.ntt_a.p, a_ne, N * 32, d.stream));
         src = d.ntt_a.as<Fr>(); dst = d.ntt_a.as<Fr>();
     }
     rc = ntt_enqueue(ctx, d, src, 0, d.ntt_b.as<Fr>(), 0, dst, 0, 1, ext_k, omega, &scale, fz);
     if (rc) return rc;
-    if (!on_device) H2B_CK(cudaMemcpyAsync(out, dst, out_len * 32, cudaMemcpyDeviceToHost, d.stream));
+    if (!on_device) H2B_CK(d.ring.d2h(out, dst, out_len * 32, d.stream));
     return end_call(ctx, d);
 }
 int h2b_extended_to_coeff(h2b_ctx* ctx, const void* a_ne, void* out, uint32_t ext_k, const void* ext_omega_inv32,
@@ -1125,8 +1143,8 @@ static int batch_impl(h2b_ctx* ctx, const void* const* in_cols, void* const* out
     for (size_t base = 0; base < n_cols; base += chunk * nd) {
         std::vector<std::vector<size_t>> mine(nd);
         for (size_t c = base; c < std::min(n_cols, base + chunk * nd); c++) mine[(c - base) % nd].push_back(c);
-        for (size_t di = 0; di < nd; di++) {
-            if (mine[di].empty()) continue;
+        // one host thread per device: staged copies of pageable columns block their caller (hostcopy.hpp)
+        auto run_dev = [&](size_t di) -> int {
             Dev& d = ctx->devs[di];
             size_t m = mine[di].size();
             H2B_CK(cudaSetDevice(d.id));
@@ -1134,12 +1152,25 @@ static int batch_impl(h2b_ctx* ctx, const void* const* in_cols, void* const* out
             H2B_CK(d.ntt_b.reserve(m * N * 32));
             begin_call(d);
             for (size_t i = 0; i < m; i++)
-                H2B_CK(cudaMemcpyAsync(d.ntt_a.as<Fr>() + i * N, in_cols[mine[di][i]], nin * 32, cudaMemcpyHostToDevice, d.stream));
+                H2B_CK(d.ring.h2d(d.ntt_a.as<Fr>() + i * N, in_cols[mine[di][i]], nin * 32, d.stream));
             int rc = ntt_enqueue(ctx, d, d.ntt_a.as<Fr>(), N, d.ntt_b.as<Fr>(), N, d.ntt_a.as<Fr>(), N, (uint32_t)m, log_n, omega, scale, fz);
             if (rc) return rc;
             for (size_t i = 0; i < m; i++)
-                H2B_CK(cudaMemcpyAsync(out_cols[mine[di][i]], d.ntt_a.as<Fr>() + i * N, N * 32, cudaMemcpyDeviceToHost, d.stream));
+                H2B_CK(d.ring.d2h(out_cols[mine[di][i]], d.ntt_a.as<Fr>() + i * N, N * 32, d.stream));
             H2B_CK(cudaEventRecord(d.ev_last, d.stream));
+            return H2B_OK;
+        };
+        std::vector<size_t> active;
+        for (size_t di = 0; di < nd; di++) if (!mine[di].empty()) active.push_back(di);
+        if (active.size() == 1) {
+            int rc = run_dev(active[0]);
+            if (rc) return rc;
+        } else {
+            std::vector<int> rcs(active.size(), H2B_OK);
+            std::vector<std::thread> th;
+            for (size_t u = 0; u < active.size(); u++) th.emplace_back([&, u] { rcs[u] = run_dev(active[u]); });
+            for (auto& t : th) t.join();
+            for (int rc : rcs) if (rc) return rc;
         }
         for (size_t di = 0; di < nd; di++) {
             if (mine[di].empty()) continue;
@@ -1194,11 +1225,11 @@ static int batch_invert_impl(h2b_ctx* ctx, void* a, size_t n, bool on_device) {
     if (!on_device && n) {
         H2B_CK(d.p_in.reserve(n * 32));
         buf = d.p_in.as<Fr>();
-        H2B_CK(cudaMemcpyAsync(buf, a, n * 32, cudaMemcpyHostToDevice, d.stream));
+        H2B_CK(d.ring.h2d(buf, a, n * 32, d.stream));
     }
     int rc = poly_batch_invert_enqueue(ctx, d, buf, n);
     if (rc) return rc;
-    if (!on_device && n) H2B_CK(cudaMemcpyAsync(a, buf, n * 32, cudaMemcpyDeviceToHost, d.stream));
+    if (!on_device && n) H2B_CK(d.ring.d2h(a, buf, n * 32, d.stream));
     return end_call(ctx, d);
 }
 int h2b_batch_invert(h2b_ctx* ctx, void* a, size_t n) { return batch_invert_impl(ctx, a, n, false); }
@@ -1218,12 +1249,12 @@ static int grand_product_impl(h2b_ctx* ctx, const void* v, size_t n, const void*
     if (!on_device) {
         H2B_CK(d.p_in.reserve(std::max<size_t>(n, 1) * 32));
         H2B_CK(d.p_out.reserve(std::max<size_t>(out_len, 1) * 32));
-        if (n) H2B_CK(cudaMemcpyAsync(d.p_in.p, v, n * 32, cudaMemcpyHostToDevice, d.stream));
+        if (n) H2B_CK(d.ring.h2d(d.p_in.p, v, n * 32, d.stream));
         src = d.p_in.as<Fr>(); dst = d.p_out.as<Fr>();
     }
     int rc = poly_grand_product_enqueue(ctx, d, src, n, init, dst, out_len);
     if (rc) return rc;
-    if (!on_device && out_len) H2B_CK(cudaMemcpyAsync(z, dst, out_len * 32, cudaMemcpyDeviceToHost, d.stream));
+    if (!on_device && out_len) H2B_CK(d.ring.d2h(z, dst, out_len * 32, d.stream));
     return end_call(ctx, d);
 }
 int h2b_grand_product(h2b_ctx* ctx, const void* v, size_t n, const void* init32, void* z, size_t out_len) {
@@ -1248,15 +1279,15 @@ static int horner_impl(h2b_ctx* ctx, const void* a, size_t n, const void* b32, v
     H2B_CK(d.m_counters.reserve(256));
     if (!on_device) {
         H2B_CK(d.p_in.reserve(n * 32));
-        H2B_CK(cudaMemcpyAsync(d.p_in.p, a, n * 32, cudaMemcpyHostToDevice, d.stream));
+        H2B_CK(d.ring.h2d(d.p_in.p, a, n * 32, d.stream));
         src = d.p_in.as<Fr>();
         if (q) { H2B_CK(d.p_out.reserve(std::max<size_t>(n - 1, 1) * 32)); dq = d.p_out.as<Fr>(); }
     }
     Fr* d_final = out32 ? d.m_counters.as<Fr>() : nullptr;
     int rc = poly_horner_enqueue(ctx, d, src, n, b, q ? dq : nullptr, d_final);
     if (rc) return rc;
-    if (!on_device && q && n > 1) H2B_CK(cudaMemcpyAsync(q, dq, (n - 1) * 32, cudaMemcpyDeviceToHost, d.stream));
-    if (out32) H2B_CK(cudaMemcpyAsync(out32, d_final, 32, cudaMemcpyDeviceToHost, d.stream));
+    if (!on_device && q && n > 1) H2B_CK(d.ring.d2h(q, dq, (n - 1) * 32, d.stream));
+    if (out32) H2B_CK(d.ring.d2h(out32, d_final, 32, d.stream));
     return end_call(ctx, d);
 }
 int h2b_eval_polynomial(h2b_ctx* ctx, const void* poly, size_t n, const void* point32, void* out32) {
@@ -1306,7 +1337,7 @@ int h2b_quotient_graph_device(h2b_ctx* ctx, const h2b_graph* g, const void* cons
     H2B_CK(d.q_stage.reserve(st.host.size() + 64));
     H2B_CK(d.q_scratch.reserve(std::max<size_t>((size_t)g->n_intermediates * nthreads * 32, 256)));
     begin_call(d);
-    H2B_CK(cudaMemcpyAsync(d.q_stage.p, st.host.data(), st.host.size(), cudaMemcpyHostToDevice, d.stream));
+    H2B_CK(d.ring.h2d(d.q_stage.p, st.host.data(), st.host.size(), d.stream));
     uint8_t* base = d.q_stage.as<uint8_t>();
     GraphArgs A;
     A.prog = (const uint32_t*)(base + o_prog); A.n_words = (uint32_t)g->n_words; A.n_rot = (uint32_t)g->n_rotations;
@@ -1343,7 +1374,7 @@ int h2b_quotient_permutation_device(h2b_ctx* ctx, void* d_values, const void* co
            o_cp = st.put(d_col_perms, n_cols * sizeof(void*));
     H2B_CK(d.q_stage.reserve(st.host.size() + 64));
     begin_call(d);
-    H2B_CK(cudaMemcpyAsync(d.q_stage.p, st.host.data(), st.host.size(), cudaMemcpyHostToDevice, d.stream));
+    H2B_CK(d.ring.h2d(d.q_stage.p, st.host.data(), st.host.size(), d.stream));
     uint8_t* base = d.q_stage.as<uint8_t>();
     PermFoldArgs A;
     A.values = (Fr*)d_values; A.sets = (const Fr* const*)(base + o_sets); A.col_values = (const Fr* const*)(base + o_cv);
