@@ -46,7 +46,7 @@ class CopyPool {
     struct Job { char* dst; const char* src; size_t len; Call* call; };
     CopyPool() {
         unsigned hw = std::thread::hardware_concurrency();
-        unsigned n = hw >= 16 ? 6 : (hw >= 8 ? 4 : (hw >= 4 ? 2 : 0));
+        unsigned n = hw >= 64 ? 16 : (hw >= 32 ? 12 : (hw >= 16 ? 8 : (hw >= 8 ? 4 : (hw >= 4 ? 2 : 0))));
         if (const char* env = std::getenv("H2B_COPY_THREADS")) { int v = std::atoi(env); if (v >= 0 && v <= 32) n = (unsigned)v; }
         for (unsigned i = 0; i < n; i++) workers_.emplace_back([this] { run(); });
     }
