@@ -409,13 +409,15 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
     if (lines_path) {
         // low-latency path: row / column sums, masked sums per index bit, Horner over the bits (msm.cuh 6b)
         const uint32_t w = lg_nb / 2, h = lg_nb - w, H = 1u << h, W = 1u << w;
-        H2B_CK(d.m_wpart.reserve(((size_t)kw * (H + W) + (size_t)kw * (h + w + 1) + kw) * sizeof(Xyzz)));
+        const uint32_t cs = H / W;                  // column sums in H / W segments: every line job then sums W buckets
+        const uint32_t nl = H + cs * W;
+        H2B_CK(d.m_wpart.reserve(((size_t)kw * nl + (size_t)kw * (h + w + 1) + kw) * sizeof(Xyzz)));
         wpart = d.m_wpart.as<Xyzz>();
         Xyzz* lines = wpart;
-        Xyzz* terms = wpart + (size_t)kw * (H + W);
+        Xyzz* terms = wpart + (size_t)kw * nl;
         set_sums = terms + (size_t)kw * (h + w + 1);
-        H2B_LAUNCH(d, "msm_reduce", MK.reduce_lines, dim3((H + W + 3) / 4, kw, 1), MSM_REDUCE_THREADS, 0, (const Xyzz*)buckets, g.nb, w, lines);
-        H2B_LAUNCH(d, "msm_reduce", MK.reduce_masked, dim3(h + w + 1, kw, 1), MSM_REDUCE_THREADS, 0, (const Xyzz*)lines, h, w, terms);
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce_lines, dim3((nl + 3) / 4, kw, 1), MSM_REDUCE_THREADS, 0, (const Xyzz*)buckets, g.nb, w, cs, lines);
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce_masked, dim3(h + w + 1, kw, 1), MSM_REDUCE_THREADS, 0, (const Xyzz*)lines, h, w, cs, terms);
         H2B_LAUNCH(d, "msm_reduce", MK.reduce_combine, kw, 64, 0, (const Xyzz*)terms, h, w, set_sums);
     } else if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
         dim3 grid(slices, kw, 1);

@@ -469,17 +469,22 @@ msm_reduce_final_kernel(uint32_t slices, uint32_t log_block_buckets, const Xyzz*
 //   combine grid (sets), two warps: Horner over the bits, acc <- 2 acc + S_b  (h + w doublings and additions in total).
 // Same 2 additions per bucket as the running-sum kernel above, but a dependency depth of ~40 additions instead of ~100.
 __global__ void __launch_bounds__(MSM_REDUCE_THREADS)
-msm_reduce_lines_kernel(const Xyzz* __restrict__ buckets, uint32_t nb, uint32_t w, Xyzz* __restrict__ lines) {
+msm_reduce_lines_kernel(const Xyzz* __restrict__ buckets, uint32_t nb, uint32_t w, uint32_t cs, Xyzz* __restrict__ lines) {
     // one WARP per row / column (no block barrier: the four warps of a block are independent lines); a lane sums count/32
     // strided elements, then a 5-step tree through the warp's slice of shared memory.
     __shared__ Xyzz sh[MSM_REDUCE_THREADS];
+    // lines[] layout per set: D_0..D_{H-1}, then cs column-sum segments of W entries each (segment g covers rows
+    // [g * H / cs, (g + 1) * H / cs)); cs is chosen by the host so that row and column jobs have the same length.
     const uint32_t W = 1u << w, H = nb >> w, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, set = blockIdx.y;
     const uint32_t job = blockIdx.x * (MSM_REDUCE_THREADS / 32) + warp;
-    if (job >= H + W) return;
+    if (job >= H + cs * W) return;
     const Xyzz* b = buckets + (size_t)set * nb;
     uint32_t start, stride, count;
     if (job < H) { start = job * W; stride = 1; count = W; }           // row job: D_hi
-    else { start = job - H; stride = W; count = H; }                   // column job: C_lo
+    else {                                                             // column job: a segment of C_lo
+        const uint32_t g = (job - H) >> w, lo = (job - H) & (W - 1u), rows = H / cs;
+        start = g * rows * W + lo; stride = W; count = rows;
+    }
     Xyzz acc = Xyzz::identity();
     for (uint32_t i = lane; i < count; i += 32) acc = xyzz_add(acc, xyzz_load(b + start + (size_t)i * stride));
     Xyzz* ws = sh + warp * 32;
@@ -489,15 +494,15 @@ msm_reduce_lines_kernel(const Xyzz* __restrict__ buckets, uint32_t nb, uint32_t 
         if (lane < st) ws[lane] = xyzz_add(ws[lane], ws[lane + st]);
         __syncwarp();
     }
-    if (lane == 0) xyzz_store(lines + (size_t)set * (H + W) + job, ws[0]);
+    if (lane == 0) xyzz_store(lines + (size_t)set * (H + cs * W) + job, ws[0]);
 }
 __global__ void __launch_bounds__(MSM_REDUCE_THREADS)
-msm_reduce_masked_kernel(const Xyzz* __restrict__ lines, uint32_t h, uint32_t w, Xyzz* __restrict__ terms) {
+msm_reduce_masked_kernel(const Xyzz* __restrict__ lines, uint32_t h, uint32_t w, uint32_t cs, Xyzz* __restrict__ terms) {
     __shared__ Xyzz sh[MSM_REDUCE_THREADS];
     const uint32_t H = 1u << h, W = 1u << w, t = threadIdx.x, job = blockIdx.x, set = blockIdx.y;
-    const Xyzz* D = lines + (size_t)set * (H + W);
+    const Xyzz* D = lines + (size_t)set * (H + cs * W);
     const Xyzz* src = job < h ? D : (job < h + w ? D + H : D);
-    const uint32_t count = job < h ? H : (job < h + w ? W : H);
+    const uint32_t count = job < h ? H : (job < h + w ? cs * W : H);       // the cs column segments share their weights: i mod W
     const uint32_t mask = job < h ? (1u << job) : (job < h + w ? (1u << (job - h)) : 0u);     // 0: plain sum (V)
     Xyzz acc = Xyzz::identity();
     for (uint32_t i = t; i < count; i += MSM_REDUCE_THREADS)

@@ -22,8 +22,8 @@ struct MsmKernelTable {
     void (*reduce)(MsmGeom, const Xyzz*, uint32_t, uint32_t, Xyzz*, Xyzz*);
     void (*reduce_final)(uint32_t, uint32_t, const Xyzz*, const Xyzz*, Xyzz*);
     void (*reduce_small)(MsmGeom, const Xyzz*, Xyzz*);
-    void (*reduce_lines)(const Xyzz*, uint32_t, uint32_t, Xyzz*);
-    void (*reduce_masked)(const Xyzz*, uint32_t, uint32_t, Xyzz*);
+    void (*reduce_lines)(const Xyzz*, uint32_t, uint32_t, uint32_t, Xyzz*);
+    void (*reduce_masked)(const Xyzz*, uint32_t, uint32_t, uint32_t, Xyzz*);
     void (*reduce_combine)(const Xyzz*, uint32_t, uint32_t, Xyzz*);
     void (*imad_wide_peak)(uint32_t, uint32_t, unsigned long long*);
     void (*field_mul_peak)(uint32_t, Fq*);
