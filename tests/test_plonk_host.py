@@ -1,0 +1,213 @@
+"""CPU tests of the prover mirror (yet-another-halo2-fork_b200/plonk) over the python-int oracle ops: the host logic of
+halo2_backend/src/plonk/{prover,keygen}.rs, the four argument provers, the Blake2b transcript and SHPLONK, end to end:
+create_proof -> bytes -> verify_proof restatement (oracle/plonk_verifier.py), as halo2_proofs/tests/frontend_backend_split.rs:595-643
+does with the real crates."""
+import hashlib
+
+import numpy as np
+import pytest
+
+import h2b200
+from h2b200 import fields as F
+from h2b200 import plonk
+from h2b200.plonk import arguments as A
+from h2b200.plonk import example, rng as RNG, shplonk, transcript as T
+from oracle import plonk_ops, plonk_verifier
+from oracle import pyref as R
+
+K = 6
+SECRET = 0x1234567
+
+
+@pytest.fixture(scope="module")
+def setup():
+    circ = example.MyCircuit(K, 42)
+    cc = circ.compile()
+    cs = plonk.circuit.ConstraintSystemBack(cc.cs)
+    ops = plonk_ops.RefOps(K, SECRET, R.EvaluationDomain(cs.degree(), K))
+    vk = plonk.keygen_vk(ops, cc)
+    pk = plonk.keygen_pk(ops, vk, cc)
+    return circ, ops, vk, pk
+
+
+def _prove(circ, ops, pk, rng, witness=None, num_threads=4):
+    tr = plonk.Blake2bWrite()
+    plonk.create_proof(ops, pk, circ.instances(), witness or circ.witness, rng, tr, num_threads=num_threads)
+    return tr.finalize()
+
+
+def test_constraint_system_shape(setup):
+    """degree 6 from the lookup (plonk/circuit.rs:354-373), 5 blinding factors, 4 permutation columns in
+    one set (chunk_len = degree - 2), queries collected gates -> lookups -> shuffles -> permutation columns (keygen.rs:305-341)."""
+    _, _, vk, _ = setup
+    cs = vk.cs
+    assert cs.degree() == 6 and cs.blinding_factors() == 5 and cs.minimum_rows() == 8
+    assert cs.advice_queries == [(0, 0), (1, 0), (2, 0), (0, 1), (3, 0)]
+    assert cs.instance_queries == [(0, 0)]
+    assert cs.fixed_queries[0] == (5, 0) and (0, 0) in cs.fixed_queries and len(cs.fixed_queries) == 7   # s_instance is never queried
+    assert cs.phases() == [0, 1]
+    assert vk.domain.extended_k == K + 3 and vk.domain.quotient_poly_degree == 5
+
+
+def test_proof_verifies_and_is_deterministic(setup):
+    circ, ops, vk, pk = setup
+    proof = _prove(circ, ops, pk, RNG.OneNg())
+    # 4 advice + 2 + 1 + 1 + 1 + 1 + 5 points, 5 + 7 + 1 + 4 + 2 + 5 + 2 scalars, 2 opening points
+    assert len(proof) == 32 * (4 + 2 + 1 + 1 + 1 + 1 + 5 + 5 + 7 + 1 + 4 + 2 + 5 + 2 + 2)
+    assert plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << K)
+    assert proof == _prove(circ, ops, pk, RNG.OneNg())
+    assert proof != _prove(circ, ops, pk, RNG.OneNg(), num_threads=3), "the thread count seeds the random polynomial"
+    other = _prove(circ, ops, pk, RNG.ChaCha20Rng(bytes(range(32))))
+    assert other != proof and plonk_verifier.verify_proof(vk, circ.instances(), other, SECRET, 1 << K)
+
+
+def test_verifier_rejects(setup):
+    circ, ops, vk, pk = setup
+    proof = _prove(circ, ops, pk, RNG.OneNg())
+    for pos in (40, 32 * 12 + 3, len(proof) - 5):
+        bad = bytearray(proof)
+        bad[pos] ^= 1
+        try:
+            assert not plonk_verifier.verify_proof(vk, circ.instances(), bytes(bad), SECRET, 1 << K)
+        except ValueError:
+            pass                                              # not a curve point / not a canonical scalar
+    inst = circ.instances()
+    inst[0][2] += 1
+    assert not plonk_verifier.verify_proof(vk, inst, proof, SECRET, 1 << K)
+
+    def broken(column, row, value):
+        def w(phase, ch):
+            cols = circ.witness(phase, ch)
+            if phase == 0:
+                cols[column] = cols[column].copy()
+                cols[column][row] = F.fr_mont(value)
+            return cols
+        return w
+    for column, row, value in ((2, 0, 5), (1, 36, 7), (0, 8, 3)):    # gate, shuffle, copy constraint
+        bad = _prove(circ, ops, pk, RNG.OneNg(), witness=broken(column, row, value))
+        assert not plonk_verifier.verify_proof(vk, circ.instances(), bad, SECRET, 1 << K)
+    with pytest.raises(A.ConstraintSystemFailure):                    # lookup/prover.rs:440 -> Error::ConstraintSystemFailure
+        _prove(circ, ops, pk, RNG.OneNg(), witness=broken(0, 20, 12345))
+
+
+def test_commit_phase_errors(setup):
+    """prover.rs:343-390."""
+    circ, ops, _, pk = setup
+    p = plonk.ProverSingle(ops, pk, circ.instances(), RNG.OneNg(), plonk.Blake2bWrite())
+    with pytest.raises(plonk.prover.ProverError, match="Committing invalid phase"):
+        p.commit_phase(1, circ.witness(1, {0: 1}))
+    with pytest.raises(plonk.prover.ProverError, match="expected no advice column"):
+        w = circ.witness(0, {})
+        w[3] = w[0]
+        p.commit_phase(0, w)
+    with pytest.raises(plonk.prover.ProverError, match="to have length"):
+        w = circ.witness(0, {})
+        w[0] = w[0][:-1]
+        p.commit_phase(0, w)
+    with pytest.raises(plonk.prover.ProverError, match="InvalidInstances"):
+        plonk.ProverSingle(ops, pk, [], RNG.OneNg(), plonk.Blake2bWrite())
+
+
+def test_transcript_protocol():
+    """transcript.rs:308-322, 358-418: the byte protocol, restated with hashlib directly."""
+    tw = T.Blake2bWrite()
+    g = (1, 2)
+    tw.common_scalar(5)
+    tw.write_point(g)
+    tw.write_scalar(7)
+    c1 = tw.squeeze_challenge_scalar()
+    c2 = tw.squeeze_challenge_scalar()
+    h = hashlib.blake2b(digest_size=64, person=b"Halo2-Transcript")
+    h.update(b"\x02" + (5).to_bytes(32, "little"))
+    h.update(b"\x01" + (1).to_bytes(32, "little") + (2).to_bytes(32, "little"))
+    h.update(b"\x02" + (7).to_bytes(32, "little"))
+    h.update(b"\x00")
+    assert c1 == int.from_bytes(h.copy().digest(), "little") % F.R_MOD
+    h.update(b"\x00")
+    assert c2 == int.from_bytes(h.copy().digest(), "little") % F.R_MOD and c1 != c2
+    proof = tw.finalize()
+    assert proof == (1).to_bytes(32, "little") + (7).to_bytes(32, "little")      # y = 2 is even: no sign bit
+    tr = T.Blake2bRead(proof)
+    tr.common_scalar(5)
+    assert tr.read_point() == g and tr.read_scalar() == 7
+    assert tr.squeeze_challenge_scalar() == c1
+    with pytest.raises(IOError):
+        tw.write_point(None)                                                      # transcript.rs:401-406
+
+
+def test_point_encoding_round_trip():
+    pts = [R.g1_mul(R.G1_GEN, s) for s in (1, 2, 3, 0xDEADBEEF, F.R_MOD - 1)]
+    for p in pts + [None]:
+        b = T.g1_to_bytes(p)
+        assert len(b) == 32 and T.g1_from_bytes(b) == p
+    neg = (pts[1][0], F.Q_MOD - pts[1][1])
+    assert T.g1_to_bytes(neg)[:31] == T.g1_to_bytes(pts[1])[:31] and T.g1_to_bytes(neg) != T.g1_to_bytes(pts[1])
+    with pytest.raises(ValueError):
+        T.g1_from_bytes((4).to_bytes(32, "little"))                               # x = 4: x^3 + 3 = 67 is not a square mod q
+    with pytest.raises(ValueError):
+        T.fr_from_repr(F.R_MOD.to_bytes(32, "little"))
+
+
+def test_chacha20_stream():
+    """ChaCha20 with the all-zero key, block counter 0, zero nonce: the published keystream (RFC 7539 test vector #1 family)."""
+    ks = RNG.chacha20_blocks(bytes(32), 0, 2)
+    assert ks[0].astype("<u4").tobytes().hex().startswith("76b8e0ada0f13d90405d6ae55386bd28bdd219b8a08ded1aa836efcc8b770dc7")
+    a = RNG.ChaCha20Rng(bytes(32))
+    words = [a.next_u64() for _ in range(72)]                                     # crosses two 64-word refills
+    b = RNG.ChaCha20Rng(bytes(32))
+    assert [int(x) for x in b.random_fr_limbs(9).reshape(-1)] == words
+    c = RNG.ChaCha20Rng(bytes(32))
+    assert c.fill_bytes(13) + c.fill_bytes(3) != b"" and c.index == 4 + 1         # 13 bytes consume 4 words, 3 bytes 1 word
+    d = RNG.ChaCha20Rng(bytes(32))
+    assert d.next_u32() == words[0] & 0xFFFFFFFF and d.next_u64() == (words[0] >> 32) | ((words[1] & 0xFFFFFFFF) << 32)
+    one = RNG.OneNg()
+    assert one.random_fr() == sum(((1 << 32) | 1) << (64 * i) for i in range(8)) % F.R_MOD and one.fill_bytes(5) == b"\x01\0\0\0\x01"
+
+
+def test_permute_expression_pair():
+    """lookup/prover.rs:398-494 against a literal python restatement (sorted input, BTreeMap of leftovers, pop from the back)."""
+    rng = np.random.default_rng(5)
+    for _ in range(20):
+        u = int(rng.integers(1, 40))
+        table = [int(x) for x in rng.integers(0, 12, size=u)]
+        inp = [table[int(i)] for i in rng.integers(0, u, size=u)]
+        srt = sorted(inp)
+        leftover = {}
+        for t in table:
+            leftover[t] = leftover.get(t, 0) + 1
+        out, repeated = [0] * u, []
+        for row, v in enumerate(srt):
+            if row == 0 or v != srt[row - 1]:
+                out[row] = v
+                leftover[v] -= 1
+            else:
+                repeated.append(row)
+        for coeff in sorted(leftover):
+            for _ in range(leftover[coeff]):
+                out[repeated.pop()] = coeff
+        limbs = lambda xs: np.array([[x, 0, 0, x >> 1] for x in xs], dtype=np.uint64)   # two significant limbs
+        pi, pt = A.permute_expression_pair(limbs(inp), limbs(table))
+        assert [int(r[0]) for r in pi] == srt and [int(r[0]) for r in pt] == out
+    with pytest.raises(A.ConstraintSystemFailure):
+        A.permute_expression_pair(np.array([[1, 0, 0, 0]], dtype=np.uint64), np.array([[2, 0, 0, 0]], dtype=np.uint64))
+
+
+def test_parallelize_chunks_and_interpolation():
+    assert A.parallelize_chunks(10, 4) == [(0, 3), (3, 3), (6, 2), (8, 2)]        # arithmetic.rs:148-170
+    assert A.parallelize_chunks(3, 8) == [(0, 1), (1, 1), (2, 1)]
+    assert A.parallelize_chunks(16, 4) == [(0, 4), (4, 4), (8, 4), (12, 4)]
+    pts, evs = [3, 7, 11, 20], [5, 1, 9, 2]
+    poly = shplonk.lagrange_interpolate(pts, evs)                                 # arithmetic.rs:177-232 and its test :263-280
+    assert len(poly) == 4 and [shplonk.eval_small(poly, p) for p in pts] == evs
+    assert shplonk.lagrange_interpolate([4], [9]) == [9]
+    assert shplonk.evaluate_vanishing_polynomial([1, 2], 5) == 12
+
+
+def test_intermediate_sets_grouping():
+    """shplonk.rs:46-137: commitments with the same point set share a rotation set, in first-seen order; points ascend."""
+    q = [(5, "a", 1), (9, "a", 2), (5, "b", 3), (9, "b", 4), (5, "c", 5), (9, "a", 2)]
+    sets, points = shplonk.construct_intermediate_sets(q, lambda x: x[1], lambda x: x[2])
+    assert points == [5, 9] and len(sets) == 2
+    assert sets[0].points == [5, 9] and [c[0][1] for c in sets[0].commitments] == ["a", "b"]
+    assert [c[1] for c in sets[0].commitments] == [[1, 2], [3, 4]]
+    assert sets[1].points == [5] and sets[1].commitments[0][1] == [5]

@@ -4,6 +4,7 @@ Importing this package does not touch the GPU; constructing a `Context` loads li
 if it is missing or no sm_100 device is present (there is no CPU fallback).
 """
 from . import evaluation, fields, synth
+from . import plonk
 from ._lib import H2bError, LIB_PATH, SYMBOLS, load
 from .arithmetic import PolyOps
 from .domain import EvaluationDomain
@@ -11,5 +12,5 @@ from .engine import (B200Engine, BaseDescriptor, CoeffsDescriptor, Context, Plon
                      window_bits)
 from .kzg import ParamsKZG
 
-__all__ = ["evaluation", "fields", "synth", "H2bError", "LIB_PATH", "SYMBOLS", "load", "EvaluationDomain", "B200Engine", "BaseDescriptor",
+__all__ = ["evaluation", "fields", "synth", "plonk", "H2bError", "LIB_PATH", "SYMBOLS", "load", "EvaluationDomain", "B200Engine", "BaseDescriptor",
            "CoeffsDescriptor", "Context", "PlonkEngine", "PlonkEngineConfig", "ParamsKZG", "PolyOps", "shard_range", "window_bits"]

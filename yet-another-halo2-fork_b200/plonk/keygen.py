@@ -1,0 +1,202 @@
+"""keygen_vk / keygen_pk: halo2_backend/src/plonk/keygen.rs:43-187, permutation/keygen.rs and the Evaluator constructor
+(plonk/evaluation.rs:174-255), with every size-n / size-n*e vector produced on the device through `ops`.
+
+Not a performance target (keygen is outside the proving hot path) but it uses the same kernels: commit_lagrange for
+the fixed and sigma columns, lagrange_to_coeff / coeff_to_extended for the cosets the quotient evaluation reads.
+"""
+from __future__ import annotations
+
+import hashlib
+from dataclasses import dataclass, field
+from typing import List, Optional
+
+import numpy as np
+
+from .. import fields as F
+from ..evaluation import ADVICE, BETA, CONSTANT, GAMMA, PREVIOUS, THETA, Y, GraphEvaluator
+from . import circuit as C
+from . import polyexpr as PX
+from .transcript import fr_from_uniform_bytes
+
+FR_DELTA = pow(7, 1 << F.FR_S, F.R_MOD)          # Fr::DELTA = g^(2^S), g = 7
+
+
+class Assembly:
+    """permutation/keygen.rs:20-125: union-find over cells with cycle splicing."""
+
+    def __init__(self, n: int, columns: List[C.Column]):
+        self.n = n
+        self.columns = list(columns)
+        m = len(columns)
+        self.map_col = np.repeat(np.arange(m, dtype=np.int64)[:, None], n, axis=1)
+        self.map_row = np.repeat(np.arange(n, dtype=np.int64)[None, :], m, axis=0)
+        self.aux_col = self.map_col.copy()
+        self.aux_row = self.map_row.copy()
+        self.sizes = np.ones((m, n), dtype=np.int64)
+
+    @staticmethod
+    def new_from_assembly_mid(n: int, columns: List[C.Column], copies) -> "Assembly":
+        a = Assembly(n, columns)
+        for (lc, lr), (rc, rr) in copies:
+            a.copy(lc, lr, rc, rr)
+        return a
+
+    def copy(self, left_column: C.Column, left_row: int, right_column: C.Column, right_row: int) -> None:
+        try:
+            lc, rc = self.columns.index(tuple(left_column)), self.columns.index(tuple(right_column))
+        except ValueError as e:
+            raise KeyError(f"ColumnNotInPermutation: {e}")
+        if left_row >= self.n or right_row >= self.n:
+            raise IndexError("BoundsFailure")
+        left = (int(self.aux_col[lc, left_row]), int(self.aux_row[lc, left_row]))
+        right = (int(self.aux_col[rc, right_row]), int(self.aux_row[rc, right_row]))
+        if left == right:
+            return
+        if self.sizes[left] < self.sizes[right]:
+            left, right = right, left
+        self.sizes[left] += self.sizes[right]
+        i = right
+        while True:
+            self.aux_col[i], self.aux_row[i] = left
+            i = (int(self.map_col[i]), int(self.map_row[i]))
+            if i == right:
+                break
+        tmp = (self.map_col[lc, left_row], self.map_row[lc, left_row])
+        self.map_col[lc, left_row], self.map_row[lc, left_row] = self.map_col[rc, right_row], self.map_row[rc, right_row]
+        self.map_col[rc, right_row], self.map_row[rc, right_row] = tmp
+
+    def permutations(self, ops, omega: int):
+        """The sigma columns in Lagrange form: permutations[i][j] = delta^i' * omega^j' for mapping(i, j) = (i', j')
+        (permutation/keygen.rs:139-176, 228-262)."""
+        m, n = len(self.columns), self.n
+        if m == 0:
+            return []
+        omega_powers = ops.grand_product(ops.full(n, omega), 1, n)
+        deltaomega = [omega_powers if i == 0 else PX.lincomb(ops, [(pow(FR_DELTA, i, F.R_MOD), omega_powers)]) for i in range(m)]
+        table = ops.concat(deltaomega)
+        return [ops.gather_rows(table, self.map_col[i] * n + self.map_row[i]) for i in range(m)]
+
+
+class Evaluator:
+    """plonk/evaluation.rs:174-255: the calculation graphs of the custom gates, each lookup and each shuffle."""
+
+    def __init__(self, cs: C.ConstraintSystemBack):
+        self.custom_gates = GraphEvaluator()
+        parts = tuple(self.custom_gates.add_expression(poly) for _, poly in cs.gates)
+        self.custom_gates.add_calculation(("horner", (PREVIOUS,), parts, (Y,)))
+        self.lookups: List[GraphEvaluator] = []
+        for lookup in cs.lookups:
+            g = GraphEvaluator()
+            lc = lambda exprs: g.add_calculation(("horner", (CONSTANT, 0), tuple(g.add_expression(e) for e in exprs), (THETA,)))
+            compressed_input_coset = lc(lookup.input_expressions)
+            compressed_table_coset = lc(lookup.table_expressions)
+            right_gamma = g.add_calculation(("add", compressed_table_coset, (GAMMA,)))
+            left = g.add_calculation(("add", compressed_input_coset, (BETA,)))
+            g.add_calculation(("mul", left, right_gamma))
+            self.lookups.append(g)
+        self.shuffles: List[GraphEvaluator] = []
+        for shuffle in cs.shuffles:
+            for exprs in (shuffle.input_expressions, shuffle.shuffle_expressions):
+                g = GraphEvaluator()
+                compressed = g.add_calculation(("horner", (CONSTANT, 0), tuple(g.add_expression(e) for e in exprs), (THETA,)))
+                g.add_calculation(("add", compressed, (GAMMA,)))
+                self.shuffles.append(g)
+
+
+@dataclass
+class VerifyingKey:                                       # plonk.rs:43-50
+    domain: object
+    fixed_commitments: list
+    permutation_commitments: list                         # permutation::VerifyingKey.commitments
+    cs: C.ConstraintSystemBack
+    cs_degree: int
+    transcript_repr: int = 0
+
+    def hash_into(self, transcript) -> None:              # plonk.rs:205-213
+        transcript.common_scalar(self.transcript_repr)
+
+
+@dataclass
+class PermutationProvingKey:                              # permutation.rs ProvingKey
+    permutations: list
+    polys: list
+    cosets: list
+
+
+@dataclass
+class ProvingKey:                                         # plonk.rs:242-252
+    vk: VerifyingKey
+    l0: object
+    l_last: object
+    l_active_row: object
+    fixed_values: list
+    fixed_polys: list
+    fixed_cosets: list
+    permutation: PermutationProvingKey
+    ev: Evaluator
+
+    def get_vk(self) -> VerifyingKey:
+        return self.vk
+
+
+def _fixed_column(ops, col):
+    if isinstance(col, np.ndarray) and col.ndim == 2:
+        return ops.upload(col)
+    return ops.from_ints(list(col))
+
+
+def _transcript_repr(vk: VerifyingKey) -> int:
+    """plonk.rs:170-203: BLAKE2b-512, personal "Halo2-Verify-Key", over len || `{:?}` of the pinned key.  The Debug string of the
+    reference cannot be reproduced without Rust, so a deterministic description of the same fields stands in for it:
+    PARITY UNPINNED, and callers holding the reference's value can overwrite `vk.transcript_repr`."""
+    d = vk.domain
+    s = repr(("PinnedVerificationKey", hex(F.Q_MOD), hex(F.R_MOD), (d.k, d.extended_k, hex(d.omega)), vk.cs.pinned_repr(),
+              vk.fixed_commitments, vk.permutation_commitments)).encode()
+    h = hashlib.blake2b(digest_size=64, person=b"Halo2-Verify-Key")
+    h.update(len(s).to_bytes(8, "little"))
+    h.update(s)
+    return fr_from_uniform_bytes(h.digest())
+
+
+def keygen_vk(ops, circuit: C.CompiledCircuit) -> VerifyingKey:
+    """keygen.rs:43-100.  `ops` is bound to a domain of the right k; the quotient degree is re-derived from the circuit."""
+    cs = C.ConstraintSystemBack(circuit.cs)
+    n = ops.n
+    if n < cs.minimum_rows():
+        raise ValueError(f"not enough rows available (k = {ops.k})")
+    assert ops.domain.quotient_poly_degree == cs.degree() - 1, "ops.domain must be EvaluationDomain::new(cs.degree(), k)"
+    assembly = Assembly.new_from_assembly_mid(n, cs.permutation_columns, circuit.preprocessing.copies)
+    sigma = assembly.permutations(ops, ops.domain.omega)
+    permutation_commitments = [ops.commit_lagrange(p) for p in sigma]
+    fixed_commitments = [ops.commit_lagrange(_fixed_column(ops, col)) for col in circuit.preprocessing.fixed]
+    vk = VerifyingKey(ops.domain, fixed_commitments, permutation_commitments, cs, cs.degree())
+    vk.transcript_repr = _transcript_repr(vk)
+    return vk
+
+
+def keygen_pk(ops, vk: VerifyingKey, circuit: C.CompiledCircuit) -> ProvingKey:
+    """keygen.rs:103-187."""
+    cs, n = vk.cs, ops.n
+    if n < cs.minimum_rows():
+        raise ValueError(f"not enough rows available (k = {ops.k})")
+    fixed_values = [_fixed_column(ops, col) for col in circuit.preprocessing.fixed]
+    fixed_polys = [ops.lagrange_to_coeff(ops.clone(v)) for v in fixed_values]
+    fixed_cosets = [ops.coeff_to_extended(p) for p in fixed_polys]
+    bf = cs.blinding_factors()
+
+    def indicator(rows):
+        p = ops.zeros(n)
+        for r in rows:
+            ops.write_ints(p, r, [1])
+        return ops.coeff_to_extended(ops.lagrange_to_coeff(p))
+
+    l0 = indicator([0])
+    l_blind = indicator(range(n - bf, n))
+    l_last = indicator([n - bf - 1])
+    l_active_row = PX.pointwise(ops, C.sub(C.const(1), C.add(PX.col(0), PX.col(1))), [l_last, l_blind], extended=True)
+    assembly = Assembly.new_from_assembly_mid(n, cs.permutation_columns, circuit.preprocessing.copies)
+    permutations = assembly.permutations(ops, ops.domain.omega)
+    polys = [ops.lagrange_to_coeff(ops.clone(p)) for p in permutations]
+    cosets = [ops.coeff_to_extended(p) for p in polys]
+    return ProvingKey(vk, l0, l_last, l_active_row, fixed_values, fixed_polys, fixed_cosets,
+                      PermutationProvingKey(permutations, polys, cosets), Evaluator(cs))

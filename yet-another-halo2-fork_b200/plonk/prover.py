@@ -1,0 +1,188 @@
+"""ProverSingle: halo2_backend/src/plonk/prover.rs restated over device-resident polynomials.
+
+    ProverSingle.new / new_with_engine     prover.rs:62-105, 181-326   vk hash, instance scalars into the transcript, instance polys
+    commit_phase(phase, witness)           prover.rs:329-499           blinding rows, blinds, commit_lagrange per column, challenges
+    create_proof()                         prover.rs:517-897           theta .. x, the four arguments, evaluate_h, evals, SHPLONK
+
+One circuit instance per prover (the reference's `ProverSingle`); the batch `Prover` over several circuits is not mirrored.
+All size-n and size-n*e vectors live on the device (`ops`); the host holds scalars, the transcript and the RNG.
+KZG: `P::QUERY_INSTANCE == false` (shplonk/prover.rs:113), so instance columns enter the transcript as scalars and are not opened.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+
+from .. import fields as F
+from . import arguments as A
+from . import shplonk
+from .keygen import FR_DELTA, ProvingKey
+
+R = F.R_MOD
+
+
+class ProverError(Exception):
+    """plonk::Error (plonk/error.rs)."""
+
+
+def evaluate_h(ops, pk: ProvingKey, advice_polys, instance_polys, challenges, y, beta, gamma, theta, lookups, shuffles, permutation):
+    """Evaluator::evaluate_h (plonk/evaluation.rs:317-623) for one circuit: all columns to the extended coset, the custom-gate graph
+    over every extended row, then the permutation / lookup / shuffle folds, each `value = value * y + term`."""
+    cs, ev = pk.vk.cs, pk.ev
+    fixed = pk.fixed_cosets
+    advice = [ops.coeff_to_extended(p) for p in advice_polys]                       # evaluation.rs:344-352
+    instance = [ops.coeff_to_extended(p) for p in instance_polys]                   # evaluation.rs:353-361
+    values = ops.graph(ev.custom_gates, fixed, advice, instance, challenges, beta, gamma, theta, y, extended=True)
+    if permutation:                                                                 # evaluation.rs:397-493
+        source = {"advice": advice, "fixed": fixed, "instance": instance}
+        col_values = [source[kind][index] for kind, index in cs.permutation_columns]
+        values = ops.permutation_fold(values, [s.permutation_product_coset for s in permutation], col_values,
+                                      pk.permutation.cosets, cs.degree() - 2, pk.l0, pk.l_last, pk.l_active_row, beta, gamma, y,
+                                      FR_DELTA, cs.blinding_factors())
+    for n_l, lookup in enumerate(lookups):                                          # evaluation.rs:496-567
+        product_coset = ops.coeff_to_extended(lookup.product_poly)
+        permuted_input_coset = ops.coeff_to_extended(lookup.permuted_input_poly)
+        permuted_table_coset = ops.coeff_to_extended(lookup.permuted_table_poly)
+        table_values = ops.graph(ev.lookups[n_l], fixed, advice, instance, challenges, beta, gamma, theta, y, extended=True)
+        values = ops.lookup_fold(values, table_values, product_coset, permuted_input_coset, permuted_table_coset, pk.l0, pk.l_last,
+                                 pk.l_active_row, beta, gamma, y)
+    for n_s, shuffle in enumerate(shuffles):                                        # evaluation.rs:570-620
+        product_coset = ops.coeff_to_extended(shuffle.product_poly)
+        input_values = ops.graph(ev.shuffles[2 * n_s], fixed, advice, instance, challenges, beta, gamma, theta, y, extended=True)
+        shuffle_values = ops.graph(ev.shuffles[2 * n_s + 1], fixed, advice, instance, challenges, beta, gamma, theta, y,
+                                   extended=True)
+        values = ops.shuffle_fold(values, input_values, shuffle_values, product_coset, pk.l0, pk.l_last, pk.l_active_row, y)
+    return values
+
+
+class ProverSingle:
+    def __init__(self, ops, pk: ProvingKey, instance: Sequence[Sequence[int]], rng, transcript, num_threads: int = 1):
+        """prover.rs:181-326.  `instance`: one list of canonical ints per instance column.  `num_threads` is the reference's
+        `current_num_threads()` (it seeds the vanishing argument's random polynomial, vanishing/prover.rs:57-81)."""
+        cs = pk.vk.cs
+        if len(instance) != cs.num_instance_columns:
+            raise ProverError("InvalidInstances")
+        self.ops, self.pk, self.rng, self.transcript, self.num_threads = ops, pk, rng, transcript, num_threads
+        pk.vk.hash_into(transcript)                                                 # [TRANSCRIPT-1]
+        n = ops.n
+        self.phases = cs.phases()
+        self.instance_values, self.instance_polys = [], []
+        for values in instance:                                                     # [TRANSCRIPT-2]
+            if len(values) > n - (cs.blinding_factors() + 1):
+                raise ProverError("InstanceTooLarge")
+            for v in values:
+                transcript.common_scalar(v)
+            poly = ops.zeros(n)
+            ops.write_ints(poly, 0, list(values))
+            self.instance_values.append(poly)
+            self.instance_polys.append(ops.lagrange_to_coeff(ops.clone(poly)))
+        self.advice_polys: List[Optional[object]] = [None] * cs.num_advice_columns
+        self.advice_blinds: List[int] = [0] * cs.num_advice_columns
+        self.challenges: Dict[int, int] = {}
+        self.next_phase_index = 0
+
+    @staticmethod
+    def new(ops, pk, instance, rng, transcript, num_threads: int = 1) -> "ProverSingle":
+        return ProverSingle(ops, pk, instance, rng, transcript, num_threads)
+
+    # prover.rs:329-499
+    def commit_phase(self, phase: int, witness: Sequence[Optional[object]]) -> Dict[int, int]:
+        ops, cs, rng = self.ops, self.pk.vk.cs, self.rng
+        if self.next_phase_index >= len(self.phases):
+            raise ProverError("All phases already committed")
+        current_phase = self.phases[self.next_phase_index]
+        if phase != current_phase:
+            raise ProverError(f"Committing invalid phase.  Expected {current_phase}, got {phase}")
+        column_indices = [i for i, p in enumerate(cs.advice_column_phase) if p == current_phase]
+        if len(witness) != cs.num_advice_columns:
+            raise ProverError(f"unexpected length in witness_circuitk.  Got {len(witness)}, expected {cs.num_advice_columns}")
+        n = ops.n
+        columns = {}
+        for column_index, advice_column in enumerate(witness):
+            if column_index in column_indices:
+                if advice_column is None:
+                    raise ProverError(f"expected advice column with index {column_index} at phase {current_phase}")
+                poly = ops.as_poly(advice_column)
+                if ops.rows(poly) != n:
+                    raise ProverError(f"expected advice column with index {column_index} to have length {n}")
+                columns[column_index] = poly
+            elif advice_column is not None:
+                raise ProverError(f"expected no advice column with index {column_index} at phase {current_phase}")
+        unusable_rows_start = n - (cs.blinding_factors() + 1)
+        unblinded = set(cs.unblinded_advice_columns)
+        for column_index in column_indices:                                         # prover.rs:406-421
+            if column_index not in unblinded:
+                ops.write_ints(columns[column_index], unusable_rows_start, A._draw(rng, n - unusable_rows_start))
+        blinds = [0 if i in unblinded else rng.random_fr() for i in column_indices]  # prover.rs:424-434
+        commitments = ops.commit_lagrange_many([columns[i] for i in column_indices])
+        for c in commitments:                                                       # [TRANSCRIPT-3]
+            self.transcript.write_point(c)
+        for column_index, blind in zip(column_indices, blinds):
+            self.advice_polys[column_index] = columns[column_index]
+            self.advice_blinds[column_index] = blind
+        for index, ch_phase in enumerate(cs.challenge_phase):                       # [TRANSCRIPT-4]
+            if ch_phase == current_phase:
+                assert index not in self.challenges
+                self.challenges[index] = self.transcript.squeeze_challenge_scalar()
+        self.next_phase_index += 1
+        return dict(self.challenges)
+
+    # prover.rs:517-897
+    def create_proof(self) -> None:
+        ops, pk, rng, transcript = self.ops, self.pk, self.rng, self.transcript
+        cs, domain = pk.vk.cs, pk.vk.domain
+        assert len(self.challenges) == cs.num_challenges
+        challenges = [self.challenges[i] for i in range(cs.num_challenges)]
+        advice_values, instance_values = self.advice_polys, self.instance_values
+
+        theta = transcript.squeeze_challenge_scalar()                               # [TRANSCRIPT-5]
+        permuted_lookups = [A.lookup_commit_permuted(ops, lookup, pk, theta, advice_values, instance_values, challenges, rng,
+                                                     transcript) for lookup in cs.lookups]          # [TRANSCRIPT-6]
+        beta = transcript.squeeze_challenge_scalar()                                # [TRANSCRIPT-7]
+        gamma = transcript.squeeze_challenge_scalar()                               # [TRANSCRIPT-8]
+        permutation = A.permutation_commit(ops, pk, advice_values, instance_values, beta, gamma, rng, transcript)   # [TRANSCRIPT-9]
+        lookups = [A.lookup_commit_product(ops, p, pk, beta, gamma, rng, transcript) for p in permuted_lookups]     # [TRANSCRIPT-10]
+        shuffles = [A.shuffle_commit_product(ops, s, pk, theta, gamma, advice_values, instance_values, challenges, rng, transcript)
+                    for s in cs.shuffles]                                           # [TRANSCRIPT-11]
+        vanishing = A.vanishing_commit(ops, domain, rng, transcript, self.num_threads)              # [TRANSCRIPT-12]
+        advice_polys = [ops.lagrange_to_coeff(p) for p in advice_values]            # prover.rs:665-685 (consumes the Lagrange form)
+        y = transcript.squeeze_challenge_scalar()                                   # [TRANSCRIPT-13]
+        h_poly = evaluate_h(ops, pk, advice_polys, self.instance_polys, challenges, y, beta, gamma, theta, lookups, shuffles,
+                            permutation)
+        vanishing = A.vanishing_construct(ops, vanishing, domain, h_poly, rng, transcript)          # [TRANSCRIPT-14]
+        del h_poly
+        x = transcript.squeeze_challenge_scalar()                                   # [TRANSCRIPT-15]
+        xn = pow(x, ops.n, R)
+        for column, at in cs.advice_queries:                                        # [TRANSCRIPT-17]
+            transcript.write_scalar(ops.eval_polynomial(advice_polys[column], domain.rotate_omega(x, at)))
+        for column, at in cs.fixed_queries:                                         # [TRANSCRIPT-18]
+            transcript.write_scalar(ops.eval_polynomial(pk.fixed_polys[column], domain.rotate_omega(x, at)))
+        vanishing = A.vanishing_evaluate(ops, vanishing, x, xn, transcript)         # [TRANSCRIPT-19]
+        A.permutation_pk_evaluate(ops, pk, x, transcript)                           # [TRANSCRIPT-20]
+        A.permutation_evaluate(ops, permutation, pk, x, transcript)                 # [TRANSCRIPT-21]
+        for c in lookups:                                                           # [TRANSCRIPT-22]
+            A.lookup_evaluate(ops, c, domain, x, transcript)
+        for c in shuffles:                                                          # [TRANSCRIPT-23]
+            A.shuffle_evaluate(ops, c, domain, x, transcript)
+        queries = [(domain.rotate_omega(x, at), advice_polys[column], self.advice_blinds[column])
+                   for column, at in cs.advice_queries]                             # prover.rs:842-851
+        queries += A.permutation_open(permutation, pk, x)
+        for c in lookups:
+            queries += A.lookup_open(c, domain, x)
+        for c in shuffles:
+            queries += A.shuffle_open(c, domain, x)
+        queries += [(domain.rotate_omega(x, at), pk.fixed_polys[column], 0) for column, at in cs.fixed_queries]
+        queries += A.permutation_pk_open(pk, x)
+        queries += A.vanishing_open(vanishing, x)
+        shplonk.create_proof(ops, transcript, queries)                              # prover.rs:884-890
+
+
+def create_proof(ops, pk: ProvingKey, instance, witness_fn, rng, transcript, num_threads: int = 1) -> None:
+    """plonk::create_proof for one circuit (halo2_proofs/src/plonk/prover.rs:38-123): `witness_fn(phase, challenges)` plays the
+    WitnessCalculator and returns the advice columns of that phase (None for the others)."""
+    prover = ProverSingle(ops, pk, instance, rng, transcript, num_threads)
+    challenges: Dict[int, int] = {}
+    for phase in prover.phases:
+        challenges = prover.commit_phase(phase, witness_fn(phase, challenges))
+    prover.create_proof()
