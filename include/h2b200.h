@@ -214,6 +214,14 @@ uint64_t h2b_launch_count(const h2b_ctx* ctx);   /* kernels launched by this con
 /* synthetic benchmark input: d_out[i] = [t0 + i]G as 64-byte affine points, on device 0. */
 int h2b_synth_bases(h2b_ctx* ctx, void* d_out, size_t n, uint64_t t0);
 
+/* ---- set-up helpers (not on the proving hot path) -----------------------------------------------------------------
+ * h2b_g1_fixed_base_mul_device: d_out[i] = [k_i] G (64-byte affine, G = (1, 2)) for n Montgomery scalars on device 0: the fixed-base
+ *                       multiplications of ParamsKZG::setup (poly/kzg/commitment.rs:74-112: g[i] = [s^i] G, g_lagrange[i] = [L_i(s)] G).
+ * h2b_fr_from_u512_device: `Fr::from_u512` / `from_uniform_bytes` / `Fr::random` (halo2curves 0.6): n x 64 bytes, each a little-endian
+ *                       512-bit integer, reduced mod r into Montgomery form (vanishing/prover.rs:76-81 draws n of them). */
+int h2b_g1_fixed_base_mul_device(h2b_ctx* ctx, const void* d_scalars, size_t n, void* d_out_affine);
+int h2b_fr_from_u512_device(h2b_ctx* ctx, const void* d_limbs64, size_t n, void* d_out);
+
 /* integer-multiply pipe calibration: runs a dependent-free IMAD.WIDE loop on every SM and returns the
  * sustained rate in units of 32x32->64 multiply-adds per second (the MSM / NTT roofline denominator). */
 int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_s);

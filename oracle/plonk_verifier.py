@@ -64,7 +64,7 @@ class _Msm:
         return acc
 
 
-def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n: int) -> bool:
+def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n: int, debug: dict = None) -> bool:
     cs, domain = vk.cs, vk.domain
     if len(instances) != cs.num_instance_columns:
         raise VerifyError("InvalidInstances")
@@ -166,6 +166,9 @@ def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n
                         l_last * (sh["product_eval"] ** 2 - sh["product_eval"]) % P,
                         (left - right) * active % P]
     expected_h_eval = _fold(y, expressions) * _inv(xn - 1) % P                      # vanishing/verifier.rs:88-96
+    if debug is not None:
+        debug.update(x=x, y=y, theta=theta, beta=beta, gamma=gamma, expected_h_eval=expected_h_eval, expressions=expressions,
+                     challenges=challenges)
     h_commitment = _Msm()
     for c in reversed(h_commitments):
         h_commitment.scale(xn)

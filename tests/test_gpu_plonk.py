@@ -65,3 +65,43 @@ def test_proof_verifies_k12(ctx):
         assert not plonk_verifier.verify_proof(vk, circ.instances(), bytes(bad), SECRET, 1 << k)
     except ValueError:
         pass
+
+
+def test_params_setup_matches_the_oracle(ctx):
+    """ParamsKZG::setup (kzg/commitment.rs:64-131) on the device == the C restatement, point for point."""
+    k = 7
+    dom = R.EvaluationDomain(3, k)
+    g, gl = C.kzg_setup(k, C.mont_from_int(SECRET, R.R_MOD), C.mont_from_int(dom.omega, R.R_MOD))
+    params = h2b200.ParamsKZG.setup(k, SECRET, h2b200.B200Engine(ctx))
+    assert np.array_equal(params.g.cpu().numpy().view(np.uint64), g)
+    assert np.array_equal(params.g_lagrange.cpu().numpy().view(np.uint64), gl)
+
+
+def test_fr_from_u512(ctx):
+    """Fr::from_u512 / from_uniform_bytes: 512-bit little-endian integer mod r, edge values included."""
+    engine = h2b200.B200Engine(ctx)
+    ops = DeviceOps(None, engine, h2b200.EvaluationDomain(3, 4, ctx))
+    rng = np.random.default_rng(3)
+    limbs = rng.integers(0, 1 << 63, size=(67, 8), dtype=np.uint64) * np.uint64(2) + rng.integers(0, 2, size=(67, 8), dtype=np.uint64)
+    full = np.uint64(0xFFFFFFFFFFFFFFFF)
+    limbs[0] = 0
+    limbs[1] = full
+    limbs[2] = [int(x) for x in h2b200.fields.limbs(R.R_MOD)] + [0, 0, 0, 0]
+    limbs[3] = [0, 0, 0, 0] + [int(x) for x in h2b200.fields.limbs(R.R_MOD - 1)]
+    limbs[4, :4], limbs[4, 4:] = full, 0
+    exp = [sum(int(row[i]) << (64 * i) for i in range(8)) % R.R_MOD for row in limbs]
+    assert ops.to_ints(ops.from_u512(limbs)) == exp
+
+
+def test_proof_k16_device_srs(ctx):
+    """A 2^16-row proof with the SRS built on the device; checked by the verify_proof restatement."""
+    k = 16
+    circ = example.MyCircuit(k, 5)
+    cc = circ.compile()
+    cs = plonk.circuit.ConstraintSystemBack(cc.cs)
+    engine = h2b200.B200Engine(ctx)
+    ops = DeviceOps(h2b200.ParamsKZG.setup(k, SECRET, engine), engine, h2b200.EvaluationDomain(cs.degree(), k, ctx))
+    vk = plonk.keygen_vk(ops, cc)
+    pk = plonk.keygen_pk(ops, vk, cc)
+    proof = _prove(circ, ops, pk, RNG.OneNg(), 16)
+    assert plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << k)

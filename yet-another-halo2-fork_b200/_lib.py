@@ -59,6 +59,8 @@ SYMBOLS = {
     "h2b_launch_count": (_u64, [_vp]),
     "h2b_imad_peak": (_int, [_vp, _pd, _pd]),
     "h2b_synth_bases": (_int, [_vp, _vp, _sz, _u64]),
+    "h2b_g1_fixed_base_mul_device": (_int, [_vp, _vp, _sz, _vp]),
+    "h2b_fr_from_u512_device": (_int, [_vp, _vp, _sz, _vp]),
 }
 
 

@@ -22,6 +22,7 @@
 #include "msm_kernels.hpp"
 #include "poly_kernels.hpp"
 #include "quotient_kernels.hpp"
+#include "setup_kernels.hpp"
 #include "ntt.cuh"
 #include "ntt_plan.hpp"
 #include "ntt_kernels.hpp"
@@ -1498,6 +1499,33 @@ int h2b_synth_bases(h2b_ctx* ctx, void* d_out, size_t n, uint64_t t0) {
     H2B_CK(cudaSetDevice(d.id));
     begin_call(d);
     if (n) H2B_LAUNCH(d, "synth_bases", MK.synth_bases, (unsigned)((n + 127) / 128), 128, 0, (Affine*)d_out, (uint64_t)n, t0);
+    H2B_CK(cudaGetLastError());
+    return end_call(ctx, d);
+}
+
+// ---- set-up helpers (ParamsKZG::setup fixed-base multiplications, Fr::random wide reduction) ----------------
+const SetupKernelTable& SK = setup_kernel_table();
+
+int h2b_g1_fixed_base_mul_device(h2b_ctx* ctx, const void* d_scalars, size_t n, void* d_out) {
+    if (!ctx) return H2B_E_INVALID;
+    if (n && (!d_scalars || !d_out)) return ctx->fail(H2B_E_INVALID, "g1_fixed_base_mul: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    begin_call(d);
+    if (n) H2B_LAUNCH(d, "g1_fixed_base_mul", SK.fixed_base_mul, (unsigned)((n + 127) / 128), 128, 0, (const Fr*)d_scalars, (uint64_t)n, (Affine*)d_out);
+    H2B_CK(cudaGetLastError());
+    return end_call(ctx, d);
+}
+
+int h2b_fr_from_u512_device(h2b_ctx* ctx, const void* d_limbs, size_t n, void* d_out) {
+    if (!ctx) return H2B_E_INVALID;
+    if (n && (!d_limbs || !d_out)) return ctx->fail(H2B_E_INVALID, "fr_from_u512: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    begin_call(d);
+    if (n) H2B_LAUNCH(d, "fr_from_u512", SK.fr_from_u512, (unsigned)((n + 255) / 256), 256, 0, (const uint32_t*)d_limbs, (uint64_t)n, (Fr*)d_out);
     H2B_CK(cudaGetLastError());
     return end_call(ctx, d);
 }

@@ -37,12 +37,18 @@ class DeviceOps:
         return DeviceOps(self.params, self.engine, domain)
 
     # ---- data movement ------------------------------------------------------------------------------------------------------
+    # torch launches its copies / fills on its own stream while the library works on the context's streams: every torch-side
+    # write is completed (`_done`) before the tensor can reach a library call.  Library calls are synchronous on return.
+    def _done(self, t=None):
+        self.torch.cuda.current_stream().synchronize()
+        return t
+
     def from_ints(self, values: Sequence[int]):
         return self.upload(F.fr_array(list(values)))
 
     def upload(self, mont: np.ndarray):
         a = np.ascontiguousarray(mont, dtype=np.uint64).reshape(-1, 4)
-        return self.torch.from_numpy(a.view(np.int64)).to("cuda")
+        return self._done(self.torch.from_numpy(a.view(np.int64)).to("cuda"))
 
     def download(self, p) -> np.ndarray:
         return p.cpu().numpy().view(np.uint64)
@@ -51,10 +57,10 @@ class DeviceOps:
         return [F.fr_int(row) for row in self.download(p)]
 
     def zeros(self, rows: int):
-        return self.torch.zeros((rows, 4), dtype=self.torch.int64, device="cuda")
+        return self._done(self.torch.zeros((rows, 4), dtype=self.torch.int64, device="cuda"))
 
     def clone(self, p):
-        return p.clone()
+        return self._done(p.clone())
 
     def rows(self, p) -> int:
         return p.shape[0]
@@ -62,26 +68,27 @@ class DeviceOps:
     def write_ints(self, p, start: int, values: Sequence[int]) -> None:
         if len(values):
             p[start:start + len(values)] = self.upload(F.fr_array(list(values)))
+            self._done()
 
     def read_ints(self, p, start: int, count: int) -> List[int]:
         return [F.fr_int(row) for row in self.download(p[start:start + count])]
 
     def slice(self, p, start: int, count: int):
-        return p[start:start + count].clone()
+        return self._done(p[start:start + count].clone())
 
     def resize(self, p, rows: int):
         if p.shape[0] >= rows:
-            return p[:rows].clone()
+            return self._done(p[:rows].clone())
         out = self.zeros(rows)
         out[:p.shape[0]] = p
-        return out
+        return self._done(out)
 
     def gather_rows(self, p, index: np.ndarray):
         idx = self.torch.from_numpy(np.ascontiguousarray(index, dtype=np.int64)).to("cuda")
-        return p.index_select(0, idx)
+        return self._done(p.index_select(0, idx))
 
     def concat(self, parts):
-        return self.torch.cat(list(parts), dim=0)
+        return self._done(self.torch.cat(list(parts), dim=0))
 
     # ---- transforms (poly/domain.rs) ---------------------------------------------------------------------------------------
     def lagrange_to_coeff(self, p):
@@ -163,7 +170,7 @@ class DeviceOps:
         from . import circuit as C
         from . import polyexpr as PX
         r_inv = pow(F.MONT_R, -1, F.R_MOD)
-        return self.download(PX.pointwise(self, C.mul(PX.col(0), C.const(r_inv)), [p])[:rows])
+        return self.download(PX.pointwise(self, C.mul(PX.col(0), C.const(r_inv)), [p])[:rows].contiguous())
 
     def from_canonical(self, canon: np.ndarray, rows: int):
         """(m, 4) canonical limbs -> a Montgomery polynomial of `rows` elements (zero padded)."""
@@ -171,9 +178,16 @@ class DeviceOps:
         from . import polyexpr as PX
         raw = self.zeros(rows)
         raw[:canon.shape[0]] = self.upload(canon)
+        self._done()
         return PX.pointwise(self, C.mul(PX.col(0), C.const(F.MONT_R % F.R_MOD)), [raw])
 
     def from_u512(self, limbs: np.ndarray):
         """`Fr::random` / `from_u512`: (m, 8) uint64 little-endian limbs of 512-bit integers, reduced mod r."""
-        return self.from_u512_device(limbs) if hasattr(self.ctx.lib, "h2b_fr_from_u512_device") else \
-            self.from_ints([sum(int(row[i]) << (64 * i) for i in range(8)) % F.R_MOD for row in limbs])
+        import ctypes
+        limbs = np.ascontiguousarray(limbs, dtype=np.uint64).reshape(-1, 8)
+        m = limbs.shape[0]
+        src = self.torch.from_numpy(limbs.view(np.int64)).to("cuda")
+        out = self.zeros(m)
+        self.ctx.check(self.ctx.lib.h2b_fr_from_u512_device(self.ctx.handle, ctypes.c_void_p(src.data_ptr()), m,
+                                                            ctypes.c_void_p(out.data_ptr())))
+        return out
