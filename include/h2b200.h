@@ -221,6 +221,11 @@ int h2b_synth_bases(h2b_ctx* ctx, void* d_out, size_t n, uint64_t t0);
  *                       512-bit integer, reduced mod r into Montgomery form (vanishing/prover.rs:76-81 draws n of them). */
 int h2b_g1_fixed_base_mul_device(h2b_ctx* ctx, const void* d_scalars, size_t n, void* d_out_affine);
 int h2b_fr_from_u512_device(h2b_ctx* ctx, const void* d_limbs64, size_t n, void* d_out);
+/* h2b_fr_random_chacha20_device: the random polynomial of the vanishing argument (plonk/vanishing/prover.rs:57-81).  Stream i is
+ *                       rand_chacha::ChaCha20Rng::from_seed(seeds32[i]) (host, n_streams x 32 bytes) and fills
+ *                       d_out[offsets[i] .. offsets[i+1]) (host offsets, n_streams + 1 entries, offsets[0] = 0) with consecutive
+ *                       Fr::random draws: element j of a stream = from_u512(ChaCha20 block j).  One thread per element. */
+int h2b_fr_random_chacha20_device(h2b_ctx* ctx, const void* seeds32, const uint64_t* offsets, size_t n_streams, void* d_out);
 
 /* integer-multiply pipe calibration: runs a dependent-free IMAD.WIDE loop on every SM and returns the
  * sustained rate in units of 32x32->64 multiply-adds per second (the MSM / NTT roofline denominator). */

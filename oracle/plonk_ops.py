@@ -95,6 +95,18 @@ class RefOps:
     def from_u512(self, limbs: np.ndarray):
         return [sum(int(row[i]) << (64 * i) for i in range(8)) % P for row in limbs]
 
+    def permute_expression_pair(self, compressed_input, compressed_table, usable: int):
+        from h2b200.plonk.arguments import permute_expression_pair
+        pi, pt = permute_expression_pair(self.to_canonical(compressed_input, usable), self.to_canonical(compressed_table, usable))
+        return self.from_canonical(pi, self.n), self.from_canonical(pt, self.n)
+
+    def random_poly_chacha20(self, seeds, chunks):
+        from h2b200.plonk.rng import ChaCha20Rng
+        out = []
+        for seed, (_, length) in zip(seeds, chunks):
+            out += self.from_u512(ChaCha20Rng.from_seed(seed).random_fr_limbs(length))
+        return out
+
     # ---- transforms ---------------------------------------------------------------------------------------------------------
     def lagrange_to_coeff(self, p):
         return self.domain.lagrange_to_coeff(p)

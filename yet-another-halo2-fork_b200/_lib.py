@@ -61,6 +61,7 @@ SYMBOLS = {
     "h2b_synth_bases": (_int, [_vp, _vp, _sz, _u64]),
     "h2b_g1_fixed_base_mul_device": (_int, [_vp, _vp, _sz, _vp]),
     "h2b_fr_from_u512_device": (_int, [_vp, _vp, _sz, _vp]),
+    "h2b_fr_random_chacha20_device": (_int, [_vp, _vp, ctypes.POINTER(ctypes.c_uint64), _sz, _vp]),
 }
 
 

@@ -1530,6 +1530,30 @@ int h2b_fr_from_u512_device(h2b_ctx* ctx, const void* d_limbs, size_t n, void* d
     return end_call(ctx, d);
 }
 
+int h2b_fr_random_chacha20_device(h2b_ctx* ctx, const void* seeds32, const uint64_t* offsets, size_t n_streams, void* d_out) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!n_streams) return H2B_OK;
+    if (!seeds32 || !offsets || !d_out) return ctx->fail(H2B_E_INVALID, "fr_random_chacha20: null argument");
+    for (size_t i = 0; i < n_streams; i++)
+        if (offsets[i] > offsets[i + 1]) return ctx->fail(H2B_E_INVALID, "fr_random_chacha20: offsets must not decrease");
+    if (offsets[0] != 0) return ctx->fail(H2B_E_INVALID, "fr_random_chacha20: offsets[0] must be 0");
+    const uint64_t n = offsets[n_streams];
+    if (!n) return H2B_OK;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    Stage st;
+    size_t o_seeds = st.put(seeds32, n_streams * 32), o_off = st.put(offsets, (n_streams + 1) * sizeof(uint64_t));
+    H2B_CK(d.q_stage.reserve(st.host.size() + 64));
+    begin_call(d);
+    H2B_CK(d.ring.h2d(d.q_stage.p, st.host.data(), st.host.size(), d.stream));
+    uint8_t* base = d.q_stage.as<uint8_t>();
+    H2B_LAUNCH(d, "fr_random_chacha20", SK.fr_random_chacha20, (unsigned)((n + 255) / 256), 256, 0, (const uint32_t*)(base + o_seeds),
+               (const uint64_t*)(base + o_off), (uint32_t)n_streams, n, (Fr*)d_out);
+    H2B_CK(cudaGetLastError());
+    return end_call(ctx, d);
+}
+
 int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_s) {
     if (!ctx || !wide_mads_per_s || !field_muls_per_s) return H2B_E_INVALID;
     std::lock_guard<std::mutex> lk(ctx->mu);

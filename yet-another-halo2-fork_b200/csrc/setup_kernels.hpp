@@ -8,6 +8,7 @@ namespace h2b {
 struct SetupKernelTable {
     void (*fixed_base_mul)(const Fr*, uint64_t, Affine*);
     void (*fr_from_u512)(const uint32_t*, uint64_t, Fr*);
+    void (*fr_random_chacha20)(const uint32_t*, const uint64_t*, uint32_t, uint64_t, Fr*);
 };
 const SetupKernelTable& setup_kernel_table();
 }  // namespace h2b

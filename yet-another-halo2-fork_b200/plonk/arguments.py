@@ -20,7 +20,6 @@ from ..evaluation import CONSTANT, THETA, GraphEvaluator
 from . import circuit as C
 from . import polyexpr as PX
 from .keygen import FR_DELTA
-from .rng import ChaCha20Rng, limbs512_to_ints
 
 R = F.R_MOD
 
@@ -91,12 +90,10 @@ def lookup_commit_permuted(ops, arg: C.LookupArgument, pk, theta: int, advice_va
                                                          challenges)
     p.compressed_table_expression = compress_expressions(ops, arg.table_expressions, theta, pk, advice_values, instance_values,
                                                          challenges)
-    perm_in, perm_tab = permute_expression_pair(ops.to_canonical(p.compressed_input_expression, usable),
-                                                ops.to_canonical(p.compressed_table_expression, usable))
+    p.permuted_input_expression, p.permuted_table_expression = ops.permute_expression_pair(
+        p.compressed_input_expression, p.compressed_table_expression, usable)
     in_tail, tab_tail = _draw(rng, bf + 1), _draw(rng, bf + 1)                     # lookup/prover.rs:469-471
-    p.permuted_input_expression = ops.from_canonical(perm_in, n)
     ops.write_ints(p.permuted_input_expression, usable, in_tail)
-    p.permuted_table_expression = ops.from_canonical(perm_tab, n)
     ops.write_ints(p.permuted_table_expression, usable, tab_tail)
 
     def commit_values(values):                                                      # lookup/prover.rs:129-135
@@ -300,11 +297,9 @@ def vanishing_commit(ops, domain, rng, transcript, num_threads: int) -> Vanishin
         offsets += [start + i * chunk_size for i in range(num_threads - len(offsets))]
     offsets = offsets[:num_threads]
     seeds = {off: rng.fill_bytes(32) for off in offsets}                            # vanishing/prover.rs:70-73, in iterator order
-    pieces = []
-    for off, length in parallelize_chunks(n, num_threads):
-        pieces.append(ChaCha20Rng.from_seed(seeds[off]).random_fr_limbs(length))
+    chunks = parallelize_chunks(n, num_threads)
     c = VanishingCommitted()
-    c.random_poly = ops.from_u512(np.concatenate(pieces, axis=0))
+    c.random_poly = ops.random_poly_chacha20([seeds[off] for off, _ in chunks], chunks)
     c.random_blind = rng.random_fr()
     transcript.write_point(ops.commit(c.random_poly))
     return c
