@@ -266,6 +266,48 @@ def proof_sequence_resident(ctx, eng):
     return ms, ctx.launch_count() - l0
 
 
+def k20_proof(ctx, eng, k: int = SEQ_K, reps: int = 3):
+    """A real proof: the reference's frontend_backend_split circuit (gate with rotation, lookup, shuffle, copy constraints,
+    second-phase column, instance) at 2^k rows, through the prover mirror (plonk.create_proof = keygen'd pk + ProverSingle +
+    SHPLONK + Blake2b transcript) with every vector on the device.  tests/test_gpu_plonk.py checks the same path byte for byte
+    against the CPU restatement and with the verify_proof restatement; here it is only timed.  Timed region = create_proof incl.
+    witness columns handed over as host arrays (H2D inside) and the proof bytes coming back."""
+    import hashlib
+    import torch
+    import h2b200
+    from h2b200 import plonk
+    from h2b200.plonk import example, rng as RNG
+    from h2b200.plonk.ops import DeviceOps
+    t0 = time.perf_counter()
+    circ = example.MyCircuit(k, 42)
+    cc = circ.compile()
+    cs = plonk.circuit.ConstraintSystemBack(cc.cs)
+    params = h2b200.ParamsKZG.setup(k, 0x1234567, eng)
+    ops = DeviceOps(params, eng, h2b200.EvaluationDomain(cs.degree(), k, ctx))
+    pk = plonk.keygen_pk(ops, plonk.keygen_vk(ops, cc), cc)
+    circ.witness(0, {})                                       # first-phase columns are an input of the prover: laid out once
+    setup_s = time.perf_counter() - t0
+    times, launches, proof = [], 0, b""
+    for rep in range(reps + 1):
+        tr = plonk.Blake2bWrite()
+        l0 = ctx.launch_count()
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        plonk.create_proof(ops, pk, circ.instances(), circ.witness, RNG.OneNg(), tr, num_threads=16)
+        torch.cuda.synchronize()
+        if rep:
+            times.append((time.perf_counter() - t) * 1e3)
+        launches = ctx.launch_count() - l0
+        proof = tr.finalize()
+    d = ops.domain
+    return {"what": f"create_proof of the frontend_backend_split circuit at k = {k} (KZG / SHPLONK / Blake2b; degree {cs.degree()}, "
+                    f"extended_k = {d.extended_k}, {circ.units} units of 51 rows), host witness columns in, proof bytes out",
+            "value": min(times), "unit": "ms", "runs_ms": times, "gpu_launches": launches, "proof_bytes": len(proof),
+            "proof_sha256": hashlib.sha256(proof).hexdigest(), "rng": "OneNg, num_threads = 16",
+            "h2d_bytes_per_proof": 4 * 32 * (1 << k), "d2h_bytes_per_proof": len(proof),
+            "setup_keygen_s": setup_s, "verified": "tests/test_gpu_plonk.py (verify_proof restatement, and proof bytes == CPU restatement)"}
+
+
 def proof_sequence_cpu():
     """One call of each kind through the oracle port, scaled by SEQ_COUNTS (bounded sample)."""
     from oracle import cref as C
@@ -514,10 +556,14 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
             "what": "same MSM / NTT counts with device-resident columns, plus the Z-polynomial inversions / running products, the "
                     "quotient folds over 2^23 rows and the opening helpers (SURVEY 8f N1-N3) on the device; witness upload included",
             "extra_counts": RES_COUNTS, "value": res_ms, "unit": "ms", "gpu_launches": res_launches}
+        line["k20_proof"] = k20_proof(ctx, eng)
         if not args.no_cpu:
             cpu_total, cpu_parts, thr = proof_sequence_cpu()
             line["k20_kernel_sequence"]["cpu_baseline"] = {"value": cpu_total, "unit": "ms", "cores": thr, "kind": "port",
                                                            "sample": "one call of each kind timed, scaled by the counts", "per_call_ms": cpu_parts}
+            line["k20_proof"]["cpu_baseline"] = {"value": cpu_total, "unit": "ms", "cores": thr, "kind": "port",
+                                                 "sample": "the MSM + NTT calls of the same proof only (a lower bound on the reference prover): "
+                                                           "one call of each kind timed, scaled by the counts"}
     if world == 1 and not args.no_cpu:
         ms, threads = cpu_msm_sample(CPU_SAMPLE_K)
         line["cpu_baseline"] = {"value": scale_to_full(ms, CPU_SAMPLE_K, MSM_K), "unit": "ms", "cores": threads, "kind": "port",

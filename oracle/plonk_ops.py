@@ -131,6 +131,9 @@ class RefOps:
     def commit_lagrange_many(self, polys):
         return [self.commit_lagrange(p) for p in polys]
 
+    def commit_many(self, polys):
+        return [self.commit(p) for p in polys]
+
     # ---- pointwise programs ---------------------------------------------------------------------------------------------------
     def graph(self, g, fixed, advice, instance, challenges, beta, gamma, theta, y, extended: bool, previous=None):
         d = self.domain

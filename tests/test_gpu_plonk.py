@@ -105,3 +105,19 @@ def test_proof_k16_device_srs(ctx):
     pk = plonk.keygen_pk(ops, vk, cc)
     proof = _prove(circ, ops, pk, RNG.OneNg(), 16)
     assert plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << k)
+
+
+def test_proof_k20_verifies(ctx):
+    """BASELINE config 4 size: a 2^20-row proof (extended domain 2^23), SRS built on the device, accepted by the verify_proof
+    restatement; a second run with the same RNG gives the same bytes."""
+    k = 20
+    circ = example.MyCircuit(k, 42)
+    cc = circ.compile()
+    cs = plonk.circuit.ConstraintSystemBack(cc.cs)
+    engine = h2b200.B200Engine(ctx)
+    ops = DeviceOps(h2b200.ParamsKZG.setup(k, SECRET, engine), engine, h2b200.EvaluationDomain(cs.degree(), k, ctx))
+    vk = plonk.keygen_vk(ops, cc)
+    pk = plonk.keygen_pk(ops, vk, cc)
+    proof = _prove(circ, ops, pk, RNG.OneNg(), 16)
+    assert plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << k)
+    assert proof == _prove(circ, ops, pk, RNG.OneNg(), 16)

@@ -96,13 +96,13 @@ def lookup_commit_permuted(ops, arg: C.LookupArgument, pk, theta: int, advice_va
     ops.write_ints(p.permuted_input_expression, usable, in_tail)
     ops.write_ints(p.permuted_table_expression, usable, tab_tail)
 
-    def commit_values(values):                                                      # lookup/prover.rs:129-135
-        poly = ops.lagrange_to_coeff(ops.clone(values))
-        blind = rng.random_fr()
-        return poly, blind, ops.commit_lagrange(values)
-
-    p.permuted_input_poly, p.permuted_input_blind, c_in = commit_values(p.permuted_input_expression)
-    p.permuted_table_poly, p.permuted_table_blind, c_tab = commit_values(p.permuted_table_expression)
+    # commit_values (lookup/prover.rs:129-135) for both columns; the two commit_lagrange MSMs share one batched pipeline (the
+    # blinds are drawn in the reference's order and commitments do not consume randomness)
+    p.permuted_input_poly = ops.lagrange_to_coeff(ops.clone(p.permuted_input_expression))
+    p.permuted_input_blind = rng.random_fr()
+    p.permuted_table_poly = ops.lagrange_to_coeff(ops.clone(p.permuted_table_expression))
+    p.permuted_table_blind = rng.random_fr()
+    c_in, c_tab = ops.commit_lagrange_many([p.permuted_input_expression, p.permuted_table_expression])
     transcript.write_point(c_in)
     transcript.write_point(c_tab)
     return p
@@ -316,8 +316,8 @@ def vanishing_construct(ops, committed: VanishingCommitted, domain, h_poly, rng,
     c = VanishingConstructed()
     c.h_pieces = [ops.slice(h, i * n, n) for i in range(ops.rows(h) // n)]
     c.h_blinds = _draw(rng, len(c.h_pieces))
-    for piece in c.h_pieces:
-        transcript.write_point(ops.commit(piece))
+    for commitment in ops.commit_many(c.h_pieces):                                  # vanishing/prover.rs:136-146
+        transcript.write_point(commitment)
     c.committed = committed
     return c
 

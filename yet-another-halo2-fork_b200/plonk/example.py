@@ -50,6 +50,7 @@ class MyCircuit:
         self.units = max_rows // UNIT_ROWS
         assert self.units >= 1, "k too small for one unit"
         self._unit = self._layout_unit()
+        self._phase0 = None                                 # the first-phase columns do not depend on anything: tiled once
 
     # ---- one unit (synthesize_unit, :223-422) -----------------------------------------------------------------------------
     def _layout_unit(self):
@@ -134,7 +135,9 @@ class MyCircuit:
     def witness(self, phase: int, challenges: Dict[int, int]) -> List[Optional[np.ndarray]]:
         adv, _, rlc_rows, _ = self._unit
         if phase == 0:
-            return [self._tile(adv[A_]), self._tile(adv[B_]), self._tile(adv[C_]), None]
+            if self._phase0 is None:
+                self._phase0 = [self._tile(adv[A_]), self._tile(adv[B_]), self._tile(adv[C_])]
+            return [c.copy() for c in self._phase0] + [None]
         ch = challenges[0]
         e = [0] * UNIT_ROWS
         for row, a, b in rlc_rows:

@@ -164,6 +164,13 @@ class DeviceOps:
         out = self.engine.msm_batch(polys, self.params._gl_desc)
         return [F.jacobian_to_affine_ints(j) for j in out]
 
+    def commit_many(self, polys):
+        """The h-piece commits of the vanishing argument (vanishing/prover.rs:136-140), one batched MSM against `g`."""
+        polys = list(polys)
+        if not polys:
+            return []
+        return [F.jacobian_to_affine_ints(j) for j in self.engine.msm_batch(polys, self.params._g_desc)]
+
     def to_canonical(self, p, rows: int) -> np.ndarray:
         """First `rows` elements as canonical little-endian limbs (what `Fr: Ord` compares): a Montgomery multiplication by the
         element whose Montgomery form is 1 strips the factor R."""
