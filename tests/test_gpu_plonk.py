@@ -121,3 +121,25 @@ def test_proof_k20_verifies(ctx):
     proof = _prove(circ, ops, pk, RNG.OneNg(), 16)
     assert plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << k)
     assert proof == _prove(circ, ops, pk, RNG.OneNg(), 16)
+
+
+@pytest.mark.parametrize("minimum_degree", [5, None])
+def test_standard_plonk_bytes_match(ctx, minimum_degree):
+    """benches/plonk.rs circuit: one permutation set (minimum_degree 5, the benchmark's setting) and three chained sets (degree 3)."""
+    k = 6
+    circ = example.StandardPlonk(k, 9, minimum_degree)
+    cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circ)
+    ref_ops = plonk_ops.RefOps(k, SECRET, ref_dom)
+    ref_pk = plonk.keygen_pk(ref_ops, plonk.keygen_vk(ref_ops, cc), cc)
+    proof = _prove(circ, ops, pk, RNG.ChaCha20Rng(bytes(range(32))), 5)
+    assert proof == _prove(circ, ref_ops, ref_pk, RNG.ChaCha20Rng(bytes(range(32))), 5)
+    assert plonk_verifier.verify_proof(vk, [], proof, SECRET, 1 << k)
+
+
+def test_standard_plonk_k12(ctx):
+    """BASELINE.json configs[0]: the plonk benchmark circuit at k = 12 (KZG-BN254, SHPLONK)."""
+    k = 12
+    circ = example.StandardPlonk(k, 3, 5)
+    _, _, _, ops, vk, pk = _device_setup(ctx, k, circ)
+    proof = _prove(circ, ops, pk, RNG.OneNg(), 16)
+    assert plonk_verifier.verify_proof(vk, [], proof, SECRET, 1 << k)

@@ -211,3 +211,28 @@ def test_intermediate_sets_grouping():
     assert sets[0].points == [5, 9] and [c[0][1] for c in sets[0].commitments] == ["a", "b"]
     assert [c[1] for c in sets[0].commitments] == [[1, 2], [3, 4]]
     assert sets[1].points == [5] and sets[1].commitments[0][1] == [5]
+
+
+@pytest.mark.parametrize("minimum_degree,n_sets", [(5, 1), (None, 3)])
+def test_standard_plonk_circuit(minimum_degree, n_sets):
+    """halo2_proofs/benches/plonk.rs circuit (BASELINE configs[0] shape): no lookups / shuffles / instance; with the degree left
+    at 3 the three permuted columns need three chained grand products (permutation/prover.rs:96-190, verifier.rs:126-143)."""
+    k = 5
+    circ = example.StandardPlonk(k, 7, minimum_degree)
+    cc = circ.compile()
+    cs = plonk.circuit.ConstraintSystemBack(cc.cs)
+    assert cs.degree() == (minimum_degree or 3) and cs.blinding_factors() == 5
+    ops = plonk_ops.RefOps(k, SECRET, R.EvaluationDomain(cs.degree(), k))
+    vk = plonk.keygen_vk(ops, cc)
+    pk = plonk.keygen_pk(ops, vk, cc)
+    proof = _prove(circ, ops, pk, RNG.ChaCha20Rng(bytes(32)), num_threads=2)
+    n_points = 3 + n_sets + 1 + (cs.degree() - 1) + 2
+    n_scalars = 3 + 4 + 1 + 3 + (3 * n_sets - 1)
+    assert len(proof) == 32 * (n_points + n_scalars)
+    assert plonk_verifier.verify_proof(vk, [], proof, SECRET, 1 << k)
+
+    def broken(phase, ch):
+        cols = circ.witness(phase, ch)
+        cols[1][3] = F.fr_mont(11)            # b at an "add" row: breaks the gate there and the copy b1 == c0
+        return cols
+    assert not plonk_verifier.verify_proof(vk, [], _prove(circ, ops, pk, RNG.OneNg(), witness=broken), SECRET, 1 << k)

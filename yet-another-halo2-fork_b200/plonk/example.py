@@ -143,3 +143,45 @@ class MyCircuit:
         for row, a, b in rlc_rows:
             e[row] = (a + ch * b) % R
         return [None, None, None, self._tile(e)]
+
+
+class StandardPlonk:
+    """The circuit of the reference's proving benchmark (halo2_proofs/benches/plonk.rs:28-266; BASELINE.json configs[0] at k = 12):
+    three advice columns under one "combined add-mult" gate a*sa + b*sb + a*b*sm - c*sc, all three in the permutation, no lookups,
+    no instance.  2^(k-1) - 3 times: a row a * a = a^2 and a row a + a^2 = c, tied by two copy constraints (:241-256).
+    `minimum_degree` = 5 as in the benchmark (:201) gives one permutation set of three columns; None leaves the degree at 3 and
+    chunk_len at 1, i.e. three chained permutation sets (permutation/prover.rs:96-190)."""
+
+    def __init__(self, k: int, a: int = 3, minimum_degree: Optional[int] = 5):
+        self.k, self.n, self.a, self.minimum_degree = k, 1 << k, a % R, minimum_degree
+        self.reps = (1 << (k - 1)) - 3
+        assert self.reps >= 1
+
+    def constraint_system(self) -> C.ConstraintSystemMid:
+        a, b, c = (C.query("advice", i) for i in range(3))
+        sm, sa, sb, sc = (C.query("fixed", i) for i in range(4))
+        gate = C.sub(C.add(C.add(C.mul(a, sa), C.mul(b, sb)), C.mul(C.mul(a, b), sm)), C.mul(c, sc))   # :217-229
+        return C.ConstraintSystemMid(num_fixed_columns=4, num_advice_columns=3, num_instance_columns=0,
+                                     advice_column_phase=[0, 0, 0], gates=[("Combined add-mult", gate)],
+                                     permutation_columns=[("advice", 0), ("advice", 1), ("advice", 2)],
+                                     minimum_degree=self.minimum_degree)
+
+    def _columns(self, pair):
+        out = np.zeros((self.n, 4), dtype=np.uint64)
+        out[:2 * self.reps] = np.tile(F.fr_array(pair), (self.reps, 1))
+        return out
+
+    def compile(self) -> C.CompiledCircuit:
+        fixed = [self._columns(p) for p in ([1, 0], [0, 1], [0, 1], [1, 1])]                         # sm, sa, sb, sc
+        copies = []
+        for i in range(self.reps):
+            copies.append(((("advice", 0), 2 * i), (("advice", 0), 2 * i + 1)))
+            copies.append(((("advice", 1), 2 * i + 1), (("advice", 2), 2 * i)))
+        return C.CompiledCircuit(C.Preprocessing(copies, fixed), self.constraint_system())
+
+    def instances(self) -> List[List[int]]:
+        return []
+
+    def witness(self, phase: int, challenges: Dict[int, int]) -> List[Optional[np.ndarray]]:
+        a, sq = self.a, self.a * self.a % R
+        return [self._columns([a, a]), self._columns([a, sq]), self._columns([sq, (sq + a) % R])]
