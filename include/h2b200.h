@@ -133,6 +133,11 @@ int h2b_ntt_batch(h2b_ctx* ctx, void* const* cols, size_t n_cols, uint32_t log_n
 int h2b_coeff_to_extended_batch(h2b_ctx* ctx, const void* const* in_cols, void* const* out_cols, size_t n_cols,
                                 uint32_t k, uint32_t ext_k, const void* ext_omega32, const void* g_coset32,
                                 const void* g_coset_inv32);
+/* the same for device-resident columns (all on device 0 of the context): column c is transformed on device c mod G, moved there and
+ * back by peer copies over NVLink (the independent per-column coset NTTs of evaluate_h, plonk/evaluation.rs:344-361). */
+int h2b_coeff_to_extended_batch_device(h2b_ctx* ctx, const void* const* d_in_cols, void* const* d_out_cols, size_t n_cols,
+                                       uint32_t k, uint32_t ext_k, const void* ext_omega32, const void* g_coset32,
+                                       const void* g_coset_inv32);
 
 /* ---- polynomial helpers between the accelerated steps ------------------------------------
  * The serial O(n) loops of create_proof that sit between MSM and NTT calls, as tiled prefix computations.

@@ -114,6 +114,9 @@ class RefOps:
     def coeff_to_extended(self, p):
         return self.domain.coeff_to_extended(p)
 
+    def coeff_to_extended_many(self, polys):
+        return [self.coeff_to_extended(p) for p in polys]
+
     def extended_to_coeff(self, p, divide_by_vanishing: bool = False):
         if divide_by_vanishing:
             p = self.domain.divide_by_vanishing_poly(p)

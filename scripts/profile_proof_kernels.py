@@ -7,7 +7,7 @@ from h2b200 import plonk
 from h2b200.plonk import example, rng as RNG, arguments as A, prover as PR, shplonk as SH
 from h2b200.plonk.ops import DeviceOps
 k = int(sys.argv[1]) if len(sys.argv) > 1 else 20
-ctx = h2b200.Context([0]); engine = h2b200.B200Engine(ctx)
+ctx = h2b200.Context([int(x) for x in os.environ.get('H2B_DEVICES','0').split(',')]); engine = h2b200.B200Engine(ctx)
 circ = example.MyCircuit(k, 42); cc = circ.compile(); cs = plonk.circuit.ConstraintSystemBack(cc.cs)
 ops = DeviceOps(h2b200.ParamsKZG.setup(k, 0x1234567, engine), engine, h2b200.EvaluationDomain(cs.degree(), k, ctx))
 vk = plonk.keygen_vk(ops, cc); pk = plonk.keygen_pk(ops, vk, cc)

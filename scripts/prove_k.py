@@ -16,7 +16,9 @@ from h2b200.plonk.ops import DeviceOps
 k = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 SECRET = 0x1234567
-ctx = h2b200.Context([0])
+devices = [int(x) for x in os.environ.get('H2B_DEVICES', '0').split(',')]
+ctx = h2b200.Context(devices)
+out_devices = devices
 engine = h2b200.B200Engine(ctx)
 t = time.time()
 circ = example.MyCircuit(k, 42)
@@ -33,7 +35,7 @@ vk = plonk.keygen_vk(ops, cc)
 pk = plonk.keygen_pk(ops, vk, cc)
 torch.cuda.synchronize()
 print(f"keygen: {time.time() - t:.2f} s", flush=True)
-out = {"k": k, "runs": []}
+out = {"k": k, "devices": out_devices, "runs": []}
 for rep in range(reps):
     tr = plonk.Blake2bWrite()
     l0 = ctx.launch_count()

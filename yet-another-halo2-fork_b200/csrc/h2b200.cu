@@ -549,6 +549,7 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
         max_ms = std::max(max_ms, (double)ms);
         msm_fold_slices(d, infos[di], windows_out);
     }
+    H2B_CK(cudaSetDevice(ctx->devs[0].id));      // the caller's (torch's) current device is device 0 of the context
     ctx->last_ms = max_ms;
     return H2B_OK;
 }
@@ -643,7 +644,10 @@ int precompute_shard(h2b_ctx* ctx, Dev& d, BasesShard& sh) {
 int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, bool allow_pre, uint64_t* handle_out) {
     Bases B;
     B.n = n;
-    size_t nd = on_device ? 1 : ctx->devs.size();
+    // Host bases are cut into one contiguous point range per device.  Device-resident bases (on device 0) are adopted in place
+    // by a single-device context; a multi-device context keeps range 0 where it is and hands the other ranges to their devices
+    // over NVLink (peer copy), so that a device-resident SRS (ParamsKZG::setup) shards exactly like a host one.
+    size_t nd = ctx->devs.size();
     B.shard.resize(ctx->devs.size());
     size_t per = (n + nd - 1) / nd;
     for (size_t di = 0; di < nd; di++) {
@@ -653,14 +657,20 @@ int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, bo
         if (sh.count == 0) continue;
         Dev& d = ctx->devs[di];
         H2B_CK(cudaSetDevice(d.id));
-        if (on_device) { sh.d = const_cast<void*>(bases); sh.owned = false; }
-        else {
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(bases) + sh.start * 64;
+        if (on_device && di == 0) { sh.d = const_cast<uint8_t*>(src); sh.owned = false; }
+        else if (on_device) {
             H2B_CK(cudaMalloc(&sh.d, sh.count * 64));
-            H2B_CK(d.ring.h2d(sh.d, reinterpret_cast<const uint8_t*>(bases) + sh.start * 64, sh.count * 64, d.stream));
+            H2B_CK(cudaMemcpyPeerAsync(sh.d, d.id, src, ctx->devs[0].id, sh.count * 64, d.stream));
+            H2B_CK(cudaStreamSynchronize(d.stream));
+        } else {
+            H2B_CK(cudaMalloc(&sh.d, sh.count * 64));
+            H2B_CK(d.ring.h2d(sh.d, src, sh.count * 64, d.stream));
             H2B_CK(cudaStreamSynchronize(d.stream));
         }
         if (allow_pre) { int rc = precompute_shard(ctx, d, sh); if (rc) return rc; }
     }
+    H2B_CK(cudaSetDevice(ctx->devs[0].id));
     uint64_t h = ctx->next_handle++;
     ctx->bases.emplace(h, std::move(B));
     *handle_out = h;
@@ -674,6 +684,7 @@ void release_bases(h2b_ctx* ctx, Bases& B) {
             if (B.shard[di].d && B.shard[di].owned) cudaFree(B.shard[di].d);
             if (B.shard[di].pre) cudaFree(B.shard[di].pre);
         }
+    if (!ctx->devs.empty()) cudaSetDevice(ctx->devs[0].id);
 }
 
 
@@ -841,6 +852,18 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
         int rc = ntt_prepare_device(ctx);
         if (rc) { g_init_error = ctx->err; delete ctx; return rc; }
     }
+    // Device-resident scalars / columns live on device 0 and are handed to the other devices by cudaMemcpyAsync device-to-device:
+    // with peer access these copies ride NVLink / NVSwitch; without it the driver stages them through host memory.
+    for (size_t i = 0; i < ids.size(); i++)
+        for (size_t j = 0; j < ids.size(); j++) {
+            if (i == j) continue;
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, ids[i], ids[j]) == cudaSuccess && can) {
+                cudaSetDevice(ids[i]);
+                cudaError_t pe = cudaDeviceEnablePeerAccess(ids[j], 0);
+                if (pe != cudaSuccess) cudaGetLastError();      // already enabled by the caller (torch, another context): fine
+            }
+        }
     cudaSetDevice(ctx->devs[0].id);
     *out = ctx;
     return H2B_OK;
@@ -1214,6 +1237,75 @@ int h2b_coeff_to_extended_batch(h2b_ctx* ctx, const void* const* in_cols, void* 
     fz.in_len = (uint64_t)1 << k;
     fz.in_pat = pat;
     return batch_impl(ctx, in_cols, out_cols, n_cols, k, ext_k, omega, nullptr, fz);
+}
+
+// Device-resident columns (all on device 0 of the context), extended on every device of the context: column c goes to device
+// c mod G; a remote device pulls its n inputs over NVLink, transforms in its own buffers and pushes the n*e evaluations back into
+// the caller's output buffer on device 0 (peer copies on the device's stream).  The independent coset NTTs of evaluate_h
+// (plonk/evaluation.rs:344-361, 497-505, 571) are exactly this shape.  No collective: every column is independent.
+int h2b_coeff_to_extended_batch_device(h2b_ctx* ctx, const void* const* d_in_cols, void* const* d_out_cols, size_t n_cols,
+                                       uint32_t k, uint32_t ext_k, const void* ext_omega32, const void* g_coset32,
+                                       const void* g_coset_inv32) {
+    if (!ctx) return H2B_E_INVALID;
+    if ((n_cols && (!d_in_cols || !d_out_cols)) || !ext_omega32 || !g_coset32 || !g_coset_inv32)
+        return ctx->fail(H2B_E_INVALID, "coeff_to_extended_batch_device: null argument");
+    for (size_t c = 0; c < n_cols; c++)
+        if (!d_in_cols[c] || !d_out_cols[c]) return ctx->fail(H2B_E_INVALID, "coeff_to_extended_batch_device: null column");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = ntt_args_ok(ctx, ext_k);
+    if (rc) return rc;
+    if (k > ext_k) return ctx->fail(H2B_E_INVALID, "coeff_to_extended_batch_device: k > extended_k");
+    if (!n_cols) { ctx->last_ms = 0; return H2B_OK; }
+    const size_t n = (size_t)1 << k, N = (size_t)1 << ext_k, nd = ctx->devs.size();
+    const Fr omega = fr_from_bytes(ext_omega32);
+    Fr pat[2] = {fr_from_bytes(g_coset32), fr_from_bytes(g_coset_inv32)};
+    const int dev0 = ctx->devs[0].id;
+    auto run_dev = [&](size_t di) -> int {
+        Dev& d = ctx->devs[di];
+        H2B_CK(cudaSetDevice(d.id));
+        H2B_CK(d.ntt_b.reserve(N * 32));
+        if (di) H2B_CK(d.ntt_a.reserve(N * 32));
+        NttFused fz;
+        fz.in_len = n;
+        fz.in_pat = pat;
+        begin_call(d);
+        for (size_t c = di; c < n_cols; c += nd) {
+            if (di == 0) {
+                int r = ntt_enqueue(ctx, d, (const Fr*)d_in_cols[c], 0, d.ntt_b.as<Fr>(), 0, (Fr*)d_out_cols[c], 0, 1, ext_k, omega, nullptr, fz);
+                if (r) return r;
+            } else {
+                H2B_CK(cudaMemcpyPeerAsync(d.ntt_a.p, d.id, d_in_cols[c], dev0, n * 32, d.stream));
+                int r = ntt_enqueue(ctx, d, d.ntt_a.as<Fr>(), 0, d.ntt_b.as<Fr>(), 0, d.ntt_a.as<Fr>(), 0, 1, ext_k, omega, nullptr, fz);
+                if (r) return r;
+                H2B_CK(cudaMemcpyPeerAsync(d_out_cols[c], dev0, d.ntt_a.p, d.id, N * 32, d.stream));
+            }
+        }
+        H2B_CK(cudaEventRecord(d.ev_last, d.stream));
+        return H2B_OK;
+    };
+    const size_t active = std::min(nd, n_cols);
+    if (active == 1) {
+        rc = run_dev(0);
+        if (rc) return rc;
+    } else {
+        std::vector<int> rcs(active, H2B_OK);
+        std::vector<std::thread> th;
+        for (size_t u = 0; u < active; u++) th.emplace_back([&, u] { rcs[u] = run_dev(u); });
+        for (auto& t : th) t.join();
+        for (int r : rcs) if (r) return r;
+    }
+    double max_ms = 0;
+    for (size_t di = 0; di < active; di++) {
+        Dev& d = ctx->devs[di];
+        H2B_CK(cudaSetDevice(d.id));
+        H2B_CK(cudaStreamSynchronize(d.stream));
+        float ms = 0.f;
+        H2B_CK(cudaEventElapsedTime(&ms, d.ev_first, d.ev_last));
+        max_ms = std::max(max_ms, (double)ms);
+    }
+    H2B_CK(cudaSetDevice(dev0));
+    ctx->last_ms = max_ms;
+    return H2B_OK;
 }
 
 // ---- polynomial helpers -----------------------------------------------------------

@@ -149,6 +149,23 @@ class EvaluationDomain:
                                                 _vp(self._m["g_coset_inv"])))
         return outs
 
+    def coeff_to_extended_many(self, cols):
+        """Device-resident columns, spread over the devices of the context (h2b_coeff_to_extended_batch_device)."""
+        import torch
+        cols = list(cols)
+        if not cols:
+            return []
+        for x in cols:
+            assert self._rows(x) == 1 << self.k, "coeff_to_extended: wrong length"
+        outs = [torch.empty((self.extended_len(), 4), dtype=x.dtype, device=x.device) for x in cols]
+        lib, c = self.ctx.lib, self.ctx
+        inp = (ctypes.c_void_p * len(cols))(*[x.data_ptr() for x in cols])
+        outp = (ctypes.c_void_p * len(cols))(*[x.data_ptr() for x in outs])
+        c.check(lib.h2b_coeff_to_extended_batch_device(c.handle, inp, outp, len(cols), self.k, self.extended_k,
+                                                       _vp(self._m["extended_omega"]), _vp(self._m["g_coset"]),
+                                                       _vp(self._m["g_coset_inv"])))
+        return outs
+
     def lagrange_to_coeff_batch(self, cols):
         cols = [np.ascontiguousarray(x, dtype=np.uint64) for x in cols]
         for x in cols:

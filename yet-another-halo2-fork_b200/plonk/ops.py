@@ -97,6 +97,10 @@ class DeviceOps:
     def coeff_to_extended(self, p):
         return self.domain.coeff_to_extended(p)
 
+    def coeff_to_extended_many(self, polys):
+        """The independent coset NTTs of evaluate_h (evaluation.rs:344-361, 497-505, 571), spread over the context's devices."""
+        return self.domain.coeff_to_extended_many(polys)
+
     def extended_to_coeff(self, p, divide_by_vanishing: bool = False):
         return self.domain.extended_to_coeff(p, divide_by_vanishing=divide_by_vanishing)
 

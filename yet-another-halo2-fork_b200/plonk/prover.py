@@ -31,8 +31,15 @@ def evaluate_h(ops, pk: ProvingKey, advice_polys, instance_polys, challenges, y,
     over every extended row, then the permutation / lookup / shuffle folds, each `value = value * y + term`."""
     cs, ev = pk.vk.cs, pk.ev
     fixed = pk.fixed_cosets
-    advice = [ops.coeff_to_extended(p) for p in advice_polys]                       # evaluation.rs:344-352
-    instance = [ops.coeff_to_extended(p) for p in instance_polys]                   # evaluation.rs:353-361
+    # every coset extension of this function in one call (evaluation.rs:344-361, 497-505, 571): the columns are independent, a
+    # multi-device context spreads them over its GPUs
+    todo = list(advice_polys) + list(instance_polys)
+    for lookup in lookups:
+        todo += [lookup.product_poly, lookup.permuted_input_poly, lookup.permuted_table_poly]
+    todo += [shuffle.product_poly for shuffle in shuffles]
+    cosets = ops.coeff_to_extended_many(todo)
+    advice, cosets = cosets[:len(advice_polys)], cosets[len(advice_polys):]
+    instance, cosets = cosets[:len(instance_polys)], cosets[len(instance_polys):]
     values = ops.graph(ev.custom_gates, fixed, advice, instance, challenges, beta, gamma, theta, y, extended=True)
     if permutation:                                                                 # evaluation.rs:397-493
         source = {"advice": advice, "fixed": fixed, "instance": instance}
@@ -41,18 +48,19 @@ def evaluate_h(ops, pk: ProvingKey, advice_polys, instance_polys, challenges, y,
                                       pk.permutation.cosets, cs.degree() - 2, pk.l0, pk.l_last, pk.l_active_row, beta, gamma, y,
                                       FR_DELTA, cs.blinding_factors())
     for n_l, lookup in enumerate(lookups):                                          # evaluation.rs:496-567
-        product_coset = ops.coeff_to_extended(lookup.product_poly)
-        permuted_input_coset = ops.coeff_to_extended(lookup.permuted_input_poly)
-        permuted_table_coset = ops.coeff_to_extended(lookup.permuted_table_poly)
+        product_coset, permuted_input_coset, permuted_table_coset = cosets[:3]
+        cosets = cosets[3:]
         table_values = ops.graph(ev.lookups[n_l], fixed, advice, instance, challenges, beta, gamma, theta, y, extended=True)
         values = ops.lookup_fold(values, table_values, product_coset, permuted_input_coset, permuted_table_coset, pk.l0, pk.l_last,
                                  pk.l_active_row, beta, gamma, y)
+        del product_coset, permuted_input_coset, permuted_table_coset, table_values
     for n_s, shuffle in enumerate(shuffles):                                        # evaluation.rs:570-620
-        product_coset = ops.coeff_to_extended(shuffle.product_poly)
+        product_coset, cosets = cosets[0], cosets[1:]
         input_values = ops.graph(ev.shuffles[2 * n_s], fixed, advice, instance, challenges, beta, gamma, theta, y, extended=True)
         shuffle_values = ops.graph(ev.shuffles[2 * n_s + 1], fixed, advice, instance, challenges, beta, gamma, theta, y,
                                    extended=True)
         values = ops.shuffle_fold(values, input_values, shuffle_values, product_coset, pk.l0, pk.l_last, pk.l_active_row, y)
+        del product_coset, input_values, shuffle_values
     return values
 
 
