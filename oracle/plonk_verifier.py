@@ -64,7 +64,8 @@ class _Msm:
         return acc
 
 
-def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n: int, debug: dict = None) -> bool:
+def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n: int, debug: dict = None,
+                 multiopen: str = "shplonk") -> bool:
     cs, domain = vk.cs, vk.domain
     if len(instances) != cs.num_instance_columns:
         raise VerifyError("InvalidInstances")
@@ -209,6 +210,8 @@ def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n
                  "random": lambda: random_poly_commitment}[kind]()
         return _Msm([(1, point)])
 
+    if multiopen == "gwc":
+        return _verify_gwc(t, queries, commitment_msm, s)
     # shplonk/verifier.rs:47-139
     rotation_sets, super_point_set = SH.construct_intermediate_sets(queries, lambda q: q[1], lambda q: q[2])
     y_s = t.squeeze_challenge_scalar()
@@ -246,6 +249,37 @@ def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n
     outer.append_term(u, h2)
     left, right = h2, outer.eval()
     return R.g1_mul(left, s % P) == right                                           # kzg/msm.rs:188-206 via the trapdoor
+
+
+def _verify_gwc(t, queries, commitment_msm, s: int) -> bool:
+    """gwc/verifier.rs:40-123 + DualMSM::check through the trapdoor: s * left == right."""
+    from h2b200.plonk import gwc
+    v = t.squeeze_challenge_scalar()
+    commitment_data = gwc.construct_intermediate_sets(queries)
+    w = [t.read_point() for _ in commitment_data]
+    u = t.squeeze_challenge_scalar()
+    if t.remaining():
+        raise VerifyError("trailing bytes in the proof")
+    commitment_multi, eval_multi, witness, witness_with_aux, power_of_u = _Msm(), 0, _Msm(), _Msm(), 1
+    for (z, qs), wi in zip(commitment_data, w):
+        batch, eval_batch, power_of_v = _Msm(), 0, 1
+        for q in qs:
+            m = commitment_msm(q[1])
+            m.scale(power_of_v)
+            batch.add_msm(m)
+            eval_batch = (eval_batch + power_of_v * q[2]) % P
+            power_of_v = power_of_v * v % P
+        batch.scale(power_of_u)
+        commitment_multi.add_msm(batch)
+        eval_multi = (eval_multi + power_of_u * eval_batch) % P
+        witness_with_aux.append_term(power_of_u * z, wi)
+        witness.append_term(power_of_u, wi)
+        power_of_u = power_of_u * u % P
+    right = _Msm()
+    right.add_msm(witness_with_aux)
+    right.add_msm(commitment_multi)
+    right.append_term(eval_multi, R.g1_neg(R.G1_GEN))
+    return R.g1_mul(witness.eval(), s % P) == right.eval()
 
 
 def _fold(factor: int, values: Sequence[int]) -> int:

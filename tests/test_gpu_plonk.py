@@ -143,3 +143,19 @@ def test_standard_plonk_k12(ctx):
     _, _, _, ops, vk, pk = _device_setup(ctx, k, circ)
     proof = _prove(circ, ops, pk, RNG.OneNg(), 16)
     assert plonk_verifier.verify_proof(vk, [], proof, SECRET, 1 << k)
+
+
+def test_gwc_bytes_match(ctx):
+    """The GWC opening (multiopen/gwc/prover.rs) on the device == the CPU restatement; accepted by the VerifierGWC restatement."""
+    k = 6
+    circ = example.MyCircuit(k, 42)
+    cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circ)
+    ref_ops = plonk_ops.RefOps(k, SECRET, ref_dom)
+    ref_pk = plonk.keygen_pk(ref_ops, plonk.keygen_vk(ref_ops, cc), cc)
+    proofs = []
+    for o, key in ((ops, pk), (ref_ops, ref_pk)):
+        tr = plonk.Blake2bWrite()
+        plonk.create_proof(o, key, circ.instances(), circ.witness, RNG.OneNg(), tr, num_threads=4, multiopen="gwc")
+        proofs.append(tr.finalize())
+    assert proofs[0] == proofs[1]
+    assert plonk_verifier.verify_proof(vk, circ.instances(), proofs[0], SECRET, 1 << k, multiopen="gwc")

@@ -236,3 +236,20 @@ def test_standard_plonk_circuit(minimum_degree, n_sets):
         cols[1][3] = F.fr_mont(11)            # b at an "add" row: breaks the gate there and the copy b1 == c0
         return cols
     assert not plonk_verifier.verify_proof(vk, [], _prove(circ, ops, pk, RNG.OneNg(), witness=broken), SECRET, 1 << k)
+
+
+def test_gwc_multiopen(setup):
+    """ProverGWC / VerifierGWC (multiopen/gwc/prover.rs:45-90, verifier.rs:40-123): one witness commitment per distinct point."""
+    circ, ops, vk, pk = setup
+    tr = plonk.Blake2bWrite()
+    plonk.create_proof(ops, pk, circ.instances(), circ.witness, RNG.OneNg(), tr, num_threads=4, multiopen="gwc")
+    proof = tr.finalize()
+    shplonk_proof = _prove(circ, ops, pk, RNG.OneNg())
+    assert proof[:-3 * 32] == shplonk_proof[:-2 * 32]                  # same transcript up to the opening; 3 points: x, x*w, x/w
+    assert plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << K, multiopen="gwc")
+    bad = bytearray(proof)
+    bad[200] ^= 4
+    try:
+        assert not plonk_verifier.verify_proof(vk, circ.instances(), bytes(bad), SECRET, 1 << K, multiopen="gwc")
+    except ValueError:
+        pass

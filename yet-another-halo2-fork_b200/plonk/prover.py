@@ -16,7 +16,7 @@ import numpy as np
 
 from .. import fields as F
 from . import arguments as A
-from . import shplonk
+from . import gwc, shplonk
 from .keygen import FR_DELTA, ProvingKey
 
 R = F.R_MOD
@@ -65,13 +65,15 @@ def evaluate_h(ops, pk: ProvingKey, advice_polys, instance_polys, challenges, y,
 
 
 class ProverSingle:
-    def __init__(self, ops, pk: ProvingKey, instance: Sequence[Sequence[int]], rng, transcript, num_threads: int = 1):
+    def __init__(self, ops, pk: ProvingKey, instance: Sequence[Sequence[int]], rng, transcript, num_threads: int = 1,
+                 multiopen: str = "shplonk"):
         """prover.rs:181-326.  `instance`: one list of canonical ints per instance column.  `num_threads` is the reference's
         `current_num_threads()` (it seeds the vanishing argument's random polynomial, vanishing/prover.rs:57-81)."""
         cs = pk.vk.cs
         if len(instance) != cs.num_instance_columns:
             raise ProverError("InvalidInstances")
         self.ops, self.pk, self.rng, self.transcript, self.num_threads = ops, pk, rng, transcript, num_threads
+        self.multiopen = {"shplonk": shplonk, "gwc": gwc}[multiopen]        # the `P: commitment::Prover` type parameter
         pk.vk.hash_into(transcript)                                                 # [TRANSCRIPT-1]
         n = ops.n
         self.phases = cs.phases()
@@ -91,8 +93,8 @@ class ProverSingle:
         self.next_phase_index = 0
 
     @staticmethod
-    def new(ops, pk, instance, rng, transcript, num_threads: int = 1) -> "ProverSingle":
-        return ProverSingle(ops, pk, instance, rng, transcript, num_threads)
+    def new(ops, pk, instance, rng, transcript, num_threads: int = 1, multiopen: str = "shplonk") -> "ProverSingle":
+        return ProverSingle(ops, pk, instance, rng, transcript, num_threads, multiopen)
 
     # prover.rs:329-499
     def commit_phase(self, phase: int, witness: Sequence[Optional[object]]) -> Dict[int, int]:
@@ -183,13 +185,14 @@ class ProverSingle:
         queries += [(domain.rotate_omega(x, at), pk.fixed_polys[column], 0) for column, at in cs.fixed_queries]
         queries += A.permutation_pk_open(pk, x)
         queries += A.vanishing_open(vanishing, x)
-        shplonk.create_proof(ops, transcript, queries)                              # prover.rs:884-890
+        self.multiopen.create_proof(ops, transcript, queries)                       # prover.rs:884-890
 
 
-def create_proof(ops, pk: ProvingKey, instance, witness_fn, rng, transcript, num_threads: int = 1) -> None:
+def create_proof(ops, pk: ProvingKey, instance, witness_fn, rng, transcript, num_threads: int = 1,
+                 multiopen: str = "shplonk") -> None:
     """plonk::create_proof for one circuit (halo2_proofs/src/plonk/prover.rs:38-123): `witness_fn(phase, challenges)` plays the
     WitnessCalculator and returns the advice columns of that phase (None for the others)."""
-    prover = ProverSingle(ops, pk, instance, rng, transcript, num_threads)
+    prover = ProverSingle(ops, pk, instance, rng, transcript, num_threads, multiopen)
     challenges: Dict[int, int] = {}
     for phase in prover.phases:
         challenges = prover.commit_phase(phase, witness_fn(phase, challenges))
