@@ -502,7 +502,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
     hbm_achieved = alg_bytes / (acc_ms * 1e-3) / 1e9 if acc_ms else 0.0
     roofline = {
         "kernel": "msm_accumulate_kernel", "launches_per_step": acc_launches_per_step,
-        "bound": "imad (integer-multiply pipe; neither hbm nor tensor binds this path)",
+        "bound": "imad", "bound_note": "integer-multiply pipe: neither hbm nor tensor binds this path (SURVEY.md 8d, north_star); the hbm figures are under `hbm`",
         "achieved": imad_achieved, "peak": wide_peak, "unit": "IMAD.WIDE/s", "frac": imad_achieved / wide_peak if wide_peak else None,
         "peak_source": "h2b_imad_peak: IMAD.WIDE.U32.X carry chains measured live in this run (half-rate on sm_100a; "
                        "profiles/r1_imad_micro.txt, r1_fp64_micro.txt: FP64 and ALU ops do not co-issue beside it)",
@@ -526,7 +526,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
         "metric": f"fr_ntt_2^{NTT_K}_ms", "value": ntt_ms, "unit": "ms", "passes": npass, "aggregate_ntt_per_s": world * 1e3 / ntt_ms,
         "e2e": {"value": ntt_e2e_ms, "unit": "ms", "h2d_bytes_per_step": 32 << NTT_K, "d2h_bytes_per_step": 32 << NTT_K},
         "roofline": {"kernel": "ntt_pass_kernel (all passes of one transform)",
-                     "bound": "imad (SURVEY.md 8d: max(hbm_fraction, imad_fraction); 254-bit butterflies are multiplier bound)",
+                     "bound": "imad", "bound_note": "SURVEY.md 8d: max(hbm_fraction, imad_fraction); 254-bit butterflies are multiplier bound",
                      "achieved": ntt_imad, "peak": wide_peak, "unit": "IMAD.WIDE/s", "frac": ntt_imad / wide_peak if wide_peak else None,
                      "algorithmic": f"(n/2) log2 n = {ntt_muls:.4g} field muls x {WIDE_PER_FIELD_MUL} IMAD.WIDE",
                      "traffic": (ncu_traffic("ntt_pass_kernel", NTT_K) or 0) * npass or None,

@@ -53,4 +53,7 @@ if os.environ.get("H2B_VERIFY", "1") == "1":
     ok = plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << k)
     print(f"verify (python restatement): {ok}, {time.time() - t:.2f} s")
     out["verified"] = bool(ok)
+free, total = torch.cuda.mem_get_info()
+out["torch_peak_gib"] = torch.cuda.max_memory_allocated() / 2**30
+out["device0_used_gib"] = (total - free) / 2**30
 print(json.dumps(out))

@@ -137,7 +137,7 @@ class MyCircuit:
         if phase == 0:
             if self._phase0 is None:
                 self._phase0 = [self._tile(adv[A_]), self._tile(adv[B_]), self._tile(adv[C_])]
-            return [c.copy() for c in self._phase0] + [None]
+            return list(self._phase0) + [None]                  # read-only: the prover uploads them
         ch = challenges[0]
         e = [0] * UNIT_ROWS
         for row, a, b in rlc_rows:
