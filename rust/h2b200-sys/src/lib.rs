@@ -84,4 +84,14 @@ extern "C" {
     pub fn h2b_quotient_shuffle_device(ctx: *mut h2b_ctx, d_values: *mut c_void, d_input_values: *const c_void,
                                        d_shuffle_values: *const c_void, d_product: *const c_void, d_l0: *const c_void,
                                        d_l_last: *const c_void, d_l_active: *const c_void, y32: *const c_void, k: u32, ext_k: u32) -> c_int;
+    // device-resident columns spread over the context's GPUs (the independent coset NTTs of evaluate_h, evaluation.rs:344-361)
+    pub fn h2b_coeff_to_extended_batch_device(ctx: *mut h2b_ctx, d_in_cols: *const *const c_void, d_out_cols: *const *mut c_void,
+                                              n_cols: usize, k: u32, ext_k: u32, ext_omega32: *const c_void,
+                                              g_coset32: *const c_void, g_coset_inv32: *const c_void) -> c_int;
+    // set-up and randomness helpers: ParamsKZG::setup (kzg/commitment.rs:64-131), Fr::from_uniform_bytes, and the vanishing
+    // argument's per-thread ChaCha20 streams (vanishing/prover.rs:57-81)
+    pub fn h2b_g1_fixed_base_mul_device(ctx: *mut h2b_ctx, d_scalars: *const c_void, n: usize, d_out_affine: *mut c_void) -> c_int;
+    pub fn h2b_fr_from_u512_device(ctx: *mut h2b_ctx, d_limbs64: *const c_void, n: usize, d_out: *mut c_void) -> c_int;
+    pub fn h2b_fr_random_chacha20_device(ctx: *mut h2b_ctx, seeds32: *const c_void, offsets: *const u64, n_streams: usize,
+                                         d_out: *mut c_void) -> c_int;
 }

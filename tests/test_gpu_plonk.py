@@ -159,3 +159,49 @@ def test_gwc_bytes_match(ctx):
         proofs.append(tr.finalize())
     assert proofs[0] == proofs[1]
     assert plonk_verifier.verify_proof(vk, circ.instances(), proofs[0], SECRET, 1 << k, multiopen="gwc")
+
+
+def test_new_entry_points_reject_bad_arguments(ctx):
+    """The set-up / randomness / batch entry points return H2B_E_INVALID (never crash) on null or inconsistent arguments."""
+    import ctypes
+    import torch
+    lib, h = ctx.lib, ctx.handle
+    buf = torch.zeros((16, 8), dtype=torch.int64, device="cuda")
+    p = ctypes.c_void_p(buf.data_ptr())
+    assert lib.h2b_g1_fixed_base_mul_device(h, None, 4, p) != 0
+    assert lib.h2b_g1_fixed_base_mul_device(h, p, 0, None) == 0
+    assert lib.h2b_fr_from_u512_device(h, p, 4, None) != 0
+    seeds = (ctypes.c_uint8 * 64)()
+    offs = (ctypes.c_uint64 * 3)(0, 5, 3)
+    assert lib.h2b_fr_random_chacha20_device(h, seeds, offs, 2, p) != 0            # decreasing offsets
+    offs = (ctypes.c_uint64 * 3)(1, 5, 8)
+    assert lib.h2b_fr_random_chacha20_device(h, seeds, offs, 2, p) != 0            # offsets[0] != 0
+    assert lib.h2b_fr_random_chacha20_device(h, None, None, 0, None) == 0
+    one = F_mont1 = h2b200.fields.fr_mont(1)
+    vp = one.ctypes.data_as(ctypes.c_void_p)
+    cols = (ctypes.c_void_p * 1)(buf.data_ptr())
+    assert lib.h2b_coeff_to_extended_batch_device(h, cols, None, 1, 2, 3, vp, vp, vp) != 0
+    assert lib.h2b_coeff_to_extended_batch_device(h, cols, cols, 1, 5, 3, vp, vp, vp) != 0     # k > extended_k
+    assert lib.h2b_coeff_to_extended_batch_device(h, None, None, 0, 2, 3, vp, vp, vp) == 0
+
+
+def test_random_poly_chacha20_matches_numpy(ctx):
+    """h2b_fr_random_chacha20_device == rand_chacha semantics restated in numpy (plonk/rng.py), ragged chunks included."""
+    engine = h2b200.B200Engine(ctx)
+    ops = DeviceOps(None, engine, h2b200.EvaluationDomain(3, 4, ctx))
+    seeds = [bytes([i + 1] * 32) for i in range(3)]
+    chunks = [(0, 70), (70, 1), (71, 259)]
+    got = ops.to_ints(ops.random_poly_chacha20(seeds, chunks))
+    exp = []
+    for seed, (_, length) in zip(seeds, chunks):
+        exp += RNG.limbs512_to_ints(RNG.ChaCha20Rng(seed).random_fr_limbs(length))
+    assert got == exp
+
+
+def test_coeff_to_extended_many_matches_single(ctx):
+    dom = h2b200.EvaluationDomain(6, 9, ctx)
+    import torch
+    cols = [torch.from_numpy(C.random_fr(1 << 9, 40 + i).view(np.int64)).cuda() for i in range(5)]
+    many = dom.coeff_to_extended_many(cols)
+    for c, m in zip(cols, many):
+        assert torch.equal(dom.coeff_to_extended(c), m)
