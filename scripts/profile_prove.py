@@ -16,4 +16,4 @@ def run():
     torch.cuda.synchronize()
 run()
 pr = cProfile.Profile(); pr.enable(); run(); pr.disable()
-st = pstats.Stats(pr); st.sort_stats("cumulative").print_stats(45)
+st = pstats.Stats(pr); st.sort_stats("tottime").print_stats(32)

@@ -51,6 +51,7 @@ class MyCircuit:
         assert self.units >= 1, "k too small for one unit"
         self._unit = self._layout_unit()
         self._phase0 = None                                 # the first-phase columns do not depend on anything: tiled once
+        self._buffers, self._pinned = {}, []
 
     # ---- one unit (synthesize_unit, :223-422) -----------------------------------------------------------------------------
     def _layout_unit(self):
@@ -114,9 +115,25 @@ class MyCircuit:
         cell = lambda kind, col, row: adv[col][row]
         return [[self.input] + [cell(*c) for c in self._instance_cells]]                              # :117-135
 
-    def _tile(self, unit_column: List[int]) -> np.ndarray:
-        out = np.zeros((self.n, 4), dtype=np.uint64)
-        out[:self.units * UNIT_ROWS] = np.tile(F.fr_array(unit_column), (self.units, 1))
+    def _host_buffer(self, name: str) -> np.ndarray:
+        """An (n, 4) uint64 host column, zeroed once and reused; page-locked when a CUDA device is present so that the prover's
+        upload is a straight DMA (the witness calculator's output buffers; the rows past the last unit stay zero)."""
+        if name not in self._buffers:
+            buf = None
+            try:
+                import torch
+                if torch.cuda.is_available():
+                    t = torch.zeros((self.n, 4), dtype=torch.int64).pin_memory()
+                    self._pinned.append(t)
+                    buf = t.numpy().view(np.uint64)
+            except ImportError:
+                pass
+            self._buffers[name] = buf if buf is not None else np.zeros((self.n, 4), dtype=np.uint64)
+        return self._buffers[name]
+
+    def _tile(self, unit_column: List[int], name: Optional[str] = None) -> np.ndarray:
+        out = self._host_buffer(name) if name else np.zeros((self.n, 4), dtype=np.uint64)
+        out[:self.units * UNIT_ROWS].reshape(self.units, UNIT_ROWS, 4)[:] = F.fr_array(unit_column)
         return out
 
     def compile(self) -> C.CompiledCircuit:
@@ -136,13 +153,13 @@ class MyCircuit:
         adv, _, rlc_rows, _ = self._unit
         if phase == 0:
             if self._phase0 is None:
-                self._phase0 = [self._tile(adv[A_]), self._tile(adv[B_]), self._tile(adv[C_])]
+                self._phase0 = [self._tile(adv[A_], "a"), self._tile(adv[B_], "b"), self._tile(adv[C_], "c")]
             return list(self._phase0) + [None]                  # read-only: the prover uploads them
         ch = challenges[0]
         e = [0] * UNIT_ROWS
         for row, a, b in rlc_rows:
             e[row] = (a + ch * b) % R
-        return [None, None, None, self._tile(e)]
+        return [None, None, None, self._tile(e, "e")]
 
 
 class StandardPlonk:
