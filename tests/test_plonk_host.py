@@ -253,3 +253,22 @@ def test_gwc_multiopen(setup):
         assert not plonk_verifier.verify_proof(vk, circ.instances(), bytes(bad), SECRET, 1 << K, multiopen="gwc")
     except ValueError:
         pass
+
+
+def test_golden_proofs_regenerate():
+    """tests/golden/proofs.json is what make_golden_proofs.py produces today (the CPU restatement has not drifted), and the
+    restated verifier accepts every stored proof."""
+    import hashlib
+    import importlib.util
+    import json
+    import os
+    here = os.path.dirname(__file__)
+    spec = importlib.util.spec_from_file_location("make_golden_proofs", os.path.join(here, "golden", "make_golden_proofs.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    gold = json.load(open(os.path.join(here, "golden", "proofs.json")))
+    for case in gold["proofs"]:
+        proof, vk, circ = gen.prove(case, lambda k, cs: plonk_ops.RefOps(k, SECRET, R.EvaluationDomain(cs.degree(), k)))
+        assert proof.hex() == case["proof"] and hashlib.sha256(proof).hexdigest() == case["sha256"], case["name"]
+        assert plonk_verifier.verify_proof(vk, circ.instances(), bytes.fromhex(case["proof"]), SECRET, 1 << case["k"],
+                                           multiopen=case["multiopen"])
