@@ -46,7 +46,8 @@ enum {
     H2B_E_INVALID = -1,   /* bad argument (null pointer, length mismatch, log_n out of range, unknown handle) */
     H2B_E_CUDA = -2,      /* CUDA runtime / launch failure */
     H2B_E_NOMEM = -3,     /* device or host allocation failed */
-    H2B_E_NODEVICE = -4   /* no usable GPU */
+    H2B_E_NODEVICE = -4,  /* no usable GPU */
+    H2B_E_CONSTRAINT = -5 /* the inputs violate the relation being proven (plonk::Error::ConstraintSystemFailure) */
 };
 
 /* ---- context ------------------------------------------------------------------------------------------
@@ -218,6 +219,17 @@ uint64_t h2b_launch_count(const h2b_ctx* ctx);   /* kernels launched by this con
 
 /* synthetic benchmark input: d_out[i] = [t0 + i]G as 64-byte affine points, on device 0. */
 int h2b_synth_bases(h2b_ctx* ctx, void* d_out, size_t n, uint64_t t0);
+
+/* ---- lookup argument ---------------------------------------------------------------------------------------------------
+ * h2b_lookup_permute_device = permute_expression_pair (plonk/lookup/prover.rs:398-494) on the first `usable` of n rows of the two
+ *                       compressed columns (device 0, Montgomery Fr): d_out_input = the input values sorted by canonical value
+ *                       (`Fr: Ord`), d_out_table = the table values arranged so that every first occurrence of an input value sits
+ *                       beside the same table value and the left-over table values fill the repeated rows from the last one backwards
+ *                       in ascending order (the reference's BTreeMap walk + `repeated_input_rows.pop()`).  Rows usable..n of both
+ *                       outputs are zeroed (the caller blinds them, :469-471).  H2B_E_CONSTRAINT when an input value does not
+ *                       occur in the table (Error::ConstraintSystemFailure, :440).  Outputs must not alias the inputs. */
+int h2b_lookup_permute_device(h2b_ctx* ctx, const void* d_input, const void* d_table, size_t usable, size_t n, void* d_out_input,
+                              void* d_out_table);
 
 /* ---- set-up helpers (not on the proving hot path) -----------------------------------------------------------------
  * h2b_g1_fixed_base_mul_device: d_out[i] = [k_i] G (64-byte affine, G = (1, 2)) for n Montgomery scalars on device 0: the fixed-base

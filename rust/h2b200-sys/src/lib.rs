@@ -94,4 +94,7 @@ extern "C" {
     pub fn h2b_fr_from_u512_device(ctx: *mut h2b_ctx, d_limbs64: *const c_void, n: usize, d_out: *mut c_void) -> c_int;
     pub fn h2b_fr_random_chacha20_device(ctx: *mut h2b_ctx, seeds32: *const c_void, offsets: *const u64, n_streams: usize,
                                          d_out: *mut c_void) -> c_int;
+    // permute_expression_pair of the lookup argument (lookup/prover.rs:398-494); -5 = ConstraintSystemFailure
+    pub fn h2b_lookup_permute_device(ctx: *mut h2b_ctx, d_input: *const c_void, d_table: *const c_void, usable: usize, n: usize,
+                                     d_out_input: *mut c_void, d_out_table: *mut c_void) -> c_int;
 }

@@ -205,3 +205,31 @@ def test_coeff_to_extended_many_matches_single(ctx):
     many = dom.coeff_to_extended_many(cols)
     for c, m in zip(cols, many):
         assert torch.equal(dom.coeff_to_extended(c), m)
+
+
+def test_lookup_permute_matches_host_restatement(ctx):
+    """h2b_lookup_permute_device == the numpy restatement of permute_expression_pair (lookup/prover.rs:398-494), on columns with
+    many repeats, values spanning all four limbs, and a table larger than the set of inputs; missing value -> ConstraintSystemFailure."""
+    from h2b200.plonk import arguments as A
+    engine = h2b200.B200Engine(ctx)
+    for k, usable, seed in ((4, 10, 1), (10, 1000, 2), (13, (1 << 13) - 6, 3)):
+        ops = DeviceOps(None, engine, h2b200.EvaluationDomain(3, k, ctx))
+        n = 1 << k
+        rng = np.random.default_rng(seed)
+        pool = [int(x) for x in rng.integers(0, 1 << 62, size=max(3, usable // 7))]
+        pool = [(p * 0x9E3779B97F4A7C15F39CC0605CEDC835 * (i + 1)) % R.R_MOD for i, p in enumerate(pool)]
+        table = [pool[int(i)] for i in rng.integers(0, len(pool), size=usable)]
+        present = sorted(set(table))
+        inp = [present[int(i)] for i in rng.integers(0, len(present), size=usable)]
+        pad = lambda xs: xs + [12345] * (n - usable)
+        d_in, d_tab = ops.from_ints(pad(inp)), ops.from_ints(pad(table))
+        got_in, got_tab = ops.permute_expression_pair(d_in, d_tab, usable)
+        exp_in, exp_tab = A.permute_expression_pair(ops.to_canonical(d_in, usable), ops.to_canonical(d_tab, usable))
+        assert np.array_equal(ops.to_canonical(got_in, usable), exp_in)
+        assert np.array_equal(ops.to_canonical(got_tab, usable), exp_tab)
+        assert ops.read_ints(got_in, usable, n - usable) == [0] * (n - usable) == ops.read_ints(got_tab, usable, n - usable)
+        bad = list(inp)
+        bad[usable // 2] = (max(present) + 1) % R.R_MOD
+        if bad[usable // 2] not in present:
+            with pytest.raises(A.ConstraintSystemFailure):
+                ops.permute_expression_pair(ops.from_ints(pad(bad)), d_tab, usable)

@@ -8,7 +8,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libh2b200.so")
 
-H2B_OK, H2B_E_INVALID, H2B_E_CUDA, H2B_E_NOMEM, H2B_E_NODEVICE = 0, -1, -2, -3, -4
+H2B_OK, H2B_E_INVALID, H2B_E_CUDA, H2B_E_NOMEM, H2B_E_NODEVICE, H2B_E_CONSTRAINT = 0, -1, -2, -3, -4, -5
 MSM_WINDOW_BYTES = 128
 MSM_MAX_WINDOWS = 64
 
@@ -62,6 +62,7 @@ SYMBOLS = {
     "h2b_synth_bases": (_int, [_vp, _vp, _sz, _u64]),
     "h2b_g1_fixed_base_mul_device": (_int, [_vp, _vp, _sz, _vp]),
     "h2b_fr_from_u512_device": (_int, [_vp, _vp, _sz, _vp]),
+    "h2b_lookup_permute_device": (_int, [_vp, _vp, _vp, _sz, _sz, _vp, _vp]),
     "h2b_fr_random_chacha20_device": (_int, [_vp, _vp, ctypes.POINTER(ctypes.c_uint64), _sz, _vp]),
 }
 

@@ -23,6 +23,7 @@
 #include "poly_kernels.hpp"
 #include "quotient_kernels.hpp"
 #include "setup_kernels.hpp"
+#include "lookup_kernels.hpp"
 #include "ntt.cuh"
 #include "ntt_plan.hpp"
 #include "ntt_kernels.hpp"
@@ -1644,6 +1645,36 @@ int h2b_fr_random_chacha20_device(h2b_ctx* ctx, const void* seeds32, const uint6
                (const uint64_t*)(base + o_off), (uint32_t)n_streams, n, (Fr*)d_out);
     H2B_CK(cudaGetLastError());
     return end_call(ctx, d);
+}
+
+// ---- lookup argument: permute_expression_pair (lookup/prover.rs:398-494) -----------------------------------
+int h2b_lookup_permute_device(h2b_ctx* ctx, const void* d_input, const void* d_table, size_t usable, size_t n, void* d_out_input,
+                              void* d_out_table) {
+    if (!ctx) return H2B_E_INVALID;
+    if (n && (!d_input || !d_table || !d_out_input || !d_out_table)) return ctx->fail(H2B_E_INVALID, "lookup_permute: null argument");
+    if (usable > n || usable >= ((size_t)1 << 30)) return ctx->fail(H2B_E_INVALID, "lookup_permute: usable rows out of range");
+    if (!n) return H2B_OK;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    const size_t need = lookup_permute_scratch_bytes((uint32_t)usable);
+    H2B_CK(d.q_scratch.reserve(need));
+    H2B_CK(d.reserve_pinned(256));
+    begin_call(d);
+    uint32_t* d_status = nullptr;
+    int launches = 0;
+    d.prof_begin("lookup_permute");
+    H2B_CK(lookup_permute_run(d.launch_stream, (const Fr*)d_input, (const Fr*)d_table, (uint32_t)usable, (uint64_t)n, (Fr*)d_out_input,
+                              (Fr*)d_out_table, d.q_scratch.p, d.q_scratch.cap, &d_status, &launches));
+    d.prof_end();
+    d.launches += launches;
+    H2B_CK(cudaMemcpyAsync(d.pinned, d_status, 4, cudaMemcpyDeviceToHost, d.launch_stream));
+    int rc = end_call(ctx, d);
+    if (rc) return rc;
+    const uint32_t status = *reinterpret_cast<const uint32_t*>(d.pinned);
+    if (status & 1u) return ctx->fail(H2B_E_CONSTRAINT, "lookup_permute: an input value is missing from the table (ConstraintSystemFailure)");
+    if (status & 2u) return ctx->fail(H2B_E_CONSTRAINT, "lookup_permute: table multiset does not cover the repeated rows");
+    return H2B_OK;
 }
 
 int h2b_imad_peak(h2b_ctx* ctx, double* wide_mads_per_s, double* field_muls_per_s) {

@@ -220,48 +220,18 @@ class DeviceOps:
         return out
 
     def permute_expression_pair(self, compressed_input, compressed_table, usable: int):
-        """lookup/prover.rs:398-494 (`permute_expression_pair`) on the usable rows, device resident: the reference sorts the input
-        column, keeps a BTreeMap of table multiplicities and fills repeated rows from the back; here the same assignment is computed
-        with sort / scan / scatter index bookkeeping on the device (torch: plumbing, no field arithmetic), on the canonical values
-        `Fr: Ord` compares.  Returns two n-row Montgomery polynomials whose last n - usable rows are zero (the caller blinds them).
-        Must equal arguments.permute_expression_pair, which the CPU twin uses (tests/test_gpu_plonk.py compares the proof bytes)."""
-        from . import circuit as C
-        from . import polyexpr as PX
+        """lookup/prover.rs:398-494 (`permute_expression_pair`) on the usable rows, device resident (h2b_lookup_permute_device:
+        256-bit radix sort of the canonical values, dense ranks, table histogram, one emit kernel).  Returns two n-row Montgomery
+        polynomials whose last n - usable rows are zero (the caller blinds them).  Equals arguments.permute_expression_pair, which
+        the CPU twin uses (tests/test_gpu_plonk.py compares the proof bytes)."""
+        import ctypes
+        from .. import _lib
         from .arguments import ConstraintSystemFailure
-        t, u, n = self.torch, usable, self.n
-        r_inv = pow(F.MONT_R, -1, F.R_MOD)
-        both = t.cat([PX.pointwise(self, C.mul(PX.col(0), C.const(r_inv)), [p])[:u] for p in (compressed_input, compressed_table)], 0)
-        sign = t.tensor(-0x8000000000000000, dtype=t.int64, device="cuda")
-        order = t.arange(2 * u, device="cuda")
-        for limb in range(4):                                   # LSD radix over the four limbs, unsigned order, stable
-            key = (both[order, limb] ^ sign)
-            order = order[t.sort(key, stable=True).indices]
-        srt = both[order]
-        new_group = t.ones(2 * u, dtype=t.bool, device="cuda")
-        new_group[1:] = (srt[1:] != srt[:-1]).any(dim=1)
-        gid = t.cumsum(new_group.to(t.int64), 0) - 1
-        rank = t.empty(2 * u, dtype=t.int64, device="cuda")
-        rank[order] = gid
-        values = srt[new_group]                                 # value of each rank, ascending
-        n_groups = values.shape[0]
-        sorted_in = t.sort(rank[:u]).values
-        first = t.ones(u, dtype=t.bool, device="cuda")
-        first[1:] = sorted_in[1:] != sorted_in[:-1]
-        counts = t.bincount(rank[u:], minlength=n_groups)
-        distinct = sorted_in[first]
-        if bool((counts[distinct] == 0).any()):
+        out_in, out_tab = self.zeros(self.n), self.zeros(self.n)
+        ptr = lambda t: ctypes.c_void_p(t.data_ptr())
+        rc = self.ctx.lib.h2b_lookup_permute_device(self.ctx.handle, ptr(compressed_input), ptr(compressed_table), usable, self.n,
+                                                    ptr(out_in), ptr(out_tab))
+        if rc == _lib.H2B_E_CONSTRAINT:
             raise ConstraintSystemFailure("lookup input value missing from the table")
-        counts[distinct] -= 1
-        leftover = t.repeat_interleave(t.arange(n_groups, device="cuda"), counts)
-        repeated_rows = t.nonzero(~first).flatten()
-        assert leftover.shape[0] == repeated_rows.shape[0]
-        table_rank = sorted_in.clone()
-        table_rank[repeated_rows.flip(0)] = leftover
-        to_mont = C.mul(PX.col(0), C.const(F.MONT_R % F.R_MOD))
-        out = []
-        for ranks in (sorted_in, table_rank):
-            raw = t.zeros((n, 4), dtype=t.int64, device="cuda")
-            raw[:u] = values[ranks]
-            self._done()
-            out.append(PX.pointwise(self, to_mont, [raw]))
-        return out[0], out[1]
+        self.ctx.check(rc)
+        return out_in, out_tab
