@@ -47,6 +47,13 @@ class RefOps:
         r_inv = pow(1 << 256, -1, P)
         return [sum(int(x) << (64 * i) for i, x in enumerate(row)) * r_inv % P for row in np.asarray(mont).reshape(-1, 4)]
 
+    # RefOps polynomials are canonical ints; "raw" bytes are the Montgomery limbs the device holds, so that serialised keys agree
+    def download_bytes(self, p) -> bytes:
+        return b"".join((v * (1 << 256) % P).to_bytes(32, "little") for v in p)
+
+    def upload_raw(self, limbs: np.ndarray):
+        return self.upload(limbs)
+
     def to_ints(self, p) -> List[int]:
         return list(p)
 

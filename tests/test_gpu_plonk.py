@@ -233,3 +233,22 @@ def test_lookup_permute_matches_host_restatement(ctx):
         if bad[usable // 2] not in present:
             with pytest.raises(A.ConstraintSystemFailure):
                 ops.permute_expression_pair(ops.from_ints(pad(bad)), d_tab, usable)
+
+
+@pytest.mark.parametrize("fmt", ["Processed", "RawBytes"])
+def test_key_serialization_matches_cpu_and_round_trips(ctx, fmt):
+    """The serialised proving key of the device prover is byte-identical to the CPU restatement's (plonk.rs:276-287), reads back
+    into device polynomials, and proves the same bytes (halo2_proofs/tests/serialization.rs:131-195)."""
+    from h2b200.plonk import serialization as S
+    k = 5
+    circ = example.StandardPlonk(k, 9, 5)
+    cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circ)
+    ref_ops = plonk_ops.RefOps(k, SECRET, ref_dom)
+    ref_pk = plonk.keygen_pk(ref_ops, plonk.keygen_vk(ref_ops, cc), cc)
+    blob = S.pk_write(ops, pk, fmt)
+    assert blob == S.pk_write(ref_ops, ref_pk, fmt) and len(blob) == S.pk_bytes_length(ops, pk, fmt)
+    pk2 = S.pk_read(ops, blob, fmt, cs)
+    assert S.pk_write(ops, pk2, fmt) == blob
+    proof = _prove(circ, ops, pk2, RNG.OneNg(), 2)
+    assert proof == _prove(circ, ops, pk, RNG.OneNg(), 2)
+    assert plonk_verifier.verify_proof(pk2.vk, [], proof, SECRET, 1 << k)

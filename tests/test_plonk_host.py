@@ -272,3 +272,41 @@ def test_golden_proofs_regenerate():
         assert proof.hex() == case["proof"] and hashlib.sha256(proof).hexdigest() == case["sha256"], case["name"]
         assert plonk_verifier.verify_proof(vk, circ.instances(), bytes.fromhex(case["proof"]), SECRET, 1 << case["k"],
                                            multiopen=case["multiopen"])
+
+
+@pytest.mark.parametrize("fmt", ["Processed", "RawBytes", "RawBytesUnchecked"])
+def test_key_serialization_round_trip(setup, fmt):
+    """halo2_proofs/tests/serialization.rs:131-195: write the proving key, read it back, prove with it, verify; plus the byte
+    lengths of plonk.rs:131-139, 259-272 and the verifying-key round trip (plonk.rs:57-118)."""
+    from h2b200.plonk import serialization as S
+    circ, ops, vk, pk = setup
+    vk_bytes = S.vk_write(vk, fmt)
+    assert len(vk_bytes) == S.vk_bytes_length(vk, fmt) and vk_bytes[0] == 0x04 and vk_bytes[1] == K
+    vk2 = S.vk_read(vk_bytes, fmt, vk.cs, lambda degree, k: R.EvaluationDomain(degree, k))
+    assert vk2.fixed_commitments == vk.fixed_commitments and vk2.permutation_commitments == vk.permutation_commitments
+    assert vk2.transcript_repr == vk.transcript_repr
+    pk_bytes = S.pk_write(ops, pk, fmt)
+    assert len(pk_bytes) == S.pk_bytes_length(ops, pk, fmt)
+    pk2 = S.pk_read(ops, pk_bytes, fmt, vk.cs)
+    assert pk2.l0 == pk.l0 and pk2.l_active_row == pk.l_active_row and pk2.fixed_cosets == pk.fixed_cosets
+    assert pk2.permutation.polys == pk.permutation.polys and S.pk_write(ops, pk2, fmt) == pk_bytes
+    proof = _prove(circ, ops, pk2, RNG.OneNg())
+    assert proof == _prove(circ, ops, pk, RNG.OneNg())
+    assert plonk_verifier.verify_proof(vk2, circ.instances(), proof, SECRET, 1 << K)
+
+
+def test_key_serialization_rejects():
+    from h2b200.plonk import serialization as S
+    with pytest.raises(IOError, match="version"):
+        S.vk_read(bytes([3, 6, 0, 0, 0, 0]), "RawBytes", None, None)
+    r = S._Reader(b"\x00\x00\x00\x01" + F.R_MOD.to_bytes(32, "little"))
+    with pytest.raises(IOError, match="prime field"):
+        S.read_polynomial(None, r, "Processed")
+    g = (1, 2)
+    for fmt in S.FORMATS:
+        assert S.read_point(S._Reader(S.write_point(g, fmt)), fmt) == g and len(S.write_point(g, fmt)) == S.point_byte_length(fmt)
+        assert S.read_point(S._Reader(S.write_point(None, fmt)), fmt) is None
+    bad = F.fq_mont(1).tobytes() + F.fq_mont(3).tobytes()                  # (1, 3) is not on the curve
+    with pytest.raises(IOError, match="curve"):
+        S.read_point(S._Reader(bad), "RawBytes")
+    assert S.read_point(S._Reader(bad), "RawBytesUnchecked") == (1, 3)

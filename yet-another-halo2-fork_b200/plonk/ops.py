@@ -53,6 +53,14 @@ class DeviceOps:
     def download(self, p) -> np.ndarray:
         return p.cpu().numpy().view(np.uint64)
 
+    def download_bytes(self, p) -> bytes:
+        """The device buffer as it is: rows x 32 bytes, little-endian limbs."""
+        return self.download(p).tobytes()
+
+    def upload_raw(self, limbs: np.ndarray):
+        """(rows, 4) little-endian uint64 limbs taken as they are (no conversion)."""
+        return self.upload(np.ascontiguousarray(limbs, dtype=np.uint64))
+
     def to_ints(self, p) -> List[int]:
         return [F.fr_int(row) for row in self.download(p)]
 
