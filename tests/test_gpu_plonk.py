@@ -252,3 +252,27 @@ def test_key_serialization_matches_cpu_and_round_trips(ctx, fmt):
     proof = _prove(circ, ops, pk2, RNG.OneNg(), 2)
     assert proof == _prove(circ, ops, pk, RNG.OneNg(), 2)
     assert plonk_verifier.verify_proof(pk2.vk, [], proof, SECRET, 1 << k)
+
+
+def test_multi_device_proof_matches_single_device():
+    """One context over two GPUs (MSMs sharded by point range, evaluate_h's coset NTTs dealt round-robin): the proof
+    bytes equal the single-device proof.  Skipped on a one-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    k = 10
+    circ = example.MyCircuit(k, 42)
+    proofs = []
+    for devices in ([0], [0, 1]):
+        c = h2b200.Context(devices)
+        try:
+            cc = circ.compile()
+            cs = plonk.circuit.ConstraintSystemBack(cc.cs)
+            engine = h2b200.B200Engine(c)
+            ops = DeviceOps(h2b200.ParamsKZG.setup(k, SECRET, engine), engine, h2b200.EvaluationDomain(cs.degree(), k, c))
+            vk = plonk.keygen_vk(ops, cc)
+            proofs.append(_prove(circ, ops, plonk.keygen_pk(ops, vk, cc), RNG.OneNg(), 8))
+        finally:
+            c.close()
+    assert proofs[0] == proofs[1]
+    assert plonk_verifier.verify_proof(vk, circ.instances(), proofs[1], SECRET, 1 << k)
