@@ -66,33 +66,46 @@ class _Msm:
 
 def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n: int, debug: dict = None,
                  multiopen: str = "shplonk") -> bool:
+    """verify_proof_single (plonk/verifier.rs:29-47): one circuit."""
+    return verify_proof_batch(vk, [instances], proof, s, n, debug, multiopen)
+
+
+def verify_proof_batch(vk, circuits_instances: Sequence[Sequence[Sequence[int]]], proof: bytes, s: int, n: int, debug: dict = None,
+                       multiopen: str = "shplonk") -> bool:
+    """verify_proof (plonk/verifier.rs:49-511) for `num_proofs` instances of one circuit proven in one transcript."""
     cs, domain = vk.cs, vk.domain
-    if len(instances) != cs.num_instance_columns:
-        raise VerifyError("InvalidInstances")
+    for instances in circuits_instances:
+        if len(instances) != cs.num_instance_columns:
+            raise VerifyError("InvalidInstances")
+    num_proofs = len(circuits_instances)
+    proofs = range(num_proofs)
     t = Blake2bRead(proof)
     vk.hash_into(t)
-    for column in instances:
-        for v in column:
-            t.common_scalar(v)
-    advice_commitments = [None] * cs.num_advice_columns
+    for instances in circuits_instances:
+        for column in instances:
+            for v in column:
+                t.common_scalar(v)
+    advice_commitments = [[None] * cs.num_advice_columns for _ in proofs]
     challenges = [0] * cs.num_challenges
     for phase in cs.phases():                                                       # verifier.rs:151-176
-        for i, p in enumerate(cs.advice_column_phase):
-            if p == phase:
-                advice_commitments[i] = t.read_point()
+        for c in proofs:
+            for i, p in enumerate(cs.advice_column_phase):
+                if p == phase:
+                    advice_commitments[c][i] = t.read_point()
         for i, p in enumerate(cs.challenge_phase):
             if p == phase:
                 challenges[i] = t.squeeze_challenge_scalar()
     theta = t.squeeze_challenge_scalar()
-    lookups = [{"permuted_input": t.read_point(), "permuted_table": t.read_point()} for _ in cs.lookups]
+    lookups = [[{"permuted_input": t.read_point(), "permuted_table": t.read_point()} for _ in cs.lookups] for _ in proofs]
     beta = t.squeeze_challenge_scalar()
     gamma = t.squeeze_challenge_scalar()
     chunk_len = vk.cs_degree - 2
     n_sets = (len(cs.permutation_columns) + chunk_len - 1) // chunk_len
-    perm_sets = [{"commitment": t.read_point()} for _ in range(n_sets)]
-    for l in lookups:
-        l["product"] = t.read_point()
-    shuffles = [{"product": t.read_point()} for _ in cs.shuffles]
+    perm_sets = [[{"commitment": t.read_point()} for _ in range(n_sets)] for _ in proofs]
+    for c in proofs:
+        for l in lookups[c]:
+            l["product"] = t.read_point()
+    shuffles = [[{"product": t.read_point()} for _ in cs.shuffles] for _ in proofs]
     random_poly_commitment = t.read_point()
     y = t.squeeze_challenge_scalar()
     h_commitments = [t.read_point() for _ in range(domain.quotient_poly_degree)]
@@ -101,101 +114,110 @@ def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n
     # instance evals by Lagrange interpolation (QUERY_INSTANCE == false), verifier.rs:243-279
     min_rot = min([0] + [rot for _, rot in cs.instance_queries])
     max_rot = max([0] + [rot for _, rot in cs.instance_queries])
-    max_len = max([len(c) for c in instances], default=0)
+    max_len = max([len(col) for instances in circuits_instances for col in instances], default=0)
     l_i_s = l_i_range(domain, x, xn, list(range(-max_rot, max_len + abs(min_rot))))
     instance_evals = []
-    for column, rot in cs.instance_queries:
-        vals = instances[column]
-        offset = max_rot - rot
-        instance_evals.append(sum(a * b for a, b in zip(vals, l_i_s[offset:offset + len(vals)])) % P)
-    advice_evals = [t.read_scalar() for _ in cs.advice_queries]
+    for instances in circuits_instances:
+        evals_c = []
+        for column, rot in cs.instance_queries:
+            vals = instances[column]
+            offset = max_rot - rot
+            evals_c.append(sum(a * b for a, b in zip(vals, l_i_s[offset:offset + len(vals)])) % P)
+        instance_evals.append(evals_c)
+    advice_evals = [[t.read_scalar() for _ in cs.advice_queries] for _ in proofs]
     fixed_evals = [t.read_scalar() for _ in cs.fixed_queries]
     random_eval = t.read_scalar()
     permutation_evals = [t.read_scalar() for _ in vk.permutation_commitments]
-    for i, st in enumerate(perm_sets):                                              # permutation/verifier.rs:66-96
-        st["eval"], st["next_eval"] = t.read_scalar(), t.read_scalar()
-        st["last_eval"] = t.read_scalar() if i + 1 < len(perm_sets) else None
-    for l in lookups:                                                               # lookup/verifier.rs:62-86
-        l["product_eval"], l["product_next_eval"] = t.read_scalar(), t.read_scalar()
-        l["permuted_input_eval"], l["permuted_input_inv_eval"], l["permuted_table_eval"] = (t.read_scalar(), t.read_scalar(),
-                                                                                            t.read_scalar())
-    for sh in shuffles:
-        sh["product_eval"], sh["product_next_eval"] = t.read_scalar(), t.read_scalar()
+    for c in proofs:
+        for i, st in enumerate(perm_sets[c]):                                       # permutation/verifier.rs:66-96
+            st["eval"], st["next_eval"] = t.read_scalar(), t.read_scalar()
+            st["last_eval"] = t.read_scalar() if i + 1 < len(perm_sets[c]) else None
+    for c in proofs:
+        for l in lookups[c]:                                                        # lookup/verifier.rs:62-86
+            l["product_eval"], l["product_next_eval"] = t.read_scalar(), t.read_scalar()
+            l["permuted_input_eval"], l["permuted_input_inv_eval"], l["permuted_table_eval"] = (t.read_scalar(), t.read_scalar(),
+                                                                                                t.read_scalar())
+    for c in proofs:
+        for sh in shuffles[c]:
+            sh["product_eval"], sh["product_next_eval"] = t.read_scalar(), t.read_scalar()
 
     bf = cs.blinding_factors()
     l_evals = l_i_range(domain, x, xn, list(range(-(bf + 1), 1)))
     assert len(l_evals) == 2 + bf
     l_last, l_blind, l_0 = l_evals[0], sum(l_evals[1:1 + bf]) % P, l_evals[1 + bf]
     active = (1 - (l_last + l_blind)) % P
-    ev = lambda e: C.evaluate_at(e, fixed_evals, advice_evals, instance_evals, challenges, cs.query_index)
-    compress = lambda exprs: _fold(theta, [ev(e) for e in exprs])
-    expressions = [ev(poly) for _, poly in cs.gates]
-    # permutation/verifier.rs:100-194
-    if perm_sets:
-        expressions.append(l_0 * (1 - perm_sets[0]["eval"]) % P)
-        last = perm_sets[-1]["eval"]
-        expressions.append((last * last - last) * l_last % P)
-        for prev, cur in zip(perm_sets, perm_sets[1:]):
-            expressions.append((cur["eval"] - prev["last_eval"]) * l_0 % P)
-        evals_of = {"advice": advice_evals, "fixed": fixed_evals, "instance": instance_evals}
-        for chunk_index, st in enumerate(perm_sets):
-            cols = cs.permutation_columns[chunk_index * chunk_len:(chunk_index + 1) * chunk_len]
-            pevals = permutation_evals[chunk_index * chunk_len:(chunk_index + 1) * chunk_len]
-            col_evals = [evals_of[kind][cs.get_any_query_index(kind, index, 0)] for kind, index in cols]
-            left = st["next_eval"]
-            for e, pe in zip(col_evals, pevals):
-                left = left * (e + beta * pe + gamma) % P
-            right = st["eval"]
-            current_delta = beta * x % P * pow(FR_DELTA, chunk_index * chunk_len, P) % P
-            for e in col_evals:
-                right = right * (e + current_delta + gamma) % P
-                current_delta = current_delta * FR_DELTA % P
-            expressions.append((left - right) * active % P)
-    for l, arg in zip(lookups, cs.lookups):                                         # lookup/verifier.rs:90-163
-        left = l["product_next_eval"] * (l["permuted_input_eval"] + beta) % P * (l["permuted_table_eval"] + gamma) % P
-        right = l["product_eval"] * (compress(arg.input_expressions) + beta) % P * (compress(arg.table_expressions) + gamma) % P
-        a_minus_s = (l["permuted_input_eval"] - l["permuted_table_eval"]) % P
-        expressions += [l_0 * (1 - l["product_eval"]) % P,
-                        l_last * (l["product_eval"] ** 2 - l["product_eval"]) % P,
-                        (left - right) * active % P,
-                        l_0 * a_minus_s % P,
-                        a_minus_s * (l["permuted_input_eval"] - l["permuted_input_inv_eval"]) % P * active % P]
-    for sh, arg in zip(shuffles, cs.shuffles):                                      # shuffle/verifier.rs:55-115
-        left = sh["product_next_eval"] * (compress(arg.shuffle_expressions) + gamma) % P
-        right = sh["product_eval"] * (compress(arg.input_expressions) + gamma) % P
-        expressions += [l_0 * (1 - sh["product_eval"]) % P,
-                        l_last * (sh["product_eval"] ** 2 - sh["product_eval"]) % P,
-                        (left - right) * active % P]
+    expressions = []
+    for c in proofs:
+        ev = lambda e: C.evaluate_at(e, fixed_evals, advice_evals[c], instance_evals[c], challenges, cs.query_index)
+        compress = lambda exprs: _fold(theta, [ev(e) for e in exprs])
+        expressions += [ev(poly) for _, poly in cs.gates]
+        sets = perm_sets[c]
+        if sets:                                                                    # permutation/verifier.rs:100-194
+            expressions.append(l_0 * (1 - sets[0]["eval"]) % P)
+            last = sets[-1]["eval"]
+            expressions.append((last * last - last) * l_last % P)
+            for prev, cur in zip(sets, sets[1:]):
+                expressions.append((cur["eval"] - prev["last_eval"]) * l_0 % P)
+            evals_of = {"advice": advice_evals[c], "fixed": fixed_evals, "instance": instance_evals[c]}
+            for chunk_index, st in enumerate(sets):
+                cols = cs.permutation_columns[chunk_index * chunk_len:(chunk_index + 1) * chunk_len]
+                pevals = permutation_evals[chunk_index * chunk_len:(chunk_index + 1) * chunk_len]
+                col_evals = [evals_of[kind][cs.get_any_query_index(kind, index, 0)] for kind, index in cols]
+                left = st["next_eval"]
+                for e, pe in zip(col_evals, pevals):
+                    left = left * (e + beta * pe + gamma) % P
+                right = st["eval"]
+                current_delta = beta * x % P * pow(FR_DELTA, chunk_index * chunk_len, P) % P
+                for e in col_evals:
+                    right = right * (e + current_delta + gamma) % P
+                    current_delta = current_delta * FR_DELTA % P
+                expressions.append((left - right) * active % P)
+        for l, arg in zip(lookups[c], cs.lookups):                                  # lookup/verifier.rs:90-163
+            left = l["product_next_eval"] * (l["permuted_input_eval"] + beta) % P * (l["permuted_table_eval"] + gamma) % P
+            right = l["product_eval"] * (compress(arg.input_expressions) + beta) % P * (compress(arg.table_expressions) + gamma) % P
+            a_minus_s = (l["permuted_input_eval"] - l["permuted_table_eval"]) % P
+            expressions += [l_0 * (1 - l["product_eval"]) % P,
+                            l_last * (l["product_eval"] ** 2 - l["product_eval"]) % P,
+                            (left - right) * active % P,
+                            l_0 * a_minus_s % P,
+                            a_minus_s * (l["permuted_input_eval"] - l["permuted_input_inv_eval"]) % P * active % P]
+        for sh, arg in zip(shuffles[c], cs.shuffles):                               # shuffle/verifier.rs:55-115
+            left = sh["product_next_eval"] * (compress(arg.shuffle_expressions) + gamma) % P
+            right = sh["product_eval"] * (compress(arg.input_expressions) + gamma) % P
+            expressions += [l_0 * (1 - sh["product_eval"]) % P,
+                            l_last * (sh["product_eval"] ** 2 - sh["product_eval"]) % P,
+                            (left - right) * active % P]
     expected_h_eval = _fold(y, expressions) * _inv(xn - 1) % P                      # vanishing/verifier.rs:88-96
     if debug is not None:
         debug.update(x=x, y=y, theta=theta, beta=beta, gamma=gamma, expected_h_eval=expected_h_eval, expressions=expressions,
                      challenges=challenges)
     h_commitment = _Msm()
-    for c in reversed(h_commitments):
+    for cm in reversed(h_commitments):
         h_commitment.scale(xn)
-        h_commitment.append_term(1, c)
+        h_commitment.append_term(1, cm)
 
     # the verifier queries (commitment handle, point, eval), verifier.rs:437-499
     rot = domain.rotate_omega
     queries = []
-    for qi, (column, at) in enumerate(cs.advice_queries):
-        queries.append((rot(x, at), ("advice", column), advice_evals[qi]))
     x_next, x_last, x_inv = rot(x, 1), rot(x, -(bf + 1)), rot(x, -1)
-    for i, st in enumerate(perm_sets):
-        queries.append((x, ("perm_z", i), st["eval"]))
-        queries.append((x_next, ("perm_z", i), st["next_eval"]))
-    for i in reversed(range(len(perm_sets) - 1)):
-        queries.append((x_last, ("perm_z", i), perm_sets[i]["last_eval"]))
-    for i, l in enumerate(lookups):
-        queries += [(x, ("lk_z", i), l["product_eval"]), (x, ("lk_in", i), l["permuted_input_eval"]),
-                    (x, ("lk_tab", i), l["permuted_table_eval"]), (x_inv, ("lk_in", i), l["permuted_input_inv_eval"]),
-                    (x_next, ("lk_z", i), l["product_next_eval"])]
-    for i, sh in enumerate(shuffles):
-        queries += [(x, ("sh_z", i), sh["product_eval"]), (x_next, ("sh_z", i), sh["product_next_eval"])]
+    for c in proofs:
+        for qi, (column, at) in enumerate(cs.advice_queries):
+            queries.append((rot(x, at), ("advice", c, column), advice_evals[c][qi]))
+        for i, st in enumerate(perm_sets[c]):
+            queries.append((x, ("perm_z", c, i), st["eval"]))
+            queries.append((x_next, ("perm_z", c, i), st["next_eval"]))
+        for i in reversed(range(len(perm_sets[c]) - 1)):
+            queries.append((x_last, ("perm_z", c, i), perm_sets[c][i]["last_eval"]))
+        for i, l in enumerate(lookups[c]):
+            queries += [(x, ("lk_z", c, i), l["product_eval"]), (x, ("lk_in", c, i), l["permuted_input_eval"]),
+                        (x, ("lk_tab", c, i), l["permuted_table_eval"]), (x_inv, ("lk_in", c, i), l["permuted_input_inv_eval"]),
+                        (x_next, ("lk_z", c, i), l["product_next_eval"])]
+        for i, sh in enumerate(shuffles[c]):
+            queries += [(x, ("sh_z", c, i), sh["product_eval"]), (x_next, ("sh_z", c, i), sh["product_next_eval"])]
     for qi, (column, at) in enumerate(cs.fixed_queries):
-        queries.append((rot(x, at), ("fixed", column), fixed_evals[qi]))
+        queries.append((rot(x, at), ("fixed", 0, column), fixed_evals[qi]))
     for i, e in enumerate(permutation_evals):
-        queries.append((x, ("sigma", i), e))
+        queries.append((x, ("sigma", 0, i), e))
     queries.append((x, ("h",), expected_h_eval))
     queries.append((x, ("random",), random_eval))
 
@@ -203,11 +225,13 @@ def verify_proof(vk, instances: Sequence[Sequence[int]], proof: bytes, s: int, n
         kind = handle[0]
         if kind == "h":
             return _Msm(h_commitment.terms)
-        point = {"advice": lambda: advice_commitments[handle[1]], "perm_z": lambda: perm_sets[handle[1]]["commitment"],
-                 "lk_z": lambda: lookups[handle[1]]["product"], "lk_in": lambda: lookups[handle[1]]["permuted_input"],
-                 "lk_tab": lambda: lookups[handle[1]]["permuted_table"], "sh_z": lambda: shuffles[handle[1]]["product"],
-                 "fixed": lambda: vk.fixed_commitments[handle[1]], "sigma": lambda: vk.permutation_commitments[handle[1]],
-                 "random": lambda: random_poly_commitment}[kind]()
+        if kind == "random":
+            return _Msm([(1, random_poly_commitment)])
+        c, i = handle[1], handle[2]
+        point = {"advice": lambda: advice_commitments[c][i], "perm_z": lambda: perm_sets[c][i]["commitment"],
+                 "lk_z": lambda: lookups[c][i]["product"], "lk_in": lambda: lookups[c][i]["permuted_input"],
+                 "lk_tab": lambda: lookups[c][i]["permuted_table"], "sh_z": lambda: shuffles[c][i]["product"],
+                 "fixed": lambda: vk.fixed_commitments[i], "sigma": lambda: vk.permutation_commitments[i]}[kind]()
         return _Msm([(1, point)])
 
     if multiopen == "gwc":

@@ -276,3 +276,21 @@ def test_multi_device_proof_matches_single_device():
             c.close()
     assert proofs[0] == proofs[1]
     assert plonk_verifier.verify_proof(vk, circ.instances(), proofs[1], SECRET, 1 << k)
+
+
+def test_batch_proving_bytes_match(ctx):
+    """Two circuit instances in one transcript (`Prover`, prover.rs:130-175): evaluate_h chains the second circuit's custom-gate
+    Horner through PreviousValue on the device (evaluation.rs:366-395); bytes equal the CPU restatement, verifier accepts."""
+    k = 6
+    circuits = [example.MyCircuit(k, 42), example.MyCircuit(k, 77)]
+    cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circuits[0])
+    ref_ops = plonk_ops.RefOps(k, SECRET, ref_dom)
+    ref_pk = plonk.keygen_pk(ref_ops, plonk.keygen_vk(ref_ops, cc), cc)
+    instances = [c.instances() for c in circuits]
+    proofs = []
+    for o, key in ((ops, pk), (ref_ops, ref_pk)):
+        tr = plonk.Blake2bWrite()
+        plonk.create_proof_batch(o, key, instances, [c.witness for c in circuits], RNG.OneNg(), tr, num_threads=4)
+        proofs.append(tr.finalize())
+    assert proofs[0] == proofs[1]
+    assert plonk_verifier.verify_proof_batch(vk, instances, proofs[0], SECRET, 1 << k)

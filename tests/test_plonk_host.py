@@ -310,3 +310,22 @@ def test_key_serialization_rejects():
     with pytest.raises(IOError, match="curve"):
         S.read_point(S._Reader(bad), "RawBytes")
     assert S.read_point(S._Reader(bad), "RawBytesUnchecked") == (1, 3)
+
+
+def test_batch_proving_two_circuits(setup):
+    """`Prover` over two instances of the circuit in one transcript (prover.rs:130-175, create_proof with `circuits: &[C]`,
+    halo2_proofs/src/plonk/prover.rs:60-123; verifier.rs `num_proofs` loops)."""
+    _, ops, vk, pk = setup
+    circuits = [example.MyCircuit(K, 42), example.MyCircuit(K, 1000)]
+    instances = [c.instances() for c in circuits]
+    tr = plonk.Blake2bWrite()
+    plonk.create_proof_batch(ops, pk, instances, [c.witness for c in circuits], RNG.ChaCha20Rng(bytes(32)), tr, num_threads=2)
+    proof = tr.finalize()
+    single = len(_prove(circuits[0], ops, pk, RNG.OneNg()))
+    # per circuit: 4 advice + 2 + 1 + 1 + 1 points and 5 + 2 + 5 + 2 scalars more; the rest is shared
+    assert len(proof) == single + 32 * (9 + 14)
+    assert plonk_verifier.verify_proof_batch(vk, instances, proof, SECRET, 1 << K)
+    assert not plonk_verifier.verify_proof_batch(vk, instances[::-1], proof, SECRET, 1 << K)
+    with pytest.raises(plonk.prover.ProverError, match="witness.len"):
+        p = plonk.Prover(ops, pk, instances, RNG.OneNg(), plonk.Blake2bWrite())
+        p.commit_phase(0, [circuits[0].witness(0, {})])
