@@ -97,4 +97,16 @@ extern "C" {
     // permute_expression_pair of the lookup argument (lookup/prover.rs:398-494); -5 = ConstraintSystemFailure
     pub fn h2b_lookup_permute_device(ctx: *mut h2b_ctx, d_input: *const c_void, d_table: *const c_void, usable: usize, n: usize,
                                      d_out_input: *mut c_void, d_out_table: *mut c_void) -> c_int;
+    // multi-process sharding (one rank per GPU): each rank returns the window sums of its point range, any rank folds them
+    pub fn h2b_msm_windows(ctx: *mut h2b_ctx, bases_handle: u64, scalars: *const c_void, scalars_on_device: c_int, n: usize,
+                           n_total: usize, out_windows: *mut c_void, c_out: *mut u32, windows_out: *mut u32) -> c_int;
+    pub fn h2b_msm_combine(parts: *const c_void, n_parts: u32, c: u32, windows: u32, out96: *mut c_void) -> c_int;
+    // measurement hooks and synthetic benchmark input (bench only)
+    pub fn h2b_version() -> *const c_char;
+    pub fn h2b_last_call_ms(ctx: *const h2b_ctx) -> f64;
+    pub fn h2b_profile_enable(ctx: *mut h2b_ctx, on: c_int) -> c_int;
+    pub fn h2b_profile_read(ctx: *mut h2b_ctx, json_out: *mut c_char, cap: usize) -> c_int;
+    pub fn h2b_launch_count(ctx: *const h2b_ctx) -> u64;
+    pub fn h2b_synth_bases(ctx: *mut h2b_ctx, d_out: *mut c_void, n: usize, t0: u64) -> c_int;
+    pub fn h2b_imad_peak(ctx: *mut h2b_ctx, wide_mads_per_s: *mut f64, field_muls_per_s: *mut f64) -> c_int;
 }

@@ -31,6 +31,13 @@ def test_header_symbols_are_exported_and_bound():
     assert set(names) <= exported
 
 
+def test_rust_sys_crate_declares_every_header_symbol():
+    # rust/h2b200-sys is the binding a maintainer adds on the reference side; no cargo here, so the check is textual
+    src = open(os.path.join(ROOT, "rust", "h2b200-sys", "src", "lib.rs")).read()
+    declared = set(re.findall(r"\bpub fn (h2b_[a-z0-9_]+)\s*\(", src))
+    assert declared == set(header_functions())
+
+
 def test_library_is_sm100a_only():
     out = subprocess.run(["cuobjdump", "-lelf", h2b200.LIB_PATH], capture_output=True, text=True).stdout
     archs = set(re.findall(r"sm_(\d+a?)", out))
