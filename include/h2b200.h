@@ -158,6 +158,13 @@ int h2b_grand_product(h2b_ctx* ctx, const void* v, size_t n, const void* init32,
 int h2b_grand_product_device(h2b_ctx* ctx, const void* d_v, size_t n, const void* init32, void* d_z, size_t out_len);
 int h2b_eval_polynomial(h2b_ctx* ctx, const void* poly, size_t n, const void* point32, void* out32);
 int h2b_eval_polynomial_device(h2b_ctx* ctx, const void* d_poly, size_t n, const void* point32, void* out32);
+/* h2b_eval_polynomial_batch_device: out32s[i] = eval_polynomial(d_polys[i], points32[i]) for `count` device-resident polynomials
+ * of n coefficients each -- the evaluations create_proof writes after the challenge x (plonk/prover.rs:742-811: advice, fixed,
+ * random, permutation, lookup and shuffle polynomials at x and its rotations) and the ones the multi-open argument takes
+ * (poly/query.rs:62-64 via shplonk/prover.rs:117-131) in two launches and one result copy instead of three launches and a
+ * synchronisation each.  points32 = count x 32 bytes (Montgomery), out32s = count x 32 bytes on the host.  An API extension. */
+int h2b_eval_polynomial_batch_device(h2b_ctx* ctx, const void* const* d_polys, size_t n, const void* points32, size_t count,
+                                     void* out32s);
 int h2b_kate_division(h2b_ctx* ctx, const void* a, size_t n, const void* b32, void* q);
 int h2b_kate_division_device(h2b_ctx* ctx, const void* d_a, size_t n, const void* b32, void* d_q);
 

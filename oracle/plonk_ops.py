@@ -178,5 +178,8 @@ class RefOps:
     def eval_polynomial(self, p, point: int) -> int:
         return R.eval_polynomial(p, point)
 
+    def eval_polynomials(self, pairs) -> list:
+        return [R.eval_polynomial(p, point) for p, point in pairs]
+
     def kate_division(self, p, b: int):
         return R.kate_division(p, b)

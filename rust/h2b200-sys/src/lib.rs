@@ -63,6 +63,8 @@ extern "C" {
     pub fn h2b_grand_product_device(ctx: *mut h2b_ctx, d_v: *const c_void, n: usize, init32: *const c_void, d_z: *mut c_void, out_len: usize) -> c_int;
     pub fn h2b_eval_polynomial(ctx: *mut h2b_ctx, poly: *const c_void, n: usize, point32: *const c_void, out32: *mut c_void) -> c_int;
     pub fn h2b_eval_polynomial_device(ctx: *mut h2b_ctx, d_poly: *const c_void, n: usize, point32: *const c_void, out32: *mut c_void) -> c_int;
+    pub fn h2b_eval_polynomial_batch_device(ctx: *mut h2b_ctx, d_polys: *const *const c_void, n: usize, points32: *const c_void,
+                                            count: usize, out32s: *mut c_void) -> c_int;
     pub fn h2b_kate_division(ctx: *mut h2b_ctx, a: *const c_void, n: usize, b32: *const c_void, q: *mut c_void) -> c_int;
     pub fn h2b_kate_division_device(ctx: *mut h2b_ctx, d_a: *const c_void, n: usize, b32: *const c_void, d_q: *mut c_void) -> c_int;
     // quotient evaluation (plonk/evaluation.rs:317-623), device resident

@@ -110,6 +110,35 @@ def test_device_resident_variants(ops):
     assert np.array_equal(inv.cpu().numpy().view(np.uint64), C.batch_invert(a))
 
 
+@pytest.mark.parametrize("n", [1, 7, 2048, 2049, (1 << 16) + 3, (1 << 19) + 4097])
+def test_eval_polynomial_batch(ops, n):
+    """h2b_eval_polynomial_batch_device: many (polynomial, point) pairs in one call == the oracle, pair by pair."""
+    import torch
+    polys = [C.random_fr(n, 900 + i) for i in range(3)]
+    devs = [torch.from_numpy(a.view(np.int64)).cuda() for a in polys]
+    points = [0, 1, R.R_MOD - 1, 5, 0x1234567890ABCDEF1234567890ABCDEF % R.R_MOD, 77, 78]
+    pairs = [(i % 3, pt) for i, pt in enumerate(points)] + [(0, 5), (2, 5)]           # repeated polynomials and points
+    got = ops.eval_polynomials([(devs[i], pt) for i, pt in pairs])
+    exp = [C.int_from_mont(C.eval_polynomial(polys[i], m(pt)), R.R_MOD) for i, pt in pairs]
+    assert got == exp
+    assert got == [ops.eval_polynomial(devs[i], pt) for i, pt in pairs]
+
+
+def test_eval_polynomial_batch_edges(ops):
+    import torch
+    assert ops.eval_polynomials([]) == []
+    a = C.random_fr(300, 3)
+    d = torch.from_numpy(a.view(np.int64)).cuda()
+    # host arrays and mixed lengths fall back to single evaluations, same values
+    b = C.random_fr(17, 4)
+    got = ops.eval_polynomials([(d, 9), (b, 9), (a, 11)])
+    assert got == [R.eval_polynomial(C.ints_from_fr_array(a, R.R_MOD), 9), R.eval_polynomial(C.ints_from_fr_array(b, R.R_MOD), 9),
+                   R.eval_polynomial(C.ints_from_fr_array(a, R.R_MOD), 11)]
+    many = ops.eval_polynomials([(d, 1000 + i) for i in range(130)])                  # more jobs than one wave of blocks per tile
+    ints = C.ints_from_fr_array(a, R.R_MOD)
+    assert many == [R.eval_polynomial(ints, 1000 + i) for i in range(130)]
+
+
 def test_permutation_product_shape(ops):
     """The sequence of permutation/prover.rs:118-166 on the GPU: denominators -> batch_invert -> numerators -> running product."""
     n = 1 << 12

@@ -46,6 +46,7 @@ SYMBOLS = {
     "h2b_grand_product_device": (_int, [_vp, _vp, _sz, _vp, _vp, _sz]),
     "h2b_eval_polynomial": (_int, [_vp, _vp, _sz, _vp, _vp]),
     "h2b_eval_polynomial_device": (_int, [_vp, _vp, _sz, _vp, _vp]),
+    "h2b_eval_polynomial_batch_device": (_int, [_vp, _vp, _sz, _vp, _sz, _vp]),
     "h2b_kate_division": (_int, [_vp, _vp, _sz, _vp, _vp]),
     "h2b_kate_division_device": (_int, [_vp, _vp, _sz, _vp, _vp]),
     "h2b_quotient_graph_device": (_int, [_vp, _vp, ctypes.POINTER(_vp), _sz, ctypes.POINTER(_vp), _sz, ctypes.POINTER(_vp), _sz,

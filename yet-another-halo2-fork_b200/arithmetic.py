@@ -48,6 +48,23 @@ class PolyOps:
             c.check(lib.h2b_eval_polynomial(c.handle, _vp(a) if n else None, n, _vp(pt), _vp(out)))
         return F.fr_int(out)
 
+    def eval_polynomials(self, pairs) -> list:
+        """[eval_polynomial(poly, point) for poly, point in pairs] for device-resident polynomials of one length, in one library
+        call (h2b_eval_polynomial_batch_device): the evaluation phase of create_proof (plonk/prover.rs:742-811)."""
+        pairs = list(pairs)
+        if not pairs:
+            return []
+        c, lib = self.ctx, self.ctx.lib
+        n = _rows(pairs[0][0])
+        if not all(_is_torch_cuda(p) and _rows(p) == n for p, _ in pairs):
+            return [self.eval_polynomial(p, pt) for p, pt in pairs]
+        count = len(pairs)
+        ptrs = (ctypes.c_void_p * count)(*[p.data_ptr() for p, _ in pairs])
+        pts = np.stack([F.fr_mont(pt) for _, pt in pairs])
+        out = np.zeros((count, 4), dtype=np.uint64)
+        c.check(lib.h2b_eval_polynomial_batch_device(c.handle, ctypes.cast(ptrs, ctypes.c_void_p), n, _vp(pts), count, _vp(out)))
+        return [F.fr_int(out[i]) for i in range(count)]
+
     def kate_division(self, a, b: int):
         """arithmetic.rs:99-120: quotient of a(X) by (X - b), remainder dropped; len(a) - 1 coefficients."""
         c, lib = self.ctx, self.ctx.lib

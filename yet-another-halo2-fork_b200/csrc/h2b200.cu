@@ -1394,6 +1394,44 @@ int h2b_eval_polynomial_device(h2b_ctx* ctx, const void* d_poly, size_t n, const
     if (ctx && !out32) return ctx->fail(H2B_E_INVALID, "eval_polynomial: null argument");
     return horner_impl(ctx, d_poly, n, point32, nullptr, out32, true, "eval_polynomial");
 }
+// count independent evaluations of length-n device polynomials in two launches and one result copy
+int h2b_eval_polynomial_batch_device(h2b_ctx* ctx, const void* const* d_polys, size_t n, const void* points32, size_t count,
+                                     void* out32s) {
+    if (!ctx) return H2B_E_INVALID;
+    if (count && (!d_polys || !points32 || !out32s)) return ctx->fail(H2B_E_INVALID, "eval_polynomial_batch: null argument");
+    for (size_t i = 0; i < count; i++)
+        if (!d_polys[i] && n) return ctx->fail(H2B_E_INVALID, "eval_polynomial_batch: null polynomial");
+    if (count > 65535) return ctx->fail(H2B_E_INVALID, "eval_polynomial_batch: more than 65535 evaluations in one call");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    if (count == 0) { ctx->last_ms = 0; return H2B_OK; }
+    if (n == 0) { std::memset(out32s, 0, count * 32); ctx->last_ms = 0; return H2B_OK; }          // empty sums
+    const uint32_t tiles = poly_tiles(n);
+    const uint64_t pad = (uint64_t)tiles * POLY_TILE - n;
+    std::vector<HornerJob> jobs(count);
+    for (size_t i = 0; i < count; i++) {
+        HornerJob& J = jobs[i];
+        J.a = (const Fr*)d_polys[i];
+        J.reserved = 0;
+        J.b = fr_from_bytes((const uint8_t*)points32 + 32 * i);
+        J.bk = fe_pow_u64(J.b, (uint64_t)POLY_K);
+        J.bt = fe_pow_u64(J.b, (uint64_t)POLY_TILE);
+    }
+    const size_t jobs_bytes = count * sizeof(HornerJob);
+    H2B_CK(d.q_stage.reserve(jobs_bytes + count * 32 + 64));
+    H2B_CK(d.p_tiles.reserve((size_t)tiles * count * 32 + 64));
+    begin_call(d);
+    H2B_CK(d.ring.h2d(d.q_stage.p, jobs.data(), jobs_bytes, d.stream));
+    const HornerJob* dj = d.q_stage.as<HornerJob>();
+    Fr* d_out = (Fr*)(d.q_stage.as<uint8_t>() + ((jobs_bytes + 31) & ~(size_t)31));
+    Fr* tv = d.p_tiles.as<Fr>();
+    H2B_LAUNCH(d, "poly_horner_batch", PK.horner_batch_tile_reduce, dim3(tiles, (unsigned)count), POLY_T, 0, dj, (uint64_t)n, pad, tiles, tv);
+    H2B_LAUNCH(d, "poly_horner_batch", PK.horner_batch_totals, (unsigned)count, POLY_T, 0, dj, (const Fr*)tv, tiles, d_out);
+    H2B_CK(cudaGetLastError());
+    H2B_CK(d.ring.d2h(out32s, d_out, count * 32, d.stream));
+    return end_call(ctx, d);       // synchronises: the job vector may go out of scope
+}
 int h2b_kate_division(h2b_ctx* ctx, const void* a, size_t n, const void* b32, void* q) {
     if (ctx && !q) return ctx->fail(H2B_E_INVALID, "kate_division: null argument");
     return horner_impl(ctx, a, n, b32, q, nullptr, false, "kate_division");

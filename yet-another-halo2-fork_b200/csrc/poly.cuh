@@ -47,6 +47,13 @@ H2B_HD Fe<P> fe_inv_window(const Fe<P>& a) {
     return acc;
 }
 
+// one (polynomial, point) pair of a batched evaluation (poly_horner_batch_* kernels)
+struct alignas(16) HornerJob {
+    const Fr* a;
+    uint64_t reserved;
+    Fr b, bk, bt;          // the point, b^POLY_K, b^POLY_TILE
+};
+
 #if defined(__CUDACC__) && !defined(H2B_NO_KERNELS)
 
 struct PolyShared { Fr s[2][POLY_T]; };
@@ -274,6 +281,54 @@ poly_horner_scan_totals_kernel(Fr* tile_val, uint32_t ntiles, Fr bt, Fr* final_o
         carry = out;
     }
     if (t == 0 && final_out) fe_store(final_out, carry);
+}
+// ---- batched evaluation: count (polynomial, point) pairs of one length in two launches ---------------------------------
+// The evaluations a proof writes after the challenge x (prover.rs:742-811) and the ones the multi-open argument takes
+// (shplonk/prover.rs:117-131) are dozens of independent eval_polynomial calls: one job per pair, grid.y = job.
+__global__ void __launch_bounds__(POLY_T)
+poly_horner_batch_tile_reduce_kernel(const HornerJob* __restrict__ jobs, uint64_t n, uint64_t pad, uint32_t tiles,
+                                     Fr* __restrict__ tile_val) {
+    __shared__ PolyShared sh;
+    const HornerJob* job = jobs + blockIdx.y;
+    const Fr* __restrict__ a = job->a;
+    const Fr b = fe_load(&job->b);
+    const uint32_t t = threadIdx.x;
+    const uint64_t j0 = (uint64_t)blockIdx.x * POLY_TILE + (uint64_t)t * POLY_K;
+    Fr pw[POLY_LOG_T];
+    horner_powers(fe_load(&job->bk), pw);
+    Fr s = Fr::zero();
+#pragma unroll
+    for (int k = 0; k < POLY_K; k++) {
+        Fr r = horner_view(a, n, pad, j0 + k);
+        s = k == 0 ? r : fe_add(fe_mul(s, b), r);
+    }
+    int cur;
+    Fr incl = block_scan_horner(s, pw, sh, t, cur);
+    if (t == POLY_T - 1) fe_store(tile_val + (size_t)blockIdx.y * tiles + blockIdx.x, incl);
+}
+// one block per job folds that job's tile values: out[job] = sum_i tile_val[i] * bT^(tiles-1-i)
+__global__ void __launch_bounds__(POLY_T)
+poly_horner_batch_totals_kernel(const HornerJob* __restrict__ jobs, const Fr* __restrict__ tile_val, uint32_t tiles,
+                                Fr* __restrict__ out) {
+    __shared__ PolyShared sh;
+    const HornerJob* job = jobs + blockIdx.x;
+    const Fr* tv = tile_val + (size_t)blockIdx.x * tiles;
+    const Fr bt = fe_load(&job->bt);
+    const uint32_t t = threadIdx.x;
+    Fr pw[POLY_LOG_T];
+    horner_powers(bt, pw);
+    Fr carry = Fr::zero();
+    for (uint32_t base = 0; base < tiles; base += POLY_T) {
+        Fr v = base + t < tiles ? fe_load(tv + base + t) : Fr::zero();
+        if (t == 0) v = fe_add(fe_mul(carry, bt), v);
+        int cur;
+        block_scan_horner(v, pw, sh, t, cur);
+        uint32_t last = tiles - base < (uint32_t)POLY_T ? tiles - base - 1 : POLY_T - 1;
+        Fr o = fe_load(&sh.s[cur][last]);
+        __syncthreads();
+        carry = o;
+    }
+    if (t == 0) fe_store(out + blockIdx.x, carry);
 }
 // phase 3 (kate): q[n-2-j] = s_j for j <= n-2, seeded with the tile carry-in
 __global__ void __launch_bounds__(POLY_T)

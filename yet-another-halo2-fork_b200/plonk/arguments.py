@@ -24,6 +24,28 @@ from .keygen import FR_DELTA
 R = F.R_MOD
 
 
+class EvalBatch:
+    """The evaluations create_proof writes after the challenge x (plonk/prover.rs:742-811, and the `evaluate` methods of the argument
+    provers) depend on nothing the transcript produces in between: the `*_evaluate` functions record their (polynomial, point)
+    pairs here in transcript order, `flush` evaluates them in ONE device call (h2b_eval_polynomial_batch_device) and writes the
+    scalars in that order.  The values are kept by (id(polynomial), point) so that the multi-open argument, which the reference
+    lets evaluate the same pairs again (poly/query.rs:62-64), can reuse them."""
+
+    def __init__(self, ops):
+        self.ops, self.pairs, self.known = ops, [], {}
+
+    def add(self, poly, point: int) -> None:
+        self.pairs.append((poly, point))
+
+    def flush(self, transcript) -> dict:
+        values = self.ops.eval_polynomials(self.pairs)
+        for (poly, point), value in zip(self.pairs, values):
+            transcript.write_scalar(value)
+            self.known[(id(poly), point)] = value
+        self.pairs = []
+        return self.known
+
+
 class ConstraintSystemFailure(Exception):
     """plonk::Error::ConstraintSystemFailure."""
 
@@ -132,12 +154,12 @@ def lookup_commit_product(ops, p: LookupPermuted, pk, beta: int, gamma: int, rng
     return c
 
 
-def lookup_evaluate(ops, c: LookupCommitted, domain, x: int, transcript) -> None:
+def lookup_evaluate(ops, c: LookupCommitted, domain, x: int, evals) -> None:
     """lookup/prover.rs:329-359."""
     x_inv, x_next = domain.rotate_omega(x, -1), domain.rotate_omega(x, 1)
     for poly, point in ((c.product_poly, x), (c.product_poly, x_next), (c.permuted_input_poly, x), (c.permuted_input_poly, x_inv),
                         (c.permuted_table_poly, x)):
-        transcript.write_scalar(ops.eval_polynomial(poly, point))
+        evals.add(poly, point)
 
 
 def lookup_open(c: LookupCommitted, domain, x: int):
@@ -198,20 +220,20 @@ def permutation_commit(ops, pk, advice, instance, beta: int, gamma: int, rng, tr
     return sets
 
 
-def permutation_pk_evaluate(ops, pk, x: int, transcript) -> None:
+def permutation_pk_evaluate(ops, pk, x: int, evals) -> None:
     """permutation/prover.rs:219-231."""
     for poly in pk.permutation.polys:
-        transcript.write_scalar(ops.eval_polynomial(poly, x))
+        evals.add(poly, x)
 
 
-def permutation_evaluate(ops, sets: List[PermutationSet], pk, x: int, transcript) -> None:
+def permutation_evaluate(ops, sets: List[PermutationSet], pk, x: int, evals) -> None:
     """permutation/prover.rs:233-278."""
     domain, bf = pk.vk.domain, pk.vk.cs.blinding_factors()
     for i, s in enumerate(sets):
-        transcript.write_scalar(ops.eval_polynomial(s.permutation_product_poly, x))
-        transcript.write_scalar(ops.eval_polynomial(s.permutation_product_poly, domain.rotate_omega(x, 1)))
+        evals.add(s.permutation_product_poly, x)
+        evals.add(s.permutation_product_poly, domain.rotate_omega(x, 1))
         if i + 1 < len(sets):
-            transcript.write_scalar(ops.eval_polynomial(s.permutation_product_poly, domain.rotate_omega(x, -(bf + 1))))
+            evals.add(s.permutation_product_poly, domain.rotate_omega(x, -(bf + 1)))
 
 
 def permutation_open(sets: List[PermutationSet], pk, x: int):
@@ -258,10 +280,10 @@ def shuffle_commit_product(ops, arg: C.ShuffleArgument, pk, theta: int, gamma: i
     return c
 
 
-def shuffle_evaluate(ops, c: ShuffleCommitted, domain, x: int, transcript) -> None:
+def shuffle_evaluate(ops, c: ShuffleCommitted, domain, x: int, evals) -> None:
     """shuffle/prover.rs:207-228."""
-    transcript.write_scalar(ops.eval_polynomial(c.product_poly, x))
-    transcript.write_scalar(ops.eval_polynomial(c.product_poly, domain.rotate_omega(x, 1)))
+    evals.add(c.product_poly, x)
+    evals.add(c.product_poly, domain.rotate_omega(x, 1))
 
 
 def shuffle_open(c: ShuffleCommitted, domain, x: int):
@@ -326,7 +348,7 @@ class VanishingEvaluated:
     pass
 
 
-def vanishing_evaluate(ops, c: VanishingConstructed, x: int, xn: int, transcript) -> VanishingEvaluated:
+def vanishing_evaluate(ops, c: VanishingConstructed, x: int, xn: int, evals) -> VanishingEvaluated:
     """vanishing/prover.rs:154-186."""
     e = VanishingEvaluated()
     terms, acc = [], 1
@@ -337,7 +359,7 @@ def vanishing_evaluate(ops, c: VanishingConstructed, x: int, xn: int, transcript
     e.h_blind = 0
     for blind in reversed(c.h_blinds):
         e.h_blind = (e.h_blind * xn + blind) % R
-    transcript.write_scalar(ops.eval_polynomial(c.committed.random_poly, x))
+    evals.add(c.committed.random_poly, x)
     e.committed = c.committed
     return e
 

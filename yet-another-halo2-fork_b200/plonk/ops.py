@@ -153,6 +153,9 @@ class DeviceOps:
     def eval_polynomial(self, p, point: int) -> int:
         return self.poly.eval_polynomial(p, point)
 
+    def eval_polynomials(self, pairs) -> list:
+        return self.poly.eval_polynomials(pairs)
+
     def kate_division(self, p, b: int):
         return self.poly.kate_division(p, b)
 

@@ -185,21 +185,23 @@ class Prover:
         del h_poly
         x = transcript.squeeze_challenge_scalar()                                   # [TRANSCRIPT-15]
         xn = pow(x, ops.n, R)
+        evals = A.EvalBatch(ops)                                                    # one device call for [TRANSCRIPT-17..23]
         for c in circuits:                                                          # [TRANSCRIPT-17]
             for column, at in cs.advice_queries:
-                transcript.write_scalar(ops.eval_polynomial(advice_polys[c][column], domain.rotate_omega(x, at)))
+                evals.add(advice_polys[c][column], domain.rotate_omega(x, at))
         for column, at in cs.fixed_queries:                                         # [TRANSCRIPT-18]
-            transcript.write_scalar(ops.eval_polynomial(pk.fixed_polys[column], domain.rotate_omega(x, at)))
-        vanishing = A.vanishing_evaluate(ops, vanishing, x, xn, transcript)         # [TRANSCRIPT-19]
-        A.permutation_pk_evaluate(ops, pk, x, transcript)                           # [TRANSCRIPT-20]
+            evals.add(pk.fixed_polys[column], domain.rotate_omega(x, at))
+        vanishing = A.vanishing_evaluate(ops, vanishing, x, xn, evals)              # [TRANSCRIPT-19]
+        A.permutation_pk_evaluate(ops, pk, x, evals)                                # [TRANSCRIPT-20]
         for c in circuits:                                                          # [TRANSCRIPT-21]
-            A.permutation_evaluate(ops, permutations[c], pk, x, transcript)
+            A.permutation_evaluate(ops, permutations[c], pk, x, evals)
         for c in circuits:                                                          # [TRANSCRIPT-22]
             for committed in lookups[c]:
-                A.lookup_evaluate(ops, committed, domain, x, transcript)
+                A.lookup_evaluate(ops, committed, domain, x, evals)
         for c in circuits:                                                          # [TRANSCRIPT-23]
             for committed in shuffles[c]:
-                A.shuffle_evaluate(ops, committed, domain, x, transcript)
+                A.shuffle_evaluate(ops, committed, domain, x, evals)
+        known_evals = evals.flush(transcript)
         queries = []
         for c in circuits:                                                          # prover.rs:817-866
             queries += [(domain.rotate_omega(x, at), advice_polys[c][column], self.advice_blinds[c][column])
@@ -212,7 +214,7 @@ class Prover:
         queries += [(domain.rotate_omega(x, at), pk.fixed_polys[column], 0) for column, at in cs.fixed_queries]
         queries += A.permutation_pk_open(pk, x)
         queries += A.vanishing_open(vanishing, x)
-        self.multiopen.create_proof(ops, transcript, queries)                       # prover.rs:884-890
+        self.multiopen.create_proof(ops, transcript, queries, known_evals)                      # prover.rs:884-890
 
 
 class ProverSingle(Prover):

@@ -8,7 +8,7 @@ A query is (point, poly, blind); polynomials are compared by identity like `Poly
 """
 from __future__ import annotations
 
-from typing import Dict, List, Sequence, Tuple
+from typing import Dict, List, Optional, Sequence, Tuple
 
 from .. import fields as F
 from . import polyexpr as PX
@@ -85,16 +85,22 @@ def construct_intermediate_sets(queries: Sequence[tuple], get_commitment, get_ev
     return sets, sorted(super_point_set)
 
 
-def create_proof(ops, transcript, queries: Sequence[tuple]) -> None:
-    """shplonk/prover.rs:117-305.  Writes the two opening commitments h and h' to the transcript."""
+def create_proof(ops, transcript, queries: Sequence[tuple], known_evals: Optional[Dict[Tuple[int, int], int]] = None) -> None:
+    """shplonk/prover.rs:117-305.  Writes the two opening commitments h and h' to the transcript.  `known_evals` holds values
+    the caller already has, keyed (id(polynomial), point); the remaining queries are evaluated in one batched device call."""
     n = ops.n
-    cache: Dict[Tuple[int, int], int] = {}
+    cache: Dict[Tuple[int, int], int] = dict(known_evals or {})
+    missing, seen = [], set()
+    for q in queries:
+        key = (id(q[1]), q[0])
+        if key not in cache and key not in seen:
+            seen.add(key)
+            missing.append((q[1], q[0]))
+    for (poly, point), value in zip(missing, ops.eval_polynomials(missing)):
+        cache[(id(poly), point)] = value
 
     def get_eval(q):                                            # poly/query.rs:62-64
-        key = (id(q[1]), q[0])
-        if key not in cache:
-            cache[key] = ops.eval_polynomial(q[1], q[0])
-        return cache[key]
+        return cache[(id(q[1]), q[0])]
 
     y = transcript.squeeze_challenge_scalar()
     rotation_sets, super_point_set = construct_intermediate_sets(queries, lambda q: id(q[1]), get_eval)
