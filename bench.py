@@ -250,8 +250,7 @@ def proof_sequence_resident(ctx, eng):
         sv = shuf.evaluate(ctx, ext[4:6], ext[0:4], [], [], beta, gamma, theta, y, SEQ_K, ext_k)
         E.shuffle_fold(ctx, values, sv, table_values, ext[6], ext[8], ext[9], ext[9], y, SEQ_K, ext_k)
         h = dom.extended_to_coeff(values, divide_by_vanishing=True)
-        for i in range(RES_COUNTS["eval_polynomial"]):
-            ops.eval_polynomial(coeffs[i % len(coeffs)], 123457 + i)
+        ops.eval_polynomials([(coeffs[i % len(coeffs)], 123457 + i) for i in range(RES_COUNTS["eval_polynomial"])])   # one call, as the prover does
         for i in range(RES_COUNTS["kate_division"]):
             ops.kate_division(coeffs[i], 987 + i)
         return h
