@@ -106,6 +106,7 @@ def cpu_msm_sample(sample_k: int, reps: int = 1):
     """Times the C restatement of halo2curves best_multiexp (oracle/h2ref.c) on 2^sample_k points; returns
     (ms for the sample, threads).  Same input generators as the GPU arm."""
     from oracle import cref as C
+    C.use_all_host_cores()                   # torchrun exports OMP_NUM_THREADS=1 to its ranks
     n = 1 << sample_k
     s, b = C.random_fr(n, 1), C.gen_bases(n, 1)
     best = float("inf")
@@ -119,6 +120,7 @@ def cpu_msm_sample(sample_k: int, reps: int = 1):
 def cpu_ntt_sample(sample_k: int):
     from oracle import cref as C
     from oracle import pyref as R
+    C.use_all_host_cores()
     a = C.random_fr(1 << sample_k, 2)
     w = C.mont_from_int(pow(R.ROOT_OF_UNITY, 1 << (28 - sample_k), R.R_MOD), R.R_MOD)
     t = time.perf_counter()
@@ -311,6 +313,7 @@ def proof_sequence_cpu():
     """One call of each kind through the oracle port, scaled by SEQ_COUNTS (bounded sample)."""
     from oracle import cref as C
     from oracle import pyref as R
+    C.use_all_host_cores()
     n = 1 << SEQ_K
     d = R.EvaluationDomain(SEQ_J, SEQ_K)
     m = lambda x: C.mont_from_int(x, R.R_MOD)

@@ -29,8 +29,11 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        if not os.path.exists(_SO):
-            build()
+        try:
+            build()                      # no-op when libh2ref.so is newer than h2ref.c
+        except Exception:
+            if not os.path.exists(_SO):
+                raise
         _lib = ctypes.CDLL(_SO)
         vp, sz, u32, u64 = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_uint64
         sigs = {
@@ -57,6 +60,7 @@ def lib():
             "h2ref_gen_bases": [vp, sz, u64],
             "h2ref_kzg_setup": [u32, vp, vp, vp, vp],
             "h2ref_num_threads": [],
+            "h2ref_set_num_threads": [ctypes.c_int],
         }
         for name, args in sigs.items():
             fn = getattr(_lib, name)
@@ -72,6 +76,14 @@ def _p(a: np.ndarray):
 
 def num_threads() -> int:
     return lib().h2ref_num_threads()
+
+
+def use_all_host_cores() -> int:
+    """Give the OpenMP loops every core this process may run on (the launcher may have exported OMP_NUM_THREADS=1)."""
+    import os
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().h2ref_set_num_threads(n)
+    return num_threads()
 
 
 def random_fr(n: int, seed: int) -> np.ndarray:

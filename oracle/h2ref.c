@@ -570,3 +570,12 @@ void h2ref_kzg_setup(uint32_t k, const void *s_, const void *omega_, void *g_out
     free(pj); free(sc_g); free(sc_l);
 }
 int h2ref_num_threads(void) { return ref_threads(); }
+/* The timed CPU baseline uses every host core whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1 to its ranks,
+ * which would time the rayon-style loops of the reference on one thread). */
+void h2ref_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
