@@ -313,20 +313,29 @@ int msm_chunk_plan(h2b_ctx* ctx, uint32_t n, uint32_t idx_offset, uint32_t c, ui
 
 // Binning stage of one chunk, enqueued on the SORT stream into sort set `S`: histogram, offsets, scatter, population order,
 // oversized-bucket task list.
-int msm_stage_sort(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, const Fr* scalars) {
+// Buffers of one sort set for a chunk of this plan (growing a buffer frees it, which waits for the device: the streamed MSM
+// therefore sizes both of its sets for its largest chunk before the first one is enqueued).
+int msm_sort_reserve(h2b_ctx* ctx, MsmSortSet& S, const MsmChunkPlan& pl) {
     const MsmGeom& g = pl.sp.g;
-    const uint32_t nkeys = pl.sp.nkeys, n = g.n, nblk = pl.nblk;
-    const uint64_t max_entries = (uint64_t)n * g.windows;
+    const uint32_t nkeys = pl.sp.nkeys;
+    const uint64_t max_entries = (uint64_t)g.n * g.windows;
     H2B_CK(S.counts.reserve((size_t)nkeys * 4));
     H2B_CK(S.offsets.reserve((size_t)nkeys * 4));
     H2B_CK(S.ends.reserve((size_t)nkeys * 4));
     H2B_CK(S.order.reserve((size_t)nkeys * 4));
     H2B_CK(S.entries.reserve(std::max<size_t>((size_t)max_entries * 4, 256)));
-    H2B_CK(S.blocksums.reserve((size_t)nblk * 4 + 256));
+    H2B_CK(S.blocksums.reserve((size_t)pl.nblk * 4 + 256));
     H2B_CK(S.sizehist.reserve((size_t)MSM_SIZE_BINS * 4));
     H2B_CK(S.long_info.reserve((size_t)pl.max_long * sizeof(MsmLongInfo)));
     H2B_CK(S.long_tasks.reserve((size_t)pl.max_tasks * sizeof(MsmLongTask)));
     H2B_CK(S.counters.reserve(256));
+    return H2B_OK;
+}
+int msm_stage_sort(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, const Fr* scalars) {
+    const MsmGeom& g = pl.sp.g;
+    const uint32_t nkeys = pl.sp.nkeys, n = g.n, nblk = pl.nblk;
+    const uint64_t max_entries = (uint64_t)n * g.windows;
+    { int rc0 = msm_sort_reserve(ctx, S, pl); if (rc0) return rc0; }
     uint32_t* counts = S.counts.as<uint32_t>();
     uint32_t* offsets = S.offsets.as<uint32_t>();
     uint32_t* ends = S.ends.as<uint32_t>();
@@ -487,8 +496,19 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
             size_t k = std::min<size_t>(8, cnt >> (staged && !on_device ? 18 : 20));
             if (k > 1) chunk = (cnt + k - 1) / k;
         }
-        if (const char* env = std::getenv("H2B_MSM_CHUNKS")) { int k = std::atoi(env); if (k >= 1 && k <= 64) chunk = (cnt + k - 1) / k; }
-        size_t nchunks = (cnt + chunk - 1) / chunk;
+        // (host scalars only: there the first chunk also waits for its PCIe copy; with device-resident scalars the shorter
+        // chunks cost the accumulation more than the earlier start saves -- profiles/README.md)
+        bool ramp = chunk < cnt && staged && !on_device && !std::getenv("H2B_MSM_NO_RAMP");
+        if (const char* env = std::getenv("H2B_MSM_CHUNKS")) { int k = std::atoi(env); if (k >= 1 && k <= 64) { chunk = (cnt + k - 1) / k; ramp = false; } }
+        // Chunk boundaries.  Nothing hides the binning of the FIRST chunk, so the pipeline starts with a short chunk and doubles
+        // it until the steady chunk size is reached: each chunk's accumulation still covers the binning of the next one.
+        std::vector<size_t> bounds{0};
+        if (ramp)
+            for (size_t sz = std::max<size_t>(chunk / 8, (size_t)1 << 17); sz < chunk && bounds.back() + sz + chunk <= cnt; sz *= 2)
+                bounds.push_back(bounds.back() + sz);
+        while (bounds.back() < cnt) bounds.push_back(std::min(cnt, bounds.back() + chunk));
+        if (bounds.size() > 2 && cnt - bounds[bounds.size() - 2] < chunk / 4) bounds.erase(bounds.end() - 2);   // no runt at the end
+        size_t nchunks = bounds.size() - 1;
         const Fr* dev_scalars = reinterpret_cast<const Fr*>(scalars) + sh.start;
         const uint8_t* host_src = reinterpret_cast<const uint8_t*>(scalars) + sh.start * 32;
         if (staged) {
@@ -498,8 +518,16 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
             dev_scalars = d.m_scalars.as<Fr>();
         }
         H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.ev_first, 0));
+        if (nchunks > 1) {               // both sort sets sized for the largest chunk up front
+            size_t longest = 0;
+            for (size_t k = 0; k < nchunks; k++) longest = std::max(longest, bounds[k + 1] - bounds[k]);
+            MsmChunkPlan big;
+            rc = msm_chunk_plan(ctx, (uint32_t)longest, 0u, use_c, stride, &big);
+            if (rc) return rc;
+            for (int q = 0; q < 2; q++) { rc = msm_sort_reserve(ctx, d.ms[q], big); if (rc) return rc; }
+        }
         for (size_t k = 0; k < nchunks && rc == H2B_OK; k++) {
-            size_t lo = k * chunk, len = std::min(chunk, cnt - lo);
+            size_t lo = bounds[k], len = bounds[k + 1] - lo;
             MsmSortSet& S = d.ms[k & 1];
             MsmChunkPlan pl;
             rc = msm_chunk_plan(ctx, (uint32_t)len, stride ? (uint32_t)lo : 0u, use_c, stride, &pl);
