@@ -5,8 +5,10 @@
     python bench.py --impl reference --gpus N --steps K ...  the reference's CPU algorithm (oracle port, host cores)
 
 A "step" is one 2^24-point MSM over resident bases (BASELINE.json configs[1]).  With N > 1 GPUs the MSM is sharded
-by contiguous point range (strong scaling): every rank reduces its own range to per-window sums, the ranks all-gather
-W x 128 bytes over NCCL, rank 0 folds them.  One JSON line is printed by rank 0.
+by contiguous point range (strong scaling): every rank reduces its own range, the last kernel of the reduction stores the
+rank's reduced terms (20 points) into every peer's mailbox over NVLink, waits for theirs and folds them (h2b_msm_sharded:
+no NCCL call and no host staging on the data path).  The inputs are the SAME 2^24 scalars / bases at every N (ChaCha20
+seeds of SURVEY.md 8d, sliced by rank), so `result_sha256` must not change with N.  One JSON line is printed by rank 0.
 """
 from __future__ import annotations
 
@@ -26,7 +28,9 @@ if ROOT not in sys.path:
 
 MSM_K = int(os.environ.get("H2B_BENCH_MSM_K", "24"))
 NTT_K = int(os.environ.get("H2B_BENCH_NTT_K", "24"))
-CPU_SAMPLE_K = int(os.environ.get("H2B_BENCH_CPU_K", "20"))
+CPU_BUDGET_S = float(os.environ.get("H2B_BENCH_CPU_BUDGET_S", "240"))     # wall-clock cap of the reference arm's timed loop
+NTT_BATCH_COLS = int(os.environ.get("H2B_BENCH_NTT_COLS", "16"))
+NTT_BATCH_K = int(os.environ.get("H2B_BENCH_NTT_BATCH_K", "22"))          # columns of 2^22 coefficients -> 2^24 evaluations (e = 4)
 # SURVEY.md §8(d) algorithmic work: XYZZ mixed additions for the best window size, 10 field multiplications each,
 # 128 IMAD.WIDE (32x32->64 multiply-add) per Montgomery multiplication (64 product + 64 reduction).
 MSM_ADDS = {16: 1.475e6, 18: 5.014e6, 20: 1.769e7, 22: 6.488e7, 24: 2.317e8, 26: 8.556e8}
@@ -35,8 +39,8 @@ MULS_PER_MADD = 10
 
 
 def workload_config(world: int) -> dict:
-    return {"workload": f"configs[1]: best_multiexp BN254 G1 MSM, 2^{MSM_K} points ([t0+i]G bases, uniform scalars), "
-                        f"sharded by point range over {world} GPU(s)",
+    return {"workload": f"configs[1]: best_multiexp BN254 G1 MSM, 2^{MSM_K} points (bases [t0+i]G, t0 from ChaCha20 seed [2;32]; scalars = "
+                        f"Fr::random draws of ChaCha20 seed [1;32]; SURVEY.md 8d), sharded by point range over {world} GPU(s)",
             "window_bits": int(os.environ.get("H2B_MSM_C", "0")) or "auto",
             "l2": "inputs (1.5 GiB) exceed the 126 MB L2; no flush needed"}
 
@@ -49,16 +53,21 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+TRAFFIC_FILE = "r2_full_size_dram_traffic.json"
+
+
 def ncu_traffic(kernel_prefix: str, size_k: int):
     """DRAM bytes per launch (read + write) from the committed `ncu` capture of the same kernel at the same size
-    (profiles/r1_full_size_dram_traffic.json, taken at 2^24); None when the size differs."""
-    path = os.path.join(ROOT, "profiles", "r1_full_size_dram_traffic.json")
+    (profiles/r2_full_size_dram_traffic.json, taken at 2^24 on this round's code: scripts/capture_traffic.sh); None when the
+    size differs or the capture is absent.  Returns (bytes, source)."""
+    path = os.path.join(ROOT, "profiles", TRAFFIC_FILE)
     if size_k != 24 or not os.path.exists(path):
-        return None
-    rows = [r for r in json.load(open(path)) if r["kernel"].startswith(kernel_prefix)]
+        return None, None
+    doc = json.load(open(path))
+    rows = [r for r in doc["kernels"] if r["kernel"].startswith(kernel_prefix)]
     if not rows:
-        return None
-    return float(np.mean([r["dram_read_bytes"] + r["dram_write_bytes"] for r in rows]))
+        return None, None
+    return float(np.mean([r["dram_read_bytes"] + r["dram_write_bytes"] for r in rows])), f"profiles/{TRAFFIC_FILE} (commit {doc.get('commit', '?')})"
 
 
 class ClockSampler:
@@ -100,38 +109,46 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------------------
-# CPU restatement (oracle port): bounded sample, all host threads
+# CPU restatement (oracle port), all host threads, at the REAL size of the metric (no extrapolation)
 # ---------------------------------------------------------------------------------------------------------
-def cpu_msm_sample(sample_k: int, reps: int = 1):
-    """Times the C restatement of halo2curves best_multiexp (oracle/h2ref.c) on 2^sample_k points; returns
-    (ms for the sample, threads).  Same input generators as the GPU arm."""
+_CPU_INPUTS = {}
+
+
+def cpu_inputs(k: int):
+    """the same seeded inputs as the GPU arm, generated by the oracle's own ChaCha20 (cached per size)"""
     from oracle import cref as C
-    C.use_all_host_cores()                   # torchrun exports OMP_NUM_THREADS=1 to its ranks
-    n = 1 << sample_k
-    s, b = C.random_fr(n, 1), C.gen_bases(n, 1)
-    best = float("inf")
-    for _ in range(reps):
-        t = time.perf_counter()
-        C.best_multiexp(s, b)
-        best = min(best, (time.perf_counter() - t) * 1e3)
-    return best, C.num_threads()
+    if k not in _CPU_INPUTS:
+        C.use_all_host_cores()                   # torchrun exports OMP_NUM_THREADS=1 to its ranks
+        n = 1 << k
+        _CPU_INPUTS[k] = (C.random_fr_chacha20(n, C.SEED_SCALARS), C.gen_bases(n, C.bench_t0()))
+    return _CPU_INPUTS[k]
 
 
-def cpu_ntt_sample(sample_k: int):
+def cpu_msm(k: int):
+    """One best_multiexp restatement (oracle/h2ref.c) on 2^k points; returns (ms, threads, affine result)."""
+    from oracle import cref as C
+    s, b = cpu_inputs(k)
+    t = time.perf_counter()
+    r = C.best_multiexp(s, b)
+    ms = (time.perf_counter() - t) * 1e3
+    return ms, C.num_threads(), C.to_affine(r)
+
+
+def cpu_ntt(k: int):
     from oracle import cref as C
     from oracle import pyref as R
     C.use_all_host_cores()
-    a = C.random_fr(1 << sample_k, 2)
-    w = C.mont_from_int(pow(R.ROOT_OF_UNITY, 1 << (28 - sample_k), R.R_MOD), R.R_MOD)
+    a = C.random_fr_chacha20(1 << k, C.SEED_SCALARS)
+    w = C.mont_from_int(pow(R.ROOT_OF_UNITY, 1 << (28 - k), R.R_MOD), R.R_MOD)
+    lib, p = C.lib(), a.ctypes.data_as(__import__("ctypes").c_void_p)
     t = time.perf_counter()
-    C.best_fft(a, w, sample_k)
+    lib.h2ref_best_fft(p, w.ctypes.data_as(__import__("ctypes").c_void_p), k)      # in place: no copy inside the timed region
     return (time.perf_counter() - t) * 1e3
 
 
-def scale_to_full(ms: float, sample_k: int, full_k: int) -> float:
-    """Linear-in-n extrapolation of a sample to the full size (optimistic for the CPU: Pippenger's per-point cost
-    falls slowly with n, an NTT's rises with log n)."""
-    return ms * float(1 << (full_k - sample_k))
+def point_sha256(affine_or_jac) -> str:
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(affine_or_jac, dtype=np.uint64)[:8].tobytes()).hexdigest()
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -339,29 +356,44 @@ def proof_sequence_cpu():
 
 
 def run_reference(args, rank: int, world: int):
+    """The reference's CPU algorithm for the path (C port of halo2curves 0.6 best_multiexp: the reference is Rust and cannot be
+    built here), all host threads, on the SAME 2^MSM_K inputs as the GPU arm.  Every step is one full-size MSM: nothing is
+    extrapolated.  If `--steps` full-size runs would exceed CPU_BUDGET_S of wall clock the loop stops early and the line's
+    `steps` says how many were timed (`steps_requested` keeps the flag)."""
     if rank != 0:
         return
     from oracle import cref as C
-    for _ in range(max(0, args.warmup) and 1):       # one warm-up pass is enough for a CPU loop
-        cpu_msm_sample(min(CPU_SAMPLE_K, 16))
-    times = []
-    for _ in range(args.steps):
-        ms, threads = cpu_msm_sample(CPU_SAMPLE_K)
+    C.use_all_host_cores()
+    t_gen = time.perf_counter()
+    cpu_inputs(MSM_K)
+    gen_s = time.perf_counter() - t_gen
+    if args.warmup > 0:                            # one small warm-up pass (thread pool, page tables); a CPU loop needs no more
+        s, b = cpu_inputs(MSM_K)
+        C.best_multiexp(np.ascontiguousarray(s[: 1 << 16]), np.ascontiguousarray(b[: 1 << 16]))
+    times, res = [], None
+    t_loop = time.perf_counter()
+    for i in range(args.steps):
+        ms, threads, res = cpu_msm(MSM_K)
         times.append(ms)
-    sample_ms = float(np.mean(times))
-    full_ms = scale_to_full(sample_ms, CPU_SAMPLE_K, MSM_K)
-    ntt_ms = cpu_ntt_sample(CPU_SAMPLE_K)
-    sample = (f"best_multiexp restatement on 2^{CPU_SAMPLE_K} points per step ({sample_ms:.1f} ms), scaled x{1 << (MSM_K - CPU_SAMPLE_K)} "
-              f"linearly to 2^{MSM_K}")
+        elapsed = time.perf_counter() - t_loop
+        if i + 1 < args.steps and elapsed + elapsed / (i + 1) > CPU_BUDGET_S:
+            break
+    ms_per_step = float(np.mean(times))
+    ntt_ms = cpu_ntt(NTT_K)
+    sample = (f"C restatement of halo2curves 0.6 best_multiexp (rayon chunk-per-thread Booth Pippenger), {len(times)} full-size "
+              f"2^{MSM_K} MSM(s) on {C.num_threads()} threads, mean; inputs generated in {gen_s:.1f} s outside the timed loop")
     line = {
-        "impl": "reference", "metric": f"bn254_msm_2^{MSM_K}_ms", "value": full_ms, "unit": "ms", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": full_ms, "higher_is_better": False, "scaling": "strong",
+        "impl": "reference", "metric": f"bn254_msm_2^{MSM_K}_ms", "value": ms_per_step, "unit": "ms", "n_gpus": args.gpus,
+        "steps": len(times), "steps_requested": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "measured_at": MSM_K, "runs_ms": times,
+        "higher_is_better": False, "scaling": "strong",
         "vs_baseline": None, "dtype": "u32x8 (254-bit Montgomery integers)", "data": "synthetic",
-        "config": workload_config(args.gpus),
-        "cpu_baseline": {"value": full_ms, "unit": "ms", "cores": C.num_threads(), "kind": "port", "sample": sample},
-        "e2e": {"value": full_ms, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "ntt": {"metric": f"fr_ntt_2^{NTT_K}_ms", "value": scale_to_full(ntt_ms, CPU_SAMPLE_K, NTT_K) * NTT_K / CPU_SAMPLE_K, "unit": "ms",
-                "sample": f"best_fft restatement on 2^{CPU_SAMPLE_K} ({ntt_ms:.1f} ms), scaled by n log n"},
+        "config": workload_config(args.gpus), "parity": "unpinned",
+        "result_sha256": point_sha256(res),
+        "cpu_baseline": {"value": ms_per_step, "unit": "ms", "cores": C.num_threads(), "kind": "port", "sample": sample},
+        "e2e": {"value": ms_per_step, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "ntt": {"metric": f"fr_ntt_2^{NTT_K}_ms", "value": ntt_ms, "unit": "ms", "measured_at": NTT_K,
+                "sample": f"best_fft restatement (bit-reverse + radix-2, recursive split over threads) on 2^{NTT_K}, one run"},
         "gpu_launches": 0,
     }
     emit(line)
@@ -371,7 +403,6 @@ def run_reference(args, rank: int, world: int):
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------
 def run_gpu(args, rank: int, world: int, local_rank: int):
-    import ctypes
     import torch
     import torch.distributed as dist
     import h2b200
@@ -384,7 +415,9 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     ctx = h2b200.Context([local_rank])
     eng = h2b200.B200Engine(ctx)
-    F = h2b200.fields
+    # NCCL carries only the set-up and timing plumbing (mailbox handles, barriers, max over ranks): the MSM's own exchange is
+    # the library's peer-store kernel
+    eng.peer_attach(rank, world, h2b200.dist_all_gather_bytes if world > 1 else None)
 
     def barrier():
         if world > 1:
@@ -398,26 +431,30 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # ---- inputs: this rank's contiguous point range ------------------------------------------------------
+    # ---- inputs: the SAME 2^MSM_K problem at every N, this rank's contiguous point range of it --------------------
     n_total = 1 << MSM_K
     lo, hi = n_total * rank // world, n_total * (rank + 1) // world
     n_loc = hi - lo
-    d_bases = h2b200.synth.device_bases(ctx, n_loc, 1 + lo)
-    desc = eng.get_base_descriptor(d_bases)
-    h_scalars = torch.from_numpy(h2b200.synth.random_scalars(n_loc, 1234 + rank).view(np.int64)).pin_memory()
-    d_scalars = h_scalars.cuda()
+    t0 = h2b200.synth.bench_t0()
+    d_bases = h2b200.synth.device_bases(ctx, n_loc, t0 + lo)
+    torch.cuda.synchronize()
+    t_reg = time.perf_counter()
+    desc = eng.get_base_descriptor(d_bases)          # registration = copy-free adoption + window-multiple precomputation
+    torch.cuda.synchronize()
+    registration_ms = (time.perf_counter() - t_reg) * 1e3
+    pre_c, registration_bytes = desc.info()
+    all_scalars = h2b200.synth.chacha_scalars_device(ctx, n_total)
+    d_scalars = all_scalars[lo:hi].clone()
+    del all_scalars
+    torch.cuda.empty_cache()
+    pageable = d_scalars.cpu().numpy().view(np.uint64)             # an ordinary host array: what a Rust Vec<Fr> is
+    h_pinned = torch.from_numpy(pageable.view(np.int64)).pin_memory()
 
     def msm_step(scalars):
-        """one whole MSM; returns the normalised result on rank 0 (None elsewhere)"""
+        """one whole MSM; every rank returns the normalised result"""
         if world == 1:
             return eng.msm_with_cached_base(scalars, desc)
-        w, c = eng.msm_windows(scalars, desc, n_total)
-        mine = torch.from_numpy(w.view(np.int64)).cuda()
-        allw = torch.empty((world,) + tuple(mine.shape), dtype=mine.dtype, device="cuda")
-        dist.all_gather_into_tensor(allw, mine)
-        if rank == 0:
-            return eng.msm_combine(allw.cpu().numpy().view(np.uint64), c)
-        return None
+        return eng.msm_sharded(scalars, desc, n_total)
 
     sampler = ClockSampler(local_rank)
     sampler.start()                      # nvidia-smi needs ~0.3 s to deliver its first row: start it under the warm-up load
@@ -428,13 +465,13 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
     launches0 = ctx.launch_count()
     barrier()
     n_rows_before = len(sampler.rows)
-    t0 = time.perf_counter()
+    t0w = time.perf_counter()
     dev_ms = []
     for _ in range(args.steps):
         res_dev = msm_step(d_scalars)
         dev_ms.append(ctx.last_call_ms())          # CUDA events on the launching stream, first to last enqueued operation
     barrier()
-    wall_ms = (time.perf_counter() - t0) * 1e3
+    wall_ms = (time.perf_counter() - t0w) * 1e3
     n_rows_timed = len(sampler.rows) - n_rows_before
     launches = ctx.launch_count() - launches0
     prof = ctx.profile_read()
@@ -442,46 +479,102 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
     ms_per_step = max_over_ranks(wall_ms / args.steps)
     max_dev_ms = max_over_ranks(float(np.mean(dev_ms)))
 
-    # ---- e2e: host (pinned) scalars in, 96-byte point out, through the same public call ----------------------
-    for _ in range(min(args.warmup, 2)):
-        msm_step(h_scalars.numpy().view(np.uint64))
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        res_e2e = msm_step(h_scalars.numpy().view(np.uint64))
-    barrier()
-    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
-    if rank == 0 and not np.array_equal(res_dev, res_e2e):
+    # ---- e2e: host scalars in, 96-byte point out, through the same public call.  `e2e` = PAGEABLE buffers (what the reference
+    # hands over), `e2e_pinned` = page-locked ones ----------------------------------------------------------------------
+    def timed_e2e(src):
+        for _ in range(min(args.warmup, 2)):
+            msm_step(src)
+        barrier()
+        t = time.perf_counter()
+        for _ in range(args.steps):
+            r = msm_step(src)
+        barrier()
+        return max_over_ranks((time.perf_counter() - t) * 1e3 / args.steps), r
+
+    e2e_ms, res_e2e = timed_e2e(pageable)
+    e2e_pinned_ms, res_pin = timed_e2e(h_pinned.numpy().view(np.uint64))
+    if not (np.array_equal(res_dev, res_e2e) and np.array_equal(res_dev, res_pin)):
         raise SystemExit("bench: device-resident and host-buffer MSM results differ")
 
     # ---- NTT 2^24: device-resident, then host buffers in/out ----------------------------------------------
     dom = h2b200.EvaluationDomain(1, NTT_K, ctx)
-    h_poly = torch.from_numpy(h2b200.synth.random_scalars(1 << NTT_K, 99 + rank).view(np.int64)).pin_memory()
-    d_poly = h_poly.cuda()
+    d_poly = h2b200.synth.chacha_scalars_device(ctx, 1 << NTT_K)
+    hp = d_poly.cpu().numpy().view(np.uint64)                       # pageable
+    hp_pinned = torch.from_numpy(hp.view(np.int64)).pin_memory()
     for _ in range(args.warmup):
         dom.coeff_to_lagrange(d_poly)
     ctx.profile_enable(True)
     ctx.profile_read()
     barrier()
-    t0 = time.perf_counter()
+    t0w = time.perf_counter()
     for _ in range(args.steps):
         dom.coeff_to_lagrange(d_poly)
     barrier()
-    ntt_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
+    ntt_ms = max_over_ranks((time.perf_counter() - t0w) * 1e3 / args.steps)
     ntt_prof = ctx.profile_read()
     ctx.profile_enable(False)
-    hp = h_poly.numpy().view(np.uint64)
-    dom.coeff_to_lagrange(hp)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        dom.coeff_to_lagrange(hp)
-    barrier()
-    ntt_e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.steps)
 
-    clocks = sampler.stop()             # sampled over every timed region of this run (MSM, e2e MSM, NTT, e2e NTT)
+    def timed_ntt_host(buf):
+        dom.coeff_to_lagrange(buf)
+        barrier()
+        t = time.perf_counter()
+        for _ in range(args.steps):
+            dom.coeff_to_lagrange(buf)
+        barrier()
+        return max_over_ranks((time.perf_counter() - t) * 1e3 / args.steps)
+
+    ntt_e2e_ms = timed_ntt_host(hp)
+    ntt_e2e_pinned_ms = timed_ntt_host(hp_pinned.numpy().view(np.uint64))
+    del d_poly, hp_pinned
+
+    # ---- batched coset NTTs dealt over the ranks (north_star: "the independent per-column NTTs of the extended-domain quotient
+    # computation are batched across GPUs"): NTT_BATCH_COLS columns of coeff_to_extended 2^22 -> 2^24 (evaluate_h,
+    # plonk/evaluation.rs:344-361); rank r takes the columns c = r (mod N); no collective ---------------------------------
+    bdom = h2b200.EvaluationDomain(5, NTT_BATCH_K, ctx)             # quotient degree 4 -> e = 4
+    my_cols = list(range(rank, NTT_BATCH_COLS, world))
+    nb_in, nb_out = 1 << NTT_BATCH_K, bdom.extended_len()
+    col_src = h2b200.synth.chacha_scalars_device(ctx, nb_in, bytes([7]) * 32)
+    d_cols = [col_src.roll(c, 0).contiguous() for c in my_cols]     # distinct columns, cheaply
+    d_outs = [torch.empty((nb_out, 4), dtype=torch.int64, device="cuda") for _ in my_cols]
+    bsteps = max(1, min(args.steps, 5))
+
+    def batch_dev():
+        bdom.coeff_to_extended_many(d_cols, d_outs)
+
+    batch_dev()
+    barrier()
+    t0w = time.perf_counter()
+    for _ in range(bsteps):
+        batch_dev()
+    barrier()
+    batch_ms = max_over_ranks((time.perf_counter() - t0w) * 1e3 / bsteps)
+    batch_digest = None
+    if my_cols:
+        import hashlib
+        batch_digest = hashlib.sha256(d_outs[0][:4096].cpu().numpy().tobytes()).hexdigest()
+    h_cols = [c.cpu().numpy().view(np.uint64) for c in d_cols]      # pageable host columns
+    h_outs = [np.empty((nb_out, 4), dtype=np.uint64) for _ in my_cols]
+    for o in h_outs:
+        o.fill(0)                                                   # touch the pages outside the timed region
+    del d_cols, d_outs, col_src
+    torch.cuda.empty_cache()
+
+    def batch_host():
+        bdom.coeff_to_extended_batch(h_cols, h_outs)
+
+    batch_host()
+    barrier()
+    t0w = time.perf_counter()
+    for _ in range(bsteps):
+        batch_host()
+    barrier()
+    batch_e2e_ms = max_over_ranks((time.perf_counter() - t0w) * 1e3 / bsteps)
+    del h_cols, h_outs
+
+    clocks = sampler.stop()             # sampled over every timed region of this run (MSM, e2e MSM, NTT, e2e NTT, batch)
     clocks["samples_in_msm_timed_region"] = n_rows_timed
     wide_peak, fmul_peak = ctx.imad_peak()
+    notice = ctx.last_notice()
     if rank != 0:
         ctx.close()
         if world > 1:
@@ -502,6 +595,7 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
     # The binding roofline of both kernels is the integer-multiply pipe ("roofline.achieved(MSM) = adds(k) x
     # IMAD / t / IMAD_peak"), so that is what `achieved/peak/frac` report; the HBM figures the contract names sit in `hbm`.
     hbm_achieved = alg_bytes / (acc_ms * 1e-3) / 1e9 if acc_ms else 0.0
+    acc_traffic, acc_traffic_src = ncu_traffic("msm_accumulate_kernel", MSM_K)
     roofline = {
         "kernel": "msm_accumulate_kernel", "launches_per_step": acc_launches_per_step,
         "bound": "imad", "bound_note": "integer-multiply pipe: neither hbm nor tensor binds this path (SURVEY.md 8d, north_star); the hbm figures are under `hbm`",
@@ -510,10 +604,13 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
                        "profiles/r1_imad_micro.txt, r1_fp64_micro.txt: FP64 and ALU ops do not co-issue beside it)",
         "field_muls_per_s_peak": fmul_peak,
         "algorithmic": f"{adds:.4g} XYZZ mixed adds x {MULS_PER_MADD} field muls x {WIDE_PER_FIELD_MUL} IMAD.WIDE per step (SURVEY.md 8d table), over the summed duration of the step's accumulate launches",
-        "executed_frac": (n_loc * 13 * 1160.0 / (acc_ms * 1e-3) / wide_peak) if (acc_ms and wide_peak) else None,
+        "executed_frac": (n_loc * 13 * 1160.0 / (acc_ms * 1e-3) / wide_peak) if (acc_ms and wide_peak and pre_c == 20) else None,
         "executed": "n x 13 windows (c = 20, precomputed window multiples) mixed adds x 1160 IMAD.WIDE "
                     "(6 mul + 2 dedicated squares + one fused product difference): fewer than the table's count, hence frac > executed_frac",
-        "traffic": (ncu_traffic("msm_accumulate_kernel", MSM_K) or 0) / world or None,
+        "traffic": (acc_traffic * acc_launches_per_step / world) if acc_traffic else None,
+        "traffic_source": acc_traffic_src or "no ncu capture of this round's code at this size: null rather than a stale figure",
+        "traffic_note": "ncu dram__bytes_read+write per accumulate launch x launches per step; 13 gathered 64-byte multiples per "
+                        "point at two DRAM atoms each dominate (algorithmic input = 96 B per point)",
         "hbm": {"bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
                 "peak_source": peak_src, "algorithmic": "96 B per point (32 B scalar + 64 B base)"},
         "kernel_ms_per_step": kernel_ms,
@@ -524,28 +621,52 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
     ntt_muls = (1 << NTT_K) / 2 * NTT_K
     ntt_imad = ntt_muls * WIDE_PER_FIELD_MUL / (ntt_kernel_ms * 1e-3)
     ntt_hbm = ntt_bytes / (ntt_kernel_ms * 1e-3) / 1e9
+    ntt_traffic, ntt_traffic_src = ncu_traffic("ntt_pass_kernel", NTT_K)
     ntt = {
-        "metric": f"fr_ntt_2^{NTT_K}_ms", "value": ntt_ms, "unit": "ms", "passes": npass, "aggregate_ntt_per_s": world * 1e3 / ntt_ms,
-        "e2e": {"value": ntt_e2e_ms, "unit": "ms", "h2d_bytes_per_step": 32 << NTT_K, "d2h_bytes_per_step": 32 << NTT_K},
+        "metric": f"fr_ntt_2^{NTT_K}_ms", "value": ntt_ms, "unit": "ms", "passes": npass,
+        "replicas_per_s": world * 1e3 / ntt_ms,
+        "replicas_note": "a single transform stays on one GPU; with N ranks these are N independent replicas (see ntt_batch for the sharded workload)",
+        "e2e": {"value": ntt_e2e_ms, "unit": "ms", "h2d_bytes_per_step": 32 << NTT_K, "d2h_bytes_per_step": 32 << NTT_K, "host_buffers": "pageable"},
+        "e2e_pinned": {"value": ntt_e2e_pinned_ms, "unit": "ms"},
         "roofline": {"kernel": "ntt_pass_kernel (all passes of one transform)",
                      "bound": "imad", "bound_note": "SURVEY.md 8d: max(hbm_fraction, imad_fraction); 254-bit butterflies are multiplier bound",
                      "achieved": ntt_imad, "peak": wide_peak, "unit": "IMAD.WIDE/s", "frac": ntt_imad / wide_peak if wide_peak else None,
                      "algorithmic": f"(n/2) log2 n = {ntt_muls:.4g} field muls x {WIDE_PER_FIELD_MUL} IMAD.WIDE",
-                     "traffic": (ncu_traffic("ntt_pass_kernel", NTT_K) or 0) * npass or None,
-                     "traffic_note": "sum over the passes of one transform (ncu dram__bytes_read+write)",
+                     "traffic": (ntt_traffic * npass) if ntt_traffic else None, "traffic_source": ntt_traffic_src,
+                     "traffic_note": f"sum over the {npass} passes of one transform (ncu dram__bytes_read+write); {npass} passes move "
+                                     f"{npass * 64} B per element + the boundary-twiddle table, against SURVEY's 2-pass figure of 128 B: a deliberate trade of "
+                                     "DRAM traffic (8-9 % of HBM peak) for multiplications on a multiplier-bound kernel",
                      "hbm": {"bound": "hbm", "achieved": ntt_hbm, "peak": hbm_peak, "unit": "GB/s", "frac": ntt_hbm / hbm_peak,
                              "algorithmic": "128 B per element (two HBM round trips, SURVEY.md 8d)"}},
+    }
+    col_in_b, col_out_b = 32 * nb_in, 32 * nb_out
+    ntt_batch = {
+        "metric": f"coeff_to_extended 2^{NTT_BATCH_K} -> 2^{bdom.extended_k}, {NTT_BATCH_COLS} independent columns dealt over the ranks (evaluate_h's coset NTTs)",
+        "value": NTT_BATCH_COLS * 1e3 / batch_ms, "unit": "columns/s", "ms_per_batch": batch_ms, "steps": bsteps, "scaling": "strong",
+        "columns_per_rank": len(my_cols), "first_column_sha256_4096_rows": batch_digest,
+        "e2e": {"value": NTT_BATCH_COLS * 1e3 / batch_e2e_ms, "unit": "columns/s", "ms_per_batch": batch_e2e_ms,
+                "h2d_bytes_per_step": col_in_b * NTT_BATCH_COLS, "d2h_bytes_per_step": col_out_b * NTT_BATCH_COLS, "host_buffers": "pageable",
+                "host_gb_per_s": (col_in_b + col_out_b) * NTT_BATCH_COLS / (batch_e2e_ms * 1e-3) / 1e9,
+                "note": "bounded by the host side: every rank's columns cross the same host memory / PCIe root complexes; see DESIGN.md 5"},
     }
     line = {
         "metric": f"bn254_msm_2^{MSM_K}_ms", "value": ms_per_step, "unit": "ms", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
         "dtype": "u32x8 (254-bit Montgomery integers)", "data": "synthetic",
-        "config": workload_config(world),
-        "e2e": {"value": e2e_ms, "unit": "ms", "h2d_bytes_per_step": 32 * n_total, "d2h_bytes_per_step": 96},
-        "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "ntt": ntt,
+        "config": workload_config(world), "parity": "unpinned",
+        "result_sha256": point_sha256(res_dev),
+        "e2e": {"value": e2e_ms, "unit": "ms", "h2d_bytes_per_step": 32 * n_total, "d2h_bytes_per_step": 96, "host_buffers": "pageable"},
+        "e2e_pinned": {"value": e2e_pinned_ms, "unit": "ms", "host_buffers": "page-locked"},
+        "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "ntt": ntt, "ntt_batch": ntt_batch,
         "msm_points_per_s": n_total / (ms_per_step * 1e-3),
+        "registration": {"ms": registration_ms, "device_bytes": registration_bytes, "precompute": pre_c != 0, "window_bits": pre_c,
+                         "points": n_loc, "notice": notice,
+                         "what": "one-off cost of get_base_descriptor on this rank's bases (device-resident): the multiples 2^(c*j) * P of every window"},
+        "exchange": ("none (one GPU)" if world == 1 else
+                     "h2b_msm_sharded: reduced terms stored into every peer's mailbox over NVLink by the last kernel of the reduction, "
+                     "folded on the device; every rank returns the whole result (NCCL only for set-up, barriers and max-over-ranks timing)"),
         "timing": {"value": "host clock around the synchronous calls, bracketed by barrier + cuda synchronize, max over ranks "
-                            "(includes the host-side window combine and normalisation)",
+                            "(includes the host-side Horner over the reduced terms and the normalisation)",
                    "device_events_ms_per_step": max_dev_ms},
     }
     if world == 1 and not args.no_seq:
@@ -566,18 +687,22 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
             line["k20_proof"]["cpu_baseline"] = {"value": cpu_total, "unit": "ms", "cores": thr, "kind": "port",
                                                  "sample": "the MSM + NTT calls of the same proof only (a lower bound on the reference prover): "
                                                            "one call of each kind timed, scaled by the counts"}
-    if world == 1 and not args.no_cpu:
-        ms, threads = cpu_msm_sample(CPU_SAMPLE_K)
-        line["cpu_baseline"] = {"value": scale_to_full(ms, CPU_SAMPLE_K, MSM_K), "unit": "ms", "cores": threads, "kind": "port",
-                                "sample": f"C restatement of halo2curves 0.6 best_multiexp (rayon chunk-per-thread Booth Pippenger) on 2^{CPU_SAMPLE_K} "
-                                          f"points: {ms:.1f} ms, scaled x{1 << (MSM_K - CPU_SAMPLE_K)} linearly"}
-        nms = cpu_ntt_sample(CPU_SAMPLE_K)
-        ntt["cpu_baseline"] = {"value": scale_to_full(nms, CPU_SAMPLE_K, NTT_K) * NTT_K / CPU_SAMPLE_K, "unit": "ms", "cores": threads, "kind": "port",
-                               "sample": f"best_fft restatement on 2^{CPU_SAMPLE_K}: {nms:.1f} ms, scaled by n log n"}
-    emit(line)
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+    if world == 1 and not args.no_cpu:
+        # the CPU port beside it, on the SAME inputs at the SAME size (one full 2^24 MSM, ~10 s; one full 2^24 NTT, ~3 s), and the
+        # one check of the GPU result against the oracle at the headline size
+        ms, threads, cpu_res = cpu_msm(MSM_K)
+        line["cpu_baseline"] = {"value": ms, "unit": "ms", "cores": threads, "kind": "port", "measured_at": MSM_K,
+                                "sample": f"C restatement of halo2curves 0.6 best_multiexp (rayon chunk-per-thread Booth Pippenger): one full 2^{MSM_K} MSM on the same inputs, no extrapolation"}
+        line["result_matches_cpu_oracle"] = bool(np.array_equal(cpu_res, res_dev[:8]))
+        nms = cpu_ntt(NTT_K)
+        ntt["cpu_baseline"] = {"value": nms, "unit": "ms", "cores": threads, "kind": "port", "measured_at": NTT_K,
+                               "sample": f"best_fft restatement on 2^{NTT_K}: one full-size run"}
+        if not line["result_matches_cpu_oracle"]:
+            raise SystemExit("bench: the 2^%d MSM result differs from the CPU oracle" % MSM_K)
+    emit(line)
 
 
 _JSON_FD = None

@@ -60,6 +60,14 @@ void h2b_destroy(h2b_ctx* ctx);
 const char* h2b_last_error(const h2b_ctx* ctx);
 int h2b_device_count(void);
 const char* h2b_version(void);
+/* h2b_last_notice: the most recent non-fatal notice of the context ("" if none), e.g. that h2b_bases_register had to skip the
+ *                  window precomputation for lack of device memory (MSMs on that handle are 2-3x slower).
+ * h2b_set_option:  tuning knobs of one context.  Each knob is also read ONCE from the environment in h2b_init (variable =
+ *                  "H2B_" + upper-case name); value NULL or "" restores the default.  Names: msm_c, msm_pre_c, msm_precompute,
+ *                  msm_chunks, msm_no_ramp, msm_no_batch, msm_reduce_classic, msm_reduce_seg, acc_variant, msm_sort,
+ *                  ntt_split ("9,9,6"), ntt_full_table_max_log, peer_timeout_ms.  Unknown name -> H2B_E_INVALID. */
+const char* h2b_last_notice(const h2b_ctx* ctx);
+int h2b_set_option(h2b_ctx* ctx, const char* name, const char* value);
 
 /* ---- MSM: MsmAccel<G1Affine> ---------------------------------------------------------------------------
  * h2b_bases_register     = MsmAccel::get_base_descriptor (zal.rs:82): copy n affine bases to the device(s)
@@ -83,6 +91,10 @@ int h2b_bases_release(h2b_ctx* ctx, uint64_t handle);
 int h2b_msm(h2b_ctx* ctx, uint64_t bases_handle, const void* scalars, size_t n, void* out96);
 int h2b_msm_raw(h2b_ctx* ctx, const void* bases, const void* scalars, size_t n, void* out96);
 int h2b_msm_device(h2b_ctx* ctx, uint64_t bases_handle, const void* d_scalars, size_t n, void* out96);
+/* h2b_bases_info: what a registered handle holds: *window_bits_out = c of the precomputed window multiples (0 = none: the
+ *                 multiples were disabled, too small to pay, or did not fit -- see h2b_last_notice), *device_bytes_out = device
+ *                 memory the handle owns (13.9 GB for 2^24 points at c = 20).  Either pointer may be NULL. */
+int h2b_bases_info(h2b_ctx* ctx, uint64_t bases_handle, uint32_t* window_bits_out, uint64_t* device_bytes_out);
 
 /* Multi-process sharding (one process per GPU, point-range partition): each rank computes the per-window
  * bucket sums of its own range, the ranks exchange H2B_MSM_WINDOW_BYTES * windows bytes (a tiny all-gather),
@@ -94,6 +106,22 @@ int h2b_msm_device(h2b_ctx* ctx, uint64_t bases_handle, const void* d_scalars, s
 int h2b_msm_windows(h2b_ctx* ctx, uint64_t bases_handle, const void* scalars, int scalars_on_device, size_t n,
                     size_t n_total, void* out_windows, uint32_t* c_out, uint32_t* windows_out);
 int h2b_msm_combine(const void* parts, uint32_t n_parts, uint32_t c, uint32_t windows, void* out96);
+/* The same sharding with the exchange INSIDE the library and on the device (SURVEY.md 8a `partials_gather` as the epilogue of
+ * the window combine): every rank owns a small device mailbox; the last kernel of a rank's reduction stores its reduced terms
+ * (<= 64 points) into every peer's mailbox over NVLink, waits for theirs and folds them, so each rank returns the WHOLE result
+ * with no collective call and no host staging.
+ *   h2b_peer_export : allocate this context's mailbox; handle64_out receives the 64-byte CUDA IPC handle the other processes
+ *                     need, *local_ptr_out (optional) the device pointer for peers living in the SAME process.
+ *   h2b_peer_attach : handles = world x 64 bytes in rank order (e.g. all-gathered by the launcher); local_ptrs (optional,
+ *                     world entries) overrides the handle of a same-process peer with its pointer.  One device per context.
+ *   h2b_msm_sharded : this rank's n scalars against its registered range; every rank must call it, with equal shard sizes
+ *                     (the ranks must reduce with the same window geometry; a mismatch or a missing peer is reported as
+ *                     H2B_E_CUDA after `peer_timeout_ms`).  out96 = the normalised sum over all ranks, on every rank. */
+#define H2B_PEER_HANDLE_BYTES 64
+int h2b_peer_export(h2b_ctx* ctx, void* handle64_out, void** local_ptr_out);
+int h2b_peer_attach(h2b_ctx* ctx, int rank, int world, const void* handles, void* const* local_ptrs_or_null);
+int h2b_msm_sharded(h2b_ctx* ctx, uint64_t bases_handle, const void* scalars, int scalars_on_device, size_t n, size_t n_total,
+                    void* out96);
 /* h2b_msm_batch: n_cols MSMs of n scalars each against bases[0..n) of ONE handle -- the per-column commits of a prover phase
  * (plonk/prover.rs:436-440 `.iter().map(commit_lagrange)`, vanishing/prover.rs:136-140 the h pieces).  out96s receives
  * n_cols x 96 bytes.  Same results as n_cols calls of h2b_msm; the columns share one pipeline (binning of column k+1 overlaps

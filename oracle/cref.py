@@ -57,6 +57,8 @@ def lib():
             "h2ref_fr_mul": [vp, vp, vp], "h2ref_fq_mul": [vp, vp, vp],
             "h2ref_fr_add": [vp, vp, vp], "h2ref_fr_sub": [vp, vp, vp], "h2ref_fr_inv": [vp, vp],
             "h2ref_random_fr": [vp, sz, u64],
+            "h2ref_random_fr_chacha20": [vp, sz, vp, u64],
+            "h2ref_chacha20_block": [vp, u64, vp],
             "h2ref_gen_bases": [vp, sz, u64],
             "h2ref_kzg_setup": [u32, vp, vp, vp, vp],
             "h2ref_num_threads": [],
@@ -90,6 +92,32 @@ def random_fr(n: int, seed: int) -> np.ndarray:
     out = np.empty((n, 4), dtype=np.uint64)
     lib().h2ref_random_fr(_p(out), n, seed)
     return out
+
+
+def chacha20_block(seed: bytes, counter: int) -> np.ndarray:
+    """16 little-endian keystream words of one rand_chacha ChaCha20 block (64-bit counter, stream 0)."""
+    assert len(seed) == 32
+    out = np.zeros(16, dtype=np.uint32)
+    lib().h2ref_chacha20_block(ctypes.c_char_p(seed), counter, out.ctypes.data_as(ctypes.c_void_p))
+    return out
+
+
+def random_fr_chacha20(n: int, seed: bytes, first_block: int = 0) -> np.ndarray:
+    """SURVEY.md 8(d): n consecutive `Fr::random` draws of ChaCha20Rng::from_seed(seed), starting at draw `first_block`."""
+    assert len(seed) == 32
+    out = np.empty((n, 4), dtype=np.uint64)
+    lib().h2ref_random_fr_chacha20(_p(out), n, ctypes.c_char_p(seed), first_block)
+    return out
+
+
+# SURVEY.md 8(d) seeds of the synthetic benchmark inputs
+SEED_SCALARS, SEED_POINTS, SEED_SRS = bytes([1]) * 32, bytes([2]) * 32, bytes([3]) * 32
+
+
+def bench_t0() -> int:
+    """bases are [t0 + i]G with t0 = the first next_u64() of ChaCha20Rng::from_seed([2u8; 32])"""
+    w = chacha20_block(SEED_POINTS, 0)
+    return int(w[0]) | (int(w[1]) << 32)
 
 
 def gen_bases(n: int, t0: int = 1) -> np.ndarray:

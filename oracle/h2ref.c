@@ -522,6 +522,52 @@ void h2ref_random_fr(void *out_, size_t n, uint64_t seed) {
         fe_mul(&out[i], &v, &FR.r2, &FR);
     }
 }
+/* SURVEY.md 8(d) seeded inputs: element j = Fr::random(rng) for rng = rand_chacha::ChaCha20Rng::from_seed(seed32), i.e.
+ * (halo2curves 0.6, recalled -- SURVEY A.2) eight next_u64() = the sixteen little-endian words of ChaCha20 block
+ * first_block + j (64-bit block counter in words 12-13, stream id 0, 20 rounds), read as a 512-bit little-endian integer and
+ * reduced mod r:  lo + hi * 2^256  ->  lo * R2 * R^-1 + hi * R2 * R2 * R^-2 ... in Montgomery terms mont(lo) + mont(hi) * mont(2^256). */
+#define ROTL32(v, c) (((v) << (c)) | ((v) >> (32 - (c))))
+#define CHACHA_QR(a, b, c, d) a += b; d ^= a; d = ROTL32(d, 16); c += d; b ^= c; b = ROTL32(b, 12); a += b; d ^= a; d = ROTL32(d, 8); c += d; b ^= c; b = ROTL32(b, 7);
+static void chacha20_block(const uint32_t key[8], uint64_t counter, uint32_t out[16]) {
+    uint32_t in[16] = {0x61707865u, 0x3320646eu, 0x79622d32u, 0x6b206574u, key[0], key[1], key[2], key[3], key[4], key[5], key[6], key[7],
+                       (uint32_t)counter, (uint32_t)(counter >> 32), 0, 0};
+    uint32_t x[16];
+    memcpy(x, in, sizeof x);
+    for (int i = 0; i < 10; i++) {
+        CHACHA_QR(x[0], x[4], x[8], x[12]) CHACHA_QR(x[1], x[5], x[9], x[13]) CHACHA_QR(x[2], x[6], x[10], x[14]) CHACHA_QR(x[3], x[7], x[11], x[15])
+        CHACHA_QR(x[0], x[5], x[10], x[15]) CHACHA_QR(x[1], x[6], x[11], x[12]) CHACHA_QR(x[2], x[7], x[8], x[13]) CHACHA_QR(x[3], x[4], x[9], x[14])
+    }
+    for (int i = 0; i < 16; i++) out[i] = x[i] + in[i];
+}
+void h2ref_chacha20_block(const void *seed32, uint64_t counter, void *out64) {
+    uint32_t key[8], w[16];
+    memcpy(key, seed32, 32);
+    chacha20_block(key, counter, w);
+    memcpy(out64, w, 64);
+}
+void h2ref_random_fr_chacha20(void *out_, size_t n, const void *seed32, uint64_t first_block) {
+    fe *out = (fe *)out_;
+    uint32_t key[8];
+    memcpy(key, seed32, 32);
+    #pragma omp parallel for schedule(static)
+    for (long i = 0; i < (long)n; i++) {
+        uint32_t w[16];
+        chacha20_block(key, first_block + (uint64_t)i, w);
+        uint64_t lo[4], hi[4];
+        for (int l = 0; l < 4; l++) {
+            lo[l] = (uint64_t)w[2 * l] | ((uint64_t)w[2 * l + 1] << 32);
+            hi[l] = (uint64_t)w[8 + 2 * l] | ((uint64_t)w[8 + 2 * l + 1] << 32);
+        }
+        while (geq_p(lo, FR.p)) sub_p(lo, FR.p);
+        while (geq_p(hi, FR.p)) sub_p(hi, FR.p);
+        fe a, b, ma, mb;
+        memcpy(a.l, lo, 32); memcpy(b.l, hi, 32);
+        fe_mul(&ma, &a, &FR.r2, &FR);                 /* mont(lo) */
+        fe_mul(&mb, &b, &FR.r2, &FR);                 /* mont(hi) */
+        fe_mul(&mb, &mb, &FR.r2, &FR);                /* mont(hi * 2^256): times mont(R) = R2 */
+        fe_add(&out[i], &ma, &mb, &FR);
+    }
+}
 /* n distinct affine bases P_i = [t0 + i]G, G = (1,2): incremental adds + batch normalisation */
 void h2ref_gen_bases(void *out_, size_t n, uint64_t t0) {
     g1a *out = (g1a *)out_;

@@ -11,6 +11,7 @@ pub struct h2b_ctx {
 pub const H2B_OK: c_int = 0;
 pub const H2B_MSM_WINDOW_BYTES: usize = 128;
 pub const H2B_MSM_MAX_WINDOWS: usize = 64;
+pub const H2B_PEER_HANDLE_BYTES: usize = 64;
 
 /// `h2b_graph` of include/h2b200.h: the reference's `GraphEvaluator` (plonk/evaluation.rs:187-196) flattened.
 #[repr(C)]
@@ -30,6 +31,9 @@ extern "C" {
     pub fn h2b_destroy(ctx: *mut h2b_ctx);
     pub fn h2b_last_error(ctx: *const h2b_ctx) -> *const c_char;
     pub fn h2b_device_count() -> c_int;
+    pub fn h2b_last_notice(ctx: *const h2b_ctx) -> *const c_char;
+    pub fn h2b_set_option(ctx: *mut h2b_ctx, name: *const c_char, value: *const c_char) -> c_int;
+    pub fn h2b_bases_info(ctx: *mut h2b_ctx, bases_handle: u64, window_bits_out: *mut u32, device_bytes_out: *mut u64) -> c_int;
     pub fn h2b_bases_register(ctx: *mut h2b_ctx, bases: *const c_void, n: usize, handle_out: *mut u64) -> c_int;
     pub fn h2b_bases_release(ctx: *mut h2b_ctx, handle: u64) -> c_int;
     pub fn h2b_msm(ctx: *mut h2b_ctx, bases_handle: u64, scalars: *const c_void, n: usize, out96: *mut c_void) -> c_int;
@@ -103,6 +107,11 @@ extern "C" {
     pub fn h2b_msm_windows(ctx: *mut h2b_ctx, bases_handle: u64, scalars: *const c_void, scalars_on_device: c_int, n: usize,
                            n_total: usize, out_windows: *mut c_void, c_out: *mut u32, windows_out: *mut u32) -> c_int;
     pub fn h2b_msm_combine(parts: *const c_void, n_parts: u32, c: u32, windows: u32, out96: *mut c_void) -> c_int;
+    // the same sharding with the exchange inside the library: peer mailboxes over CUDA IPC / NVLink, folded on the device
+    pub fn h2b_peer_export(ctx: *mut h2b_ctx, handle64_out: *mut c_void, local_ptr_out: *mut *mut c_void) -> c_int;
+    pub fn h2b_peer_attach(ctx: *mut h2b_ctx, rank: c_int, world: c_int, handles: *const c_void, local_ptrs_or_null: *const *mut c_void) -> c_int;
+    pub fn h2b_msm_sharded(ctx: *mut h2b_ctx, bases_handle: u64, scalars: *const c_void, scalars_on_device: c_int, n: usize,
+                           n_total: usize, out96: *mut c_void) -> c_int;
     // measurement hooks and synthetic benchmark input (bench only)
     pub fn h2b_version() -> *const c_char;
     pub fn h2b_last_call_ms(ctx: *const h2b_ctx) -> f64;

@@ -41,3 +41,17 @@ def ctx():
 def engine(ctx):
     import h2b200
     return h2b200.B200Engine(ctx)
+
+
+@pytest.fixture
+def knob(ctx):
+    """Set tuning knobs of the shared context for one test (h2b_set_option) and restore the defaults afterwards."""
+    touched = []
+
+    def set_(name, value):
+        ctx.set_option(name, value)
+        touched.append(name)
+
+    yield set_
+    for name in touched:
+        ctx.set_option(name, None)

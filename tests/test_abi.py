@@ -38,6 +38,30 @@ def test_rust_sys_crate_declares_every_header_symbol():
     assert declared == set(header_functions())
 
 
+@pytest.mark.skipif(not os.path.isdir("/root/reference/halo2_backend"), reason="the reference tree is not on this machine")
+def test_ntt_binding_patch_applies_to_the_reference():
+    """The EvaluationDomain side of the boundary has no trait: it ships as a patch of halo2_backend
+    (domain.rs:216-293 + the coset loop of evaluation.rs:344-361).  `patch --dry-run` must accept it (nothing is written)."""
+    patch = os.path.join(ROOT, "rust", "patches", "0001-halo2_backend-b200-ntt.patch")
+    with open(patch) as fh:
+        r = subprocess.run(["patch", "--dry-run", "-p1", "-d", "/root/reference"], stdin=fh, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    text = open(patch).read()
+    for needle in ("h2b_ntt(", "h2b_coeff_to_extended(", "h2b_extended_to_coeff(", "h2b_coeff_to_extended_batch(", "is_bn256_fr"):
+        assert needle in text
+    # every library function the patch calls is declared by the sys crate with that name
+    sys_src = open(os.path.join(ROOT, "rust", "h2b200-sys", "src", "lib.rs")).read()
+    for fn in set(re.findall(r"sys::(h2b_[a-z0-9_]+)\(", text)):
+        assert f"pub fn {fn}(" in sys_src, fn
+
+
+def test_rust_engine_never_caches_by_address():
+    """`msm` must not key resident bases on a (pointer, len) that can be freed and reused."""
+    src = open(os.path.join(ROOT, "rust", "h2b200-engine", "src", "lib.rs")).read()
+    assert "HashMap" not in src and "h2b_msm_raw" in src
+    assert "impl Drop for B200BaseDesc" in src and "h2b_bases_release" in src
+
+
 def test_library_is_sm100a_only():
     out = subprocess.run(["cuobjdump", "-lelf", h2b200.LIB_PATH], capture_output=True, text=True).stdout
     archs = set(re.findall(r"sm_(\d+a?)", out))

@@ -44,14 +44,11 @@ def test_best_fft_three_pass(ctx, k):
 
 
 @pytest.mark.parametrize("k,split", [(12, "4,4,4"), (12, "3,3,3,3"), (16, "8,8"), (18, "9,9"), (15, "7,8"), (13, "9,4"), (14, "5,9")])
-def test_split_overrides(ctx, k, split):
-    os.environ["H2B_NTT_SPLIT"] = split
-    try:
-        a = C.random_fr(1 << k, 3000 + k)
-        w = m(omega_for(k))
-        assert np.array_equal(gpu_ntt(ctx, a, k, w), C.best_fft(a, w, k))
-    finally:
-        os.environ.pop("H2B_NTT_SPLIT", None)
+def test_split_overrides(ctx, k, split, knob):
+    knob("ntt_split", split)
+    a = C.random_fr(1 << k, 3000 + k)
+    w = m(omega_for(k))
+    assert np.array_equal(gpu_ntt(ctx, a, k, w), C.best_fft(a, w, k))
 
 
 def test_edge_inputs(ctx):
@@ -163,3 +160,60 @@ def test_device_resident_round_trip_full_size(ctx):
     assert C.int_from_limbs(x0) == raw
     dom.lagrange_to_coeff(d)
     assert np.array_equal(d.cpu().numpy().view(np.uint64), a)
+
+
+def test_full_size_ntt_matches_the_oracle_directly(ctx):
+    """BASELINE configs[2] at its headline size against the C port itself: best_fft on 2^24 elements (seeded bench input),
+    then the inverse with the 1/n scale folded in."""
+    import torch
+    import h2b200
+    k = 24
+    C.use_all_host_cores()
+    dom = h2b200.EvaluationDomain(1, k, ctx)
+    d = h2b200.synth.chacha_scalars_device(ctx, 1 << k)
+    a = d.cpu().numpy().view(np.uint64)
+    assert np.array_equal(a[:500], C.random_fr_chacha20(500, C.SEED_SCALARS))
+    dom.coeff_to_lagrange(d)
+    exp = C.best_fft(a, m(omega_for(k)), k)
+    assert np.array_equal(d.cpu().numpy().view(np.uint64), exp)
+    dom.lagrange_to_coeff(d)
+    assert np.array_equal(d.cpu().numpy().view(np.uint64), a)
+
+
+def test_coset_extension_at_bench_size_matches_the_oracle(ctx):
+    """coeff_to_extended 2^22 -> 2^24 (the column shape of bench.py's ntt_batch leg) and extended_to_coeff back, against the C port."""
+    import h2b200
+    k = 22
+    C.use_all_host_cores()
+    dom = h2b200.EvaluationDomain(5, k, ctx)
+    ref = R.EvaluationDomain(5, k)
+    d = h2b200.synth.chacha_scalars_device(ctx, 1 << k, bytes([7]) * 32)
+    a = d.cpu().numpy().view(np.uint64)
+    ext = dom.coeff_to_extended(d)
+    exp = C.coeff_to_extended(a, k, ref.extended_k, m(ref.extended_omega), m(ref.g_coset), m(ref.g_coset_inv))
+    assert np.array_equal(ext.cpu().numpy().view(np.uint64), exp)
+    back = dom.extended_to_coeff(ext)
+    assert np.array_equal(back.cpu().numpy().view(np.uint64)[: 1 << k], a)
+    assert not back.cpu().numpy().view(np.uint64)[1 << k:].any()
+
+
+@pytest.mark.parametrize("k", [26])
+def test_round_trip_largest_bench_size(ctx, k):
+    """BASELINE's sweep ends at 2^26 (2 GiB per vector): forward + inverse == identity, X[0] == sum of inputs."""
+    import h2b200
+    dom = h2b200.EvaluationDomain(1, k, ctx)
+    d = h2b200.synth.chacha_scalars_device(ctx, 1 << k)
+    orig = d.clone()
+    dom.coeff_to_lagrange(d)
+    dom.lagrange_to_coeff(d)
+    import torch
+    assert torch.equal(d, orig)
+
+
+@pytest.mark.parametrize("k,split", [(20, "5,5,5,5"), (22, "6,6,5,5"), (21, "9,3,3,6")])
+def test_four_pass_splits_at_real_sizes(ctx, k, split, knob):
+    """The 4-pass plan is the default only from k = 28; forced here at sizes the oracle checks in a second."""
+    knob("ntt_split", split)
+    a = C.random_fr(1 << k, 4000 + k)
+    w = m(omega_for(k))
+    assert np.array_equal(gpu_ntt(ctx, a, k, w), C.best_fft(a, w, k))

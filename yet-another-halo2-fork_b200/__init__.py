@@ -8,9 +8,9 @@ from . import plonk
 from ._lib import H2bError, LIB_PATH, SYMBOLS, load
 from .arithmetic import PolyOps
 from .domain import EvaluationDomain
-from .engine import (B200Engine, BaseDescriptor, CoeffsDescriptor, Context, PlonkEngine, PlonkEngineConfig, shard_range,
-                     window_bits)
+from .engine import (B200Engine, BaseDescriptor, CoeffsDescriptor, Context, PlonkEngine, PlonkEngineConfig, dist_all_gather_bytes,
+                     shard_range, window_bits)
 from .kzg import ParamsKZG
 
 __all__ = ["evaluation", "fields", "synth", "plonk", "H2bError", "LIB_PATH", "SYMBOLS", "load", "EvaluationDomain", "B200Engine", "BaseDescriptor",
-           "CoeffsDescriptor", "Context", "PlonkEngine", "PlonkEngineConfig", "ParamsKZG", "PolyOps", "shard_range", "window_bits"]
+           "CoeffsDescriptor", "Context", "PlonkEngine", "PlonkEngineConfig", "ParamsKZG", "PolyOps", "shard_range", "window_bits", "dist_all_gather_bytes"]

@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(HERE, "libh2b200.so")
 H2B_OK, H2B_E_INVALID, H2B_E_CUDA, H2B_E_NOMEM, H2B_E_NODEVICE, H2B_E_CONSTRAINT = 0, -1, -2, -3, -4, -5
 MSM_WINDOW_BYTES = 128
 MSM_MAX_WINDOWS = 64
+PEER_HANDLE_BYTES = 64
 
 # every symbol include/h2b200.h declares: name -> (restype, argtypes)
 _vp, _sz, _u32, _u64, _int = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_int
@@ -21,6 +22,12 @@ SYMBOLS = {
     "h2b_last_error": (ctypes.c_char_p, [_vp]),
     "h2b_device_count": (_int, []),
     "h2b_version": (ctypes.c_char_p, []),
+    "h2b_last_notice": (ctypes.c_char_p, [_vp]),
+    "h2b_set_option": (_int, [_vp, ctypes.c_char_p, ctypes.c_char_p]),
+    "h2b_bases_info": (_int, [_vp, _u64, _pu32, _pu64]),
+    "h2b_peer_export": (_int, [_vp, _vp, ctypes.POINTER(_vp)]),
+    "h2b_peer_attach": (_int, [_vp, _int, _int, _vp, ctypes.POINTER(_vp)]),
+    "h2b_msm_sharded": (_int, [_vp, _u64, _vp, _int, _sz, _sz, _vp]),
     "h2b_bases_register": (_int, [_vp, _vp, _sz, _pu64]),
     "h2b_bases_register_device": (_int, [_vp, _vp, _sz, _pu64]),
     "h2b_bases_release": (_int, [_vp, _u64]),

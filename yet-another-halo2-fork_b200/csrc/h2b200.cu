@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cctype>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -91,6 +92,7 @@ struct Dev {
     size_t pinned_cap = 0;
     std::map<std::string, NttPlanDev> plans;
     bool prof = false;
+    bool peer_attr = false;
     std::vector<ProfRec> recs;
     std::vector<cudaEvent_t> ev_pool;
     uint64_t launches = 0;
@@ -125,19 +127,89 @@ struct BasesShard {
     bool owned = true;
     void* pre = nullptr;          // optional: pre_w * count precomputed multiples 2^(pre_c*j) * P_i (window-major)
     uint32_t pre_c = 0, pre_w = 0;
+    bool pre_skipped = false;     // the multiples did not fit: see h2b_last_notice
 };
-struct Bases { size_t n = 0; std::vector<BasesShard> shard; };
+struct Bases { size_t n = 0; std::vector<BasesShard> shard; bool pre_skipped = false; };
+
+#ifndef H2B_ACC_DEFAULT_VARIANT
+#define H2B_ACC_DEFAULT_VARIANT 1
+#endif
+// Tuning knobs of one context.  The H2B_* environment variables are read ONCE, in h2b_init (getenv is not safe against a
+// concurrent setenv, and a product path should not depend on the environment at call time); afterwards a knob changes only
+// through h2b_set_option, under the context lock.
+struct Tuning {
+    int msm_c = 0;                 // H2B_MSM_C          window bits of the per-window layout (0 = auto)
+    int msm_pre_c = 0;             // H2B_MSM_PRE_C      window bits of the precomputed-multiples layout (0 = auto)
+    int msm_precompute = 1;        // H2B_MSM_PRECOMPUTE 0: registered bases keep only the 64 B per point
+    int msm_chunks = 0;            // H2B_MSM_CHUNKS     number of scalar chunks of the streamed pipeline (0 = auto)
+    int msm_no_ramp = 0;           // H2B_MSM_NO_RAMP    1: equal chunks also for host scalars
+    int msm_no_batch = 0;          // H2B_MSM_NO_BATCH   1: h2b_msm_batch loops over single MSMs
+    int msm_reduce_classic = 0;    // H2B_MSM_REDUCE_CLASSIC 1: running-sum reduction for every bucket-set size
+    int msm_acc_variant = H2B_ACC_DEFAULT_VARIANT;   // H2B_ACC_VARIANT
+    int msm_reduce_seg = 256;      // H2B_MSM_REDUCE_SEG buckets per row / column segment job of the lines reduction
+    int msm_sort = 1;              // H2B_MSM_SORT       1: tiled two-level binning, 0: global-atomic count + scatter
+    int ntt_full_table_max_log = 26;   // H2B_NTT_FULL_TABLE_MAX_LOG
+    std::string ntt_split;         // H2B_NTT_SPLIT      e.g. "9,9,6"
+    int l2_fetch = 0;              // H2B_L2_FETCH       cudaLimitMaxL2FetchGranularity hint (experiments)
+    int peer_timeout_ms = 20000;   // H2B_PEER_TIMEOUT_MS how long the exchange kernel of a sharded MSM waits for a peer
+
+    // name = the environment variable without its H2B_ prefix, lower case; value == nullptr or "" restores the default
+    bool set(const std::string& name, const char* value) {
+        const bool reset = !value || !*value;
+        const int v = reset ? 0 : std::atoi(value);
+        Tuning def;
+        if (name == "msm_c") msm_c = (!reset && v >= 4 && v <= 24) ? v : def.msm_c;
+        else if (name == "msm_pre_c") msm_pre_c = (!reset && v >= 4 && v <= 24) ? v : def.msm_pre_c;
+        else if (name == "msm_precompute") msm_precompute = reset ? def.msm_precompute : (v != 0);
+        else if (name == "msm_chunks") msm_chunks = (!reset && v >= 1 && v <= 64) ? v : def.msm_chunks;
+        else if (name == "msm_no_ramp") msm_no_ramp = reset ? 0 : (v != 0);
+        else if (name == "msm_no_batch") msm_no_batch = reset ? 0 : (v != 0);
+        else if (name == "msm_reduce_classic") msm_reduce_classic = reset ? 0 : (v != 0);
+        else if (name == "acc_variant") msm_acc_variant = (!reset && v >= 0 && v < 4) ? v : def.msm_acc_variant;
+        else if (name == "msm_reduce_seg") msm_reduce_seg = (!reset && v >= 32 && v <= 4096 && (v & (v - 1)) == 0) ? v : def.msm_reduce_seg;
+        else if (name == "msm_sort") msm_sort = reset ? def.msm_sort : (v != 0);
+        else if (name == "ntt_full_table_max_log") ntt_full_table_max_log = reset ? def.ntt_full_table_max_log : v;
+        else if (name == "ntt_split") ntt_split = reset ? std::string() : std::string(value);
+        else if (name == "l2_fetch") l2_fetch = (v == 32 || v == 64 || v == 128) ? v : 0;
+        else if (name == "peer_timeout_ms") peer_timeout_ms = (!reset && v >= 1) ? v : def.peer_timeout_ms;
+        else return false;
+        return true;
+    }
+    void from_environment() {
+        static const char* names[] = {"msm_c", "msm_pre_c", "msm_precompute", "msm_chunks", "msm_no_ramp", "msm_no_batch",
+                                      "msm_reduce_classic", "msm_reduce_seg", "acc_variant", "msm_sort", "ntt_full_table_max_log", "ntt_split", "l2_fetch", "peer_timeout_ms"};
+        for (const char* nm : names) {
+            std::string env = "H2B_";
+            for (const char* c = nm; *c; c++) env.push_back((char)std::toupper((unsigned char)*c));
+            if (const char* val = std::getenv(env.c_str())) set(nm, *val ? val : "1");
+        }
+    }
+};
 
 }  // namespace
 
+// Mailboxes of a point-range sharded MSM across processes (msm.cuh 7): mine lives on device 0 of this context, the peers' are
+// mapped through CUDA IPC (or handed over as plain pointers when the peer is a context of the same process).
+struct PeerState {
+    void* mailbox = nullptr;
+    MsmPeerTable table = {};
+    std::vector<void*> opened;
+    int rank = -1, world = 0;
+    uint64_t epoch = 0;
+    uint32_t* status = nullptr;        // page-locked word the exchange kernel reports into
+};
+
 struct h2b_ctx {
+    PeerState peer;
     std::vector<Dev> devs;
     std::mutex mu;
     std::string err;
     std::map<uint64_t, Bases> bases;
     uint64_t next_handle = 1;
     double last_ms = 0.0;
-    std::mutex err_mu;                 // `fail` may be reached from the per-device host threads of a multi-GPU call
+    Tuning tune;
+    std::string status;                // last non-fatal notice (e.g. window precomputation skipped for lack of memory)
+    mutable std::mutex err_mu;         // `fail` may be reached from the per-device host threads of a multi-GPU call
     int fail(int code, const std::string& msg) { std::lock_guard<std::mutex> lk(err_mu); err = msg; return code; }
 };
 
@@ -192,11 +264,12 @@ int ntt_get_plan(h2b_ctx* ctx, Dev& d, uint32_t log_n, const Fr& omega, const Fr
     std::string key((const char*)&log_n, 4);
     key.append((const char*)&omega, 32);
     if (scale) key.append((const char*)scale, 32);
-    if (const char* env = std::getenv("H2B_NTT_SPLIT")) key.append(env);
+    key.append(ctx->tune.ntt_split);
+    key.push_back((char)ctx->tune.ntt_full_table_max_log);
     auto it = d.plans.find(key);
     if (it != d.plans.end()) { *out = &it->second; return H2B_OK; }
     NttPlanDev pd;
-    pd.plan = ntt_make_plan(log_n, omega, scale);
+    pd.plan = ntt_make_plan(log_n, omega, scale, ctx->tune.ntt_split.c_str(), (uint32_t)ctx->tune.ntt_full_table_max_log);
     pd.has_scale = scale != nullptr;
     if (scale) pd.scale = *scale;
     H2B_CK(cudaMalloc((void**)&pd.tables, pd.plan.total_elems * sizeof(Fr)));
@@ -257,11 +330,8 @@ int ntt_enqueue(h2b_ctx* ctx, Dev& d, const Fr* in, uint64_t in_stride, Fr* tmp,
 // ------------------------------------------------------------------------------------------------
 // MSM
 // ------------------------------------------------------------------------------------------------
-uint32_t msm_choose_c(size_t n_total) {
-    if (const char* env = std::getenv("H2B_MSM_C")) {
-        int v = std::atoi(env);
-        if (v >= 4 && v <= 24) return (uint32_t)v;   // c >= 4 keeps windows <= H2B_MSM_MAX_WINDOWS
-    }
+uint32_t msm_choose_c(const h2b_ctx* ctx, size_t n_total) {
+    if (ctx->tune.msm_c) return (uint32_t)ctx->tune.msm_c;   // c >= 4 keeps windows <= H2B_MSM_MAX_WINDOWS
     uint32_t lg = 0;
     while (((size_t)1 << (lg + 1)) <= n_total) lg++;
     int c = (int)lg - 4;
@@ -270,10 +340,9 @@ uint32_t msm_choose_c(size_t n_total) {
     return (uint32_t)c;
 }
 
-#ifndef H2B_ACC_DEFAULT_VARIANT
-#define H2B_ACC_DEFAULT_VARIANT 1
-#endif
-struct MsmLaunchInfo { uint32_t c, windows, slices; bool pre; };
+// What the reduction of one call leaves for the host: `windows` bucket sets, each reduced to `n_terms` points whose weighted
+// sum sum_t 2^(exps[t]) * term_t is the set's bucket sum (msm_horner_terms); d_terms = where they sit on the device.
+struct MsmLaunchInfo { uint32_t c, windows, n_terms; bool pre; uint32_t exps[MSM_MAX_TERMS]; Xyzz* d_terms; };
 const MsmKernelTable& MK = msm_kernel_table();
 
 // Enqueue the whole bucket pipeline for `n` resident (scalar, base) pairs on device d; the per-window partial
@@ -381,9 +450,7 @@ int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan
     const uint32_t* counters = S.counters.as<uint32_t>();
     Xyzz* buckets = d.m_buckets.as<Xyzz>() + (size_t)set_index * nkeys;
     {
-        int v = H2B_ACC_DEFAULT_VARIANT;
-        if (const char* env = std::getenv("H2B_ACC_VARIANT")) { int t = std::atoi(env); if (t >= 0 && t < 4) v = t; }
-        auto kern = MK.accumulate[v];
+        auto kern = MK.accumulate[ctx->tune.msm_acc_variant];
         H2B_LAUNCH(d, "msm_accumulate", kern, (nkeys + 127) / 128, 128, 0, bases, entries, offsets, ends, order, nkeys,
                    pl.long_threshold, buckets, add_to ? 1u : 0u);
     }
@@ -395,7 +462,8 @@ int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan
     return H2B_OK;
 }
 
-int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmLaunchInfo* info, uint32_t batch_sets = 0) {
+int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmLaunchInfo* info, uint32_t batch_sets = 0,
+                     bool copy_back = true) {
     MsmShape sp = msm_shape(0, c, pre_stride, 0);
     const MsmGeom& g = sp.g;
     const uint32_t kw = batch_sets ? batch_sets : sp.kw;      // a batch of MSMs: one shared-window bucket set per column
@@ -406,7 +474,6 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
         while (slices > (uint32_t)MSM_REDUCE_MAX_SLICES) { slices >>= 1; log_l++; }
     }
     H2B_CK(d.m_wpart.reserve(((size_t)kw * slices * 2 + kw) * sizeof(Xyzz)));
-    H2B_CK(d.reserve_pinned(std::max<size_t>((size_t)kw * sizeof(Xyzz), 4096)));
     Xyzz* buckets = d.m_buckets.as<Xyzz>();
     Xyzz* wpart = d.m_wpart.as<Xyzz>();
     MsmGeom gr = g;
@@ -416,20 +483,26 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
     Xyzz* set_sums = wpart + (size_t)kw * slices * 2;
     uint32_t lg_nb = 0;
     while ((1u << (lg_nb + 1)) <= g.nb) lg_nb++;
-    const bool lines_path = g.nb >= (1u << 14) && !std::getenv("H2B_MSM_REDUCE_CLASSIC");
+    const bool lines_path = g.nb >= (1u << 14) && !ctx->tune.msm_reduce_classic;
+    info->n_terms = 1;
+    info->exps[0] = 0;
     if (lines_path) {
-        // low-latency path: row / column sums, masked sums per index bit, Horner over the bits (msm.cuh 6b)
+        // low-latency path: row / column segment sums, masked sums per index bit; the Horner over the bits is left to the host
         const uint32_t w = lg_nb / 2, h = lg_nb - w, H = 1u << h, W = 1u << w;
-        const uint32_t cs = H / W;                  // column sums in H / W segments: every line job then sums W buckets
-        const uint32_t nl = H + cs * W;
-        H2B_CK(d.m_wpart.reserve(((size_t)kw * nl + (size_t)kw * (h + w + 1) + kw) * sizeof(Xyzz)));
+        const uint32_t seg = std::min<uint32_t>(W, (uint32_t)std::max(32, ctx->tune.msm_reduce_seg));   // buckets per line job
+        const uint32_t rs = W / seg, cs = H / seg;
+        const uint32_t nl = rs * H + cs * W, nt = h + w + 1;
+        H2B_CK(d.m_wpart.reserve(((size_t)kw * nl + (size_t)kw * nt) * sizeof(Xyzz)));
         wpart = d.m_wpart.as<Xyzz>();
         Xyzz* lines = wpart;
         Xyzz* terms = wpart + (size_t)kw * nl;
-        set_sums = terms + (size_t)kw * (h + w + 1);
-        H2B_LAUNCH(d, "msm_reduce", MK.reduce_lines, dim3((nl + 3) / 4, kw, 1), MSM_REDUCE_THREADS, 0, (const Xyzz*)buckets, g.nb, w, cs, lines);
-        H2B_LAUNCH(d, "msm_reduce", MK.reduce_masked, dim3(h + w + 1, kw, 1), MSM_REDUCE_THREADS, 0, (const Xyzz*)lines, h, w, cs, terms);
-        H2B_LAUNCH(d, "msm_reduce", MK.reduce_combine, kw, 64, 0, (const Xyzz*)terms, h, w, set_sums);
+        set_sums = terms;
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce_lines, dim3((nl + 3) / 4, kw, 1), MSM_REDUCE_THREADS, 0, (const Xyzz*)buckets, g.nb, w, rs, cs, lines);
+        H2B_LAUNCH(d, "msm_reduce", MK.reduce_masked, dim3(nt, kw, 1), MSM_MASKED_THREADS, 0, (const Xyzz*)lines, h, w, rs, cs, terms);
+        info->n_terms = nt;
+        for (uint32_t b = 0; b < h; b++) info->exps[b] = b + w;          // S^D_b carries 2^b * W
+        for (uint32_t b = 0; b < w; b++) info->exps[h + b] = b;          // S^C_b carries 2^b
+        info->exps[h + w] = 0;                                           // V
     } else if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
         dim3 grid(slices, kw, 1);
         H2B_LAUNCH(d, "msm_reduce", MK.reduce, grid, MSM_REDUCE_THREADS, 0, gr, buckets, slices, log_l, block_p, block_r);
@@ -438,17 +511,19 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
         H2B_LAUNCH(d, "msm_reduce", MK.reduce_small, (kw + 31) / 32, 32, 0, gr, buckets, set_sums);
     }
     H2B_CK(cudaGetLastError());
-    H2B_CK(d.ring.d2h(d.pinned, set_sums, (size_t)kw * sizeof(Xyzz), d.stream));
-    info->c = c; info->windows = kw; info->slices = 1; info->pre = pre_stride != 0;
+    const size_t out_bytes = (size_t)kw * info->n_terms * sizeof(Xyzz);
+    H2B_CK(d.reserve_pinned(std::max<size_t>(out_bytes, 4096)));
+    if (copy_back) H2B_CK(d.ring.d2h(d.pinned, set_sums, out_bytes, d.stream));
+    info->c = c; info->windows = kw; info->pre = pre_stride != 0; info->d_terms = set_sums;
     return H2B_OK;
 }
 
-// host: fold the slices of each window (after the stream has been synchronised)
-void msm_fold_slices(const Dev& d, const MsmLaunchInfo& info, Xyzz* windows /* accumulated into */) {
+// host: finish each bucket set (Horner over its terms) and add it to its window (after the stream has been synchronised)
+void msm_fold_terms(const Dev& d, const MsmLaunchInfo& info, Xyzz* windows /* accumulated into */) {
     const Xyzz* part = reinterpret_cast<const Xyzz*>(d.pinned);
     // (with precomputed multiples there is one bucket set whose sum already carries every window's weight: it joins window 0)
     for (uint32_t j = 0; j < info.windows; j++)
-        for (uint32_t s = 0; s < info.slices; s++) windows[j] = xyzz_add(windows[j], part[(size_t)j * info.slices + s]);
+        windows[j] = xyzz_add(windows[j], msm_horner_terms(part + (size_t)j * info.n_terms, info.exps, info.n_terms));
 }
 
 void begin_call(Dev& d) { cudaEventRecord(d.ev_first, d.stream); }
@@ -462,10 +537,12 @@ int end_call(h2b_ctx* ctx, Dev& d) {
 }
 
 // MSM over all devices of the context.  scalars: host pointer, or device-0 pointer when on_device.
+int msm_peer_epilogue(h2b_ctx* ctx, Dev& d, const MsmLaunchInfo& info);
+
 int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, size_t n, size_t n_total,
-            Xyzz* windows_out, uint32_t* c_out, uint32_t* windows_count) {
+            Xyzz* windows_out, uint32_t* c_out, uint32_t* windows_count, bool peer_exchange = false) {
     if (n > B.n) return ctx->fail(H2B_E_INVALID, "msm: more scalars than registered bases");
-    uint32_t c = msm_choose_c(n_total);
+    uint32_t c = msm_choose_c(ctx, n_total);
     uint32_t nw = msm_windows(c);
     if (nw > H2B_MSM_MAX_WINDOWS) return ctx->fail(H2B_E_INVALID, "msm: window size too small");
     for (uint32_t j = 0; j < nw; j++) windows_out[j] = Xyzz::identity();
@@ -498,8 +575,8 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
         }
         // (host scalars only: there the first chunk also waits for its PCIe copy; with device-resident scalars the shorter
         // chunks cost the accumulation more than the earlier start saves -- profiles/README.md)
-        bool ramp = chunk < cnt && staged && !on_device && !std::getenv("H2B_MSM_NO_RAMP");
-        if (const char* env = std::getenv("H2B_MSM_CHUNKS")) { int k = std::atoi(env); if (k >= 1 && k <= 64) { chunk = (cnt + k - 1) / k; ramp = false; } }
+        bool ramp = chunk < cnt && staged && !on_device && !ctx->tune.msm_no_ramp;
+        if (ctx->tune.msm_chunks) { chunk = (cnt + ctx->tune.msm_chunks - 1) / ctx->tune.msm_chunks; ramp = false; }
         // Chunk boundaries.  Nothing hides the binning of the FIRST chunk, so the pipeline starts with a short chunk and doubles
         // it until the steady chunk size is reached: each chunk's accumulation still covers the binning of the next one.
         std::vector<size_t> bounds{0};
@@ -518,13 +595,16 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
             dev_scalars = d.m_scalars.as<Fr>();
         }
         H2B_CK(cudaStreamWaitEvent(d.sort_stream, d.ev_first, 0));
-        if (nchunks > 1) {               // both sort sets sized for the largest chunk up front
+        {   // every buffer of the pipeline sized for the largest chunk up front: growing one later frees it, which waits for the
+            // whole device in the middle of the sort / accumulate overlap
             size_t longest = 0;
             for (size_t k = 0; k < nchunks; k++) longest = std::max(longest, bounds[k + 1] - bounds[k]);
             MsmChunkPlan big;
             rc = msm_chunk_plan(ctx, (uint32_t)longest, 0u, use_c, stride, &big);
             if (rc) return rc;
-            for (int q = 0; q < 2; q++) { rc = msm_sort_reserve(ctx, d.ms[q], big); if (rc) return rc; }
+            for (int q = 0; q < (nchunks > 1 ? 2 : 1); q++) { rc = msm_sort_reserve(ctx, d.ms[q], big); if (rc) return rc; }
+            H2B_CK(d.m_buckets.reserve((size_t)big.sp.nkeys * sizeof(Xyzz)));
+            H2B_CK(d.m_long_partials.reserve((size_t)big.max_tasks * sizeof(Xyzz)));
         }
         for (size_t k = 0; k < nchunks && rc == H2B_OK; k++) {
             size_t lo = bounds[k], len = bounds[k + 1] - lo;
@@ -552,22 +632,38 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
             S.consumed_pending = true;
         }
         if (rc) return rc;
-        rc = msm_stage_reduce(ctx, d, use_c, stride, &infos[di]);
+        rc = msm_stage_reduce(ctx, d, use_c, stride, &infos[di], 0, !peer_exchange);
         if (rc) return rc;
+        if (peer_exchange) { rc = msm_peer_epilogue(ctx, d, infos[di]); if (rc) return rc; }
         H2B_CK(cudaEventRecord(d.ev_last, d.stream));
         return H2B_OK;
     };
+    // a failed shard leaves copies / kernels in flight on three streams and `consumed` events pending: drain them so that the
+    // next call on this context starts from a clean state
+    auto drain = [&](int rc_in) -> int {
+        for (size_t di = 0; di < B.shard.size() && di < ctx->devs.size(); di++) {
+            Dev& d = ctx->devs[di];
+            cudaSetDevice(d.id);
+            cudaStreamSynchronize(d.copy_stream); cudaStreamSynchronize(d.sort_stream); cudaStreamSynchronize(d.stream);
+            d.ms[0].consumed_pending = d.ms[1].consumed_pending = false;
+            d.launch_stream = d.stream;
+        }
+        cudaGetLastError();
+        cudaSetDevice(ctx->devs[0].id);
+        return rc_in;
+    };
     for (size_t di = 0; di < B.shard.size(); di++)
         if (B.shard[di].start < n && B.shard[di].count != 0) used.push_back((int)di);
+    if (peer_exchange && used.size() != 1) return ctx->fail(H2B_E_INVALID, "msm_sharded: needs a single-device context with a non-empty range");
     if (used.size() == 1) {
         int rc = run_shard((size_t)used[0]);
-        if (rc) return rc;
+        if (rc) return drain(rc);
     } else {
         std::vector<int> rcs(used.size(), H2B_OK);
         std::vector<std::thread> th;
         for (size_t u = 0; u < used.size(); u++) th.emplace_back([&, u] { rcs[u] = run_shard((size_t)used[u]); });
         for (auto& t : th) t.join();
-        for (int rc : rcs) if (rc) return rc;
+        for (int rc : rcs) if (rc) return drain(rc);
     }
     for (int di : used) {
         Dev& d = ctx->devs[di];
@@ -576,10 +672,36 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
         float ms = 0.f;
         H2B_CK(cudaEventElapsedTime(&ms, d.ev_first, d.ev_last));
         max_ms = std::max(max_ms, (double)ms);
-        msm_fold_slices(d, infos[di], windows_out);
+        if (peer_exchange && *ctx->peer.status != 0) {
+            const uint32_t st = *ctx->peer.status;
+            return ctx->fail(H2B_E_CUDA, st >= 0x100 ? "msm_sharded: rank " + std::to_string(st - 0x100) + " reduced with a different window geometry (register equal shard sizes)"
+                                                     : "msm_sharded: timed out waiting for the terms of rank " + std::to_string(st - 1));
+        }
+        msm_fold_terms(d, infos[di], windows_out);
     }
     H2B_CK(cudaSetDevice(ctx->devs[0].id));      // the caller's (torch's) current device is device 0 of the context
     ctx->last_ms = max_ms;
+    return H2B_OK;
+}
+
+// Epilogue of the reduction in a sharded MSM across processes: ONE kernel publishes this rank's terms to every peer mailbox,
+// waits for theirs and folds them per term into the page-locked result buffer (msm.cuh 7).
+int msm_peer_epilogue(h2b_ctx* ctx, Dev& d, const MsmLaunchInfo& info) {
+    PeerState& P = ctx->peer;
+    if (P.world <= 0 || !P.mailbox) return ctx->fail(H2B_E_INVALID, "msm_sharded: h2b_peer_attach has not been called");
+    const uint32_t nt = info.windows * info.n_terms;
+    if (nt > MSM_PEER_SLOT_POINTS) return ctx->fail(H2B_E_INVALID, "msm_sharded: too many terms for one mailbox slot");
+    const size_t smem = (size_t)nt * (size_t)P.world * sizeof(Xyzz);
+    if (smem > ((size_t)200 << 10)) return ctx->fail(H2B_E_INVALID, "msm_sharded: terms x ranks exceed the shared memory of the fold");
+    if (!d.peer_attr) { H2B_CK(cudaFuncSetAttribute((const void*)MK.peer_exchange, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 << 10)); d.peer_attr = true; }
+    const uint64_t epoch = ++P.epoch;
+    // geometry tag: every rank must have reduced to the same terms with the same weights
+    uint64_t tag = ((uint64_t)info.c << 48) | ((uint64_t)info.windows << 32) | ((uint64_t)info.n_terms << 16) | (info.pre ? 1u : 0u);
+    *P.status = 0xffffffffu;
+    H2B_LAUNCH(d, "msm_peer_exchange", MK.peer_exchange, 1, 256, smem, (const Xyzz*)info.d_terms, nt, P.table, (uint32_t)P.rank,
+               (uint32_t)P.world, (uint32_t)(epoch & 1), (unsigned long long)epoch, (unsigned long long)tag,
+               (unsigned long long)ctx->tune.peer_timeout_ms * 1000000ull, reinterpret_cast<Xyzz*>(d.pinned), P.status);
+    H2B_CK(cudaGetLastError());
     return H2B_OK;
 }
 
@@ -628,17 +750,14 @@ int msm_run_batch(h2b_ctx* ctx, const Bases& B, const void* const* cols, bool on
     rc = end_call(ctx, d);
     if (rc) return rc;
     const Xyzz* part = reinterpret_cast<const Xyzz*>(d.pinned);
-    for (size_t k = 0; k < m; k++) sums_out[k] = part[k];
+    for (size_t k = 0; k < m; k++) sums_out[k] = msm_horner_terms(part + k * info.n_terms, info.exps, info.n_terms);
     *c_out = use_c;
     return H2B_OK;
 }
 
 // Window size used with precomputed multiples (one shared bucket set, so larger windows stay cheap to reduce).
-uint32_t msm_choose_pre_c(size_t n) {
-    if (const char* env = std::getenv("H2B_MSM_PRE_C")) {
-        int v = std::atoi(env);
-        if (v >= 4 && v <= 24) return (uint32_t)v;
-    }
+uint32_t msm_choose_pre_c(const h2b_ctx* ctx, size_t n) {
+    if (ctx->tune.msm_pre_c) return (uint32_t)ctx->tune.msm_pre_c;
     // Measured on B200 (profiles/README.md): c = 20 (13 windows, 2^19 buckets) wins from 2^19 points up, c = 17 from 2^16;
     // below that one bucket set has too few buckets to fill the GPU and the classic per-window layout is used (0).
     // Window sizes whose top window would hold only 1-2 scalar bits (18, 19, 21, 23) are avoided: every point would
@@ -652,15 +771,23 @@ uint32_t msm_choose_pre_c(size_t n) {
 // resident, store 2^(c*j) * P_i for every window j so that an MSM needs ONE bucket set instead of one per window.
 // Skipped (classic per-window buckets) for one-shot bases, tiny inputs, or when the multiples would not fit.
 int precompute_shard(h2b_ctx* ctx, Dev& d, BasesShard& sh) {
-    if (const char* env = std::getenv("H2B_MSM_PRECOMPUTE")) { if (std::atoi(env) == 0) return H2B_OK; }
+    if (!ctx->tune.msm_precompute) return H2B_OK;
     if (sh.count < 256) return H2B_OK;
-    uint32_t c = msm_choose_pre_c(sh.count);
+    uint32_t c = msm_choose_pre_c(ctx, sh.count);
     if (c == 0) return H2B_OK;
     uint32_t w = msm_windows(c);
     if ((uint64_t)sh.count * w >= 0x7fffffffull) return H2B_OK;
     size_t bytes = (size_t)sh.count * w * 64, free_b = 0, total_b = 0;
     H2B_CK(cudaMemGetInfo(&free_b, &total_b));
-    if (bytes > free_b / 2) return H2B_OK;
+    if (bytes > free_b / 2) {
+        // not an error, but a 2-3x slower MSM: say so (h2b_last_notice, h2b_bases_info) instead of dropping to the
+        // per-window layout silently
+        std::lock_guard<std::mutex> lk(ctx->err_mu);
+        ctx->status = "bases_register: window multiples (" + std::to_string(bytes >> 20) + " MiB) exceed half of the free device memory (" +
+                      std::to_string(free_b >> 20) + " MiB): registered WITHOUT precomputation, MSMs on this handle use one bucket set per window";
+        sh.pre_skipped = true;
+        return H2B_OK;
+    }
     H2B_CK(cudaMalloc(&sh.pre, bytes));
     H2B_LAUNCH(d, "msm_precompute", MK.precompute, (unsigned)((sh.count + 127) / 128), 128, 0, (const Affine*)sh.d,
                (Affine*)sh.pre, (uint32_t)sh.count, (uint32_t)sh.count, c, w);
@@ -670,8 +797,17 @@ int precompute_shard(h2b_ctx* ctx, Dev& d, BasesShard& sh) {
     return H2B_OK;
 }
 
-int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, bool allow_pre, uint64_t* handle_out) {
-    Bases B;
+void release_bases(h2b_ctx* ctx, Bases& B) {
+    for (size_t di = 0; di < B.shard.size(); di++)
+        {
+            cudaSetDevice(ctx->devs[di].id);
+            if (B.shard[di].d && B.shard[di].owned) cudaFree(B.shard[di].d);
+            if (B.shard[di].pre) cudaFree(B.shard[di].pre);
+        }
+    if (!ctx->devs.empty()) cudaSetDevice(ctx->devs[0].id);
+}
+
+int register_bases_impl(h2b_ctx* ctx, Bases& B, const void* bases, bool on_device, size_t n, bool allow_pre) {
     B.n = n;
     // Host bases are cut into one contiguous point range per device.  Device-resident bases (on device 0) are adopted in place
     // by a single-device context; a multi-device context keeps range 0 where it is and hands the other ranges to their devices
@@ -698,6 +834,19 @@ int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, bo
             H2B_CK(cudaStreamSynchronize(d.stream));
         }
         if (allow_pre) { int rc = precompute_shard(ctx, d, sh); if (rc) return rc; }
+        if (sh.pre_skipped) B.pre_skipped = true;
+    }
+    return H2B_OK;
+}
+
+int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, bool allow_pre, uint64_t* handle_out) {
+    Bases B;
+    int rc = register_bases_impl(ctx, B, bases, on_device, n, allow_pre);
+    if (rc) {                       // a failed copy / allocation / precomputation must not leak the shards already made
+        for (Dev& d : ctx->devs) { cudaSetDevice(d.id); cudaStreamSynchronize(d.stream); }
+        cudaGetLastError();
+        release_bases(ctx, B);
+        return rc;
     }
     H2B_CK(cudaSetDevice(ctx->devs[0].id));
     uint64_t h = ctx->next_handle++;
@@ -706,15 +855,6 @@ int register_bases(h2b_ctx* ctx, const void* bases, bool on_device, size_t n, bo
     return H2B_OK;
 }
 
-void release_bases(h2b_ctx* ctx, Bases& B) {
-    for (size_t di = 0; di < B.shard.size(); di++)
-        {
-            cudaSetDevice(ctx->devs[di].id);
-            if (B.shard[di].d && B.shard[di].owned) cudaFree(B.shard[di].d);
-            if (B.shard[di].pre) cudaFree(B.shard[di].pre);
-        }
-    if (!ctx->devs.empty()) cudaSetDevice(ctx->devs[0].id);
-}
 
 
 // ------------------------------------------------------------------------------------------------
@@ -848,6 +988,7 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
     if (!device_ids || n_devices <= 0) ids.push_back(0);
     else ids.assign(device_ids, device_ids + n_devices);
     h2b_ctx* ctx = new h2b_ctx();
+    ctx->tune.from_environment();          // the only place the H2B_* environment is consulted
     ctx->devs.resize(ids.size());
     for (size_t i = 0; i < ids.size(); i++) {
         Dev& d = ctx->devs[i];
@@ -861,10 +1002,7 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
             g_init_error = "device is not sm_100 (this library is built for B200 only)"; delete ctx; return H2B_E_NODEVICE;
         }
         d.sms = prop.multiProcessorCount;
-        if (const char* env = std::getenv("H2B_L2_FETCH")) {      // experiment knob: L2 fetch granularity hint (32 / 64 / 128 bytes)
-            int v = std::atoi(env);
-            if (v == 32 || v == 64 || v == 128) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)v);
-        }
+        if (ctx->tune.l2_fetch) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)ctx->tune.l2_fetch);   // experiment knob
         int prio_lo = 0, prio_hi = 0;
         cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
         if (cudaStreamCreateWithPriority(&d.stream, cudaStreamNonBlocking, prio_lo) != cudaSuccess ||
@@ -885,7 +1023,7 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
     // with peer access these copies ride NVLink / NVSwitch; without it the driver stages them through host memory.
     for (size_t i = 0; i < ids.size(); i++)
         for (size_t j = 0; j < ids.size(); j++) {
-            if (i == j) continue;
+            if (i == j || ids[i] == ids[j]) continue;      // (a device may be listed twice: two slots of streams / buffers on one GPU)
             int can = 0;
             if (cudaDeviceCanAccessPeer(&can, ids[i], ids[j]) == cudaSuccess && can) {
                 cudaSetDevice(ids[i]);
@@ -893,6 +1031,7 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
                 if (pe != cudaSuccess) cudaGetLastError();      // already enabled by the caller (torch, another context): fine
             }
         }
+    cudaGetLastError();                                    // a refused peer query must not surface in a later launch check
     cudaSetDevice(ctx->devs[0].id);
     *out = ctx;
     return H2B_OK;
@@ -901,6 +1040,13 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
 void h2b_destroy(h2b_ctx* ctx) {
     if (!ctx) return;
     for (auto& kv : ctx->bases) release_bases(ctx, kv.second);
+    if (ctx->peer.mailbox) {
+        cudaSetDevice(ctx->devs[0].id);
+        cudaStreamSynchronize(ctx->devs[0].stream);
+        for (void* q : ctx->peer.opened) cudaIpcCloseMemHandle(q);
+        cudaFree(ctx->peer.mailbox);
+        if (ctx->peer.status) cudaFreeHost(ctx->peer.status);
+    }
     for (Dev& d : ctx->devs) {
         cudaSetDevice(d.id);
         cudaStreamSynchronize(d.stream);
@@ -923,7 +1069,25 @@ void h2b_destroy(h2b_ctx* ctx) {
     delete ctx;
 }
 
-const char* h2b_last_error(const h2b_ctx* ctx) { return ctx ? ctx->err.c_str() : g_init_error.c_str(); }
+const char* h2b_last_error(const h2b_ctx* ctx) {
+    if (!ctx) return g_init_error.c_str();
+    // per-device host threads of a multi-GPU call may be writing ctx->err: hand out a per-thread copy taken under the lock
+    thread_local std::string copy;
+    { std::lock_guard<std::mutex> lk(ctx->err_mu); copy = ctx->err; }
+    return copy.c_str();
+}
+const char* h2b_last_notice(const h2b_ctx* ctx) {
+    if (!ctx) return "";
+    thread_local std::string copy;
+    { std::lock_guard<std::mutex> lk(ctx->err_mu); copy = ctx->status; }
+    return copy.c_str();
+}
+int h2b_set_option(h2b_ctx* ctx, const char* name, const char* value) {
+    if (!ctx || !name) return H2B_E_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!ctx->tune.set(name, value)) return ctx->fail(H2B_E_INVALID, std::string("set_option: unknown option ") + name);
+    return H2B_OK;
+}
 
 // ---- MSM -----------------------------------------------------------------------------------------
 int h2b_bases_register(h2b_ctx* ctx, const void* bases, size_t n, uint64_t* handle_out) {
@@ -979,7 +1143,7 @@ static int msm_batch_common(h2b_ctx* ctx, uint64_t handle, const void* const* co
         // one bucket set per column needs the precomputed-window layout on a single device; a 4 GiB cap on the bucket sets
         batched = n_cols > 1 && n > 0 && ctx->devs.size() == 1 && B.shard[0].pre && B.shard[0].count >= n &&
                   (size_t)n_cols * ((size_t)1 << (B.shard[0].pre_c - 1)) * sizeof(Xyzz) <= ((size_t)4 << 30) &&
-                  !std::getenv("H2B_MSM_NO_BATCH");
+                  !ctx->tune.msm_no_batch;
         if (batched) {
             std::vector<Xyzz> sums(n_cols);
             uint32_t c = 0;
@@ -1026,6 +1190,93 @@ int h2b_msm_windows(h2b_ctx* ctx, uint64_t handle, const void* scalars, int scal
     int rc = msm_run(ctx, it->second, scalars, scalars_on_device != 0, n, n_total, windows, c_out, windows_out);
     if (rc) return rc;
     std::memcpy(out_windows, windows, (size_t)*windows_out * sizeof(Xyzz));
+    return H2B_OK;
+}
+int h2b_bases_info(h2b_ctx* ctx, uint64_t handle, uint32_t* window_bits_out, uint64_t* device_bytes_out) {
+    if (!ctx) return H2B_E_INVALID;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->bases.find(handle);
+    if (it == ctx->bases.end()) return ctx->fail(H2B_E_INVALID, "bases_info: unknown handle");
+    uint32_t c = 0;
+    uint64_t bytes = 0;
+    for (const BasesShard& sh : it->second.shard) {
+        if (sh.count == 0) continue;
+        if (sh.owned) bytes += sh.count * 64;
+        if (sh.pre) { bytes += (uint64_t)sh.count * sh.pre_w * 64; c = sh.pre_c; }
+    }
+    if (window_bits_out) *window_bits_out = c;
+    if (device_bytes_out) *device_bytes_out = bytes;
+    return H2B_OK;
+}
+
+// ---- sharded MSM across processes: mailboxes over CUDA IPC / NVLink (msm.cuh 7) --------------------------------------
+int h2b_peer_export(h2b_ctx* ctx, void* handle64_out, void** local_ptr_out) {
+    if (!ctx || !handle64_out) return ctx ? ctx->fail(H2B_E_INVALID, "peer_export: null argument") : H2B_E_INVALID;
+    static_assert(sizeof(cudaIpcMemHandle_t) == H2B_PEER_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    PeerState& P = ctx->peer;
+    H2B_CK(cudaSetDevice(ctx->devs[0].id));
+    if (!P.mailbox) {
+        H2B_CK(cudaMalloc(&P.mailbox, msm_peer_mailbox_bytes()));
+        H2B_CK(cudaMemset(P.mailbox, 0, msm_peer_mailbox_bytes()));
+        H2B_CK(cudaMallocHost((void**)&P.status, 64));
+        H2B_CK(cudaDeviceSynchronize());
+    }
+    cudaIpcMemHandle_t h;
+    H2B_CK(cudaIpcGetMemHandle(&h, P.mailbox));
+    std::memcpy(handle64_out, &h, sizeof h);
+    if (local_ptr_out) *local_ptr_out = P.mailbox;
+    return H2B_OK;
+}
+int h2b_peer_attach(h2b_ctx* ctx, int rank, int world, const void* handles, void* const* local_ptrs) {
+    if (!ctx) return H2B_E_INVALID;
+    if (world < 1 || world > (int)MSM_PEER_MAX_RANKS || rank < 0 || rank >= world || (!handles && !local_ptrs && world > 1))
+        return ctx->fail(H2B_E_INVALID, "peer_attach: bad rank / world (at most 16 ranks) or no handles");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    PeerState& P = ctx->peer;
+    if (!P.mailbox) return ctx->fail(H2B_E_INVALID, "peer_attach: call h2b_peer_export first");
+    if (ctx->devs.size() != 1) return ctx->fail(H2B_E_INVALID, "peer_attach: one device per process (a multi-device context shards by itself)");
+    H2B_CK(cudaSetDevice(ctx->devs[0].id));
+    for (void* q : P.opened) cudaIpcCloseMemHandle(q);
+    P.opened.clear();
+    P.table = MsmPeerTable{};
+    for (int r = 0; r < world; r++) {
+        if (r == rank) { P.table.mailbox[r] = P.mailbox; continue; }
+        if (local_ptrs && local_ptrs[r]) {
+            // a peer context of this process: its pointer is used as it is; make sure this device may store to that one
+            cudaPointerAttributes at;
+            if (cudaPointerGetAttributes(&at, local_ptrs[r]) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != ctx->devs[0].id) {
+                int can = 0;
+                if (cudaDeviceCanAccessPeer(&can, ctx->devs[0].id, at.device) != cudaSuccess || !can)
+                    return ctx->fail(H2B_E_CUDA, "peer_attach: no peer access from device " + std::to_string(ctx->devs[0].id) + " to device " + std::to_string(at.device));
+                if (cudaDeviceEnablePeerAccess(at.device, 0) != cudaSuccess) cudaGetLastError();      // already enabled: fine
+            }
+            P.table.mailbox[r] = local_ptrs[r];
+            continue;
+        }
+        if (!handles) return ctx->fail(H2B_E_INVALID, "peer_attach: no handle for rank " + std::to_string(r));
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, reinterpret_cast<const uint8_t*>(handles) + (size_t)r * H2B_PEER_HANDLE_BYTES, sizeof h);
+        void* q = nullptr;
+        H2B_CK(cudaIpcOpenMemHandle(&q, h, cudaIpcMemLazyEnablePeerAccess));
+        P.opened.push_back(q);
+        P.table.mailbox[r] = q;
+    }
+    P.rank = rank; P.world = world; P.epoch = 0;
+    return H2B_OK;
+}
+int h2b_msm_sharded(h2b_ctx* ctx, uint64_t handle, const void* scalars, int scalars_on_device, size_t n, size_t n_total, void* out96) {
+    if (!ctx) return H2B_E_INVALID;
+    if (!out96 || (!scalars && n)) return ctx->fail(H2B_E_INVALID, "msm_sharded: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    auto it = ctx->bases.find(handle);
+    if (it == ctx->bases.end()) return ctx->fail(H2B_E_INVALID, "msm_sharded: unknown bases handle");
+    if (n == 0) return ctx->fail(H2B_E_INVALID, "msm_sharded: every rank needs a non-empty point range");
+    Xyzz windows[H2B_MSM_MAX_WINDOWS];
+    uint32_t c = 0, nw = 0;
+    int rc = msm_run(ctx, it->second, scalars, scalars_on_device != 0, n, n_total, windows, &c, &nw, true);
+    if (rc) return rc;
+    msm_finish(windows, nw, c, out96);
     return H2B_OK;
 }
 int h2b_msm_combine(const void* parts, uint32_t n_parts, uint32_t c, uint32_t windows, void* out96) {

@@ -89,7 +89,8 @@ extern "C" int hc_ntt(const void* in_, uint64_t in_len, void* out_, uint64_t out
     if (log_n == 0) { std::memcpy(out_, in_, 32); return 0; }
     Fr omega = ld<Fr>(omega_);
     Fr scale; if (scale_or_null) scale = ld<Fr>(scale_or_null);
-    NttPlan pl = ntt_make_plan(log_n, omega, scale_or_null ? &scale : nullptr);
+    // test shim only: the split override comes from the environment here (the library takes it from its context's knobs)
+    NttPlan pl = ntt_make_plan(log_n, omega, scale_or_null ? &scale : nullptr, std::getenv("H2B_NTT_SPLIT"));
     std::vector<Fr> tables(pl.total_elems);
     for (auto& seg : pl.segments) {
         Fr acc = seg.first;

@@ -88,6 +88,29 @@ H2B_HD Xyzz xyzz_mul_pow2(Xyzz p, uint32_t log2k) {
     return p;
 }
 
+// host: sum_t 2^(exps[t]) * terms[t] by one Horner pass over the distinct exponents (largest first).  The bucket reduction
+// leaves its last, strictly serial step -- ~20 dependent doublings and additions of single points -- to the host: a lone GPU
+// thread needs ~9 us per dependent point operation, the host ~0.5 us, and the terms travel with the result copy anyway.
+inline Xyzz msm_horner_terms(const Xyzz* terms, const uint32_t* exps, uint32_t n) {
+    uint32_t idx[64];
+    if (n > 64) n = 64;
+    for (uint32_t i = 0; i < n; i++) idx[i] = i;
+    for (uint32_t i = 1; i < n; i++) {                      // insertion sort by exponent, descending
+        uint32_t v = idx[i], j = i;
+        while (j > 0 && exps[idx[j - 1]] < exps[v]) { idx[j] = idx[j - 1]; j--; }
+        idx[j] = v;
+    }
+    Xyzz acc = Xyzz::identity();
+    uint32_t cur = n ? exps[idx[0]] : 0;
+    for (uint32_t i = 0; i < n; i++) {
+        const uint32_t e = exps[idx[i]];
+        for (; cur > e; cur--) acc = xyzz_double(acc);
+        acc = xyzz_add(acc, terms[idx[i]]);
+    }
+    for (; cur > 0; cur--) acc = xyzz_double(acc);
+    return acc;
+}
+
 // host: Horner over the window sums (most significant last), normalise, and write the result as the
 // reference's G1 Jacobian layout: (x, y, 1), or (0, 1, 0) for the identity.
 inline void msm_finish(const Xyzz* windows, uint32_t nw, uint32_t c, void* out96) {
@@ -113,6 +136,17 @@ struct MsmLongInfo { uint32_t key, task_base, ntasks, pad; };
 struct MsmLongTask { uint32_t key, chunk; };
 constexpr int MSM_REDUCE_THREADS = 128;
 constexpr int MSM_REDUCE_MAX_SLICES = 256;
+constexpr int MSM_MASKED_THREADS = 256;
+constexpr uint32_t MSM_MAX_TERMS = 64;           // terms one bucket set is reduced to on the device (<= 2 * 24 index bits + 1)
+// Peer exchange of the reduced terms between the ranks of a point-range sharded MSM (one process per GPU): every rank owns a
+// mailbox of 2 parities x MSM_PEER_MAX_RANKS slots; a slot holds up to MSM_PEER_SLOT_POINTS points, and one 64-bit epoch flag.
+constexpr uint32_t MSM_PEER_MAX_RANKS = 16;
+constexpr uint32_t MSM_PEER_SLOT_POINTS = 64;
+struct MsmPeerTable { void* mailbox[MSM_PEER_MAX_RANKS]; };
+H2B_HD constexpr size_t msm_peer_slot_bytes() { return (size_t)MSM_PEER_SLOT_POINTS * 128; }
+H2B_HD constexpr size_t msm_peer_flags_offset() { return 2 * (size_t)MSM_PEER_MAX_RANKS * msm_peer_slot_bytes(); }
+H2B_HD constexpr size_t msm_peer_tags_offset() { return msm_peer_flags_offset() + 2 * (size_t)MSM_PEER_MAX_RANKS * 8; }
+H2B_HD constexpr size_t msm_peer_mailbox_bytes() { return msm_peer_tags_offset() + 2 * (size_t)MSM_PEER_MAX_RANKS * 8; }
 
 #if defined(__CUDACC__) && !defined(H2B_NO_KERNELS)
 // ------------------------------------------------------------------------------------------------
@@ -462,71 +496,151 @@ msm_reduce_final_kernel(uint32_t slices, uint32_t log_block_buckets, const Xyzz*
 }
 // ---- 6b. low-latency reduction for large bucket sets (nb >= 2^14) ----------------------------------------------------
 // sum_i (i + 1) B_i with i = hi * W + lo (W = 2^w columns, H = 2^h rows):
-//     = 2^w * sum_hi hi * D_hi  +  sum_hi D_hi  +  sum_lo lo * C_lo,     D = row sums, C = column sums.
+//     = 2^w * sum_hi hi * D_hi  +  sum_lo lo * C_lo  +  sum_i B_i,        D = row sums, C = column sums.
 // Every step is a plain (unweighted) sum, so nothing is serial beyond log-depth trees:
-//   lines   grid ((H + W) / 4, sets): one warp per row / column: strided partial sums + a 5-step tree in shared memory
-//   masked  grid (h + w + 1, sets): S^D_b = sum of the D_hi whose index has bit b set (b < h), S^C_b likewise, and V = sum D_hi
-//   combine grid (sets), two warps: Horner over the bits, acc <- 2 acc + S_b  (h + w doublings and additions in total).
-// Same 2 additions per bucket as the running-sum kernel above, but a dependency depth of ~40 additions instead of ~100.
+//   lines   one warp per SEGMENT of a row / column (seg_len buckets, 2 additions per bucket in total): strided lane sums, then
+//           the four warps of a block fold their 4 x 32 lane sums through shared memory together (6 warp-steps per block
+//           instead of 5 per warp).  Row segments land at D[seg * H + hi], column segments at C[seg * W + lo].
+//   masked  grid (h + w + 1, sets): S^D_b = sum of the row partials whose hi has bit b set, S^C_b likewise over lo, V = sum D.
+//   host    sum_b 2^(b + w) S^D_b + sum_b 2^b S^C_b + V  (msm_horner_terms): ~20 dependent point operations, 0.02 ms on the
+//           host against 0.24 ms for a lone GPU thread.
 __global__ void __launch_bounds__(MSM_REDUCE_THREADS)
-msm_reduce_lines_kernel(const Xyzz* __restrict__ buckets, uint32_t nb, uint32_t w, uint32_t cs, Xyzz* __restrict__ lines) {
-    // one WARP per row / column (no block barrier: the four warps of a block are independent lines); a lane sums count/32
-    // strided elements, then a 5-step tree through the warp's slice of shared memory.
+msm_reduce_lines_kernel(const Xyzz* __restrict__ buckets, uint32_t nb, uint32_t w, uint32_t rs, uint32_t cs, Xyzz* __restrict__ lines) {
     __shared__ Xyzz sh[MSM_REDUCE_THREADS];
-    // lines[] layout per set: D_0..D_{H-1}, then cs column-sum segments of W entries each (segment g covers rows
-    // [g * H / cs, (g + 1) * H / cs)); cs is chosen by the host so that row and column jobs have the same length.
     const uint32_t W = 1u << w, H = nb >> w, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, set = blockIdx.y;
+    const uint32_t njobs = rs * H + cs * W;
     const uint32_t job = blockIdx.x * (MSM_REDUCE_THREADS / 32) + warp;
-    if (job >= H + cs * W) return;
     const Xyzz* b = buckets + (size_t)set * nb;
-    uint32_t start, stride, count;
-    if (job < H) { start = job * W; stride = 1; count = W; }           // row job: D_hi
-    else {                                                             // column job: a segment of C_lo
-        const uint32_t g = (job - H) >> w, lo = (job - H) & (W - 1u), rows = H / cs;
-        start = g * rows * W + lo; stride = W; count = rows;
-    }
     Xyzz acc = Xyzz::identity();
-    for (uint32_t i = lane; i < count; i += 32) acc = xyzz_add(acc, xyzz_load(b + start + (size_t)i * stride));
-    Xyzz* ws = sh + warp * 32;
-    ws[lane] = acc;
-    __syncwarp();
+    if (job < njobs) {
+        uint32_t start, stride, count;
+        if (job < rs * H) {                                                // segment `sg` of row hi
+            const uint32_t sg = job / H, hi = job - sg * H, len = W / rs;
+            start = hi * W + sg * len; stride = 1; count = len;
+        } else {                                                           // segment `sg` of column lo
+            const uint32_t j2 = job - rs * H, sg = j2 >> w, lo = j2 & (W - 1u), rows = H / cs;
+            start = sg * rows * W + lo; stride = W; count = rows;
+        }
+        for (uint32_t i = lane; i < count; i += 32) acc = xyzz_add(acc, xyzz_load(b + start + (size_t)i * stride));
+    }
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    // fold 4 lines x 32 lane sums: at step `st` thread t works on line t / st, lane t % st
+#pragma unroll 1
     for (uint32_t st = 16; st > 0; st >>= 1) {
-        if (lane < st) ws[lane] = xyzz_add(ws[lane], ws[lane + st]);
-        __syncwarp();
+        const uint32_t t = threadIdx.x;
+        Xyzz v;
+        const bool act = t < 4 * st;
+        const uint32_t pos = (t / st) * 32 + (t % st);
+        if (act) v = xyzz_add(sh[pos], sh[pos + st]);
+        __syncthreads();
+        if (act) sh[pos] = v;
+        __syncthreads();
     }
-    if (lane == 0) xyzz_store(lines + (size_t)set * (H + cs * W) + job, ws[0]);
+    if (threadIdx.x < 4) {
+        const uint32_t j = blockIdx.x * (MSM_REDUCE_THREADS / 32) + threadIdx.x;
+        if (j < njobs) xyzz_store(lines + (size_t)set * njobs + j, sh[threadIdx.x * 32]);
+    }
 }
-__global__ void __launch_bounds__(MSM_REDUCE_THREADS)
-msm_reduce_masked_kernel(const Xyzz* __restrict__ lines, uint32_t h, uint32_t w, uint32_t cs, Xyzz* __restrict__ terms) {
-    __shared__ Xyzz sh[MSM_REDUCE_THREADS];
+__global__ void __launch_bounds__(MSM_MASKED_THREADS)
+msm_reduce_masked_kernel(const Xyzz* __restrict__ lines, uint32_t h, uint32_t w, uint32_t rs, uint32_t cs, Xyzz* __restrict__ terms) {
+    __shared__ Xyzz sh[MSM_MASKED_THREADS];
     const uint32_t H = 1u << h, W = 1u << w, t = threadIdx.x, job = blockIdx.x, set = blockIdx.y;
-    const Xyzz* D = lines + (size_t)set * (H + cs * W);
-    const Xyzz* src = job < h ? D : (job < h + w ? D + H : D);
-    const uint32_t count = job < h ? H : (job < h + w ? cs * W : H);       // the cs column segments share their weights: i mod W
-    const uint32_t mask = job < h ? (1u << job) : (job < h + w ? (1u << (job - h)) : 0u);     // 0: plain sum (V)
+    const Xyzz* D = lines + (size_t)set * (rs * H + cs * W);
+    const bool cols = job >= h && job < h + w;
+    const Xyzz* src = cols ? D + (size_t)rs * H : D;
+    const uint32_t count = cols ? cs * W : rs * H;                    // segments of one line share its weight: index mod H (mod W)
+    const uint32_t mask = job < h ? (1u << job) : (cols ? (1u << (job - h)) : 0u);     // 0: plain sum (V)
     Xyzz acc = Xyzz::identity();
-    for (uint32_t i = t; i < count; i += MSM_REDUCE_THREADS)
+    for (uint32_t i = t; i < count; i += MSM_MASKED_THREADS)
         if (mask == 0 || (i & mask)) acc = xyzz_add(acc, xyzz_load(src + i));
     sh[t] = acc;
     __syncthreads();
-    block_tree_sum<MSM_REDUCE_THREADS>(sh, t);
+    block_tree_sum<MSM_MASKED_THREADS>(sh, t);
     if (t == 0) xyzz_store(terms + (size_t)set * (h + w + 1) + job, sh[0]);
 }
-__global__ void __launch_bounds__(64)
-msm_reduce_combine_kernel(const Xyzz* __restrict__ terms, uint32_t h, uint32_t w, Xyzz* __restrict__ set_sums) {
-    __shared__ Xyzz part;
-    const Xyzz* T = terms + (size_t)blockIdx.x * (h + w + 1);
-    Xyzz acc = Xyzz::identity();
-    if (threadIdx.x == 32) {            // warp 1: Y + V = sum_b 2^b S^C_b + V
-        for (uint32_t b = w; b-- > 0;) acc = xyzz_add(xyzz_double(acc), xyzz_load(T + h + b));
-        part = xyzz_add(acc, xyzz_load(T + h + w));
+
+// ---- 7. peer exchange (one process per GPU, MSM sharded by point range) ---------------------------------------------
+// ONE kernel publishes this rank's reduced terms into every peer's mailbox over NVLink (plain peer stores + a release flag),
+// waits for the same epoch from every peer, and folds the `world` contributions per term; the sums go straight into page-locked
+// host memory.  No NCCL call, no host staging: the exchange is the epilogue of the reduction on the compute stream.
+H2B_D void st_release_sys_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+H2B_D unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+H2B_D unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__global__ void __launch_bounds__(256)
+msm_peer_exchange_kernel(const Xyzz* __restrict__ my_terms, uint32_t n_terms, MsmPeerTable peers, uint32_t rank, uint32_t world,
+                         uint32_t parity, unsigned long long epoch, unsigned long long tag, unsigned long long timeout_ns,
+                         Xyzz* __restrict__ out_terms, uint32_t* __restrict__ status) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Xyzz* sh = reinterpret_cast<Xyzz*>(smem_raw);                      // [n_terms][world]
+    __shared__ uint32_t failed;
+    const uint32_t t = threadIdx.x, nt = blockDim.x;
+    if (t == 0) failed = 0;
+    // 1. publish: n_terms * 128 bytes into slot (parity, rank) of every mailbox, 16 bytes per store
+    const uint4* src = reinterpret_cast<const uint4*>(my_terms);
+    const uint32_t vec = n_terms * 8;
+    for (uint32_t r = 0; r < world; r++) {
+        uint4* dst = reinterpret_cast<uint4*>(static_cast<unsigned char*>(peers.mailbox[r]) +
+                                              ((size_t)parity * MSM_PEER_MAX_RANKS + rank) * msm_peer_slot_bytes());
+        for (uint32_t i = t; i < vec; i += nt) dst[i] = src[i];
+        if (t == 0)      // geometry tag (window bits, sets, terms): every rank must have reduced to the same weighted terms
+            (reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(peers.mailbox[r]) + msm_peer_tags_offset()))[parity * MSM_PEER_MAX_RANKS + rank] = tag;
     }
-    if (threadIdx.x == 0) {             // warp 0: 2^w * U, U = sum_b 2^b S^D_b
-        for (uint32_t b = h; b-- > 0;) acc = xyzz_add(xyzz_double(acc), xyzz_load(T + b));
-        acc = xyzz_mul_pow2(acc, w);
+    __threadfence_system();
+    __syncthreads();
+    if (t < world) {
+        unsigned long long* flag = reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(peers.mailbox[t]) +
+                                                                         msm_peer_flags_offset()) + parity * MSM_PEER_MAX_RANKS + rank;
+        st_release_sys_u64(flag, epoch);
+    }
+    // 2. wait for epoch from every peer (my own mailbox)
+    if (t < world) {
+        const unsigned long long* flag = reinterpret_cast<const unsigned long long*>(
+            static_cast<unsigned char*>(peers.mailbox[rank]) + msm_peer_flags_offset()) + parity * MSM_PEER_MAX_RANKS + t;
+        const unsigned long long t0 = global_timer_ns();
+        while (ld_acquire_sys_u64(flag) < epoch) {
+            if (global_timer_ns() - t0 > timeout_ns) { atomicExch(&failed, 1u + t); break; }
+            __nanosleep(200);
+        }
+        const unsigned long long* tags = reinterpret_cast<const unsigned long long*>(
+            static_cast<unsigned char*>(peers.mailbox[rank]) + msm_peer_tags_offset()) + parity * MSM_PEER_MAX_RANKS;
+        if (!failed && __ldcg(tags + t) != tag) atomicExch(&failed, 0x100u + t);
     }
     __syncthreads();
-    if (threadIdx.x == 0) xyzz_store(set_sums + blockIdx.x, xyzz_add(acc, part));
+    if (failed) { if (t == 0) *status = failed; return; }
+    // 3. fold over the ranks, per term (tree through shared memory)
+    const unsigned char* mine = static_cast<const unsigned char*>(peers.mailbox[rank]) + (size_t)parity * MSM_PEER_MAX_RANKS * msm_peer_slot_bytes();
+    for (uint32_t i = t; i < n_terms * world; i += nt) {
+        const uint32_t term = i / world, r = i - term * world;
+        // (L2 loads: the slots were written by other GPUs; nothing of them may be served from this SM's L1)
+        const uint4* q = reinterpret_cast<const uint4*>(reinterpret_cast<const Xyzz*>(mine + (size_t)r * msm_peer_slot_bytes()) + term);
+        uint4* o = reinterpret_cast<uint4*>(sh + i);
+#pragma unroll
+        for (int k = 0; k < 8; k++) o[k] = __ldcg(q + k);
+    }
+    __syncthreads();
+    uint32_t width = world;
+    while (width > 1) {
+        const uint32_t half = (width + 1) / 2;
+        for (uint32_t i = t; i < n_terms * (width / 2); i += nt) {
+            const uint32_t term = i / (width / 2), r = i - term * (width / 2);
+            sh[term * world + r] = xyzz_add(sh[term * world + r], sh[term * world + r + half]);
+        }
+        __syncthreads();
+        width = half;
+    }
+    for (uint32_t i = t; i < n_terms; i += nt) xyzz_store(out_terms + i, sh[i * world]);
+    if (t == 0) *status = 0;
 }
 
 // small-window fallback: nb < MSM_REDUCE_THREADS -> one thread per window does the whole running sum

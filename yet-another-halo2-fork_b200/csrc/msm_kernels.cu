@@ -81,7 +81,7 @@ const MsmKernelTable& msm_kernel_table() {
         msm_precompute_kernel, msm_size_hist_kernel, msm_size_scatter_kernel,
         {msm_accumulate_kernel<4, false>, msm_accumulate_kernel<4, true>, msm_accumulate_kernel<5, true>, msm_accumulate_kernel<6, true>},
         msm_long_list_kernel, msm_accumulate_long_kernel, msm_long_combine_kernel, msm_reduce_kernel, msm_reduce_final_kernel,
-        msm_reduce_small_kernel, msm_reduce_lines_kernel, msm_reduce_masked_kernel, msm_reduce_combine_kernel, imad_wide_peak_kernel, field_mul_peak_kernel, synth_bases_kernel};
+        msm_reduce_small_kernel, msm_reduce_lines_kernel, msm_reduce_masked_kernel, msm_peer_exchange_kernel, imad_wide_peak_kernel, field_mul_peak_kernel, synth_bases_kernel};
     return t;
 }
 }  // namespace h2b

@@ -22,9 +22,10 @@ struct MsmKernelTable {
     void (*reduce)(MsmGeom, const Xyzz*, uint32_t, uint32_t, Xyzz*, Xyzz*);
     void (*reduce_final)(uint32_t, uint32_t, const Xyzz*, const Xyzz*, Xyzz*);
     void (*reduce_small)(MsmGeom, const Xyzz*, Xyzz*);
-    void (*reduce_lines)(const Xyzz*, uint32_t, uint32_t, uint32_t, Xyzz*);
-    void (*reduce_masked)(const Xyzz*, uint32_t, uint32_t, uint32_t, Xyzz*);
-    void (*reduce_combine)(const Xyzz*, uint32_t, uint32_t, Xyzz*);
+    void (*reduce_lines)(const Xyzz*, uint32_t, uint32_t, uint32_t, uint32_t, Xyzz*);
+    void (*reduce_masked)(const Xyzz*, uint32_t, uint32_t, uint32_t, uint32_t, Xyzz*);
+    void (*peer_exchange)(const Xyzz*, uint32_t, MsmPeerTable, uint32_t, uint32_t, uint32_t, unsigned long long, unsigned long long,
+                          unsigned long long, Xyzz*, uint32_t*);
     void (*imad_wide_peak)(uint32_t, uint32_t, unsigned long long*);
     void (*field_mul_peak)(uint32_t, Fq*);
     void (*synth_bases)(Affine*, uint64_t, uint64_t);

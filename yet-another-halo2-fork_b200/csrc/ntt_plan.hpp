@@ -32,9 +32,9 @@ struct NttPlan {
 };
 
 // Pass split: every pass <= 2^9; column passes need >= 8 columns to the right (inner >= 8).
-// H2B_NTT_SPLIT="9,9,6" overrides (for tuning) when it sums to log_n.
-inline void ntt_choose_split(uint32_t log_n, int& n_pass, uint32_t log_s[4]) {
-    if (const char* env = std::getenv("H2B_NTT_SPLIT")) {
+// `split_override` = "9,9,6" overrides (for tuning; the context's ntt_split knob) when it sums to log_n.
+inline void ntt_choose_split(uint32_t log_n, int& n_pass, uint32_t log_s[4], const char* split_override = nullptr) {
+    if (const char* env = (split_override && *split_override) ? split_override : nullptr) {
         uint32_t v[4]; int m = 0; uint32_t sum = 0; const char* p = env;
         while (*p && m < 4) { v[m] = (uint32_t)std::strtoul(p, (char**)&p, 10); sum += v[m]; m++; if (*p == ',') p++; }
         bool ok = m >= 1 && sum == log_n;
@@ -53,10 +53,11 @@ inline void ntt_choose_split(uint32_t log_n, int& n_pass, uint32_t log_s[4]) {
 }
 
 // omega: primitive 2^log_n-th root (Montgomery); scale: optional multiplier folded into the transform.
-inline NttPlan ntt_make_plan(uint32_t log_n, const Fr& omega, const Fr* scale) {
+inline NttPlan ntt_make_plan(uint32_t log_n, const Fr& omega, const Fr* scale, const char* split_override = nullptr,
+                             uint32_t full_table_max_log = 26) {
     NttPlan pl;
     pl.log_n = log_n;
-    ntt_choose_split(log_n, pl.n_pass, pl.log_s);
+    ntt_choose_split(log_n, pl.n_pass, pl.log_s, split_override);
     pl.has_scale = scale != nullptr;
     size_t off = 0;
     for (int j = 0; j < pl.n_pass; j++) {
@@ -88,9 +89,8 @@ inline NttPlan ntt_make_plan(uint32_t log_n, const Fr& omega, const Fr* scale) {
     }
     pl.table_elems = off;
     // Full boundary tables (one multiplication saved per element per column pass) while they stay affordable:
-    // pass j needs N / outer_j entries.  H2B_NTT_FULL_TABLE_MAX_LOG (default 26) caps the largest one.
-    uint32_t cap = 26;
-    if (const char* env = std::getenv("H2B_NTT_FULL_TABLE_MAX_LOG")) cap = (uint32_t)std::atoi(env);
+    // pass j needs N / outer_j entries.  full_table_max_log (default 26) caps the largest one.
+    const uint32_t cap = full_table_max_log;
     uint32_t done = 0;
     for (int j = 0; j + 1 < pl.n_pass; j++) {
         uint32_t lg = log_n - done;

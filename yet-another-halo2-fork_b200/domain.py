@@ -135,12 +135,15 @@ class EvaluationDomain:
                                           _vp(self._m["g_coset"]), _vp(self._m["g_coset_inv"])))
         return out
 
-    def coeff_to_extended_batch(self, cols):
-        """The independent per-column coset NTTs of evaluate_h (plonk/evaluation.rs:344-361), one call."""
+    def coeff_to_extended_batch(self, cols, outs=None):
+        """The independent per-column coset NTTs of evaluate_h (plonk/evaluation.rs:344-361), one call.  `outs` = optional
+        preallocated (n * e, 4) uint64 arrays (one per column) to receive the evaluations."""
         cols = [np.ascontiguousarray(x, dtype=np.uint64) for x in cols]
         for x in cols:
             assert x.shape[0] == 1 << self.k
-        outs = [np.empty((self.extended_len(), 4), dtype=np.uint64) for _ in cols]
+        if outs is None:
+            outs = [np.empty((self.extended_len(), 4), dtype=np.uint64) for _ in cols]
+        assert len(outs) == len(cols) and all(o.shape == (self.extended_len(), 4) and o.dtype == np.uint64 and o.flags["C_CONTIGUOUS"] for o in outs)
         lib, c = self.ctx.lib, self.ctx
         inp = (ctypes.c_void_p * len(cols))(*[x.ctypes.data for x in cols])
         outp = (ctypes.c_void_p * len(cols))(*[x.ctypes.data for x in outs])
@@ -149,7 +152,7 @@ class EvaluationDomain:
                                                 _vp(self._m["g_coset_inv"])))
         return outs
 
-    def coeff_to_extended_many(self, cols):
+    def coeff_to_extended_many(self, cols, outs=None):
         """Device-resident columns, spread over the devices of the context (h2b_coeff_to_extended_batch_device)."""
         import torch
         cols = list(cols)
@@ -157,7 +160,8 @@ class EvaluationDomain:
             return []
         for x in cols:
             assert self._rows(x) == 1 << self.k, "coeff_to_extended: wrong length"
-        outs = [torch.empty((self.extended_len(), 4), dtype=x.dtype, device=x.device) for x in cols]
+        if outs is None:
+            outs = [torch.empty((self.extended_len(), 4), dtype=x.dtype, device=x.device) for x in cols]
         lib, c = self.ctx.lib, self.ctx
         inp = (ctypes.c_void_p * len(cols))(*[x.data_ptr() for x in cols])
         outp = (ctypes.c_void_p * len(cols))(*[x.data_ptr() for x in outs])

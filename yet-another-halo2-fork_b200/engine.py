@@ -74,6 +74,16 @@ class Context:
         self.check(self.lib.h2b_profile_read(self._ctx, buf, len(buf)))
         return json.loads(buf.value.decode())
 
+    def set_option(self, name: str, value=None):
+        """Tuning knob of this context (`h2b_set_option`); None restores the default.  The H2B_* environment is only read once,
+        when the context is created."""
+        v = None if value is None else str(value).encode()
+        self.check(self.lib.h2b_set_option(self._ctx, name.encode(), v))
+
+    def last_notice(self) -> str:
+        msg = self.lib.h2b_last_notice(self._ctx)
+        return msg.decode() if msg else ""
+
     def imad_peak(self):
         a, b = ctypes.c_double(), ctypes.c_double()
         self.check(self.lib.h2b_imad_peak(self._ctx, ctypes.byref(a), ctypes.byref(b)))
@@ -105,6 +115,12 @@ class BaseDescriptor:
             a, p, self.n = _host_ptr(bases, 8)
             ctx.check(ctx.lib.h2b_bases_register(ctx.handle, p, self.n, ctypes.byref(h)))
         self.handle = h.value
+
+    def info(self):
+        """(window bits of the precomputed multiples, 0 = none; device bytes the descriptor owns)"""
+        c, b = ctypes.c_uint32(), ctypes.c_uint64()
+        self.ctx.check(self.ctx.lib.h2b_bases_info(self.ctx.handle, self.handle, ctypes.byref(c), ctypes.byref(b)))
+        return c.value, b.value
 
     def release(self):
         if self.handle and self.ctx.handle:
@@ -224,6 +240,43 @@ class B200Engine:
                                                     out.ctypes.data_as(ctypes.c_void_p), ctypes.byref(c), ctypes.byref(w)))
         return out[: w.value].copy(), c.value
 
+    # --- the same sharding with the exchange inside the library, on the device (h2b_peer_* / h2b_msm_sharded)
+    def peer_export(self) -> bytes:
+        """Allocate this context's mailbox; returns its 64-byte CUDA IPC handle (self.peer_mailbox = the device pointer, which
+        peers living in the same process use instead)."""
+        handle = ctypes.create_string_buffer(_lib.PEER_HANDLE_BYTES)
+        ptr = ctypes.c_void_p()
+        self.ctx.check(self.ctx.lib.h2b_peer_export(self.ctx.handle, handle, ctypes.byref(ptr)))
+        self.peer_mailbox = ptr.value
+        return handle.raw
+
+    def peer_attach(self, rank: int, world: int, all_gather_bytes=None, local_peers=None):
+        """Join a group of `world` single-GPU contexts that shard MSMs by point range.  `all_gather_bytes(b)` must return the
+        list of every rank's 64-byte blob in rank order (torch.distributed plumbing: see `dist_all_gather_bytes`);
+        `local_peers` = {rank: B200Engine} for peers living in this process (each already `peer_export`ed)."""
+        blob = self.peer_export()
+        blobs = all_gather_bytes(blob) if all_gather_bytes is not None else [blob] * world
+        assert len(blobs) == world and all(len(b) == _lib.PEER_HANDLE_BYTES for b in blobs)
+        local = (ctypes.c_void_p * world)()
+        for r, peer_engine in (local_peers or {}).items():
+            local[r] = peer_engine.peer_mailbox
+        self.ctx.check(self.ctx.lib.h2b_peer_attach(self.ctx.handle, rank, world, b"".join(blobs), local))
+        self.peer_rank, self.peer_world = rank, world
+
+    def msm_sharded(self, coeffs, base: BaseDescriptor, n_total: int) -> np.ndarray:
+        """This rank's share of an n_total-point MSM; returns the WHOLE normalised result on every rank (h2b_msm_sharded)."""
+        out = np.zeros(12, dtype=np.uint64)
+        if _is_torch_cuda(coeffs):
+            n = coeffs.numel() * coeffs.element_size() // 32
+            ptr, on_dev = ctypes.c_void_p(coeffs.data_ptr()), 1
+        else:
+            a, ptr, n = _host_ptr(coeffs, 4)
+            on_dev = 0
+        self._check_len(n, base)
+        self.ctx.check(self.ctx.lib.h2b_msm_sharded(self.ctx.handle, base.handle, ptr, on_dev, n, n_total,
+                                                    out.ctypes.data_as(ctypes.c_void_p)))
+        return out
+
     @staticmethod
     def msm_combine(parts: np.ndarray, c: int) -> np.ndarray:
         """parts: (n_parts, windows, 16) uint64 -> normalised Jacobian."""
@@ -242,12 +295,23 @@ def shard_range(n: int, rank: int, world: int):
     return n * rank // world, n * (rank + 1) // world
 
 
-def window_bits(n_total: int) -> int:
-    """The window size every shard of an n_total-point MSM uses (mirrors msm_choose_c in csrc/h2b200.cu)."""
-    import os
-    env = os.environ.get("H2B_MSM_C")
-    if env and 4 <= int(env) <= 24:
-        return int(env)
+def dist_all_gather_bytes(blob: bytes, group=None):
+    """`all_gather_bytes` for B200Engine.peer_attach over torch.distributed (any backend): every rank's blob, in rank order."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+    mine = torch.frombuffer(bytearray(blob), dtype=torch.uint8).to(dev)
+    out = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine, group=group)
+    return [bytes(t.cpu().numpy().tobytes()) for t in out]
+
+
+def window_bits(n_total: int, msm_c: int = 0) -> int:
+    """The window size every shard of an n_total-point MSM uses (mirrors msm_choose_c in csrc/h2b200.cu; msm_c = the context's
+    `msm_c` knob when it is set)."""
+    if 4 <= msm_c <= 24:
+        return msm_c
     lg = max(n_total, 1).bit_length() - 1
     return min(16, max(4, lg - 4))
 
