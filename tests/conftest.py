@@ -3,6 +3,12 @@ import sys
 
 import pytest
 
+# Several tests run a handful of library contexts (3 streams each) side by side on ONE GPU, and the sharded-MSM test lets their
+# exchange kernels wait for each other.  With the default of 8 hardware queues, streams of different contexts alias one queue and
+# a waiting kernel can sit in front of the work it waits for; give every stream its own queue.  (Test set-up only: in production
+# every rank owns its GPU.  Must be set before the CUDA runtime initialises.)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
