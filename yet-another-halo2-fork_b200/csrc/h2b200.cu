@@ -473,16 +473,12 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
         slices = g.nb / MSM_REDUCE_THREADS;
         while (slices > (uint32_t)MSM_REDUCE_MAX_SLICES) { slices >>= 1; log_l++; }
     }
-    H2B_CK(d.m_wpart.reserve(((size_t)kw * slices * 2 + kw) * sizeof(Xyzz)));
-    Xyzz* buckets = d.m_buckets.as<Xyzz>();
-    Xyzz* wpart = d.m_wpart.as<Xyzz>();
-    MsmGeom gr = g;
-    gr.windows = kw;
-    Xyzz* block_p = wpart;
-    Xyzz* block_r = wpart + (size_t)kw * slices;
-    Xyzz* set_sums = wpart + (size_t)kw * slices * 2;
     uint32_t lg_nb = 0;
     while ((1u << (lg_nb + 1)) <= g.nb) lg_nb++;
+    Xyzz* buckets = d.m_buckets.as<Xyzz>();
+    Xyzz* set_sums = nullptr;
+    MsmGeom gr = g;
+    gr.windows = kw;
     const bool lines_path = g.nb >= (1u << 14) && !ctx->tune.msm_reduce_classic;
     info->n_terms = 1;
     info->exps[0] = 0;
@@ -492,8 +488,9 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
         const uint32_t seg = std::min<uint32_t>(W, (uint32_t)std::max(32, ctx->tune.msm_reduce_seg));   // buckets per line job
         const uint32_t rs = W / seg, cs = H / seg;
         const uint32_t nl = rs * H + cs * W, nt = h + w + 1;
+        // (ONE reservation per call: growing a buffer frees the old one, and cudaFree waits for the whole device)
         H2B_CK(d.m_wpart.reserve(((size_t)kw * nl + (size_t)kw * nt) * sizeof(Xyzz)));
-        wpart = d.m_wpart.as<Xyzz>();
+        Xyzz* wpart = d.m_wpart.as<Xyzz>();
         Xyzz* lines = wpart;
         Xyzz* terms = wpart + (size_t)kw * nl;
         set_sums = terms;
@@ -504,10 +501,17 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
         for (uint32_t b = 0; b < w; b++) info->exps[h + b] = b;          // S^C_b carries 2^b
         info->exps[h + w] = 0;                                           // V
     } else if (g.nb >= (uint32_t)MSM_REDUCE_THREADS) {
+        H2B_CK(d.m_wpart.reserve(((size_t)kw * slices * 2 + kw) * sizeof(Xyzz)));
+        Xyzz* wpart = d.m_wpart.as<Xyzz>();
+        Xyzz* block_p = wpart;
+        Xyzz* block_r = wpart + (size_t)kw * slices;
+        set_sums = wpart + (size_t)kw * slices * 2;
         dim3 grid(slices, kw, 1);
         H2B_LAUNCH(d, "msm_reduce", MK.reduce, grid, MSM_REDUCE_THREADS, 0, gr, buckets, slices, log_l, block_p, block_r);
         H2B_LAUNCH(d, "msm_reduce", MK.reduce_final, kw, MSM_REDUCE_MAX_SLICES, 0, slices, log_l + 7u, block_p, block_r, set_sums);
     } else {
+        H2B_CK(d.m_wpart.reserve((size_t)kw * sizeof(Xyzz)));
+        set_sums = d.m_wpart.as<Xyzz>();
         H2B_LAUNCH(d, "msm_reduce", MK.reduce_small, (kw + 31) / 32, 32, 0, gr, buckets, set_sums);
     }
     H2B_CK(cudaGetLastError());
@@ -1016,6 +1020,7 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
             g_init_error = "stream/event creation failed"; delete ctx; return H2B_E_CUDA;
         }
         d.launch_stream = d.stream;
+        if (d.reserve_pinned(64 << 10) != cudaSuccess) { g_init_error = "page-locked result buffer allocation failed"; delete ctx; return H2B_E_NOMEM; }
         int rc = ntt_prepare_device(ctx);
         if (rc) { g_init_error = ctx->err; delete ctx; return rc; }
     }
