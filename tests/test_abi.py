@@ -4,6 +4,7 @@ import ctypes
 import os
 import re
 import subprocess
+import sys
 
 import numpy as np
 import pytest
@@ -80,6 +81,19 @@ def test_no_product_path_through_the_oracle():
                 assert "h2ref" not in text and "import oracle" not in text and "from oracle" not in text, os.path.join(dirpath, f)
     ldd = subprocess.run(["ldd", h2b200.LIB_PATH], capture_output=True, text=True).stdout
     assert "h2ref" not in ldd
+
+
+def test_oracle_prover_is_independent():
+    """The converse: the prover oracle (and what it builds on) shares no code with the package -- its source never names the package,
+    and importing it in a fresh interpreter loads neither the package nor its CUDA library."""
+    for name in ("plonk_prover.py", "pyref.py"):
+        text = open(os.path.join(ROOT, "oracle", name)).read()
+        code = "\n".join(line for line in text.split("\n") if line.lstrip().startswith(("import ", "from ")))
+        assert "h2b200" not in code and "yet-another-halo2-fork_b200" not in code and "yet_another" not in code, name
+    probe = ("import sys; sys.path.insert(0, %r); from oracle import plonk_prover; "
+             "bad = [m for m in sys.modules if m.startswith('h2b200') or 'halo2' in m or m == 'torch' or m == 'numpy']; print(bad)" % ROOT)
+    out = subprocess.run([sys.executable, "-c", probe], capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.strip() == "[]", out.stdout + out.stderr
 
 
 @pytest.mark.skipif(h2b200.load().h2b_device_count() > 0, reason="GPU present")

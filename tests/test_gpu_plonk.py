@@ -1,7 +1,8 @@
-"""GPU parity of the whole proving pipeline: the prover mirror over DeviceOps (libh2b200.so: MSM, NTT, quotient, scans) must emit
-the same proof bytes as the same code over the python-int oracle ops, given the same RNG -- north_star's "byte-identical proof
-transcripts given a fixed blinding RNG", with the CPU restatement standing where the Rust binary cannot run -- and the proof must
-pass the verify_proof restatement."""
+"""GPU parity of the whole proving pipeline: the package's prover over DeviceOps (libh2b200.so: MSM, NTT, quotient, scans) must emit
+the same proof bytes as the INDEPENDENT prover oracle (oracle/plonk_prover.py: python ints, own keygen / transcript / RNG /
+multi-open, no code shared with the package) given the same RNG -- north_star's "byte-identical proof transcripts given a fixed
+blinding RNG", with the CPU restatement standing where the Rust binary cannot run -- and the proof must pass the verify_proof
+restatement."""
 import numpy as np
 import pytest
 
@@ -12,6 +13,7 @@ from h2b200.plonk.ops import DeviceOps
 from oracle import cref as C
 from oracle import plonk_ops, plonk_verifier
 from oracle import pyref as R
+import _plain_circuit as PC
 
 pytestmark = pytest.mark.gpu
 SECRET = 0x1234567
@@ -36,21 +38,44 @@ def _prove(circ, ops, pk, rng, num_threads=4):
     return tr.finalize()
 
 
-@pytest.mark.parametrize("k", [6, 8])
-def test_proof_bytes_match_the_cpu_restatement(ctx, k):
+def _prove_with(circuits, ops, pk, rng_spec, threads, multiopen="shplonk"):
+    tr = plonk.Blake2bWrite()
+    if isinstance(circuits, (list, tuple)):
+        plonk.create_proof_batch(ops, pk, [c.instances() for c in circuits], [c.witness for c in circuits], PC.package_rng(rng_spec),
+                                 tr, num_threads=threads, multiopen=multiopen)
+    else:
+        plonk.create_proof(ops, pk, circuits.instances(), circuits.witness, PC.package_rng(rng_spec), tr, num_threads=threads,
+                           multiopen=multiopen)
+    return tr.finalize()
+
+
+@pytest.mark.parametrize("name,k", [("StandardPlonk", 5), ("MyCircuit", 6), ("MyCircuit", 8)])
+def test_proof_bytes_match_the_cpu_restatement(ctx, name, k):
+    """k = 5, 6, 8; SHPLONK and GWC; OneNg and ChaCha20; two thread counts each (the vanishing argument's per-thread seeds,
+    vanishing/prover.rs:48-77): the device proof equals the independent oracle's, key material included."""
+    circ = example.MyCircuit(k, 42) if name == "MyCircuit" else example.StandardPlonk(k, 7, 5)
+    cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circ)
+    keys = PC.oracle_keys(circ, k, SECRET)
+    assert keys.fixed_commitments == vk.fixed_commitments and keys.permutation_commitments == vk.permutation_commitments
+    assert keys.transcript_repr == vk.transcript_repr
+    before = ctx.launch_count()
+    for rng_spec, threads, multiopen in (("OneNg", 4, "shplonk"), (PC.SEED_0_31, 3, "shplonk"), (PC.SEED_0_31, 4, "gwc"),
+                                         ("OneNg", 3, "gwc")):
+        proof = _prove_with(circ, ops, pk, rng_spec, threads, multiopen)
+        assert proof == PC.oracle_proof(keys, circ, rng_spec, threads, multiopen), \
+            f"GPU proof differs from the independent CPU restatement ({rng_spec[:8]}, {threads} threads, {multiopen})"
+        assert plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << k, multiopen=multiopen)
+    assert ctx.launch_count() > before
+
+
+def test_proof_bytes_match_the_package_prover_over_cpu_ops(ctx):
+    """The same host code over the python-int ops (oracle/plonk_ops.py): isolates a device-op difference from a host-logic one."""
+    k = 6
     circ = example.MyCircuit(k, 42)
     cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circ)
     ref_ops = plonk_ops.RefOps(k, SECRET, ref_dom)
-    ref_vk = plonk.keygen_vk(ref_ops, cc)
-    assert ref_vk.fixed_commitments == vk.fixed_commitments and ref_vk.permutation_commitments == vk.permutation_commitments
-    assert ref_vk.transcript_repr == vk.transcript_repr
-    ref_pk = plonk.keygen_pk(ref_ops, ref_vk, cc)
-    before = ctx.launch_count()
-    for make_rng, threads in ((RNG.OneNg, 4), (lambda: RNG.ChaCha20Rng(bytes(range(32))), 3)):
-        proof = _prove(circ, ops, pk, make_rng(), threads)
-        assert proof == _prove(circ, ref_ops, ref_pk, make_rng(), threads), "GPU proof differs from the CPU restatement"
-        assert plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << k)
-    assert ctx.launch_count() > before
+    ref_pk = plonk.keygen_pk(ref_ops, plonk.keygen_vk(ref_ops, cc), cc)
+    assert _prove(circ, ops, pk, RNG.OneNg(), 4) == _prove(circ, ref_ops, ref_pk, RNG.OneNg(), 4)
 
 
 def test_proof_verifies_k12(ctx):
@@ -129,10 +154,10 @@ def test_standard_plonk_bytes_match(ctx, minimum_degree):
     k = 6
     circ = example.StandardPlonk(k, 9, minimum_degree)
     cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circ)
-    ref_ops = plonk_ops.RefOps(k, SECRET, ref_dom)
-    ref_pk = plonk.keygen_pk(ref_ops, plonk.keygen_vk(ref_ops, cc), cc)
-    proof = _prove(circ, ops, pk, RNG.ChaCha20Rng(bytes(range(32))), 5)
-    assert proof == _prove(circ, ref_ops, ref_pk, RNG.ChaCha20Rng(bytes(range(32))), 5)
+    keys = PC.oracle_keys(circ, k, SECRET)
+    assert keys.transcript_repr == vk.transcript_repr
+    proof = _prove_with(circ, ops, pk, PC.SEED_0_31, 5)
+    assert proof == PC.oracle_proof(keys, circ, PC.SEED_0_31, 5)
     assert plonk_verifier.verify_proof(vk, [], proof, SECRET, 1 << k)
 
 
@@ -146,19 +171,14 @@ def test_standard_plonk_k12(ctx):
 
 
 def test_gwc_bytes_match(ctx):
-    """The GWC opening (multiopen/gwc/prover.rs) on the device == the CPU restatement; accepted by the VerifierGWC restatement."""
+    """The GWC opening (multiopen/gwc/prover.rs) on the device == the independent oracle; accepted by the VerifierGWC restatement."""
     k = 6
     circ = example.MyCircuit(k, 42)
     cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circ)
-    ref_ops = plonk_ops.RefOps(k, SECRET, ref_dom)
-    ref_pk = plonk.keygen_pk(ref_ops, plonk.keygen_vk(ref_ops, cc), cc)
-    proofs = []
-    for o, key in ((ops, pk), (ref_ops, ref_pk)):
-        tr = plonk.Blake2bWrite()
-        plonk.create_proof(o, key, circ.instances(), circ.witness, RNG.OneNg(), tr, num_threads=4, multiopen="gwc")
-        proofs.append(tr.finalize())
-    assert proofs[0] == proofs[1]
-    assert plonk_verifier.verify_proof(vk, circ.instances(), proofs[0], SECRET, 1 << k, multiopen="gwc")
+    keys = PC.oracle_keys(circ, k, SECRET)
+    proof = _prove_with(circ, ops, pk, "OneNg", 4, "gwc")
+    assert proof == PC.oracle_proof(keys, circ, "OneNg", 4, "gwc")
+    assert plonk_verifier.verify_proof(vk, circ.instances(), proof, SECRET, 1 << k, multiopen="gwc")
 
 
 def test_new_entry_points_reject_bad_arguments(ctx):
@@ -283,17 +303,13 @@ def test_multi_device_proof_matches_single_device():
 
 def test_batch_proving_bytes_match(ctx):
     """Two circuit instances in one transcript (`Prover`, prover.rs:130-175): evaluate_h chains the second circuit's custom-gate
-    Horner through PreviousValue on the device (evaluation.rs:366-395); bytes equal the CPU restatement, verifier accepts."""
+    Horner through PreviousValue on the device (evaluation.rs:366-395); bytes equal the independent oracle's, verifier accepts."""
     k = 6
     circuits = [example.MyCircuit(k, 42), example.MyCircuit(k, 77)]
     cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circuits[0])
-    ref_ops = plonk_ops.RefOps(k, SECRET, ref_dom)
-    ref_pk = plonk.keygen_pk(ref_ops, plonk.keygen_vk(ref_ops, cc), cc)
+    keys = PC.oracle_keys(circuits[0], k, SECRET)
     instances = [c.instances() for c in circuits]
-    proofs = []
-    for o, key in ((ops, pk), (ref_ops, ref_pk)):
-        tr = plonk.Blake2bWrite()
-        plonk.create_proof_batch(o, key, instances, [c.witness for c in circuits], RNG.OneNg(), tr, num_threads=4)
-        proofs.append(tr.finalize())
-    assert proofs[0] == proofs[1]
-    assert plonk_verifier.verify_proof_batch(vk, instances, proofs[0], SECRET, 1 << k)
+    for rng_spec, threads in (("OneNg", 4), (PC.SEED_0_31, 6)):
+        proof = _prove_with(circuits, ops, pk, rng_spec, threads)
+        assert proof == PC.oracle_proof(keys, circuits, rng_spec, threads)
+        assert plonk_verifier.verify_proof_batch(vk, instances, proof, SECRET, 1 << k)

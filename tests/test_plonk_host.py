@@ -255,10 +255,7 @@ def test_gwc_multiopen(setup):
         pass
 
 
-def test_golden_proofs_regenerate():
-    """tests/golden/proofs.json is what make_golden_proofs.py produces today (the CPU restatement has not drifted), and the
-    restated verifier accepts every stored proof."""
-    import hashlib
+def _golden():
     import importlib.util
     import json
     import os
@@ -266,12 +263,44 @@ def test_golden_proofs_regenerate():
     spec = importlib.util.spec_from_file_location("make_golden_proofs", os.path.join(here, "golden", "make_golden_proofs.py"))
     gen = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(gen)
-    gold = json.load(open(os.path.join(here, "golden", "proofs.json")))
+    return gen, json.load(open(os.path.join(here, "golden", "proofs.json")))
+
+
+def test_golden_proofs_regenerate():
+    """tests/golden/proofs.json is what the independent prover oracle (oracle/plonk_prover.py) writes today, the package's prover
+    over the python-int ops reproduces every stored proof byte for byte (two implementations of prover.rs that share no code), and
+    the restated verifier accepts the stored bytes."""
+    gen, gold = _golden()
+    assert [c["name"] for c in gold["proofs"]] == [c["name"] for c in gen.CASES]
     for case in gold["proofs"]:
+        if case["k"] <= 6:                        # the oracle at k = 8 takes several seconds per proof: checked on the GPU leg
+            proof, keys, _ = gen.oracle_prove(case)
+            assert proof.hex() == case["proof"] and hex(keys.transcript_repr) == case["transcript_repr"], case["name"]
         proof, vk, circ = gen.prove(case, lambda k, cs: plonk_ops.RefOps(k, SECRET, R.EvaluationDomain(cs.degree(), k)))
         assert proof.hex() == case["proof"] and hashlib.sha256(proof).hexdigest() == case["sha256"], case["name"]
+        assert hex(vk.transcript_repr) == case["transcript_repr"]
         assert plonk_verifier.verify_proof(vk, circ.instances(), bytes.fromhex(case["proof"]), SECRET, 1 << case["k"],
                                            multiopen=case["multiopen"])
+
+
+def test_pinned_vk_string_matches_the_oracle(setup):
+    """`format!("{:?}", vk.pinned())` as the package writes it (plonk/pinned.py) == the oracle's Debug model, whose structure is
+    pinned by the reference's own golden text (tests/test_oracle_prover.py); and keygen_vk takes a value from a Rust run verbatim."""
+    import _plain_circuit as PC
+    from h2b200.plonk import pinned
+    from oracle import plonk_prover as PP
+    circ, ops, vk, _ = setup
+    keys = PC.oracle_keys(circ, K, SECRET)
+    text = PP.render(PP.pinned_vk_node(keys.cs, keys.domain, keys.fixed_commitments, keys.permutation_commitments))
+    assert pinned.verification_key(vk) == text
+    assert text.startswith('PinnedVerificationKey { base_modulus: "0x30644e72e131a029b85045b68181585d97816a916871ca8d3c208c16d87cfd47", '
+                           'scalar_modulus: "0x30644e72e131a029b85045b68181585d2833e84879b9709143e1f593f0000001", '
+                           'domain: PinnedEvaluationDomain { k: 6, extended_k: 9, omega: 0x')
+    assert "num_challenges: 1, advice_column_phase: [0, 0, 0, 1], challenge_phase: [0], gates: [Product(Var(Query(QueryBack {" in text
+    assert "Var(Challenge(ChallengeMid { index: 0, phase: 0 }))" in text and 'shuffles: [Argument { name: "shuffle.0", ' in text
+    assert text.endswith("] } }") and "minimum_degree: None }, fixed_commitments: [(0x" in text
+    assert vk.transcript_repr == keys.transcript_repr
+    assert plonk.keygen_vk(ops, circ.compile(), transcript_repr=12345).transcript_repr == 12345
 
 
 @pytest.mark.parametrize("fmt", ["Processed", "RawBytes", "RawBytesUnchecked"])

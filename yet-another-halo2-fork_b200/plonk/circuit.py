@@ -218,12 +218,3 @@ class ConstraintSystemBack:
 
     def phases(self) -> List[int]:                            # plonk/circuit.rs:181-189
         return list(range(max(self.advice_column_phase, default=0) + 1))
-
-    def pinned_repr(self) -> str:
-        """Stand-in for `format!("{:?}", vk.pinned())` (plonk.rs:189-200): the Rust Debug string cannot be restated without the
-        halo2curves formatters, so this is a deterministic description of the same fields in the same order -- PARITY UNPINNED."""
-        return repr(("PinnedConstraintSystem", self.num_fixed_columns, self.num_advice_columns, self.num_instance_columns,
-                     self.num_challenges, self.advice_column_phase, self.challenge_phase, [g[1] for g in self.gates],
-                     self.advice_queries, self.instance_queries, self.fixed_queries, self.permutation_columns,
-                     [(l.input_expressions, l.table_expressions) for l in self.lookups],
-                     [(s.input_expressions, s.shuffle_expressions) for s in self.shuffles], self.minimum_degree))

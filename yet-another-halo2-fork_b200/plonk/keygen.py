@@ -15,6 +15,7 @@ import numpy as np
 from .. import fields as F
 from ..evaluation import ADVICE, BETA, CONSTANT, GAMMA, PREVIOUS, THETA, Y, GraphEvaluator
 from . import circuit as C
+from . import pinned
 from . import polyexpr as PX
 from .transcript import fr_from_uniform_bytes
 
@@ -146,20 +147,19 @@ def _fixed_column(ops, col):
 
 
 def _transcript_repr(vk: VerifyingKey) -> int:
-    """plonk.rs:170-203: BLAKE2b-512, personal "Halo2-Verify-Key", over len || `{:?}` of the pinned key.  The Debug string of the
-    reference cannot be reproduced without Rust, so a deterministic description of the same fields stands in for it:
-    PARITY UNPINNED, and callers holding the reference's value can overwrite `vk.transcript_repr`."""
-    d = vk.domain
-    s = repr(("PinnedVerificationKey", hex(F.Q_MOD), hex(F.R_MOD), (d.k, d.extended_k, hex(d.omega)), vk.cs.pinned_repr(),
-              vk.fixed_commitments, vk.permutation_commitments)).encode()
+    """plonk.rs:189-203: BLAKE2b-512, personal "Halo2-Verify-Key", over len(s) as u64 LE || s, s = `{:?}` of the pinned key
+    (pinned.py; the field / point formatting inside it is recalled from halo2curves, see there)."""
+    s = pinned.verification_key(vk).encode()
     h = hashlib.blake2b(digest_size=64, person=b"Halo2-Verify-Key")
     h.update(len(s).to_bytes(8, "little"))
     h.update(s)
     return fr_from_uniform_bytes(h.digest())
 
 
-def keygen_vk(ops, circuit: C.CompiledCircuit) -> VerifyingKey:
-    """keygen.rs:43-100.  `ops` is bound to a domain of the right k; the quotient degree is re-derived from the circuit."""
+def keygen_vk(ops, circuit: C.CompiledCircuit, transcript_repr: Optional[int] = None) -> VerifyingKey:
+    """keygen.rs:43-100.  `ops` is bound to a domain of the right k; the quotient degree is re-derived from the circuit.
+    `transcript_repr`: the value `VerifyingKey::transcript_repr()` returned in a Rust run of the same circuit, used verbatim instead
+    of the restated hash (the escape hatch while halo2curves' formatters cannot be checked here)."""
     cs = C.ConstraintSystemBack(circuit.cs)
     n = ops.n
     if n < cs.minimum_rows():
@@ -170,7 +170,7 @@ def keygen_vk(ops, circuit: C.CompiledCircuit) -> VerifyingKey:
     permutation_commitments = [ops.commit_lagrange(p) for p in sigma]
     fixed_commitments = [ops.commit_lagrange(_fixed_column(ops, col)) for col in circuit.preprocessing.fixed]
     vk = VerifyingKey(ops.domain, fixed_commitments, permutation_commitments, cs, cs.degree())
-    vk.transcript_repr = _transcript_repr(vk)
+    vk.transcript_repr = _transcript_repr(vk) if transcript_repr is None else transcript_repr % F.R_MOD
     return vk
 
 
