@@ -91,6 +91,45 @@ def test_streamed_scalar_chunks(engine, chunks, precompute, knob):
     desc.release()
 
 
+@pytest.mark.parametrize("msm_sort", [0, 1])
+@pytest.mark.parametrize("shape", ["classic_c13", "pre_c16", "pre_c20_512_bins", "pre_c22_lb12", "skewed", "chunked"])
+def test_binning_variants(engine, knob, msm_sort, shape):
+    """The two binning pipelines -- global-atomic count + scatter (H2B_MSM_SORT=0) and the tiled two-level one over shared-memory
+    atomics (msm_bin.cuh, the default) -- give the oracle's point for every key geometry: several windows' bucket sets side by
+    side (classic), one shared set with 2^15 ... 2^21 keys (1 ... 512 coarse bins of 2^10 ... 2^12 keys), skewed digits (one
+    coarse bin takes almost everything), and a streamed MSM whose chunks add into the same buckets."""
+    knob("msm_sort", msm_sort)
+    n, seed = 20000, 77
+    registered = True
+    if shape == "classic_c13":
+        knob("msm_c", 13); registered = False
+    elif shape == "pre_c16":
+        knob("msm_pre_c", 16); n = 1 << 16
+    elif shape == "pre_c20_512_bins":
+        knob("msm_pre_c", 20); n = (1 << 17) + 11
+    elif shape == "pre_c22_lb12":
+        knob("msm_pre_c", 22); n = 5000
+    elif shape == "chunked":
+        knob("msm_pre_c", 12); knob("msm_chunks", 3); n = 50001
+    s = C.random_fr(n, seed)
+    if shape == "skewed":
+        knob("msm_pre_c", 18)
+        rng = np.random.default_rng(5)
+        sel = rng.random(n)
+        s[sel < 0.5] = C.mont_from_int(1, R.R_MOD)
+        s[(sel >= 0.5) & (sel < 0.8)] = 0
+        s[(sel >= 0.8) & (sel < 0.9)] = C.mont_from_int(R.R_MOD - 1, R.R_MOD)
+    b = C.gen_bases(n, 4)
+    exp = oracle_affine(s, b)
+    if registered:
+        desc = engine.get_base_descriptor(b)
+        check(engine.msm_with_cached_base(s, desc), exp)
+        check(engine.msm_with_cached_base(s[: n // 3], desc), oracle_affine(s[: n // 3], b[: n // 3]))
+        desc.release()
+    else:
+        check(engine.msm(s, b), exp)
+
+
 def test_edge_scalars_and_bases(engine):
     n = 600
     s = C.random_fr(n, 5)

@@ -21,6 +21,7 @@
 #define H2B_NO_KERNELS 1      // kernels live in msm_kernels.cu / ntt_kernels_*.cu; this unit is host orchestration only
 #include "msm.cuh"
 #include "msm_kernels.hpp"
+#include "msm_bin.cuh"
 #include "poly_kernels.hpp"
 #include "quotient_kernels.hpp"
 #include "setup_kernels.hpp"
@@ -64,10 +65,12 @@ struct NttPlanDev {
 // on the sort stream (memory / atomic bound) while chunk k is accumulated on the compute stream (multiplier bound).
 struct MsmSortSet {
     DevBuf counts, offsets, ends, entries, order, blocksums, sizehist, long_info, long_tasks, counters;
+    DevBuf rec_key, rec_val, coarse;        // two-level binning (msm_bin.cuh): grouped records, coarse-bin totals / cursors / starts
     cudaEvent_t sorted = nullptr, consumed = nullptr;
     bool consumed_pending = false;
     void release() {
-        DevBuf* bufs[] = {&counts, &offsets, &ends, &entries, &order, &blocksums, &sizehist, &long_info, &long_tasks, &counters};
+        DevBuf* bufs[] = {&counts, &offsets, &ends, &entries, &order, &blocksums, &sizehist, &long_info, &long_tasks, &counters,
+                          &rec_key, &rec_val, &coarse};
         for (DevBuf* b : bufs) b->release();
         if (sorted) cudaEventDestroy(sorted);
         if (consumed) cudaEventDestroy(consumed);
@@ -147,7 +150,7 @@ struct Tuning {
     int msm_reduce_classic = 0;    // H2B_MSM_REDUCE_CLASSIC 1: running-sum reduction for every bucket-set size
     int msm_acc_variant = H2B_ACC_DEFAULT_VARIANT;   // H2B_ACC_VARIANT
     int msm_reduce_seg = 256;      // H2B_MSM_REDUCE_SEG buckets per row / column segment job of the lines reduction
-    int msm_sort = 1;              // H2B_MSM_SORT       1: tiled two-level binning, 0: global-atomic count + scatter
+    int msm_sort = 0;              // H2B_MSM_SORT       0: global-atomic count + scatter (faster, see msm_bin.cuh), 1: tiled two-level binning
     int ntt_full_table_max_log = 26;   // H2B_NTT_FULL_TABLE_MAX_LOG
     std::string ntt_split;         // H2B_NTT_SPLIT      e.g. "9,9,6"
     int l2_fetch = 0;              // H2B_L2_FETCH       cudaLimitMaxL2FetchGranularity hint (experiments)
@@ -398,6 +401,11 @@ int msm_sort_reserve(h2b_ctx* ctx, MsmSortSet& S, const MsmChunkPlan& pl) {
     H2B_CK(S.long_info.reserve((size_t)pl.max_long * sizeof(MsmLongInfo)));
     H2B_CK(S.long_tasks.reserve((size_t)pl.max_tasks * sizeof(MsmLongTask)));
     H2B_CK(S.counters.reserve(256));
+    if (ctx->tune.msm_sort && msm_bin_supported(nkeys)) {
+        H2B_CK(S.rec_key.reserve(std::max<size_t>((size_t)max_entries * 2, 256)));
+        H2B_CK(S.rec_val.reserve(std::max<size_t>((size_t)max_entries * 4, 256)));
+        H2B_CK(S.coarse.reserve((size_t)(2 * MSM_BIN_MAX_COARSE + 8) * 4));
+    }
     return H2B_OK;
 }
 int msm_stage_sort(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, const Fr* scalars) {
@@ -416,17 +424,44 @@ int msm_stage_sort(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, 
 
     d.launch_stream = d.sort_stream;
     cudaStream_t st = d.sort_stream;
-    cudaError_t e1 = cudaMemsetAsync(counts, 0, (size_t)nkeys * 4, st);
+    const bool tiled = ctx->tune.msm_sort && msm_bin_supported(nkeys);
+    cudaError_t e1 = tiled ? cudaSuccess : cudaMemsetAsync(counts, 0, (size_t)nkeys * 4, st);
     cudaError_t e2 = cudaMemsetAsync(sizehist, 0, (size_t)MSM_SIZE_BINS * 4, st);
     cudaError_t e3 = cudaMemsetAsync(counters, 0, 256, st);
     if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) { d.launch_stream = d.stream; H2B_CK(e1); H2B_CK(e2); H2B_CK(e3); }
     const uint32_t tb = 256;
-    if (n) H2B_LAUNCH(d, "msm_count", MK.count, (n + tb - 1) / tb, tb, 0, g, scalars, counts);
-    H2B_LAUNCH(d, "msm_scan", MK.scan_block_sums, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums);
-    H2B_LAUNCH(d, "msm_scan", MK.scan_single_block, 1, SCAN_BLOCK, 0, blocksums, nblk, (uint32_t*)nullptr);
-    H2B_LAUNCH(d, "msm_scan", MK.scan_apply, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums, offsets, ends);
-    if (n) H2B_LAUNCH(d, "msm_scatter", MK.scatter, (n + tb - 1) / tb, tb, 0, g, scalars, ends, entries);
-    H2B_LAUNCH(d, "msm_order", MK.size_hist, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist);
+    if (tiled) {
+        // two-level binning, shared-memory atomics only (msm_bin.cuh): digits + coarse totals, scan of the totals, partition into
+        // coarse bins, one block per coarse bin for offsets / ends / placement / population histogram
+        static const MsmBinKernelTable& BK = msm_bin_kernel_table();
+        static const int prepared = BK.prepare();
+        if (prepared != 0) { d.launch_stream = d.stream; return ctx->fail(H2B_E_CUDA, "msm: cannot reserve the shared memory of the binning kernel"); }
+        const uint32_t lb = msm_bin_low_bits(nkeys), ncoarse = (nkeys + (1u << lb) - 1u) >> lb;
+        uint32_t* cursor = S.coarse.as<uint32_t>();                       // [0, ncoarse]: totals -> exclusive scan -> run cursors
+        uint32_t* start = cursor + MSM_BIN_MAX_COARSE + 4;                // [0, ncoarse]: the scan, kept; start[ncoarse] = total
+        uint32_t* digits = entries;                                        // the digit words are dead once partitioned
+        cudaError_t e4 = cudaMemsetAsync(cursor, 0, (size_t)(2 * MSM_BIN_MAX_COARSE + 8) * 4, st);
+        if (e4 != cudaSuccess) { d.launch_stream = d.stream; H2B_CK(e4); }
+        const uint32_t tiles = (n + MSM_BIN_TILE - 1) / MSM_BIN_TILE;
+        if (n) H2B_LAUNCH(d, "msm_count", BK.digits, tiles, MSM_BIN_THREADS, 0, g, scalars, digits, cursor, lb, ncoarse);
+        H2B_LAUNCH(d, "msm_scan", MK.scan_single_block, 1, SCAN_BLOCK, 0, cursor, ncoarse, start + ncoarse);
+        cudaError_t e5 = cudaMemcpyAsync(start, cursor, (size_t)ncoarse * 4, cudaMemcpyDeviceToDevice, st);
+        if (e5 != cudaSuccess) { d.launch_stream = d.stream; H2B_CK(e5); }
+        const uint32_t ptile = msm_part_tile(g.windows);
+        if (n) H2B_LAUNCH(d, "msm_scatter", BK.partition, (n + ptile - 1) / ptile, MSM_PART_THREADS, msm_part_smem(), g,
+                          (const uint32_t*)digits, cursor, S.rec_key.as<unsigned short>(), S.rec_val.as<uint32_t>(), lb, ncoarse, ptile);
+        const uint32_t slices = msm_bin_slices(lb, max_entries, ncoarse), cap = msm_bin_cap(lb);
+        H2B_LAUNCH(d, "msm_scatter", BK.bin, ncoarse * slices, MSM_PART_THREADS, MSM_BIN_SMEM_BUDGET, (const uint32_t*)start,
+                   (const unsigned short*)S.rec_key.as<unsigned short>(), (const uint32_t*)S.rec_val.as<uint32_t>(), nkeys, lb,
+                   slices, cap, offsets, ends, entries, sizehist);
+    } else {
+        if (n) H2B_LAUNCH(d, "msm_count", MK.count, (n + tb - 1) / tb, tb, 0, g, scalars, counts);
+        H2B_LAUNCH(d, "msm_scan", MK.scan_block_sums, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums);
+        H2B_LAUNCH(d, "msm_scan", MK.scan_single_block, 1, SCAN_BLOCK, 0, blocksums, nblk, (uint32_t*)nullptr);
+        H2B_LAUNCH(d, "msm_scan", MK.scan_apply, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums, offsets, ends);
+        if (n) H2B_LAUNCH(d, "msm_scatter", MK.scatter, (n + tb - 1) / tb, tb, 0, g, scalars, ends, entries);
+        H2B_LAUNCH(d, "msm_order", MK.size_hist, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist);
+    }
     H2B_LAUNCH(d, "msm_order", MK.scan_single_block, 1, SCAN_BLOCK, 0, sizehist, MSM_SIZE_BINS, (uint32_t*)nullptr);
     H2B_LAUNCH(d, "msm_order", MK.size_scatter, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist, order);
     H2B_LAUNCH(d, "msm_order", MK.long_list, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, pl.long_threshold,
