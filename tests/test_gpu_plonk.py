@@ -313,3 +313,46 @@ def test_batch_proving_bytes_match(ctx):
         proof = _prove_with(circuits, ops, pk, rng_spec, threads)
         assert proof == PC.oracle_proof(keys, circuits, rng_spec, threads)
         assert plonk_verifier.verify_proof_batch(vk, instances, proof, SECRET, 1 << k)
+
+
+@pytest.mark.parametrize("name,k,workers", [("StandardPlonk", 5, 1), ("StandardPlonk3", 6, 2), ("MyCircuit", 6, 1), ("MyCircuit", 8, 3),
+                                            ("MyCircuit", 10, 8)])
+def test_coset_prover_bytes_match(ctx, name, k, workers):
+    """evaluate_h coset by coset (plonk/cosets.py: e size-n cosets instead of one extended domain of n * e rows, dealt over
+    `workers` single-device contexts -- distinct GPUs when the box has them, the same GPU otherwise): the quotient's pieces are the
+    same polynomials, so the proof bytes equal the extended path's and the independent oracle's.  The key is built without any
+    extended-length vector (keygen_pk(extended=False))."""
+    import torch
+    from h2b200.plonk.cosets import CosetProver
+    circ = {"MyCircuit": lambda: example.MyCircuit(k, 42), "StandardPlonk": lambda: example.StandardPlonk(k, 7, 5),
+            "StandardPlonk3": lambda: example.StandardPlonk(k, 7, None)}[name]()
+    cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circ)
+    lean_pk = plonk.keygen_pk(ops, vk, cc, extended=False)
+    assert lean_pk.l0 is None and lean_pk.fixed_cosets == [] and lean_pk.permutation.cosets == []
+    ndev = torch.cuda.device_count()
+    devices = [i % ndev for i in range(workers)]
+    expected = _prove_with(circ, ops, pk, PC.SEED_0_31, 3)
+    ops.cosets = CosetProver(ops, devices)
+    try:
+        e = 1 << (ops.domain.extended_k - k)
+        print(f"coset prover: k = {k}, e = {e} cosets over devices {devices} ({ndev} GPU(s) visible)")
+        for _ in range(2):                                       # the second proof reuses the per-coset key tables
+            assert _prove_with(circ, ops, lean_pk, PC.SEED_0_31, 3) == expected
+        assert _prove_with(circ, ops, lean_pk, "OneNg", 4, "gwc") == PC.oracle_proof(PC.oracle_keys(circ, k, SECRET), circ, "OneNg", 4, "gwc")
+    finally:
+        ops.cosets.close()
+        ops.cosets = None
+
+
+def test_coset_prover_batch_of_two_circuits(ctx):
+    from h2b200.plonk.cosets import CosetProver
+    k = 6
+    circuits = [example.MyCircuit(k, 42), example.MyCircuit(k, 77)]
+    cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circuits[0])
+    expected = _prove_with(circuits, ops, pk, "OneNg", 4)
+    ops.cosets = CosetProver(ops, [0, 0])
+    try:
+        assert _prove_with(circuits, ops, plonk.keygen_pk(ops, vk, cc, extended=False), "OneNg", 4) == expected
+    finally:
+        ops.cosets.close()
+        ops.cosets = None

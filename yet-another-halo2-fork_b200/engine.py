@@ -42,6 +42,7 @@ class Context:
     def __init__(self, device_ids: Optional[Sequence[int]] = None):
         self.lib = _lib.load()
         self._ctx = ctypes.c_void_p()
+        self.device_ids = [0] if device_ids is None else list(device_ids)
         if device_ids is None:
             rc = self.lib.h2b_init(ctypes.byref(self._ctx), None, 0)
         else:

@@ -214,7 +214,8 @@ def permutation_commit(ops, pk, advice, instance, beta: int, gamma: int, rng, tr
         s.permutation_product_blind = rng.random_fr()
         commitment = ops.commit_lagrange(z)
         s.permutation_product_poly = ops.lagrange_to_coeff(z)
-        s.permutation_product_coset = ops.coeff_to_extended(s.permutation_product_poly)
+        # evaluate_h reads the product on the extended coset (evaluation.rs:398-401); the coset prover extends it coset by coset
+        s.permutation_product_coset = None if getattr(ops, "cosets", None) else ops.coeff_to_extended(s.permutation_product_poly)
         transcript.write_point(commitment)
         sets.append(s)
     return sets
@@ -339,6 +340,18 @@ def vanishing_construct(ops, committed: VanishingCommitted, domain, h_poly, rng,
     c.h_pieces = [ops.slice(h, i * n, n) for i in range(ops.rows(h) // n)]
     c.h_blinds = _draw(rng, len(c.h_pieces))
     for commitment in ops.commit_many(c.h_pieces):                                  # vanishing/prover.rs:136-146
+        transcript.write_point(commitment)
+    c.committed = committed
+    return c
+
+
+def vanishing_construct_pieces(ops, committed: VanishingCommitted, pieces, rng, transcript) -> VanishingConstructed:
+    """vanishing/prover.rs:117-152 from the quotient's n-sized pieces directly (cosets.py computes them without the extended
+    domain): blinds, commitments, transcript -- the same draws and writes as vanishing_construct."""
+    c = VanishingConstructed()
+    c.h_pieces = list(pieces)
+    c.h_blinds = _draw(rng, len(c.h_pieces))
+    for commitment in ops.commit_many(c.h_pieces):
         transcript.write_point(commitment)
     c.committed = committed
     return c

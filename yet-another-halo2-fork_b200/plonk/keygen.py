@@ -135,6 +135,9 @@ class ProvingKey:                                         # plonk.rs:242-252
     fixed_cosets: list
     permutation: PermutationProvingKey
     ev: Evaluator
+    l0_poly: object = None                                # coefficient forms of l0 / l_last / l_active_row: the coset prover
+    l_last_poly: object = None                            # (cosets.py) evaluates them coset by coset
+    l_active_poly: object = None
 
     def get_vk(self) -> VerifyingKey:
         return self.vk
@@ -174,29 +177,34 @@ def keygen_vk(ops, circuit: C.CompiledCircuit, transcript_repr: Optional[int] = 
     return vk
 
 
-def keygen_pk(ops, vk: VerifyingKey, circuit: C.CompiledCircuit) -> ProvingKey:
+def keygen_pk(ops, vk: VerifyingKey, circuit: C.CompiledCircuit, extended: bool = True) -> ProvingKey:
     """keygen.rs:103-187."""
     cs, n = vk.cs, ops.n
     if n < cs.minimum_rows():
         raise ValueError(f"not enough rows available (k = {ops.k})")
     fixed_values = [_fixed_column(ops, col) for col in circuit.preprocessing.fixed]
     fixed_polys = [ops.lagrange_to_coeff(ops.clone(v)) for v in fixed_values]
-    fixed_cosets = [ops.coeff_to_extended(p) for p in fixed_polys]
     bf = cs.blinding_factors()
 
     def indicator(rows):
         p = ops.zeros(n)
         for r in rows:
             ops.write_ints(p, r, [1])
-        return ops.coeff_to_extended(ops.lagrange_to_coeff(p))
+        return ops.lagrange_to_coeff(p)
 
-    l0 = indicator([0])
-    l_blind = indicator(range(n - bf, n))
-    l_last = indicator([n - bf - 1])
-    l_active_row = PX.pointwise(ops, C.sub(C.const(1), C.add(PX.col(0), PX.col(1))), [l_last, l_blind], extended=True)
+    # extended=False: a key for the coset prover (cosets.py) -- nothing of the extended length n * e is built or kept
+    ext = (lambda p: ops.coeff_to_extended(p)) if extended else (lambda p: None)
+    fixed_cosets = [ext(p) for p in fixed_polys] if extended else []
+    l0_poly, l_blind_poly, l_last_poly = indicator([0]), indicator(range(n - bf, n)), indicator([n - bf - 1])
+    one_minus = C.sub(C.const(1), C.add(PX.col(0), PX.col(1)))
+    # 1 - (l_last + l_blind) in coefficient form: negate every coefficient, add one to the constant term
+    l_active_poly = PX.pointwise(ops, C.neg(C.add(PX.col(0), PX.col(1))), [l_last_poly, l_blind_poly])
+    ops.write_ints(l_active_poly, 0, [(ops.read_ints(l_active_poly, 0, 1)[0] + 1) % F.R_MOD])
+    l0, l_last = ext(l0_poly), ext(l_last_poly)
+    l_active_row = PX.pointwise(ops, one_minus, [l_last, ext(l_blind_poly)], extended=True) if extended else None
     assembly = Assembly.new_from_assembly_mid(n, cs.permutation_columns, circuit.preprocessing.copies)
     permutations = assembly.permutations(ops, ops.domain.omega)
     polys = [ops.lagrange_to_coeff(ops.clone(p)) for p in permutations]
-    cosets = [ops.coeff_to_extended(p) for p in polys]
+    cosets = [ext(p) for p in polys] if extended else []
     return ProvingKey(vk, l0, l_last, l_active_row, fixed_values, fixed_polys, fixed_cosets,
-                      PermutationProvingKey(permutations, polys, cosets), Evaluator(cs))
+                      PermutationProvingKey(permutations, polys, cosets), Evaluator(cs), l0_poly, l_last_poly, l_active_poly)

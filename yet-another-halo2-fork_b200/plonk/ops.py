@@ -32,6 +32,7 @@ class DeviceOps:
         self.ctx = engine.ctx
         self.poly = PolyOps(self.ctx)
         self.k, self.n = domain.k, domain.n
+        self.cosets = None          # a plonk.cosets.CosetProver: create_proof then evaluates the quotient coset by coset
 
     def with_domain(self, domain: EvaluationDomain) -> "DeviceOps":
         return DeviceOps(self.params, self.engine, domain)

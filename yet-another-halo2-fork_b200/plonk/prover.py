@@ -179,10 +179,16 @@ class Prover:
         # prover.rs:665-685 (consumes the Lagrange form)
         advice_polys = [[ops.lagrange_to_coeff(p) for p in self.advice_polys[c]] for c in circuits]
         y = transcript.squeeze_challenge_scalar()                                   # [TRANSCRIPT-13]
-        h_poly = evaluate_h(ops, pk, advice_polys, self.instance_polys, challenges, y, beta, gamma, theta, lookups, shuffles,
-                            permutations)
-        vanishing = A.vanishing_construct(ops, vanishing, domain, h_poly, rng, transcript)              # [TRANSCRIPT-14]
-        del h_poly
+        if getattr(ops, "cosets", None):                # the quotient coset by coset, dealt over the GPUs (cosets.py)
+            pieces = ops.cosets.evaluate_h_pieces(pk, advice_polys, self.instance_polys, challenges, y, beta, gamma, theta, lookups,
+                                                  shuffles, permutations)
+            vanishing = A.vanishing_construct_pieces(ops, vanishing, pieces, rng, transcript)           # [TRANSCRIPT-14]
+            del pieces
+        else:
+            h_poly = evaluate_h(ops, pk, advice_polys, self.instance_polys, challenges, y, beta, gamma, theta, lookups, shuffles,
+                                permutations)
+            vanishing = A.vanishing_construct(ops, vanishing, domain, h_poly, rng, transcript)          # [TRANSCRIPT-14]
+            del h_poly
         x = transcript.squeeze_challenge_scalar()                                   # [TRANSCRIPT-15]
         xn = pow(x, ops.n, R)
         evals = A.EvalBatch(ops)                                                    # one device call for [TRANSCRIPT-17..23]
