@@ -1,5 +1,6 @@
 """One real proof of the frontend_backend_split circuit at 2^k rows on the GPU, with a per-stage wall-clock breakdown.
-usage: python scripts/prove_k.py [k] [repeats]"""
+usage: python scripts/prove_k.py [k] [repeats]      H2B_DEVICES=0,1,2,3 for a multi-device context;
+H2B_COSETS=1: evaluate the quotient coset by coset over those devices (plonk/cosets.py) with a key that holds no extended vector."""
 import json
 import os
 import sys
@@ -32,10 +33,38 @@ print(f"ParamsKZG.setup: {time.time() - t:.2f} s", flush=True)
 ops = DeviceOps(params, engine, h2b200.EvaluationDomain(cs.degree(), k, ctx))
 t = time.time()
 vk = plonk.keygen_vk(ops, cc)
-pk = plonk.keygen_pk(ops, vk, cc)
+use_cosets = os.environ.get("H2B_COSETS", "0") == "1"
+pk = plonk.keygen_pk(ops, vk, cc, extended=not use_cosets)
+if use_cosets:
+    from h2b200.plonk.cosets import CosetProver
+    ops.cosets = CosetProver(ops, devices)
 torch.cuda.synchronize()
 print(f"keygen: {time.time() - t:.2f} s", flush=True)
-out = {"k": k, "devices": out_devices, "runs": []}
+out = {"k": k, "devices": out_devices, "cosets": use_cosets, "runs": []}
+stage_ms = {}
+if os.environ.get("H2B_STAGES", "0") == "1":          # wall-clock of the quotient stage inside create_proof (adds synchronisations)
+    from h2b200.plonk import prover as _prover
+
+    def _timed(fn, name):
+        def wrapper(*a, **kw):
+            for dev in sorted(set(devices)):
+                torch.cuda.synchronize(dev)
+            t0 = time.time()
+            r = fn(*a, **kw)
+            for dev in sorted(set(devices)):
+                torch.cuda.synchronize(dev)
+            stage_ms.setdefault(name, []).append((time.time() - t0) * 1e3)
+            return r
+        return wrapper
+    _prover.evaluate_h = _timed(_prover.evaluate_h, "evaluate_h")
+    for _name in ("lookup_commit_permuted", "permutation_commit", "lookup_commit_product", "shuffle_commit_product", "vanishing_commit",
+                  "vanishing_construct", "vanishing_construct_pieces", "vanishing_evaluate"):
+        setattr(_prover.A, _name, _timed(getattr(_prover.A, _name), _name))
+    _prover.shplonk.create_proof = _timed(_prover.shplonk.create_proof, "multiopen")
+    _prover.Prover.commit_phase = _timed(_prover.Prover.commit_phase, "commit_phase")
+    if use_cosets:
+        ops.cosets.evaluate_h_pieces = _timed(ops.cosets.evaluate_h_pieces, "evaluate_h_pieces")
+        ops.cosets._run_worker = _timed(ops.cosets._run_worker, "worker")
 for rep in range(reps):
     tr = plonk.Blake2bWrite()
     l0 = ctx.launch_count()
@@ -45,6 +74,8 @@ for rep in range(reps):
     torch.cuda.synchronize()
     dt = time.time() - t
     proof = tr.finalize()
+    import hashlib
+    out["proof_sha256"] = hashlib.sha256(proof).hexdigest()
     out["runs"].append({"ms": dt * 1e3, "launches": ctx.launch_count() - l0, "proof_bytes": len(proof)})
     print(f"create_proof: {dt * 1e3:.1f} ms, {ctx.launch_count() - l0} launches, {len(proof)} bytes", flush=True)
 if os.environ.get("H2B_VERIFY", "1") == "1":
@@ -56,4 +87,12 @@ if os.environ.get("H2B_VERIFY", "1") == "1":
 free, total = torch.cuda.mem_get_info()
 out["torch_peak_gib"] = torch.cuda.max_memory_allocated() / 2**30
 out["device0_used_gib"] = (total - free) / 2**30
+out["per_device_used_gib"] = []
+for dev in sorted(set(devices)):
+    f_, t_ = torch.cuda.mem_get_info(dev)
+    out["per_device_used_gib"].append(round((t_ - f_) / 2**30, 2))
+out["stage_ms"] = {k_: [round(v, 1) for v in vs[-4:]] for k_, vs in stage_ms.items()}
 print(json.dumps(out))
+if ops.cosets:
+    ops.cosets.close()
+    ops.cosets = None

@@ -162,7 +162,9 @@ class DeviceOps:
 
     # ---- conveniences built on the above ------------------------------------------------------------------------------------
     def full(self, rows: int, value: int):
-        return self.upload(np.tile(F.fr_mont(value), (rows, 1)))
+        """`rows` copies of one field element, filled on the device (32 bytes cross PCIe, not rows * 32)."""
+        one = self.torch.from_numpy(F.fr_mont(value).view(np.int64).reshape(1, 4)).to("cuda")
+        return self._done(one.expand(rows, 4).contiguous())
 
     def as_poly(self, x):
         """A witness column as handed to commit_phase: a device tensor (adopted), an (n, 4) uint64 Montgomery array, or ints."""
