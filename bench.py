@@ -607,8 +607,8 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
         "executed_frac": (n_loc * 13 * 1160.0 / (acc_ms * 1e-3) / wide_peak) if (acc_ms and wide_peak and pre_c == 20) else None,
         "executed": "n x 13 windows (c = 20, precomputed window multiples) mixed adds x 1160 IMAD.WIDE "
                     "(6 mul + 2 dedicated squares + one fused product difference): fewer than the table's count, hence frac > executed_frac",
-        "traffic": (acc_traffic * acc_launches_per_step / world) if acc_traffic else None,
-        "traffic_source": acc_traffic_src or "no ncu capture of this round's code at this size: null rather than a stale figure",
+        "traffic": (acc_traffic * acc_launches_per_step) if (acc_traffic and world == 1) else None,
+        "traffic_source": (acc_traffic_src if world == 1 else None) or "no ncu capture of this round's code at this size / rank count: null rather than a stale figure",
         "traffic_note": "ncu dram__bytes_read+write per accumulate launch x launches per step; 13 gathered 64-byte multiples per "
                         "point at two DRAM atoms each dominate (algorithmic input = 96 B per point)",
         "hbm": {"bound": "hbm", "achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,

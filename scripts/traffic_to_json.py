@@ -16,7 +16,9 @@ def main():
     for r in csv.DictReader(lines[start:]):
         if not r.get("Metric Name"):
             continue
-        rec = rows.setdefault(int(r["ID"]), {"id": int(r["ID"]), "kernel": r["Kernel Name"].split("(")[0].split("<")[0]})
+        name = r["Kernel Name"].replace("(anonymous namespace)::", "").replace("<unnamed>::", "")
+        name = name.split("(")[0].split("<")[0].replace("void ", "").replace("h2b::", "").strip()
+        rec = rows.setdefault(int(r["ID"]), {"id": int(r["ID"]), "kernel": name})
         val = float(r["Metric Value"].replace(",", "")) * UNIT.get(r["Metric Unit"], 1.0)
         name = r["Metric Name"]
         if name == "dram__bytes_read.sum":
