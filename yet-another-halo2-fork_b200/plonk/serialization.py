@@ -146,8 +146,12 @@ def _vk_read(r: _Reader, fmt: str, cs: C.ConstraintSystemBack, make_domain) -> K
     return vk
 
 
-def vk_read(data: bytes, fmt: str, cs: C.ConstraintSystemBack, make_domain) -> K.VerifyingKey:
-    return _vk_read(_Reader(data), fmt, cs, make_domain)
+def vk_read(data: bytes, fmt: str, cs: C.ConstraintSystemBack, make_domain, transcript_repr=None) -> K.VerifyingKey:
+    """`transcript_repr`: as in keygen_vk -- a value taken from a Rust run, used instead of the restated Debug hash."""
+    vk = _vk_read(_Reader(data), fmt, cs, make_domain)
+    if transcript_repr is not None:
+        vk.transcript_repr = transcript_repr % F.R_MOD
+    return vk
 
 
 def pk_write(ops, pk: K.ProvingKey, fmt: str) -> bytes:
