@@ -1,5 +1,6 @@
-"""world_size-2 worker (gloo, CPU): the multi-process MSM plumbing of bench.py -- shard by point range, all-gather the
-per-window sums, fold with h2b_msm_combine -- with the per-shard window sums produced by the host-emulated kernels."""
+"""world_size-2 worker (gloo, CPU): the multi-process MSM plumbing -- shard by point range, all-gather the per-window sums, fold
+with h2b_msm_combine (the path for callers without peer access) -- with the per-shard window sums produced by the host-emulated
+kernels; and the handle exchange that sets up h2b_msm_sharded (the peer-memory path bench.py uses)."""
 import ctypes
 import os
 import sys
@@ -35,8 +36,13 @@ def main():
         out = h2b200.B200Engine.msm_combine(parts, c)
         exp = C.to_affine(C.best_multiexp(s_all, b_all))
         ok = int(np.array_equal(out[:8], exp))
+    # the start-up exchange of h2b_msm_sharded: every rank's 64-byte mailbox handle, in rank order (B200Engine.peer_attach)
+    from h2b200.engine import dist_all_gather_bytes
+    blobs = dist_all_gather_bytes(bytes([rank + 1]) * h2b200._lib.PEER_HANDLE_BYTES)
+    if [b for b in blobs] != [bytes([r + 1]) * h2b200._lib.PEER_HANDLE_BYTES for r in range(world)]:
+        ok = 0
     flag = torch.tensor([ok])
-    dist.broadcast(flag, 0)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)        # any rank's failure fails all
     dist.destroy_process_group()
     sys.exit(0 if int(flag.item()) == 1 else 1)
 
