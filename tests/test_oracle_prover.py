@@ -100,3 +100,44 @@ def test_pinned_vk_is_rebuilt_from_the_circuit_alone():
     for kind in ("advice", "instance", "fixed"):
         listed = [(column(q[2][0])[1], int(q[2][1][2][0][1])) for q in field(cs_node, kind + "_queries")[1]]
         assert listed == system.queries[kind]
+
+
+@pytest.mark.parametrize("k,degree", [(3, 3), (4, 5), (4, 6), (5, 9)])
+def test_quotient_by_coset_identity(k, degree):
+    """The algebra plonk/cosets.py rests on, in python ints (no GPU): the extended coset of domain.rs:230-244 is the union of
+    e = 2^(extended_k - k) cosets s_j * H of the size-n domain (row e * r + j of the extended vector is row r of coset j), and the
+    n-sized pieces h_q of a polynomial of degree < n * e come back from the per-coset interpolants c_j by
+        h_q = zeta^(-n q) / e * sum_j eps^(-j q) c_j,      eps = w_e^n."""
+    import random
+    P = R.R_MOD
+    dom = R.EvaluationDomain(degree, k)
+    n, e = dom.n, 1 << (dom.extended_k - dom.k)
+    rnd = random.Random(1000 * k + degree)
+    pieces = [[rnd.randrange(P) for _ in range(n)] for _ in range(dom.quotient_poly_degree)]
+    h = [c for piece in pieces for c in piece]                                    # degree < n * (d - 1) <= n * e
+    ext = [R.eval_polynomial(h, R.FR_ZETA * pow(dom.extended_omega, i, P) % P) for i in range(n * e)]
+    # the vanishing polynomial is constant on a coset: t_evaluations[j] = 1 / (X^n - 1) there (domain.rs:86-111)
+    for i in range(n * e):
+        x = R.FR_ZETA * pow(dom.extended_omega, i, P) % P
+        assert (pow(x, n, P) - 1) * dom.t_evaluations[i % e] % P == 1
+    eps_inv = pow(pow(dom.extended_omega, n, P), -1, P)
+    zeta_n_inv = pow(pow(R.FR_ZETA, n, P), -1, P)
+    c = []
+    for j in range(e):
+        s_j = R.FR_ZETA * pow(dom.extended_omega, j, P) % P
+        values = ext[j::e]                                                        # coset j, rows r = 0 .. n-1
+        assert values == [R.eval_polynomial(h, s_j * pow(dom.omega, r, P) % P) for r in range(n)]
+        coeff = dom.lagrange_to_coeff(values)                                     # interpolant in X / s_j
+        s_inv = pow(s_j, -1, P)
+        c.append([v * pow(s_inv, t, P) % P for t, v in enumerate(coeff)])
+    e_inv = pow(e, -1, P)
+    for q, piece in enumerate(pieces):
+        got = [pow(zeta_n_inv, q, P) * e_inv % P * sum(pow(eps_inv, j * q, P) * c[j][t] for j in range(e)) % P for t in range(n)]
+        assert got == piece
+    # and a column on coset j is the size-n transform of its coefficients scaled by s_j^t (rotations stay inside the coset)
+    a = [rnd.randrange(P) for _ in range(n)]
+    ext_a = dom.coeff_to_extended(a)
+    for j in range(e):
+        s_j = R.FR_ZETA * pow(dom.extended_omega, j, P) % P
+        scaled = [v * pow(s_j, t, P) % P for t, v in enumerate(a)]
+        assert R.best_fft(scaled, dom.omega, k) == ext_a[j::e]

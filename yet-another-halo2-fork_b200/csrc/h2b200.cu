@@ -151,6 +151,9 @@ struct Tuning {
     int msm_acc_variant = H2B_ACC_DEFAULT_VARIANT;   // H2B_ACC_VARIANT
     int msm_reduce_seg = 256;      // H2B_MSM_REDUCE_SEG buckets per row / column segment job of the lines reduction
     int msm_sort = 0;              // H2B_MSM_SORT       0: global-atomic count + scatter (faster, see msm_bin.cuh), 1: tiled two-level binning
+    int msm_sort_tb = 256;         // H2B_MSM_SORT_TB    threads per block of the count / scatter kernels (128 or 256)
+    int sort_prio = 1;             // H2B_SORT_PRIO      priority of the binning stream against the compute stream: 1 higher,
+                                   //                    0 equal, -1 lower (read when the context creates its streams)
     int ntt_full_table_max_log = 26;   // H2B_NTT_FULL_TABLE_MAX_LOG
     std::string ntt_split;         // H2B_NTT_SPLIT      e.g. "9,9,6"
     int l2_fetch = 0;              // H2B_L2_FETCH       cudaLimitMaxL2FetchGranularity hint (experiments)
@@ -171,6 +174,8 @@ struct Tuning {
         else if (name == "acc_variant") msm_acc_variant = (!reset && v >= 0 && v < 4) ? v : def.msm_acc_variant;
         else if (name == "msm_reduce_seg") msm_reduce_seg = (!reset && v >= 32 && v <= 4096 && (v & (v - 1)) == 0) ? v : def.msm_reduce_seg;
         else if (name == "msm_sort") msm_sort = reset ? def.msm_sort : (v != 0);
+        else if (name == "msm_sort_tb") msm_sort_tb = (!reset && (v == 64 || v == 128 || v == 256 || v == 512)) ? v : def.msm_sort_tb;
+        else if (name == "sort_prio") sort_prio = (!reset && v >= -1 && v <= 1) ? v : def.sort_prio;
         else if (name == "ntt_full_table_max_log") ntt_full_table_max_log = reset ? def.ntt_full_table_max_log : v;
         else if (name == "ntt_split") ntt_split = reset ? std::string() : std::string(value);
         else if (name == "l2_fetch") l2_fetch = (v == 32 || v == 64 || v == 128) ? v : 0;
@@ -180,7 +185,7 @@ struct Tuning {
     }
     void from_environment() {
         static const char* names[] = {"msm_c", "msm_pre_c", "msm_precompute", "msm_chunks", "msm_no_ramp", "msm_no_batch",
-                                      "msm_reduce_classic", "msm_reduce_seg", "acc_variant", "msm_sort", "ntt_full_table_max_log", "ntt_split", "l2_fetch", "peer_timeout_ms"};
+                                      "msm_reduce_classic", "msm_reduce_seg", "acc_variant", "msm_sort", "msm_sort_tb", "sort_prio", "ntt_full_table_max_log", "ntt_split", "l2_fetch", "peer_timeout_ms"};
         for (const char* nm : names) {
             std::string env = "H2B_";
             for (const char* c = nm; *c; c++) env.push_back((char)std::toupper((unsigned char)*c));
@@ -429,7 +434,7 @@ int msm_stage_sort(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, 
     cudaError_t e2 = cudaMemsetAsync(sizehist, 0, (size_t)MSM_SIZE_BINS * 4, st);
     cudaError_t e3 = cudaMemsetAsync(counters, 0, 256, st);
     if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) { d.launch_stream = d.stream; H2B_CK(e1); H2B_CK(e2); H2B_CK(e3); }
-    const uint32_t tb = 256;
+    const uint32_t tb = (uint32_t)ctx->tune.msm_sort_tb;
     if (tiled) {
         // two-level binning, shared-memory atomics only (msm_bin.cuh): digits + coarse totals, scan of the totals, partition into
         // coarse bins, one block per coarse bin for offsets / ends / placement / population histogram
@@ -1044,9 +1049,12 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
         if (ctx->tune.l2_fetch) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)ctx->tune.l2_fetch);   // experiment knob
         int prio_lo = 0, prio_hi = 0;
         cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
-        if (cudaStreamCreateWithPriority(&d.stream, cudaStreamNonBlocking, prio_lo) != cudaSuccess ||
+        // numerically lower = higher priority; the binning stream runs above the compute stream by default (sort_prio)
+        const int prio_compute = ctx->tune.sort_prio < 0 ? prio_hi : prio_lo;
+        const int prio_sort = ctx->tune.sort_prio > 0 ? prio_hi : prio_lo;
+        if (cudaStreamCreateWithPriority(&d.stream, cudaStreamNonBlocking, prio_compute) != cudaSuccess ||
             cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
-            cudaStreamCreateWithPriority(&d.sort_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
+            cudaStreamCreateWithPriority(&d.sort_stream, cudaStreamNonBlocking, prio_sort) != cudaSuccess ||
             cudaEventCreate(&d.ev_first) != cudaSuccess || cudaEventCreate(&d.ev_last) != cudaSuccess ||
             cudaEventCreateWithFlags(&d.ms[0].sorted, cudaEventDisableTiming) != cudaSuccess ||
             cudaEventCreateWithFlags(&d.ms[0].consumed, cudaEventDisableTiming) != cudaSuccess ||
