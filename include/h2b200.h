@@ -54,7 +54,9 @@ enum {
  * Replaces the engine object of zal.rs:182-243 (PlonkEngine { msm_backend }): one context owns the devices,
  * streams, resident bases and twiddle tables.  device_ids == NULL, n_devices == 0 selects device 0.
  * With n_devices > 1 the MSM is sharded by contiguous point range and batched NTT columns are dealt
- * round-robin (a single NTT stays on device_ids[0]). */
+ * round-robin (a single NTT stays on device_ids[0]).
+ * h2b_destroy on a context that is unknown or already destroyed is ignored, and h2b_bases_release on such a context returns
+ * H2B_E_INVALID: hosts with garbage collectors finalise descriptors and contexts in no particular order. */
 int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices);
 void h2b_destroy(h2b_ctx* ctx);
 const char* h2b_last_error(const h2b_ctx* ctx);

@@ -447,3 +447,18 @@ def test_full_size_msm_matches_the_oracle_directly(ctx, engine):
     s, b = d_s.cpu().numpy().view(np.uint64), d_b.cpu().numpy().view(np.uint64)
     assert np.array_equal(s[:1000], C.random_fr_chacha20(1000, C.SEED_SCALARS))
     check(got, oracle_affine(s, b))
+
+
+def test_release_after_destroy_is_harmless():
+    """Garbage-collected hosts finalise in any order: releasing a descriptor of a context that is already gone, or destroying
+    a context twice, must be refused by the library, not crash it (a registry of live contexts inside libh2b200.so)."""
+    import h2b200
+    lib = h2b200.load()
+    c = h2b200.Context([0])
+    desc = h2b200.B200Engine(c).get_base_descriptor(C.gen_bases(100, 1))
+    raw = ctypes.c_void_p(c.handle.value)
+    handle = desc.handle
+    c.close()
+    assert lib.h2b_bases_release(raw, handle) == -1          # H2B_E_INVALID, no use-after-free
+    lib.h2b_destroy(raw)                                      # second destroy: ignored
+    desc.handle = 0

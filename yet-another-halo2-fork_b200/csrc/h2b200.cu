@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <set>
 #include <mutex>
 #include <thread>
 #include <string>
@@ -224,6 +225,12 @@ struct h2b_ctx {
 namespace {
 
 thread_local std::string g_init_error;
+// Contexts that are alive: host languages with garbage collectors finalise objects in no particular order at exit, so a
+// descriptor may be released (or a context destroyed) after its context is gone; those two calls check here first.
+// Function-local statics: no destruction-order dependence on other translation units.
+std::mutex& live_mu() { static std::mutex* m = new std::mutex(); return *m; }
+std::set<h2b_ctx*>& live_set() { static std::set<h2b_ctx*>* s = new std::set<h2b_ctx*>(); return *s; }
+bool ctx_is_live(h2b_ctx* c) { std::lock_guard<std::mutex> lk(live_mu()); return live_set().count(c) != 0; }
 
 #define H2B_CK(expr)                                                                                         \
     do {                                                                                                     \
@@ -1081,12 +1088,14 @@ int h2b_init(h2b_ctx** out, const int* device_ids, int n_devices) {
         }
     cudaGetLastError();                                    // a refused peer query must not surface in a later launch check
     cudaSetDevice(ctx->devs[0].id);
+    { std::lock_guard<std::mutex> lk(live_mu()); live_set().insert(ctx); }
     *out = ctx;
     return H2B_OK;
 }
 
 void h2b_destroy(h2b_ctx* ctx) {
     if (!ctx) return;
+    { std::lock_guard<std::mutex> lk(live_mu()); if (!live_set().erase(ctx)) return; }      // unknown or already destroyed
     for (auto& kv : ctx->bases) release_bases(ctx, kv.second);
     if (ctx->peer.mailbox) {
         cudaSetDevice(ctx->devs[0].id);
@@ -1149,7 +1158,7 @@ int h2b_bases_register_device(h2b_ctx* ctx, const void* d_bases, size_t n, uint6
     return register_bases(ctx, d_bases, true, n, true, handle_out);
 }
 int h2b_bases_release(h2b_ctx* ctx, uint64_t handle) {
-    if (!ctx) return H2B_E_INVALID;
+    if (!ctx || !ctx_is_live(ctx)) return H2B_E_INVALID;      // the context may have been destroyed first (it released every base)
     std::lock_guard<std::mutex> lk(ctx->mu);
     auto it = ctx->bases.find(handle);
     if (it == ctx->bases.end()) return ctx->fail(H2B_E_INVALID, "bases_release: unknown handle");
