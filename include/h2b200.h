@@ -184,6 +184,11 @@ int h2b_coeff_to_extended_batch_device(h2b_ctx* ctx, const void* const* d_in_col
  *                      n = 0 is an error (the reference panics on `a.len() - 1`). */
 int h2b_batch_invert(h2b_ctx* ctx, void* a, size_t n);
 int h2b_batch_invert_device(h2b_ctx* ctx, void* d_a, size_t n);
+/* h2b_fr_mul_device: d_out[i] = d_a[i] * d_b[i] (* scale32 when it is not NULL), n device-resident field elements; d_out may
+ * alias d_a.  The coefficient scaling a_t * s^t that puts a polynomial on the coset s * H before a size-n transform --
+ * distribute_powers_zeta (poly/domain.rs:325-341) for an arbitrary shift, given as its power table -- and the inverse scaling
+ * after the inverse transform; what evaluating the quotient coset by coset needs (plonk/cosets.py).  An API extension. */
+int h2b_fr_mul_device(h2b_ctx* ctx, const void* d_a, const void* d_b, const void* scale32_or_null, void* d_out, size_t n);
 int h2b_grand_product(h2b_ctx* ctx, const void* v, size_t n, const void* init32, void* z, size_t out_len);
 int h2b_grand_product_device(h2b_ctx* ctx, const void* d_v, size_t n, const void* init32, void* d_z, size_t out_len);
 int h2b_eval_polynomial(h2b_ctx* ctx, const void* poly, size_t n, const void* point32, void* out32);

@@ -65,7 +65,10 @@ if os.environ.get("H2B_STAGES", "0") == "1":          # wall-clock of the quotie
     if use_cosets:
         ops.cosets.evaluate_h_pieces = _timed(ops.cosets.evaluate_h_pieces, "evaluate_h_pieces")
         ops.cosets._run_worker = _timed(ops.cosets._run_worker, "worker")
+kprof = os.environ.get("H2B_KPROF", "0") == "1"     # per-kernel-family device time of the LAST proof (main context only)
 for rep in range(reps):
+    if kprof and rep == reps - 1:
+        ctx.profile_enable(True)
     tr = plonk.Blake2bWrite()
     l0 = ctx.launch_count()
     torch.cuda.synchronize()
@@ -91,6 +94,8 @@ out["per_device_used_gib"] = []
 for dev in sorted(set(devices)):
     f_, t_ = torch.cuda.mem_get_info(dev)
     out["per_device_used_gib"].append(round((t_ - f_) / 2**30, 2))
+if kprof:
+    out["kernel_ms"] = {k_: round(v["ms"], 2) for k_, v in sorted(ctx.profile_read().items(), key=lambda kv: -kv[1]["ms"])}
 out["stage_ms"] = {k_: [round(v, 1) for v in vs[-4:]] for k_, vs in stage_ms.items()}
 print(json.dumps(out))
 if ops.cosets:

@@ -149,3 +149,40 @@ def test_permutation_product_shape(ops):
     ni, di = C.ints_from_fr_array(num, R.R_MOD), C.ints_from_fr_array(den, R.R_MOD)
     exp = R.grand_product([a * pow(b, -1, R.R_MOD) % R.R_MOD for a, b in zip(ni, di)], 1, n)
     assert C.ints_from_fr_array(z, R.R_MOD) == exp
+
+
+@pytest.mark.parametrize("n", [1, 33, 4096 + 5, (1 << 18) + 1])
+def test_pointwise_mul_and_coset_scaling(ops, ctx, n):
+    """h2b_fr_mul_device: out = a * b (* scale), bit-exact against python ints, in place and out of place; with b = the power table
+    of a coset shift it is distribute_powers (domain.rs:325-341) for that shift: a size-n transform of the scaled coefficients gives
+    the polynomial's values on the coset (checked against direct evaluation at a few rows)."""
+    import ctypes
+    import torch
+    a, b = C.random_fr(n, 500 + n), C.random_fr(n, 900 + n)
+    ai = [C.int_from_mont(x, R.R_MOD) for x in a[:64]]
+    bi = [C.int_from_mont(x, R.R_MOD) for x in b[:64]]
+    da, db = (torch.from_numpy(x.view(np.int64)).cuda() for x in (a, b))
+    out = ops.mul(da, db).cpu().numpy().view(np.uint64)
+    assert [C.int_from_mont(x, R.R_MOD) for x in out[:64]] == [x * y % R.R_MOD for x, y in zip(ai, bi)]
+    tail = C.int_from_mont(out[n - 1], R.R_MOD)
+    assert tail == C.int_from_mont(a[n - 1], R.R_MOD) * C.int_from_mont(b[n - 1], R.R_MOD) % R.R_MOD
+    scaled = ops.mul(da, db, scale=7, out=da).cpu().numpy().view(np.uint64)          # in place, with the constant
+    assert [C.int_from_mont(x, R.R_MOD) for x in scaled[:64]] == [7 * x * y % R.R_MOD for x, y in zip(ai, bi)]
+    assert ctx.lib.h2b_fr_mul_device(ctx.handle, None, ctypes.c_void_p(db.data_ptr()), None, ctypes.c_void_p(da.data_ptr()), n) == -1
+    assert ctx.lib.h2b_fr_mul_device(ctx.handle, None, None, None, None, 0) == 0
+
+
+def test_coset_transform_by_scaling(ops, ctx):
+    import h2b200
+    import torch
+    k = 10
+    n = 1 << k
+    dom = h2b200.EvaluationDomain(1, k, ctx)
+    coeffs = C.random_fr(n, 77)
+    ci = [C.int_from_mont(x, R.R_MOD) for x in coeffs]
+    shift = R.FR_ZETA * pow(R.ROOT_OF_UNITY, 12345, R.R_MOD) % R.R_MOD
+    powers = torch.from_numpy(np.stack([C.mont_from_int(pow(shift, t, R.R_MOD), R.R_MOD) for t in range(n)]).view(np.int64)).cuda()
+    vals = dom.coeff_to_lagrange(ops.mul(torch.from_numpy(coeffs.view(np.int64)).cuda(), powers)).cpu().numpy().view(np.uint64)
+    for r in (0, 1, 17, n - 1):
+        x = shift * pow(dom.omega, r, R.R_MOD) % R.R_MOD
+        assert C.int_from_mont(vals[r], R.R_MOD) == R.eval_polynomial(ci, x)

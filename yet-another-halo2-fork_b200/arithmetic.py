@@ -95,6 +95,18 @@ class PolyOps:
         c.check(lib.h2b_batch_invert(c.handle, _vp(a) if n else None, n))
         return a
 
+    def mul(self, a, b, scale=None, out=None):
+        """out[i] = a[i] * b[i] (* scale): device tensors of equal length (h2b_fr_mul_device); out defaults to a new tensor."""
+        import torch
+        c, n = self.ctx, _rows(a)
+        assert _is_torch_cuda(a) and _is_torch_cuda(b) and _rows(b) == n
+        if out is None:
+            out = torch.empty_like(a)
+        sc = F.fr_mont(scale) if scale is not None else None
+        c.check(c.lib.h2b_fr_mul_device(c.handle, ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(b.data_ptr()),
+                                        _vp(sc) if sc is not None else None, ctypes.c_void_p(out.data_ptr()), n))
+        return out
+
     def grand_product(self, v, init: int = 1, out_len: Optional[int] = None):
         """z[0] = init; z[i] = z[i-1] * v[i-1] for i < out_len (default len(v), as the Z polynomials take n values)."""
         c, lib = self.ctx, self.ctx.lib

@@ -1664,6 +1664,22 @@ static int batch_invert_impl(h2b_ctx* ctx, void* a, size_t n, bool on_device) {
     if (!on_device && n) H2B_CK(d.ring.d2h(a, buf, n * 32, d.stream));
     return end_call(ctx, d);
 }
+int h2b_fr_mul_device(h2b_ctx* ctx, const void* d_a, const void* d_b, const void* scale32_or_null, void* d_out, size_t n) {
+    if (!ctx) return H2B_E_INVALID;
+    if ((!d_a || !d_b || !d_out) && n) return ctx->fail(H2B_E_INVALID, "fr_mul: null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    Dev& d = ctx->devs[0];
+    H2B_CK(cudaSetDevice(d.id));
+    begin_call(d);
+    if (n) {
+        const Fr scale = scale32_or_null ? fr_from_bytes(scale32_or_null) : Fr::zero();
+        const unsigned grid = (unsigned)std::min<size_t>((n + 255) / 256, (size_t)d.sms * 16);
+        H2B_LAUNCH(d, "poly_mul", poly_kernel_table().mul, grid, 256, 0, (const Fr*)d_a, (const Fr*)d_b, scale,
+                   scale32_or_null ? 1u : 0u, (Fr*)d_out, (uint64_t)n);
+        H2B_CK(cudaGetLastError());
+    }
+    return end_call(ctx, d);
+}
 int h2b_batch_invert(h2b_ctx* ctx, void* a, size_t n) { return batch_invert_impl(ctx, a, n, false); }
 int h2b_batch_invert_device(h2b_ctx* ctx, void* d_a, size_t n) { return batch_invert_impl(ctx, d_a, n, true); }
 

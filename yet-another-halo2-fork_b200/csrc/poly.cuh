@@ -356,6 +356,17 @@ poly_horner_tile_scan_kernel(const Fr* __restrict__ a, uint64_t n, uint64_t pad,
         if (j >= pad && j - pad + 1 < n) fe_store(q + (n - 2 - (j - pad)), c);
     }
 }
+// out[i] = a[i] * b[i] (* scale): the coefficient scaling a_t * s^t in front of a coset transform (distribute_powers_zeta,
+// domain.rs:325-341, for an arbitrary shift s given as its power table) and its inverse afterwards.  out may alias a.
+__global__ void __launch_bounds__(256)
+poly_mul_kernel(const Fr* __restrict__ a, const Fr* __restrict__ b, Fr scale, uint32_t has_scale, Fr* out, uint64_t n) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        Fr v = fe_mul(fe_load(a + i), fe_load(b + i));
+        if (has_scale) v = fe_mul(v, scale);
+        fe_store(out + i, v);
+    }
+}
 #endif  // __CUDACC__ && !H2B_NO_KERNELS
 
 }  // namespace h2b

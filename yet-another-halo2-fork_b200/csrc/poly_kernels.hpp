@@ -14,6 +14,7 @@ struct PolyKernelTable {
     void (*horner_tile_scan)(const Fr*, uint64_t, uint64_t, Fr, Fr, const Fr*, Fr*);
     void (*horner_batch_tile_reduce)(const HornerJob*, uint64_t, uint64_t, uint32_t, Fr*);
     void (*horner_batch_totals)(const HornerJob*, const Fr*, uint32_t, Fr*);
+    void (*mul)(const Fr*, const Fr*, Fr, uint32_t, Fr*, uint64_t);
 };
 const PolyKernelTable& poly_kernel_table();
 }  // namespace h2b

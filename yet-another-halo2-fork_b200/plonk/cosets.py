@@ -42,6 +42,19 @@ from .keygen import FR_DELTA
 R = F.R_MOD
 
 
+class _Ready:
+    """A column on the worker's device, possibly still in flight: get() waits for its copy once."""
+
+    def __init__(self, tensor, event=None):
+        self.tensor, self.event = tensor, event
+
+    def get(self):
+        if self.event is not None:
+            self.event.synchronize()
+            self.event = None
+        return self.tensor
+
+
 class _Worker:
     """One GPU's share: a single-device library context, the plain size-n domain on it, and the per-coset tables it owns."""
 
@@ -105,7 +118,7 @@ class CosetProver:
 
     def _to_coset(self, w: _Worker, poly, j: int):
         """coefficients (n) -> evaluations on coset j, a new tensor."""
-        scaled = PX.pointwise(w.ops, C.mul(PX.col(0), PX.col(1)), [poly, self._powers(w, j)[0]])
+        scaled = w.ops.poly.mul(poly, self._powers(w, j)[0])                         # a_t * s_j^t  (h2b_fr_mul_device)
         return w.domain.coeff_to_lagrange(scaled)
 
     def _move(self, w: _Worker, t):
@@ -138,7 +151,7 @@ class CosetProver:
         cs, ev, k, ctx = pk.vk.cs, pk.ev, self.k, w.ctx
         key = self._key_coset(w, pk, j)
         fixed, l0, l_last, l_active = key["fixed"], key["l0"], key["l_last"], key["l_active"]
-        to = lambda p: self._to_coset(w, p, j)
+        to = lambda p: self._to_coset(w, p.get(), j)                                  # p: a _Ready (fetched column)
         graph = lambda g, adv, inst, prev=None: g.evaluate(ctx, fixed, adv, inst, list(challenges), beta, gamma, theta, y, k, k,
                                                            previous=prev)
         values = None
@@ -167,17 +180,34 @@ class CosetProver:
         if values is None:
             values = w.ops.zeros(self.n)
         values = w.domain.lagrange_to_coeff(values)                                   # iNTT_n, 1/n included
-        unscale = C.mul(C.mul(PX.col(0), PX.col(1)), C.const(self.t_inv[j]))          # s_j^-t, and 1 / (X^n - 1) on this coset
-        return PX.pointwise(w.ops, unscale, [values, self._powers(w, j)[1]])
+        # s_j^-t, and 1 / (X^n - 1) which is the constant t_evaluations[j] on this coset
+        return w.ops.poly.mul(values, self._powers(w, j)[1], scale=self.t_inv[j], out=values)
 
     def _run_worker(self, wi: int, pk, circuits, challenges, y, beta, gamma, theta):
         w = self.workers[wi]
         torch = self.torch
         with torch.cuda.device(w.device):
-            local = [{"advice": [self._move(w, p) for p in c["advice"]], "instance": [self._move(w, p) for p in c["instance"]],
-                      "permutation": [self._move(w, p) for p in c["permutation"]],
-                      "lookups": [tuple(self._move(w, p) for p in l) for l in c["lookups"]],
-                      "shuffles": [self._move(w, p) for p in c["shuffles"]]} for c in circuits]
+            # Columns living on another device are pulled over NVLink on a side stream, in the order the coset evaluation reads
+            # them; each is waited for at its first use, so the transfer of the later ones hides behind the first transforms.
+            side = torch.cuda.Stream(device=w.device) if any(c["advice"] and c["advice"][0].device.index != w.device
+                                                             for c in circuits) else None
+
+            def fetch(t):
+                if t.device.index == w.device:
+                    return _Ready(t)
+                with torch.cuda.stream(side):
+                    dst = t.to(f"cuda:{w.device}", non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(side)
+                return _Ready(dst, ev)
+
+            local = []
+            for c in circuits:                               # fetch order = use order inside _coset
+                lc = {"advice": [fetch(p) for p in c["advice"]], "instance": [fetch(p) for p in c["instance"]]}
+                lc["permutation"] = [fetch(p) for p in c["permutation"]]
+                lc["lookups"] = [tuple(fetch(p) for p in l) for l in c["lookups"]]
+                lc["shuffles"] = [fetch(p) for p in c["shuffles"]]
+                local.append(lc)
             out = {}
             for j in range(wi, self.e, len(self.workers)):
                 out[j] = self._coset(w, j, pk, local, challenges, y, beta, gamma, theta)
