@@ -187,19 +187,11 @@ class CosetProver:
         w = self.workers[wi]
         torch = self.torch
         with torch.cuda.device(w.device):
-            # Columns living on another device are pulled over NVLink on a side stream, in the order the coset evaluation reads
-            # them; each is waited for at its first use, so the transfer of the later ones hides behind the first transforms.
-            side = torch.cuda.Stream(device=w.device) if any(c["advice"] and c["advice"][0].device.index != w.device
-                                                             for c in circuits) else None
-
+            # Columns living on another device are pulled over NVLink before the first coset (blocking peer copies: issuing them
+            # asynchronously on a side stream and waiting per column at first use measured SLOWER, 56 vs 46 ms per worker at
+            # k = 22 on 4 GPUs -- torch queues cross-device copies on the SOURCE device's stream, where the workers serialise).
             def fetch(t):
-                if t.device.index == w.device:
-                    return _Ready(t)
-                with torch.cuda.stream(side):
-                    dst = t.to(f"cuda:{w.device}", non_blocking=True)
-                    ev = torch.cuda.Event()
-                    ev.record(side)
-                return _Ready(dst, ev)
+                return _Ready(self._move(w, t))
 
             local = []
             for c in circuits:                               # fetch order = use order inside _coset
