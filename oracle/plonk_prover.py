@@ -30,7 +30,14 @@ What each part follows (all paths under /root/reference):
 PARITY UNPINNED where halo2curves 0.6 (absent from the tree) decides the bytes -- recalled, not verifiable here:
     * `Fr::random` = eight next_u64() as little-endian limbs of a 512-bit integer, reduced mod r;
     * `G1Affine::to_bytes` = x little-endian, bit 6 of byte 31 = y's canonical LSB, bit 7 = identity;
-    * `{:?}` of Fr / Fq = "0x" + 64 lower-case hex digits (big-endian canonical), of G1Affine = "(x, y)" / "Infinity".
+    * `{:?}` of Fr / Fq = "0x" + 64 lower-case hex digits (big-endian canonical), of G1Affine = "(x, y)" / "Infinity";
+    * `Fr: Ord` = order of the canonical (non-Montgomery) integers -- it decides the sort in the lookup argument
+      (lookup/prover.rs:418-432), the BTreeMap walk of the leftover table values (:434-466) and the BTreeSet point order
+      of SHPLONK (shplonk.rs:46-137).
+The `{:?}` forms are exercised by the reference's golden vk string (plonk_api.rs:664-1141: its field elements and points are
+printed that way, and the oracle rebuilds the string, commitments included, from the circuit alone); the reference holds no
+golden PROOF bytes, so the other three stay recalled -- and none of them changes whether a proof verifies (any total order
+gives a valid lookup permutation, any injective point encoding a valid transcript), so the verifier says nothing about them.
 The STRUCTURE of the pinned-vk Debug string is pinned: `render` reproduces the reference's own golden text
 (halo2_proofs/tests/plonk_api.rs:664-1141) from its parse tree, see tests/test_oracle_prover.py.
 

@@ -30,7 +30,9 @@ for name, env in [("default", {}), ("prio_equal", {"H2B_SORT_PRIO": "0"}), ("pri
                   ("v2_96regs", {"H2B_ACC_VARIANT": "2"}), ("v2_prio_equal_tb128", {"H2B_ACC_VARIANT": "2", "H2B_SORT_PRIO": "0", "H2B_MSM_SORT_TB": "128"}),
                   ("v2_prio_low_tb128", {"H2B_ACC_VARIANT": "2", "H2B_SORT_PRIO": "-1", "H2B_MSM_SORT_TB": "128"}),
                   ("v2_prio_high_tb128", {"H2B_ACC_VARIANT": "2", "H2B_MSM_SORT_TB": "128"}),
-                  ("tb128", {"H2B_MSM_SORT_TB": "128"}), ("prio_low_tb128", {"H2B_SORT_PRIO": "-1", "H2B_MSM_SORT_TB": "128"})]:
+                  ("tb128", {"H2B_MSM_SORT_TB": "128"}), ("reduce_seg64", {"H2B_MSM_REDUCE_SEG": "64"}),
+                  ("reduce_seg128", {"H2B_MSM_REDUCE_SEG": "128"}), ("reduce_seg512", {"H2B_MSM_REDUCE_SEG": "512"}),
+                  ("reduce_seg1024", {"H2B_MSM_REDUCE_SEG": "1024"}), ("prio_low_tb128", {"H2B_SORT_PRIO": "-1", "H2B_MSM_SORT_TB": "128"})]:
     r = subprocess.run([sys.executable, __file__, str(k), "child"], env=dict(os.environ, **env), capture_output=True, text=True)
     line = [l for l in r.stdout.split("\n") if l.startswith("RESULT")]
     out[name] = round(float(line[0].split()[1]), 3) if line else r.stderr[-300:]
