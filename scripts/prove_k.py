@@ -73,9 +73,18 @@ for rep in range(reps):
     l0 = ctx.launch_count()
     torch.cuda.synchronize()
     t = time.time()
-    plonk.create_proof(ops, pk, circ.instances(), circ.witness, RNG.OneNg(), tr, num_threads=16)
-    torch.cuda.synchronize()
-    dt = time.time() - t
+    if os.environ.get("H2B_CPROFILE", "0") == "1" and rep == reps - 1:      # host-side call tree of the last proof
+        import cProfile
+        import pstats
+        prof = cProfile.Profile()
+        prof.runcall(plonk.create_proof, ops, pk, circ.instances(), circ.witness, RNG.OneNg(), tr, num_threads=16)
+        torch.cuda.synchronize()
+        dt = time.time() - t
+        pstats.Stats(prof).sort_stats("cumulative").print_stats(45)
+    else:
+        plonk.create_proof(ops, pk, circ.instances(), circ.witness, RNG.OneNg(), tr, num_threads=16)
+        torch.cuda.synchronize()
+        dt = time.time() - t
     proof = tr.finalize()
     import hashlib
     out["proof_sha256"] = hashlib.sha256(proof).hexdigest()

@@ -227,9 +227,13 @@ def test_coeff_to_extended_many_matches_single(ctx):
         assert torch.equal(dom.coeff_to_extended(c), m)
 
 
-def test_lookup_permute_matches_host_restatement(ctx):
+@pytest.mark.parametrize("shape", ["random", "small", "mixed", "constant", "two_limbs", "high_only"])
+def test_lookup_permute_matches_host_restatement(ctx, shape):
     """h2b_lookup_permute_device == the numpy restatement of permute_expression_pair (lookup/prover.rs:398-494), on columns with
-    many repeats, values spanning all four limbs, and a table larger than the set of inputs; missing value -> ConstraintSystemFailure."""
+    many repeats and a table larger than the set of inputs; missing value -> ConstraintSystemFailure.  The shapes steer the sort
+    plan: values spanning all four limbs (top limb alone decides), small integers (one pass over a few bits), a mix of both (ties on
+    the top limb: the full limb sequence runs), one repeated value (nothing to sort), values below 2^100 and values that differ
+    only in the top limb."""
     from h2b200.plonk import arguments as A
     engine = h2b200.B200Engine(ctx)
     for k, usable, seed in ((4, 10, 1), (10, 1000, 2), (13, (1 << 13) - 6, 3)):
@@ -237,7 +241,19 @@ def test_lookup_permute_matches_host_restatement(ctx):
         n = 1 << k
         rng = np.random.default_rng(seed)
         pool = [int(x) for x in rng.integers(0, 1 << 62, size=max(3, usable // 7))]
-        pool = [(p * 0x9E3779B97F4A7C15F39CC0605CEDC835 * (i + 1)) % R.R_MOD for i, p in enumerate(pool)]
+        wide = [(p * 0x9E3779B97F4A7C15F39CC0605CEDC835 * (i + 1)) % R.R_MOD for i, p in enumerate(pool)]
+        if shape == "random":
+            pool = wide
+        elif shape == "small":
+            pool = [p % 5000 for p in pool]
+        elif shape == "mixed":
+            pool = [w if i % 3 == 0 else p % 5000 for i, (p, w) in enumerate(zip(pool, wide))]
+        elif shape == "constant":
+            pool = [wide[0]]
+        elif shape == "two_limbs":
+            pool = [w % (1 << 100) for w in wide]
+        elif shape == "high_only":
+            pool = [((w >> 192) << 192) | 77 for w in wide]
         table = [pool[int(i)] for i in rng.integers(0, len(pool), size=usable)]
         present = sorted(set(table))
         inp = [present[int(i)] for i in rng.integers(0, len(present), size=usable)]

@@ -12,17 +12,47 @@ __device__ __forceinline__ bool key_ne(const Key& a, const Key& b) {
     return ((a.l[0] ^ b.l[0]) | (a.l[1] ^ b.l[1]) | (a.l[2] ^ b.l[2]) | (a.l[3] ^ b.l[3])) != 0;
 }
 
-// keys[0..u) = canonical input values, keys[u..2u) = canonical table values; perm = identity
-__global__ void lk_canon_kernel(const Fr* __restrict__ in, const Fr* __restrict__ tab, uint32_t u, Key* __restrict__ keys,
-                                uint32_t* __restrict__ perm) {
+// keys[0..u) = canonical input values, keys[u..2u) = canonical table values; perm = identity.
+// bits[0..4) |= every key limb, bits[4..8) &= every key limb: a bit that differs between two keys is set in OR and clear in AND,
+// which tells the host which limbs (and which bit range of them) the radix passes have to look at.
+__global__ void __launch_bounds__(256)
+lk_canon_kernel(const Fr* __restrict__ in, const Fr* __restrict__ tab, uint32_t u, Key* __restrict__ keys,
+                uint32_t* __restrict__ perm, unsigned long long* __restrict__ bits) {
+    __shared__ uint32_t sh_or[8], sh_and[8];
+    if (threadIdx.x < 8) { sh_or[threadIdx.x] = 0u; sh_and[threadIdx.x] = 0xffffffffu; }
+    __syncthreads();
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= 2 * u) return;
-    Fr c = fe_from_mont(fe_load(i < u ? in + i : tab + (i - u)));
-    Key k;
+    const bool live = i < 2 * u;
+    Fr c = Fr::zero();
+    if (live) {
+        c = fe_from_mont(fe_load(i < u ? in + i : tab + (i - u)));
+        Key k;
 #pragma unroll
-    for (int j = 0; j < 4; j++) k.l[j] = (uint64_t)c.l[2 * j] | ((uint64_t)c.l[2 * j + 1] << 32);
-    keys[i] = k;
-    perm[i] = i;
+        for (int j = 0; j < 4; j++) k.l[j] = (uint64_t)c.l[2 * j] | ((uint64_t)c.l[2 * j + 1] << 32);
+        keys[i] = k;
+        perm[i] = i;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        uint32_t o = __reduce_or_sync(0xffffffffu, live ? c.l[j] : 0u);
+        uint32_t a = __reduce_and_sync(0xffffffffu, live ? c.l[j] : 0xffffffffu);
+        if ((threadIdx.x & 31) == 0) { atomicOr(&sh_or[j], o); atomicAnd(&sh_and[j], a); }
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        atomicOr(&bits[threadIdx.x], (unsigned long long)sh_or[2 * threadIdx.x] | ((unsigned long long)sh_or[2 * threadIdx.x + 1] << 32));
+        atomicAnd(&bits[4 + threadIdx.x], (unsigned long long)sh_and[2 * threadIdx.x] | ((unsigned long long)sh_and[2 * threadIdx.x + 1] << 32));
+    }
+}
+
+// After sorting on limb `t` alone: two neighbours that agree on that limb but differ elsewhere mean the lower limbs decide an
+// order somewhere, and the full least-significant-limb-first sequence has to run.
+__global__ void lk_tie_check_kernel(const Key* __restrict__ keys, const uint32_t* __restrict__ perm, uint32_t m, int t,
+                                    uint32_t* __restrict__ ties) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0 || i >= m) return;
+    Key a = keys[perm[i]], b = keys[perm[i - 1]];
+    if (a.l[t] == b.l[t] && key_ne(a, b)) *ties = 1u;
 }
 
 __global__ void lk_gather_limb_kernel(const Key* __restrict__ keys, const uint32_t* __restrict__ perm, uint32_t m, int limb,
@@ -97,7 +127,7 @@ __global__ void lk_emit_kernel(const Key* __restrict__ values, const uint32_t* _
 }
 
 struct Layout {
-    size_t keys, permA, permB, keyA, keyB, flag, gid1, rank_in, sorted_in, counts, offs, values, notfirst, rep_pos, status, cub, total;
+    size_t keys, permA, permB, keyA, keyB, flag, gid1, rank_in, sorted_in, counts, offs, values, notfirst, rep_pos, status, bits, cub, total;
     size_t cub_bytes;
 };
 
@@ -125,6 +155,7 @@ Layout layout(uint32_t u) {
     L.flag = take(m * 4); L.gid1 = take(m * 4); L.counts = take(m * 4); L.offs = take(m * 4);
     L.rank_in = take((size_t)u * 4); L.sorted_in = take((size_t)u * 4); L.notfirst = take((size_t)u * 4); L.rep_pos = take((size_t)u * 4);
     L.status = take(256);
+    L.bits = take(256);                 // 4 x OR, 4 x AND of the key limbs, then the tie flag
     L.cub_bytes = cub_temp_bytes(u);
     L.cub = take(L.cub_bytes);
     L.total = off;
@@ -163,6 +194,7 @@ cudaError_t lookup_permute_run(cudaStream_t stream, const Fr* d_input, const Fr*
     uint32_t* notfirst = reinterpret_cast<uint32_t*>(base + L.notfirst);
     uint32_t* rep_pos = reinterpret_cast<uint32_t*>(base + L.rep_pos);
     uint32_t* status = reinterpret_cast<uint32_t*>(base + L.status);
+    unsigned long long* bits = reinterpret_cast<unsigned long long*>(base + L.bits);
     void* tmp = base + L.cub;
     size_t tmp_bytes = L.cub_bytes;
     *d_status_out = status;
@@ -171,20 +203,54 @@ cudaError_t lookup_permute_run(cudaStream_t stream, const Fr* d_input, const Fr*
     const unsigned T = 256, gm = (m + T - 1) / T, gu = (u + T - 1) / T;
     LK_CK(cudaMemsetAsync(status, 0, 4, stream));
     LK_CK(cudaMemsetAsync(counts, 0, (size_t)m * 4, stream));
-    lk_canon_kernel<<<gm, T, 0, stream>>>(d_input, d_table, u, keys, perm[0]); nl++;
+    LK_CK(cudaMemsetAsync(bits, 0, 32, stream));
+    LK_CK(cudaMemsetAsync(bits + 4, 0xff, 32, stream));
+    LK_CK(cudaMemsetAsync(bits + 8, 0, 8, stream));
+    lk_canon_kernel<<<gm, T, 0, stream>>>(d_input, d_table, u, keys, perm[0], bits); nl++;
+    // Which bits differ between any two keys?  Circuit columns are small integers (one low limb varies) or compressed, random
+    // looking elements (the top limb separates them), so most of the 4 x 8 radix passes of a blind 254-bit sort look at constant
+    // or irrelevant bits.  The plan needs the masks on the host: one 64-byte read-back and a stream synchronisation.
+    unsigned long long h_bits[8];
+    LK_CK(cudaMemcpyAsync(h_bits, bits, sizeof(h_bits), cudaMemcpyDeviceToHost, stream));
+    LK_CK(cudaStreamSynchronize(stream));
+    int vary[4], nvary = 0, lo_bit[4], hi_bit[4];
+    for (int limb = 0; limb < 4; limb++) {
+        unsigned long long v = h_bits[limb] & ~h_bits[4 + limb];
+        if (!v) continue;
+        lo_bit[limb] = __builtin_ctzll(v);
+        hi_bit[limb] = 64 - __builtin_clzll(v);
+        vary[nvary++] = limb;
+    }
     int cur = 0;
-    for (int limb = 0; limb < 4; limb++) {            // least significant limb first; every pass is stable
+    auto sort_on = [&](int limb) -> cudaError_t {       // stable pass on the varying bit range of one limb
         lk_gather_limb_kernel<<<gm, T, 0, stream>>>(keys, perm[cur], m, limb, key_lo[0]); nl++;
         size_t tb = tmp_bytes;
-        LK_CK(cub::DeviceRadixSort::SortPairs(tmp, tb, (const uint64_t*)key_lo[0], key_lo[1], (const uint32_t*)perm[cur], perm[cur ^ 1],
-                                              (int)m, 0, limb == 3 ? 62 : 64, stream));
-        nl += 8;
+        cudaError_t r = cub::DeviceRadixSort::SortPairs(tmp, tb, (const uint64_t*)key_lo[0], key_lo[1], (const uint32_t*)perm[cur], perm[cur ^ 1],
+                                                        (int)m, lo_bit[limb], hi_bit[limb], stream);
+        nl += 2 + (hi_bit[limb] - lo_bit[limb] + 7) / 8;
         cur ^= 1;
+        return r;
+    };
+    bool full = nvary > 1;
+    if (nvary > 1) {
+        // optimistic: the most significant varying limb alone; exact unless two keys tie on it and differ below
+        const int t = vary[nvary - 1];
+        LK_CK(sort_on(t));
+        lk_tie_check_kernel<<<gm, T, 0, stream>>>(keys, perm[cur], m, t, reinterpret_cast<uint32_t*>(bits + 8)); nl++;
+        uint32_t ties = 0;
+        LK_CK(cudaMemcpyAsync(&ties, bits + 8, 4, cudaMemcpyDeviceToHost, stream));
+        LK_CK(cudaStreamSynchronize(stream));
+        full = ties != 0;
     }
+    if (nvary == 1) LK_CK(sort_on(vary[0]));
+    if (full)                                            // least significant limb first; every pass is stable
+        for (int q = 0; q < nvary; q++) LK_CK(sort_on(vary[q]));
     lk_flags_kernel<<<gm, T, 0, stream>>>(keys, perm[cur], m, flag); nl++;
     { size_t tb = tmp_bytes; LK_CK(cub::DeviceScan::InclusiveSum(tmp, tb, (const uint32_t*)flag, gid1, (int)m, stream)); nl += 2; }
+    int rank_bits = 1;
+    while (rank_bits < 32 && (m >> rank_bits)) rank_bits++;       // ranks are < m
     lk_rank_kernel<<<gm, T, 0, stream>>>(keys, perm[cur], flag, gid1, m, u, rank_in, counts, values); nl++;
-    { size_t tb = tmp_bytes; LK_CK(cub::DeviceRadixSort::SortKeys(tmp, tb, (const uint32_t*)rank_in, sorted_in, (int)u, 0, 32, stream)); nl += 4; }
+    { size_t tb = tmp_bytes; LK_CK(cub::DeviceRadixSort::SortKeys(tmp, tb, (const uint32_t*)rank_in, sorted_in, (int)u, 0, rank_bits, stream)); nl += 4; }
     lk_first_kernel<<<gu, T, 0, stream>>>(sorted_in, u, notfirst, counts, status); nl++;
     { size_t tb = tmp_bytes; LK_CK(cub::DeviceScan::ExclusiveSum(tmp, tb, (const uint32_t*)notfirst, rep_pos, (int)u, stream)); nl += 2; }
     { size_t tb = tmp_bytes; LK_CK(cub::DeviceScan::ExclusiveSum(tmp, tb, (const uint32_t*)counts, offs, (int)m, stream)); nl += 2; }
