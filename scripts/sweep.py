@@ -1,5 +1,6 @@
-"""Size sweep of the two hot kernels (BASELINE.json configs[1] and configs[2]): MSM 2^16..2^24 and NTT 2^16..2^26, device
-resident and through host buffers, with the per-kernel CUDA-event breakdown.  Prints one JSON object.
+"""Size sweep of the two hot kernels (BASELINE.json configs[1] and configs[2]): MSM and NTT 2^16..2^26, device resident and through
+host buffers, with the per-kernel CUDA-event breakdown; MSM inputs are the ChaCha20-seeded sets of SURVEY.md 8(d), uniform and the
+two non-uniform ones.  Prints one JSON object.
 
     python scripts/sweep.py [--msm 16,18,20,22,24] [--ntt 16,18,20,22,24,26] [--reps 5]
 """
@@ -36,12 +37,23 @@ def main():
     ctx = h2b200.Context([0])
     eng = h2b200.B200Engine(ctx)
     out = {"msm": {}, "ntt": {}, "poly": {}}
+    # point additions of the best classic Pippenger at each size (x 2720 IMAD issue slots = 1280 IMAD.WIDE)
+    table_adds = {16: 1.475e6, 18: 5.014e6, 20: 1.769e7, 22: 6.488e7, 24: 2.317e8, 26: 8.556e8}
+    import ctypes
+    wide = ctypes.c_double()
+    muls = ctypes.c_double()
+    ctx.check(ctx.lib.h2b_imad_peak(ctx.handle, ctypes.byref(wide), ctypes.byref(muls)))
+    out["imad_wide_peak_per_s"] = wide.value
+    poly = h2b200.PolyOps(ctx)
     for k in [int(x) for x in args.msm.split(",") if x]:
         n = 1 << k
-        d_bases = h2b200.synth.device_bases(ctx, n, 1)
+        d_bases = h2b200.synth.device_bases(ctx, n, h2b200.synth.bench_t0())
+        t0 = time.perf_counter()
         desc = eng.get_base_descriptor(d_bases)
-        h = torch.from_numpy(h2b200.synth.random_scalars(n, 1234).view(np.int64)).pin_memory()
-        d = h.cuda()
+        torch.cuda.synchronize()
+        reg_ms = (time.perf_counter() - t0) * 1e3
+        d = h2b200.synth.chacha_scalars_device(ctx, n, h2b200.synth.SEED_SCALARS)
+        h = d.cpu().pin_memory()
         eng.msm_with_cached_base(d, desc)
         ctx.profile_enable(True)
         ctx.profile_read()
@@ -52,10 +64,27 @@ def main():
         host_ms = timed(lambda: eng.msm_with_cached_base(hn, desc), args.reps)
         pg = np.array(hn)                 # a pageable copy: what a Rust Vec<Fr> is
         pageable_ms = timed(lambda: eng.msm_with_cached_base(pg, desc), args.reps)
-        out["msm"][k] = {"device_ms": dev_ms, "host_ms": host_ms, "host_pageable_ms": pageable_ms, "points_per_s": n / (dev_ms * 1e-3),
-                         "kernels_ms": {name: v["ms"] / (args.reps + 1) for name, v in prof.items()}}
+        rec = {"device_ms": dev_ms, "host_ms": host_ms, "host_pageable_ms": pageable_ms, "points_per_s": n / (dev_ms * 1e-3),
+               "registration_ms": reg_ms, "kernels_ms": {name: v["ms"] / (args.reps + 1) for name, v in prof.items()}}
+        if k in table_adds:
+            rec["imad_fraction_of_measured_peak"] = table_adds[k] * 1280 / (dev_ms * 1e-3) / wide.value
+        # the two non-uniform scalar sets of SURVEY.md 8(d): (i) 90 % zeros / ones + 10 % uniform, (ii) every scalar < 2^16
+        gen = torch.Generator(device="cuda")
+        gen.manual_seed(5)
+        u = torch.rand(n, device="cuda", generator=gen)
+        one = torch.from_numpy(h2b200.fields.fr_mont(1).view(np.int64).reshape(1, 4)).cuda()
+        sk = d.clone()
+        sk[u < 0.45] = 0
+        sk[(u >= 0.45) & (u < 0.9)] = one
+        rec["device_ms_90pct_zeros_ones"] = timed(lambda: eng.msm_with_cached_base(sk, desc), args.reps)
+        raw = torch.zeros((n, 4), dtype=torch.int64, device="cuda")
+        raw[:, 0] = torch.randint(0, 1 << 16, (n,), device="cuda", generator=gen)
+        r_mont = torch.from_numpy(h2b200.fields.fr_mont(pow(2, 256, h2b200.fields.R_MOD)).view(np.int64).reshape(1, 4)).cuda()
+        small = poly.mul(raw, r_mont.expand(n, 4).contiguous())       # (v, 0, 0, 0) * mont(R) = v * R = Montgomery form of v
+        rec["device_ms_scalars_below_2p16"] = timed(lambda: eng.msm_with_cached_base(small, desc), args.reps)
+        out["msm"][k] = rec
         desc.release()
-        del d_bases, d, h
+        del d_bases, d, h, sk, raw, small, u
         torch.cuda.empty_cache()
     for k in [int(x) for x in args.ntt.split(",") if x]:
         n = 1 << k
