@@ -75,7 +75,7 @@ int h2b_set_option(h2b_ctx* ctx, const char* name, const char* value);
  * h2b_bases_register     = MsmAccel::get_base_descriptor (zal.rs:82): copy n affine bases to the device(s)
  *                          once (ParamsKZG::g / g_lagrange stay resident across commits).  This is the descriptor's
  *                          "expensive preprocessing" (zal.rs:71-77): for n >= 2^16 the multiples 2^(c*j) * P_i of every
- *                          window j are computed and kept as well (13-15 x 64 B per point, ~0.1 s per 2^20 points),
+ *                          window j are computed and kept as well (13-15 x 64 B per point, ~0.04 s per 2^20 points),
  *                          so that an MSM needs one bucket set instead of one per window.  H2B_MSM_PRECOMPUTE=0
  *                          (environment) keeps only the 64 B per point.
  * h2b_bases_register_device: same, adopting a buffer that already lives on device 0 (not copied, not freed).
