@@ -92,6 +92,56 @@ def test_curve_ops(hc):
         assert C.affine_to_ints(o, R.Q_MOD) == exp, n
 
 
+def test_binary_gcd_inversion(hc):
+    """fe_inv_bgcd (msm_ba.cuh): the ALU-pipe inversion the batched-affine accumulation uses once per block and round."""
+    rnd = random.Random(5)
+    for mod, nm in ((R.Q_MOD, "fq"), (R.R_MOD, "fr")):
+        vals = [0, 1, 2, 3, mod - 1, mod - 2, (mod - 1) // 2, (mod + 1) // 2, 1 << 253, (1 << 253) - 1, (1 << 256) % mod,
+                pow(1 << 256, -1, mod)] + [1 << b for b in range(1, 253, 17)] + [rnd.randrange(1, mod) for _ in range(400)]
+        for a in vals:
+            o = np.zeros(4, dtype=np.uint64)
+            getattr(hc, f"hc_{nm}_inv_bgcd")(p(C.mont_from_int(a, mod)), p(o))
+            assert C.int_from_mont(o, mod) == (pow(a, -1, mod) if a else 0), (nm, hex(a))
+
+
+def test_batched_affine_bucket(hc):
+    """One bucket through msm_ba.cuh's phases (pairs -> shared inversion -> affine sums -> mixed additions), 1 and 2 rounds:
+    random buckets, every length around the pairing / KCAP boundaries, and the pairs the affine formula cannot take
+    (equal points, P and -P, identity bases) in every position."""
+    rnd = random.Random(6)
+    bs = C.gen_bases(96, 5)
+    pts = [C.affine_to_ints(x, R.Q_MOD) for x in bs]
+    ident = np.zeros(8, dtype=np.uint64)
+
+    def bucket(idx, negs, rounds):
+        arr = np.ascontiguousarray(np.stack([ident if i is None else bs[i] for i in idx])) if idx else np.zeros((0, 8), dtype=np.uint64)
+        ng = np.array(negs, dtype=np.uint8)
+        o = np.zeros(8, dtype=np.uint64)
+        hc.hc_msm_ba_bucket(p(arr), ng.ctypes.data_as(ctypes.c_void_p), len(idx), rounds, p(o))
+        exp = None
+        for i, s in zip(idx, negs):
+            if i is not None:
+                exp = R.g1_add(exp, R.g1_neg(pts[i]) if s else pts[i])
+        assert C.affine_to_ints(o, R.Q_MOD) == exp, (idx, negs, rounds)
+
+    for rounds in (1, 2):
+        bucket([], [], rounds)
+        bucket([0], [1], rounds)
+        bucket([0, 1], [0, 0], rounds)
+        bucket([0, 0], [0, 0], rounds)                       # doubling
+        bucket([0, 0], [0, 1], rounds)                       # P + (-P)
+        bucket([None, 3], [0, 0], rounds); bucket([3, None], [1, 0], rounds); bucket([None, None], [0, 0], rounds)
+        bucket([0, 1, 0, 1], [0, 0, 0, 0], rounds)           # round 1 meets two equal sums
+        bucket([0, 1, 0, 1], [0, 0, 1, 1], rounds)           # ... and two opposite ones
+        bucket([2, 2, 2, 2, 2, 2, 2], [0] * 7, rounds)
+        bucket([4, 5, 4, 5, 4, 5, None, 7, 7, 8], [0, 0, 1, 1, 0, 0, 0, 0, 1, 0], rounds)
+        for n in list(range(1, 12)) + [31, 32, 33, 63, 64, 65, 127, 128, 129, 130, 131, 200]:
+            bucket([rnd.randrange(96) for _ in range(n)], [rnd.randrange(2) for _ in range(n)], rounds)
+        for _ in range(30):                                  # few distinct points: collisions everywhere
+            n = rnd.randrange(2, 60)
+            bucket([rnd.choice([None, 0, 1, 2, 3]) for _ in range(n)], [rnd.randrange(2) for _ in range(n)], rounds)
+
+
 def hc_ntt(hc, a, log_n, omega, scale=None, in_len=None, out_len=None, in_pat=None, out_pat=None):
     N = 1 << log_n
     out = np.zeros((N, 4), dtype=np.uint64)

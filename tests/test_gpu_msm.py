@@ -130,6 +130,58 @@ def test_binning_variants(engine, knob, msm_sort, shape):
         check(engine.msm(s, b), exp)
 
 
+@pytest.mark.parametrize("regs", [0, 1])
+@pytest.mark.parametrize("rounds", [1, 2])
+@pytest.mark.parametrize("shape", ["classic_c8", "pre_c9", "pre_c11_chunked", "pre_c16", "collisions", "skewed", "sparse"])
+def test_batched_affine_accumulation(engine, knob, rounds, regs, shape):
+    """msm_ba.cuh: the bucket accumulation with 1 or 2 rounds of batched affine additions (pairs of a bucket's entries, ONE
+    inversion per block and round) gives the oracle's point: dense buckets (dozens of pairs per thread, more than MSM_BA_KCAP
+    of them, odd leftovers), chunks adding into the same buckets, pairs the affine formula cannot take (repeated bases with
+    equal or opposite scalars, identity bases), oversized buckets next to it, and buckets with no pair at all."""
+    knob("msm_ba", rounds)
+    knob("msm_ba_regs", regs)
+    knob("msm_ba_min_mean", 1)
+    n, registered = 30000, True
+    if shape == "classic_c8":
+        knob("msm_c", 8); registered = False                       # 128 buckets per window: ~230 entries per bucket (> 2 * KCAP)
+    elif shape == "pre_c9":
+        knob("msm_pre_c", 9); n = 20011                            # one set of 256 buckets: thousands of entries each (the long path)
+    elif shape == "pre_c11_chunked":
+        knob("msm_pre_c", 11); knob("msm_chunks", 3); n = 50001
+    elif shape == "pre_c16":
+        knob("msm_pre_c", 16); n = (1 << 17) + 3
+    elif shape == "sparse":
+        knob("msm_pre_c", 20); n = 4097                            # ~0.1 entries per bucket
+    elif shape in ("collisions", "skewed"):
+        knob("msm_pre_c", 12)
+    s = C.random_fr(n, 300 + rounds)
+    b = C.gen_bases(n, 6)
+    if shape == "collisions":
+        # a few distinct (base, scalar) pairs repeated many times: equal points and opposite points meet inside the buckets
+        m = 40
+        rng = np.random.default_rng(9)
+        pick = rng.integers(0, m, n)
+        neg = rng.random(n) < 0.3
+        b = b[pick]
+        s = s[pick]
+        s[neg] = C.fr_sub(np.zeros_like(s[neg]), s[neg])
+        b[rng.random(n) < 0.05] = 0
+    if shape == "skewed":
+        rng = np.random.default_rng(5)
+        sel = rng.random(n)
+        s[sel < 0.5] = C.mont_from_int(1, R.R_MOD)
+        s[(sel >= 0.5) & (sel < 0.8)] = 0
+        s[(sel >= 0.8) & (sel < 0.9)] = C.mont_from_int(R.R_MOD - 1, R.R_MOD)
+    exp = oracle_affine(s, b)
+    if registered:
+        desc = engine.get_base_descriptor(b)
+        check(engine.msm_with_cached_base(s, desc), exp)
+        check(engine.msm_with_cached_base(s[: n // 3], desc), oracle_affine(s[: n // 3], b[: n // 3]))
+        desc.release()
+    else:
+        check(engine.msm(s, b), exp)
+
+
 def test_edge_scalars_and_bases(engine):
     n = 600
     s = C.random_fr(n, 5)

@@ -23,6 +23,7 @@
 #include "msm.cuh"
 #include "msm_kernels.hpp"
 #include "msm_bin.cuh"
+#include "msm_ba_kernels.hpp"
 #include "poly_kernels.hpp"
 #include "quotient_kernels.hpp"
 #include "setup_kernels.hpp"
@@ -88,7 +89,7 @@ struct Dev {
     std::vector<cudaEvent_t> chunk_events;
     DevBuf ntt_a, ntt_b, ntt_tab;
     MsmSortSet ms[2];
-    DevBuf m_scalars, m_buckets, m_wpart, m_long_partials, m_counters, m_tmp_bases;
+    DevBuf m_scalars, m_buckets, m_wpart, m_long_partials, m_counters, m_tmp_bases, m_ba;
     StageRing ring;                               // pinned slots for pageable caller buffers (hostcopy.hpp)
     DevBuf q_stage, q_scratch;                    // quotient evaluation: uploaded program / pointer tables, intermediates
     DevBuf p_in, p_out, p_tiles;                  // polynomial helpers (poly.cuh): staged operands and per-tile summaries
@@ -150,6 +151,10 @@ struct Tuning {
     int msm_no_batch = 0;          // H2B_MSM_NO_BATCH   1: h2b_msm_batch loops over single MSMs
     int msm_reduce_classic = 0;    // H2B_MSM_REDUCE_CLASSIC 1: running-sum reduction for every bucket-set size
     int msm_acc_variant = H2B_ACC_DEFAULT_VARIANT;   // H2B_ACC_VARIANT
+    int msm_ba = 0;                // H2B_MSM_BA         rounds of batched affine additions in front of the mixed additions
+                                   //                    (msm_ba.cuh): 0 = none (msm_accumulate_kernel), 1, 2
+    int msm_ba_regs = 0;           // H2B_MSM_BA_REGS    0: 4 resident blocks per SM (128 registers), 1: 3 blocks (168)
+    int msm_ba_min_mean = 8;       // H2B_MSM_BA_MIN_MEAN  mean bucket population of a chunk below which the plain kernel runs
     int msm_reduce_seg = 256;      // H2B_MSM_REDUCE_SEG buckets per row / column segment job of the lines reduction
     int msm_sort = 0;              // H2B_MSM_SORT       0: global-atomic count + scatter (faster, see msm_bin.cuh), 1: tiled two-level binning
     int msm_sort_tb = 256;         // H2B_MSM_SORT_TB    threads per block of the count / scatter kernels (128 or 256)
@@ -173,6 +178,9 @@ struct Tuning {
         else if (name == "msm_no_batch") msm_no_batch = reset ? 0 : (v != 0);
         else if (name == "msm_reduce_classic") msm_reduce_classic = reset ? 0 : (v != 0);
         else if (name == "acc_variant") msm_acc_variant = (!reset && v >= 0 && v < 4) ? v : def.msm_acc_variant;
+        else if (name == "msm_ba") msm_ba = (!reset && v >= 0 && v <= 2) ? v : def.msm_ba;
+        else if (name == "msm_ba_regs") msm_ba_regs = (!reset && v >= 0 && v <= 1) ? v : def.msm_ba_regs;
+        else if (name == "msm_ba_min_mean") msm_ba_min_mean = (!reset && v >= 1) ? v : def.msm_ba_min_mean;
         else if (name == "msm_reduce_seg") msm_reduce_seg = (!reset && v >= 32 && v <= 4096 && (v & (v - 1)) == 0) ? v : def.msm_reduce_seg;
         else if (name == "msm_sort") msm_sort = reset ? def.msm_sort : (v != 0);
         else if (name == "msm_sort_tb") msm_sort_tb = (!reset && (v == 64 || v == 128 || v == 256 || v == 512)) ? v : def.msm_sort_tb;
@@ -186,7 +194,7 @@ struct Tuning {
     }
     void from_environment() {
         static const char* names[] = {"msm_c", "msm_pre_c", "msm_precompute", "msm_chunks", "msm_no_ramp", "msm_no_batch",
-                                      "msm_reduce_classic", "msm_reduce_seg", "acc_variant", "msm_sort", "msm_sort_tb", "sort_prio", "ntt_full_table_max_log", "ntt_split", "l2_fetch", "peer_timeout_ms"};
+                                      "msm_reduce_classic", "msm_reduce_seg", "msm_ba", "msm_ba_regs", "msm_ba_min_mean", "acc_variant", "msm_sort", "msm_sort_tb", "sort_prio", "ntt_full_table_max_log", "ntt_split", "l2_fetch", "peer_timeout_ms"};
         for (const char* nm : names) {
             std::string env = "H2B_";
             for (const char* c = nm; *c; c++) env.push_back((char)std::toupper((unsigned char)*c));
@@ -395,6 +403,16 @@ int msm_chunk_plan(h2b_ctx* ctx, uint32_t n, uint32_t idx_offset, uint32_t c, ui
     return H2B_OK;
 }
 
+// Batched-affine accumulation (msm_ba.cuh): how many rounds this chunk gets (0 = the plain kernel: sparse chunks have too few
+// pairs per bucket to pay for the block-wide inversion), and the scratch it needs.
+uint32_t msm_ba_rounds(const h2b_ctx* ctx, const MsmChunkPlan& pl) {
+    if (!ctx->tune.msm_ba) return 0;
+    const uint64_t mean = (uint64_t)pl.sp.g.n * pl.sp.g.windows / std::max<uint32_t>(pl.sp.nkeys, 1u);
+    return mean >= (uint64_t)ctx->tune.msm_ba_min_mean ? (uint32_t)ctx->tune.msm_ba : 0u;
+}
+uint32_t msm_ba_stride(uint32_t nkeys) { return (nkeys + MSM_BA_THREADS - 1) / MSM_BA_THREADS * MSM_BA_THREADS; }
+size_t msm_ba_bytes(uint32_t nkeys, uint32_t rounds) { return (size_t)(rounds == 2 ? 3 : 1) * MSM_BA_KCAP * msm_ba_stride(nkeys) * sizeof(Fq); }
+
 // Binning stage of one chunk, enqueued on the SORT stream into sort set `S`: histogram, offsets, scatter, population order,
 // oversized-bucket task list.
 // Buffers of one sort set for a chunk of this plan (growing a buffer frees it, which waits for the device: the streamed MSM
@@ -496,7 +514,19 @@ int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan
     const uint32_t* entries = S.entries.as<uint32_t>();
     const uint32_t* counters = S.counters.as<uint32_t>();
     Xyzz* buckets = d.m_buckets.as<Xyzz>() + (size_t)set_index * nkeys;
-    {
+    if (msm_ba_rounds(ctx, pl)) {
+        // batched affine additions in front of the mixed additions (msm_ba.cuh): scratch rows [k][thread], thread = position in
+        // the population order
+        static const MsmBaKernelTable& BA = msm_ba_kernel_table();
+        const uint32_t rounds = msm_ba_rounds(ctx, pl), stride = msm_ba_stride(nkeys);
+        H2B_CK(d.m_ba.reserve(msm_ba_bytes(nkeys, rounds)));
+        Fq* prefix = d.m_ba.as<Fq>();
+        Fq* rx = rounds == 2 ? prefix + (size_t)MSM_BA_KCAP * stride : nullptr;
+        Fq* ry = rounds == 2 ? rx + (size_t)MSM_BA_KCAP * stride : nullptr;
+        H2B_LAUNCH(d, "msm_accumulate", BA.accumulate[rounds - 1][ctx->tune.msm_ba_regs], (nkeys + MSM_BA_THREADS - 1) / MSM_BA_THREADS,
+                   MSM_BA_THREADS, 0, bases, entries, offsets, ends, order, nkeys, pl.long_threshold, buckets, add_to ? 1u : 0u,
+                   prefix, rx, ry, stride);
+    } else {
         auto kern = MK.accumulate[ctx->tune.msm_acc_variant];
         H2B_LAUNCH(d, "msm_accumulate", kern, (nkeys + 127) / 128, 128, 0, bases, entries, offsets, ends, order, nkeys,
                    pl.long_threshold, buckets, add_to ? 1u : 0u);
@@ -656,6 +686,7 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
             for (int q = 0; q < (nchunks > 1 ? 2 : 1); q++) { rc = msm_sort_reserve(ctx, d.ms[q], big); if (rc) return rc; }
             H2B_CK(d.m_buckets.reserve((size_t)big.sp.nkeys * sizeof(Xyzz)));
             H2B_CK(d.m_long_partials.reserve((size_t)big.max_tasks * sizeof(Xyzz)));
+            if (msm_ba_rounds(ctx, big)) H2B_CK(d.m_ba.reserve(msm_ba_bytes(big.sp.nkeys, msm_ba_rounds(ctx, big))));
         }
         for (size_t k = 0; k < nchunks && rc == H2B_OK; k++) {
             size_t lo = bounds[k], len = bounds[k + 1] - lo;
@@ -1109,7 +1140,7 @@ void h2b_destroy(h2b_ctx* ctx) {
         cudaStreamSynchronize(d.stream);
         for (auto& kv : d.plans) cudaFree(kv.second.tables);
         cudaStreamSynchronize(d.sort_stream);
-        DevBuf* bufs[] = {&d.ntt_a, &d.ntt_b, &d.ntt_tab, &d.m_scalars, &d.m_buckets, &d.m_wpart, &d.m_long_partials, &d.m_counters,
+        DevBuf* bufs[] = {&d.ntt_a, &d.ntt_b, &d.ntt_tab, &d.m_scalars, &d.m_buckets, &d.m_wpart, &d.m_long_partials, &d.m_ba, &d.m_counters,
                           &d.m_tmp_bases, &d.p_in, &d.p_out, &d.p_tiles, &d.q_stage, &d.q_scratch};
         for (DevBuf* b : bufs) b->release();
         d.ms[0].release(); d.ms[1].release();

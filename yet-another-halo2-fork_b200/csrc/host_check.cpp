@@ -5,6 +5,8 @@
 #include "curve.cuh"
 #include "field_wide.cuh"
 #include "poly.cuh"
+#include "msm_ba.cuh"
+#include <vector>
 using namespace h2b;
 
 template <class F> static F ld(const void* p) { F f; std::memcpy(&f, p, 32); return f; }
@@ -46,6 +48,32 @@ void hc_add_tree(const void* pts, size_t n, void* out64) {
     Affine r = n ? xyzz_to_affine(v[0]) : xyzz_to_affine(Xyzz::identity());
     std::memcpy(out64, &r, 64);
     delete[] v;
+}
+// batched-affine bucket accumulation (msm_ba.cuh): one bucket through the same per-thread phases the kernel runs -- `rounds`
+// (1 or 2) rounds of paired affine additions, the block-wide inversion replaced by the thread's own fe_inv_bgcd -- returned affine.
+void hc_fq_inv_bgcd(const void* a, void* o) { st(o, fe_inv_bgcd(ld<Fq>(a))); }
+void hc_fr_inv_bgcd(const void* a, void* o) { st(o, fe_inv_bgcd(ld<Fr>(a))); }
+void hc_msm_ba_bucket(const void* pts, const uint8_t* neg, uint32_t n, int rounds, void* out64) {
+    std::vector<uint32_t> entries(n ? n : 1);
+    for (uint32_t i = 0; i < n; i++) entries[i] = i | (neg[i] ? 0x80000000u : 0u);
+    std::vector<Fq> prefix(MSM_BA_KCAP), rx(MSM_BA_KCAP), ry(MSM_BA_KCAP);
+    MsmBaSource s0;
+    s0.bases = (const Affine*)pts; s0.entries = entries.data(); s0.rx = nullptr; s0.ry = nullptr; s0.stride = 1; s0.from_entries = true;
+    uint32_t K0 = n >> 1;
+    if (K0 > MSM_BA_KCAP) K0 = MSM_BA_KCAP;
+    Fq inv = fe_inv_bgcd(msm_ba_phase_a(s0, K0, prefix.data(), 1));
+    Xyzz acc = Xyzz::identity();
+    if (rounds == 2) {
+        uint32_t K1 = msm_ba_phase_b<true>(s0, K0, n, prefix.data(), 1, inv, acc, rx.data(), ry.data());
+        MsmBaSource s1;
+        s1.bases = nullptr; s1.entries = nullptr; s1.rx = rx.data(); s1.ry = ry.data(); s1.stride = 1; s1.from_entries = false;
+        inv = fe_inv_bgcd(msm_ba_phase_a(s1, K1 >> 1, prefix.data(), 1));
+        msm_ba_phase_b<false>(s1, K1 >> 1, K1, prefix.data(), 1, inv, acc, nullptr, nullptr);
+    } else {
+        msm_ba_phase_b<false>(s0, K0, n, prefix.data(), 1, inv, acc, nullptr, nullptr);
+    }
+    Affine r = xyzz_to_affine(acc);
+    std::memcpy(out64, &r, 64);
 }
 }
 
