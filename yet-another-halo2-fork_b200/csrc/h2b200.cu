@@ -1351,6 +1351,10 @@ int h2b_peer_attach(h2b_ctx* ctx, int rank, int world, const void* handles, void
         P.table.mailbox[r] = q;
     }
     P.rank = rank; P.world = world; P.epoch = 0;
+    // ranks attached through IPC handles are other processes on this host, each with a copy pool of its own for pageable host
+    // buffers: share the host threads between them (at N = 8, eight full-size pools oversubscribe the cores and the staging
+    // copies of a sharded MSM from pageable scalars take longer than the MSM)
+    CopyPool::instance().set_share(1u + (unsigned)P.opened.size());
     return H2B_OK;
 }
 int h2b_msm_sharded(h2b_ctx* ctx, uint64_t handle, const void* scalars, int scalars_on_device, size_t n, size_t n_total, void* out96) {
