@@ -142,6 +142,23 @@ def test_batched_affine_bucket(hc):
             bucket([rnd.choice([None, 0, 1, 2, 3]) for _ in range(n)], [rnd.randrange(2) for _ in range(n)], rounds)
 
 
+def test_stream_copy(hc):
+    """The staging ring's copy (non-temporal stores above 4 KiB, csrc/streamcopy.hpp) for every alignment of source and
+    destination and lengths around the 32 / 128-byte steps; the bytes next to the destination stay untouched."""
+    hc.hc_stream_copy.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]
+    rng = np.random.default_rng(11)
+    src = rng.integers(0, 256, 1 << 17, dtype=np.uint8)
+    for so in (0, 1, 7, 31, 33):
+        for do in (0, 1, 16, 31, 32, 63):
+            for ln in (0, 1, 31, 4095, 4096, 4097, 4096 + 127, 4096 + 128, 4096 + 129, 50000, 65536 + 5):
+                dst = np.full(ln + 256, 0xA5, dtype=np.uint8)
+                base = (-dst.ctypes.data) % 64                     # a 64-byte aligned origin inside dst
+                hc.hc_stream_copy(dst.ctypes.data + base + do, src.ctypes.data + so, ln)
+                got = dst[base + do: base + do + ln]
+                assert np.array_equal(got, src[so: so + ln]), (so, do, ln)
+                assert (dst[: base + do] == 0xA5).all() and (dst[base + do + ln:] == 0xA5).all(), (so, do, ln)
+
+
 def hc_ntt(hc, a, log_n, omega, scale=None, in_len=None, out_len=None, in_pat=None, out_pat=None):
     N = 1 << log_n
     out = np.zeros((N, 4), dtype=np.uint64)

@@ -6,6 +6,7 @@
 #include "field_wide.cuh"
 #include "poly.cuh"
 #include "msm_ba.cuh"
+#include "streamcopy.hpp"
 #include <vector>
 using namespace h2b;
 
@@ -49,6 +50,8 @@ void hc_add_tree(const void* pts, size_t n, void* out64) {
     std::memcpy(out64, &r, 64);
     delete[] v;
 }
+// the staging ring's copy (streamcopy.hpp): any alignment of either side, any length
+void hc_stream_copy(void* dst, const void* src, size_t len) { stream_copy(dst, src, len); }
 // batched-affine bucket accumulation (msm_ba.cuh): one bucket through the same per-thread phases the kernel runs -- `rounds`
 // (1 or 2) rounds of paired affine additions, the block-wide inversion replaced by the thread's own fe_inv_bgcd -- returned affine.
 void hc_fq_inv_bgcd(const void* a, void* o) { st(o, fe_inv_bgcd(ld<Fq>(a))); }
