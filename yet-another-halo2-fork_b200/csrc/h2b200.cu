@@ -67,12 +67,13 @@ struct NttPlanDev {
 // on the sort stream (memory / atomic bound) while chunk k is accumulated on the compute stream (multiplier bound).
 struct MsmSortSet {
     DevBuf counts, offsets, ends, entries, order, blocksums, sizehist, long_info, long_tasks, counters;
+    DevBuf canon;                           // canonical scalars of the chunk (count -> scatter)
     DevBuf rec_key, rec_val, coarse;        // two-level binning (msm_bin.cuh): grouped records, coarse-bin totals / cursors / starts
     cudaEvent_t sorted = nullptr, consumed = nullptr;
     bool consumed_pending = false;
     void release() {
         DevBuf* bufs[] = {&counts, &offsets, &ends, &entries, &order, &blocksums, &sizehist, &long_info, &long_tasks, &counters,
-                          &rec_key, &rec_val, &coarse};
+                          &canon, &rec_key, &rec_val, &coarse};
         for (DevBuf* b : bufs) b->release();
         if (sorted) cudaEventDestroy(sorted);
         if (consumed) cudaEventDestroy(consumed);
@@ -151,6 +152,8 @@ struct Tuning {
     int msm_no_batch = 0;          // H2B_MSM_NO_BATCH   1: h2b_msm_batch loops over single MSMs
     int msm_reduce_classic = 0;    // H2B_MSM_REDUCE_CLASSIC 1: running-sum reduction for every bucket-set size
     int msm_acc_variant = H2B_ACC_DEFAULT_VARIANT;   // H2B_ACC_VARIANT
+    int msm_canon_once = 1;        // H2B_MSM_CANON_ONCE 1: the count kernel keeps the canonical scalars for the scatter kernel (one
+                                   //                    Montgomery -> canonical multiplication per scalar instead of two)
     int msm_ba = 0;                // H2B_MSM_BA         rounds of batched affine additions in front of the mixed additions
                                    //                    (msm_ba.cuh): 0 = none (msm_accumulate_kernel), 1, 2
     int msm_ba_regs = 0;           // H2B_MSM_BA_REGS    0: 4 resident blocks per SM (128 registers), 1: 3 blocks (168)
@@ -178,6 +181,7 @@ struct Tuning {
         else if (name == "msm_no_batch") msm_no_batch = reset ? 0 : (v != 0);
         else if (name == "msm_reduce_classic") msm_reduce_classic = reset ? 0 : (v != 0);
         else if (name == "acc_variant") msm_acc_variant = (!reset && v >= 0 && v < 4) ? v : def.msm_acc_variant;
+        else if (name == "msm_canon_once") msm_canon_once = reset ? def.msm_canon_once : (v != 0);
         else if (name == "msm_ba") msm_ba = (!reset && v >= 0 && v <= 2) ? v : def.msm_ba;
         else if (name == "msm_ba_regs") msm_ba_regs = (!reset && v >= 0 && v <= 1) ? v : def.msm_ba_regs;
         else if (name == "msm_ba_min_mean") msm_ba_min_mean = (!reset && v >= 1) ? v : def.msm_ba_min_mean;
@@ -194,7 +198,7 @@ struct Tuning {
     }
     void from_environment() {
         static const char* names[] = {"msm_c", "msm_pre_c", "msm_precompute", "msm_chunks", "msm_no_ramp", "msm_no_batch",
-                                      "msm_reduce_classic", "msm_reduce_seg", "msm_ba", "msm_ba_regs", "msm_ba_min_mean", "acc_variant", "msm_sort", "msm_sort_tb", "sort_prio", "ntt_full_table_max_log", "ntt_split", "l2_fetch", "peer_timeout_ms"};
+                                      "msm_reduce_classic", "msm_reduce_seg", "msm_canon_once", "msm_ba", "msm_ba_regs", "msm_ba_min_mean", "acc_variant", "msm_sort", "msm_sort_tb", "sort_prio", "ntt_full_table_max_log", "ntt_split", "l2_fetch", "peer_timeout_ms"};
         for (const char* nm : names) {
             std::string env = "H2B_";
             for (const char* c = nm; *c; c++) env.push_back((char)std::toupper((unsigned char)*c));
@@ -431,6 +435,7 @@ int msm_sort_reserve(h2b_ctx* ctx, MsmSortSet& S, const MsmChunkPlan& pl) {
     H2B_CK(S.long_info.reserve((size_t)pl.max_long * sizeof(MsmLongInfo)));
     H2B_CK(S.long_tasks.reserve((size_t)pl.max_tasks * sizeof(MsmLongTask)));
     H2B_CK(S.counters.reserve(256));
+    if (ctx->tune.msm_canon_once) H2B_CK(S.canon.reserve(std::max<size_t>((size_t)g.n * 32, 256)));
     if (ctx->tune.msm_sort && msm_bin_supported(nkeys)) {
         H2B_CK(S.rec_key.reserve(std::max<size_t>((size_t)max_entries * 2, 256)));
         H2B_CK(S.rec_val.reserve(std::max<size_t>((size_t)max_entries * 4, 256)));
@@ -485,11 +490,12 @@ int msm_stage_sort(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, 
                    (const unsigned short*)S.rec_key.as<unsigned short>(), (const uint32_t*)S.rec_val.as<uint32_t>(), nkeys, lb,
                    slices, cap, offsets, ends, entries, sizehist);
     } else {
-        if (n) H2B_LAUNCH(d, "msm_count", MK.count, (n + tb - 1) / tb, tb, 0, g, scalars, counts);
+        Fr* canon = ctx->tune.msm_canon_once ? S.canon.as<Fr>() : nullptr;
+        if (n) H2B_LAUNCH(d, "msm_count", MK.count, (n + tb - 1) / tb, tb, 0, g, scalars, counts, canon);
         H2B_LAUNCH(d, "msm_scan", MK.scan_block_sums, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums);
         H2B_LAUNCH(d, "msm_scan", MK.scan_single_block, 1, SCAN_BLOCK, 0, blocksums, nblk, (uint32_t*)nullptr);
         H2B_LAUNCH(d, "msm_scan", MK.scan_apply, nblk, SCAN_BLOCK, 0, counts, nkeys, blocksums, offsets, ends);
-        if (n) H2B_LAUNCH(d, "msm_scatter", MK.scatter, (n + tb - 1) / tb, tb, 0, g, scalars, ends, entries);
+        if (n) H2B_LAUNCH(d, "msm_scatter", MK.scatter, (n + tb - 1) / tb, tb, 0, g, scalars, (const Fr*)canon, ends, entries);
         H2B_LAUNCH(d, "msm_order", MK.size_hist, (nkeys + tb - 1) / tb, tb, 0, offsets, ends, nkeys, sizehist);
     }
     H2B_LAUNCH(d, "msm_order", MK.scan_single_block, 1, SCAN_BLOCK, 0, sizehist, MSM_SIZE_BINS, (uint32_t*)nullptr);

@@ -153,10 +153,13 @@ H2B_HD constexpr size_t msm_peer_mailbox_bytes() { return msm_peer_tags_offset()
 // kernels
 // ------------------------------------------------------------------------------------------------
 // 1. histogram of (window, |digit|) keys.  counts has windows*nb entries.
-__global__ void msm_count_kernel(MsmGeom g, const Fr* __restrict__ scalars, uint32_t* __restrict__ counts) {
+// canon_out (optional): the canonical scalars, kept for msm_scatter_kernel so that the Montgomery -> canonical multiplication is
+// done once per scalar.
+__global__ void msm_count_kernel(MsmGeom g, const Fr* __restrict__ scalars, uint32_t* __restrict__ counts, Fr* __restrict__ canon_out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
     Fr canon = fe_from_mont(fe_load(scalars + i));
+    if (canon_out) fe_store(canon_out + i, canon);
     msm_signed_digits(canon, g.c, g.windows, [&](uint32_t j, int32_t d) {
         if (d != 0) {
             uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;
@@ -166,11 +169,12 @@ __global__ void msm_count_kernel(MsmGeom g, const Fr* __restrict__ scalars, uint
 }
 
 // 3. scatter point indices into bucket segments; cursor starts as a copy of the segment offsets.
-__global__ void msm_scatter_kernel(MsmGeom g, const Fr* __restrict__ scalars, uint32_t* __restrict__ cursor,
-                                   uint32_t* __restrict__ entries) {
+// canon (optional): what msm_count_kernel left; otherwise the scalar is converted again.
+__global__ void msm_scatter_kernel(MsmGeom g, const Fr* __restrict__ scalars, const Fr* __restrict__ canon_in,
+                                   uint32_t* __restrict__ cursor, uint32_t* __restrict__ entries) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= g.n) return;
-    Fr canon = fe_from_mont(fe_load(scalars + i));
+    Fr canon = canon_in ? fe_load(canon_in + i) : fe_from_mont(fe_load(scalars + i));
     msm_signed_digits(canon, g.c, g.windows, [&](uint32_t j, int32_t d) {
         if (d != 0) {
             uint32_t mag = d < 0 ? (uint32_t)(-d) : (uint32_t)d;

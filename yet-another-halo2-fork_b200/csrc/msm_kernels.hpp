@@ -5,8 +5,8 @@
 
 namespace h2b {
 struct MsmKernelTable {
-    void (*count)(MsmGeom, const Fr*, uint32_t*);
-    void (*scatter)(MsmGeom, const Fr*, uint32_t*, uint32_t*);
+    void (*count)(MsmGeom, const Fr*, uint32_t*, Fr*);
+    void (*scatter)(MsmGeom, const Fr*, const Fr*, uint32_t*, uint32_t*);
     void (*scan_block_sums)(const uint32_t*, uint32_t, uint32_t*);
     void (*scan_single_block)(uint32_t*, uint32_t, uint32_t*);
     void (*scan_apply)(const uint32_t*, uint32_t, const uint32_t*, uint32_t*, uint32_t*);
