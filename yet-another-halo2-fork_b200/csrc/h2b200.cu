@@ -158,7 +158,7 @@ struct Tuning {
                                    //                    (msm_ba.cuh): 0 = none (msm_accumulate_kernel), 1, 2
     int msm_ba_regs = 0;           // H2B_MSM_BA_REGS    0: 4 resident blocks per SM (128 registers), 1: 3 blocks (168)
     int msm_ba_min_mean = 8;       // H2B_MSM_BA_MIN_MEAN  mean bucket population of a chunk below which the plain kernel runs
-    int msm_reduce_seg = 256;      // H2B_MSM_REDUCE_SEG buckets per row / column segment job of the lines reduction
+    int msm_reduce_seg = 512;      // H2B_MSM_REDUCE_SEG buckets per row / column segment job of the lines reduction
     int msm_sort = 0;              // H2B_MSM_SORT       0: global-atomic count + scatter (faster, see msm_bin.cuh), 1: tiled two-level binning
     int msm_sort_tb = 256;         // H2B_MSM_SORT_TB    threads per block of the count / scatter kernels (128 or 256)
     int sort_prio = 1;             // H2B_SORT_PRIO      priority of the binning stream against the compute stream: 1 higher,

@@ -536,7 +536,7 @@ msm_reduce_final_kernel(uint32_t slices, uint32_t log_block_buckets, const Xyzz*
 //   masked  grid (h + w + 1, sets): S^D_b = sum of the row partials whose hi has bit b set, S^C_b likewise over lo, V = sum D.
 //   host    sum_b 2^(b + w) S^D_b + sum_b 2^b S^C_b + V  (msm_horner_terms): ~20 dependent point operations, 0.02 ms on the
 //           host against 0.24 ms for a lone GPU thread.
-__global__ void __launch_bounds__(MSM_REDUCE_THREADS)
+__global__ void __launch_bounds__(MSM_REDUCE_THREADS, 4)      // 128 registers: four blocks per SM (at 130 only three fit)
 msm_reduce_lines_kernel(const Xyzz* __restrict__ buckets, uint32_t nb, uint32_t w, uint32_t rs, uint32_t cs, Xyzz* __restrict__ lines) {
     __shared__ Xyzz sh[MSM_REDUCE_THREADS];
     const uint32_t W = 1u << w, H = nb >> w, lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, set = blockIdx.y;
