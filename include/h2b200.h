@@ -67,7 +67,7 @@ const char* h2b_version(void);
  * h2b_set_option:  tuning knobs of one context.  Each knob is also read ONCE from the environment in h2b_init (variable =
  *                  "H2B_" + upper-case name); value NULL or "" restores the default.  Names: msm_c, msm_pre_c, msm_precompute,
  *                  msm_chunks, msm_no_ramp, msm_no_batch, msm_reduce_classic, msm_reduce_seg, msm_ba (rounds of batched affine additions in
- *                  the bucket accumulation: 0, 1, 2), msm_ba_regs, msm_ba_min_mean, msm_canon_once, acc_variant, msm_sort, msm_sort_tb,
+ *                  the bucket accumulation: 0, 1, 2), msm_ba_regs, msm_ba_min_mean, msm_canon_once, msm_sort_blocks, acc_variant, msm_sort, msm_sort_tb,
  *                  sort_prio (read when the context creates its streams: environment only), ntt_split ("9,9,6"), ntt_full_table_max_log, peer_timeout_ms.  Unknown name -> H2B_E_INVALID. */
 const char* h2b_last_notice(const h2b_ctx* ctx);
 int h2b_set_option(h2b_ctx* ctx, const char* name, const char* value);

@@ -156,8 +156,9 @@ H2B_HD constexpr size_t msm_peer_mailbox_bytes() { return msm_peer_tags_offset()
 // canon_out (optional): the canonical scalars, kept for msm_scatter_kernel so that the Montgomery -> canonical multiplication is
 // done once per scalar.
 __global__ void msm_count_kernel(MsmGeom g, const Fr* __restrict__ scalars, uint32_t* __restrict__ counts, Fr* __restrict__ canon_out) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= g.n) return;
+    // grid-stride: the launch may be narrower than the chunk (msm_sort_blocks) so that the kernel, which is bound by the L2 and
+    // not by the SMs, takes fewer block slots away from the accumulation running beside it
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += gridDim.x * blockDim.x) {
     Fr canon = fe_from_mont(fe_load(scalars + i));
     if (canon_out) fe_store(canon_out + i, canon);
     msm_signed_digits(canon, g.c, g.windows, [&](uint32_t j, int32_t d) {
@@ -166,14 +167,14 @@ __global__ void msm_count_kernel(MsmGeom g, const Fr* __restrict__ scalars, uint
             atomicAdd(counts + (g.pre_stride ? 0 : (size_t)j * g.nb) + (mag - 1), 1u);
         }
     });
+    }
 }
 
 // 3. scatter point indices into bucket segments; cursor starts as a copy of the segment offsets.
 // canon (optional): what msm_count_kernel left; otherwise the scalar is converted again.
 __global__ void msm_scatter_kernel(MsmGeom g, const Fr* __restrict__ scalars, const Fr* __restrict__ canon_in,
                                    uint32_t* __restrict__ cursor, uint32_t* __restrict__ entries) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= g.n) return;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += gridDim.x * blockDim.x) {
     Fr canon = canon_in ? fe_load(canon_in + i) : fe_from_mont(fe_load(scalars + i));
     msm_signed_digits(canon, g.c, g.windows, [&](uint32_t j, int32_t d) {
         if (d != 0) {
@@ -183,6 +184,7 @@ __global__ void msm_scatter_kernel(MsmGeom g, const Fr* __restrict__ scalars, co
             entries[pos] = (g.pre_stride ? j * g.pre_stride + idx : idx) | (d < 0 ? 0x80000000u : 0u);
         }
     });
+    }
 }
 
 // ---- exclusive scan over uint32 (three small kernels; sizes up to a few million) ----------------
