@@ -185,6 +185,26 @@ int h2b_coeff_to_extended_batch_device(h2b_ctx* ctx, const void* const* d_in_col
  *                      n = 0 is an error (the reference panics on `a.len() - 1`). */
 int h2b_batch_invert(h2b_ctx* ctx, void* a, size_t n);
 int h2b_batch_invert_device(h2b_ctx* ctx, void* d_a, size_t n);
+/* h2b_batch_invert_device_noalloc: the same inversion (same kernels, bit-identical results) for callers that must not allocate.
+ *                      It has no counterpart in the reference, and none among the calls above either: it takes no context.
+ *                      Who needs it: a prover that has already taken all of HBM into its own arena (a cudaMalloc would fail), a
+ *                      pipeline that cannot afford the device-wide stall of a cudaMalloc / cudaFree while other streams run, or a
+ *                      component that owns a buffer and a stream but no h2b_ctx (h2b_init allocates; so does the first call of a
+ *                      new size on a context).  This call performs no cudaMalloc, cudaFree or other allocating call, ever.
+ *                      Its tile scratch is a fixed H2B_NOALLOC_SCRATCH_BYTES array inside the library image: every GPU that
+ *                      loads libh2b200.so carries it until the process exits, used or not.
+ *   d_a          n Montgomery Fr on the CURRENT device (cudaSetDevice is the caller's), inverted in place; zeros stay zero.
+ *   n            at most H2B_NOALLOC_MAX_ELEMS; more is refused with H2B_E_INVALID and a message (use the context call).
+ *   cuda_stream  a cudaStream_t (NULL = the default stream).  Unlike the rest of this header the call is NOT synchronous: it
+ *                returns once the three kernels are enqueued; the result is ready when the stream gets there.
+ *   error_out    optional; receives a static string ("" on success) -- there is no context to keep a message in.
+ *   The first call on each device looks the array's device address up (cudaGetSymbolAddress); make that first call before
+ *   any stream capture begins.  All calls share the one array per GPU and it keeps the previous call's contents (nothing in
+ *   it needs to start at zero).  Calls are safe back to back on one stream; two calls that can run at the same time on one GPU
+ *   -- different streams with no dependency between them -- race on the scratch and return garbage: order them. */
+#define H2B_NOALLOC_MAX_ELEMS (1u << 26)
+#define H2B_NOALLOC_SCRATCH_BYTES (2u << 20)
+int h2b_batch_invert_device_noalloc(void* d_a, size_t n, void* cuda_stream, const char** error_out);
 /* h2b_fr_mul_device: d_out[i] = d_a[i] * d_b[i] (* scale32 when it is not NULL), n device-resident field elements; d_out may
  * alias d_a.  The coefficient scaling a_t * s^t that puts a polynomial on the coset s * H before a size-n transform --
  * distribute_powers_zeta (poly/domain.rs:325-341) for an arbitrary shift, given as its power table -- and the inverse scaling

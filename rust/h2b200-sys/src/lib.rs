@@ -63,6 +63,8 @@ extern "C" {
     // polynomial helpers (arithmetic.rs:56-120, ff::BatchInvert, the Z running products)
     pub fn h2b_batch_invert(ctx: *mut h2b_ctx, a: *mut c_void, n: usize) -> c_int;
     pub fn h2b_batch_invert_device(ctx: *mut h2b_ctx, d_a: *mut c_void, n: usize) -> c_int;
+    // context-free, allocation-free variant (scratch inside the library image; n <= 2^26; asynchronous on `cuda_stream`)
+    pub fn h2b_batch_invert_device_noalloc(d_a: *mut c_void, n: usize, cuda_stream: *mut c_void, error_out: *mut *const c_char) -> c_int;
     pub fn h2b_fr_mul_device(ctx: *mut h2b_ctx, d_a: *const c_void, d_b: *const c_void, scale32_or_null: *const c_void, d_out: *mut c_void, n: usize) -> c_int;
     pub fn h2b_grand_product(ctx: *mut h2b_ctx, v: *const c_void, n: usize, init32: *const c_void, z: *mut c_void, out_len: usize) -> c_int;
     pub fn h2b_grand_product_device(ctx: *mut h2b_ctx, d_v: *const c_void, n: usize, init32: *const c_void, d_z: *mut c_void, out_len: usize) -> c_int;

@@ -49,6 +49,7 @@ SYMBOLS = {
     "h2b_coeff_to_extended_batch_device": (_int, [_vp, ctypes.POINTER(_vp), ctypes.POINTER(_vp), _sz, _u32, _u32, _vp, _vp, _vp]),
     "h2b_batch_invert": (_int, [_vp, _vp, _sz]),
     "h2b_batch_invert_device": (_int, [_vp, _vp, _sz]),
+    "h2b_batch_invert_device_noalloc": (_int, [_vp, _sz, _vp, ctypes.POINTER(ctypes.c_char_p)]),
     "h2b_fr_mul_device": (_int, [_vp, _vp, _vp, _vp, _vp, _sz]),
     "h2b_grand_product": (_int, [_vp, _vp, _sz, _vp, _vp, _sz]),
     "h2b_grand_product_device": (_int, [_vp, _vp, _sz, _vp, _vp, _sz]),
