@@ -360,6 +360,27 @@ def test_coset_prover_bytes_match(ctx, name, k, workers):
         ops.cosets = None
 
 
+def test_coset_key_serialization_round_trip(ctx):
+    """ADVICE r2: a key read back from bytes must drive the coset prover too (ProvingKey::read yields a fully usable key,
+    plonk.rs:289-316), and a coset-only key (extended=False) must serialise to the very bytes of the full key."""
+    from h2b200.plonk import serialization as S
+    from h2b200.plonk.cosets import CosetProver
+    k = 6
+    circ = example.MyCircuit(k, 42)
+    cc, cs, ref_dom, ops, vk, pk = _device_setup(ctx, k, circ)
+    lean_pk = plonk.keygen_pk(ops, vk, cc, extended=False)
+    blob = S.pk_write(ops, pk, "RawBytes")
+    assert S.pk_write(ops, lean_pk, "RawBytes") == blob and S.pk_bytes_length(ops, lean_pk, "RawBytes") == len(blob)
+    pk2 = S.pk_read(ops, blob, "RawBytes", cs)
+    expected = _prove_with(circ, ops, pk, "OneNg", 4)
+    ops.cosets = CosetProver(ops, [0, 0])
+    try:
+        assert _prove_with(circ, ops, pk2, "OneNg", 4) == expected
+    finally:
+        ops.cosets.close()
+        ops.cosets = None
+
+
 def test_coset_prover_batch_of_two_circuits(ctx):
     from h2b200.plonk.cosets import CosetProver
     k = 6

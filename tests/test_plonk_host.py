@@ -324,6 +324,20 @@ def test_key_serialization_round_trip(setup, fmt):
     assert plonk_verifier.verify_proof(vk2, circ.instances(), proof, SECRET, 1 << K)
 
 
+def test_coset_only_key_serialises_like_the_full_key(setup):
+    """keygen_pk(extended=False) keeps no extended-domain vectors; writing it rebuilds them, byte for byte what the full key
+    writes, and a key that was read back carries the coefficient forms of l_0 / l_last / l_active the coset prover needs."""
+    from h2b200.plonk import serialization as S
+    circ, ops, vk, pk = setup
+    lean = plonk.keygen_pk(ops, vk, circ.compile(), extended=False)
+    assert lean.l0 is None and lean.fixed_cosets == []
+    blob = S.pk_write(ops, pk, "RawBytes")
+    assert S.pk_write(ops, lean, "RawBytes") == blob and S.pk_bytes_length(ops, lean, "RawBytes") == len(blob)
+    pk2 = S.pk_read(ops, blob, "RawBytes", vk.cs)
+    assert pk2.l0_poly == pk.l0_poly and pk2.l_last_poly == pk.l_last_poly and pk2.l_active_poly == pk.l_active_poly
+    assert pk2.l0_poly is not None
+
+
 def test_key_serialization_rejects():
     from h2b200.plonk import serialization as S
     with pytest.raises(IOError, match="version"):

@@ -177,14 +177,11 @@ def keygen_vk(ops, circuit: C.CompiledCircuit, transcript_repr: Optional[int] = 
     return vk
 
 
-def keygen_pk(ops, vk: VerifyingKey, circuit: C.CompiledCircuit, extended: bool = True) -> ProvingKey:
-    """keygen.rs:103-187."""
-    cs, n = vk.cs, ops.n
-    if n < cs.minimum_rows():
-        raise ValueError(f"not enough rows available (k = {ops.k})")
-    fixed_values = [_fixed_column(ops, col) for col in circuit.preprocessing.fixed]
-    fixed_polys = [ops.lagrange_to_coeff(ops.clone(v)) for v in fixed_values]
-    bf = cs.blinding_factors()
+def indicator_polys(ops, cs):
+    """keygen.rs:134-167 in coefficient form: l_0, l_blind (the last `blinding_factors` rows), l_last, and l_active = 1 - (l_last +
+    l_blind).  They depend on the constraint system and the domain only, so a key that was read back (serialization.pk_read) gets
+    them the same way a generated one does."""
+    n, bf = ops.n, cs.blinding_factors()
 
     def indicator(rows):
         p = ops.zeros(n)
@@ -192,16 +189,44 @@ def keygen_pk(ops, vk: VerifyingKey, circuit: C.CompiledCircuit, extended: bool 
             ops.write_ints(p, r, [1])
         return ops.lagrange_to_coeff(p)
 
-    # extended=False: a key for the coset prover (cosets.py) -- nothing of the extended length n * e is built or kept
-    ext = (lambda p: ops.coeff_to_extended(p)) if extended else (lambda p: None)
-    fixed_cosets = [ext(p) for p in fixed_polys] if extended else []
     l0_poly, l_blind_poly, l_last_poly = indicator([0]), indicator(range(n - bf, n)), indicator([n - bf - 1])
-    one_minus = C.sub(C.const(1), C.add(PX.col(0), PX.col(1)))
     # 1 - (l_last + l_blind) in coefficient form: negate every coefficient, add one to the constant term
     l_active_poly = PX.pointwise(ops, C.neg(C.add(PX.col(0), PX.col(1))), [l_last_poly, l_blind_poly])
     ops.write_ints(l_active_poly, 0, [(ops.read_ints(l_active_poly, 0, 1)[0] + 1) % F.R_MOD])
+    return l0_poly, l_blind_poly, l_last_poly, l_active_poly
+
+
+def _l_active_row(ops, l_last_ext, l_blind_ext):
+    one_minus = C.sub(C.const(1), C.add(PX.col(0), PX.col(1)))
+    return PX.pointwise(ops, one_minus, [l_last_ext, l_blind_ext], extended=True)
+
+
+def extended_parts(ops, pk):
+    """(l0, l_last, l_active_row, fixed_cosets, permutation cosets) in the extended domain -- what ProvingKey::write stores
+    (plonk.rs:276-287).  A key made with keygen_pk(extended=False) does not hold them; they are rebuilt here from its coefficient
+    forms (nothing is cached: such a key exists to avoid keeping n * e rows per column)."""
+    if pk.l0 is not None:
+        return pk.l0, pk.l_last, pk.l_active_row, pk.fixed_cosets, pk.permutation.cosets
+    ext = ops.coeff_to_extended
+    _, l_blind_poly, _, _ = indicator_polys(ops, pk.vk.cs)
+    l_last = ext(pk.l_last_poly)
+    return (ext(pk.l0_poly), l_last, _l_active_row(ops, l_last, ext(l_blind_poly)), [ext(p) for p in pk.fixed_polys],
+            [ext(p) for p in pk.permutation.polys])
+
+
+def keygen_pk(ops, vk: VerifyingKey, circuit: C.CompiledCircuit, extended: bool = True) -> ProvingKey:
+    """keygen.rs:103-187."""
+    cs, n = vk.cs, ops.n
+    if n < cs.minimum_rows():
+        raise ValueError(f"not enough rows available (k = {ops.k})")
+    fixed_values = [_fixed_column(ops, col) for col in circuit.preprocessing.fixed]
+    fixed_polys = [ops.lagrange_to_coeff(ops.clone(v)) for v in fixed_values]
+    # extended=False: a key for the coset prover (cosets.py) -- nothing of the extended length n * e is built or kept
+    ext = (lambda p: ops.coeff_to_extended(p)) if extended else (lambda p: None)
+    fixed_cosets = [ext(p) for p in fixed_polys] if extended else []
+    l0_poly, l_blind_poly, l_last_poly, l_active_poly = indicator_polys(ops, cs)
     l0, l_last = ext(l0_poly), ext(l_last_poly)
-    l_active_row = PX.pointwise(ops, one_minus, [l_last, ext(l_blind_poly)], extended=True) if extended else None
+    l_active_row = _l_active_row(ops, l_last, ext(l_blind_poly)) if extended else None
     assembly = Assembly.new_from_assembly_mid(n, cs.permutation_columns, circuit.preprocessing.copies)
     permutations = assembly.permutations(ops, ops.domain.omega)
     polys = [ops.lagrange_to_coeff(ops.clone(p)) for p in permutations]

@@ -157,16 +157,22 @@ def vk_read(data: bytes, fmt: str, cs: C.ConstraintSystemBack, make_domain, tran
 def pk_write(ops, pk: K.ProvingKey, fmt: str) -> bytes:
     """plonk.rs:276-287 + permutation.rs:60-72."""
     out = vk_write(pk.vk, fmt)
-    for p in (pk.l0, pk.l_last, pk.l_active_row):
+    # (a coset-prover key, keygen_pk(extended=False), holds no extended-domain parts: they are rebuilt for the file)
+    l0, l_last, l_active_row, fixed_cosets, perm_cosets = K.extended_parts(ops, pk)
+    for p in (l0, l_last, l_active_row):
         out += write_polynomial(ops, p, fmt)
-    for polys in (pk.fixed_values, pk.fixed_polys, pk.fixed_cosets, pk.permutation.permutations, pk.permutation.polys,
-                  pk.permutation.cosets):
+    for polys in (pk.fixed_values, pk.fixed_polys, fixed_cosets, pk.permutation.permutations, pk.permutation.polys, perm_cosets):
         out += write_polynomial_slice(ops, polys, fmt)
     return out
 
 
 def pk_bytes_length(ops, pk: K.ProvingKey, fmt: str) -> int:        # plonk.rs:259-272
     rows = lambda p: ops.rows(p)
+    if pk.l0 is None:          # coset-prover key: the extended parts are not held, their sizes follow from the domain
+        ne = ops.n << (ops.domain.extended_k - ops.k)
+        held = (pk.fixed_values, pk.fixed_polys, pk.permutation.permutations, pk.permutation.polys)
+        return (vk_bytes_length(pk.vk, fmt) + 12 + 32 * 3 * ne + sum(polynomial_slice_byte_length(ops, s) for s in held)
+                + 2 * 4 + (len(pk.fixed_polys) + len(pk.permutation.polys)) * (4 + 32 * ne))
     return (vk_bytes_length(pk.vk, fmt) + 12 + 32 * (rows(pk.l0) + rows(pk.l_last) + rows(pk.l_active_row))
             + sum(polynomial_slice_byte_length(ops, s) for s in (pk.fixed_values, pk.fixed_polys, pk.fixed_cosets,
                                                                    pk.permutation.permutations, pk.permutation.polys,
@@ -180,5 +186,7 @@ def pk_read(ops, data: bytes, fmt: str, cs: C.ConstraintSystemBack) -> K.Proving
     assert vk.domain.k == ops.k and vk.domain.quotient_poly_degree == cs.degree() - 1, "ops is bound to another domain"
     l0, l_last, l_active_row = (read_polynomial(ops, r, fmt) for _ in range(3))
     fixed_values, fixed_polys, fixed_cosets, permutations, polys, cosets = (read_polynomial_vec(ops, r, fmt) for _ in range(6))
+    # the coefficient forms the coset prover reads (cosets.py) are not part of the file: rebuilt as keygen_pk builds them
+    l0_poly, _, l_last_poly, l_active_poly = K.indicator_polys(ops, cs)
     return K.ProvingKey(vk, l0, l_last, l_active_row, fixed_values, fixed_polys, fixed_cosets,
-                        K.PermutationProvingKey(permutations, polys, cosets), K.Evaluator(cs))
+                        K.PermutationProvingKey(permutations, polys, cosets), K.Evaluator(cs), l0_poly, l_last_poly, l_active_poly)
