@@ -418,6 +418,8 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
     # NCCL carries only the set-up and timing plumbing (mailbox handles, barriers, max over ranks): the MSM's own exchange is
     # the library's peer-store kernel
     eng.peer_attach(rank, world, h2b200.dist_all_gather_bytes if world > 1 else None)
+    if world > 1:
+        dist.barrier()          # h2b_peer_attach clears this rank's mailbox: every rank is attached before any rank publishes
 
     def barrier():
         if world > 1:

@@ -119,7 +119,13 @@ int h2b_msm_combine(const void* parts, uint32_t n_parts, uint32_t c, uint32_t wi
  *                     world entries) overrides the handle of a same-process peer with its pointer.  One device per context.
  *   h2b_msm_sharded : this rank's n scalars against its registered range; every rank must call it, with equal shard sizes
  *                     (the ranks must reduce with the same window geometry; a mismatch or a missing peer is reported as
- *                     H2B_E_CUDA after `peer_timeout_ms`).  out96 = the normalised sum over all ranks, on every rank. */
+ *                     H2B_E_CUDA after `peer_timeout_ms`).  out96 = the normalised sum over all ranks, on every rank.
+ *   Ordering and recovery: h2b_peer_attach clears this rank's mailbox and restarts its call counter, so EVERY rank must have
+ *   returned from h2b_peer_attach before ANY rank calls h2b_msm_sharded (a barrier in the launcher).  Every h2b_msm_sharded
+ *   call counts, refused or failed ones included, so after an error that every rank saw (or a call every rank made) the group
+ *   can simply call again.  A rank whose exchange fails marks the terms it had published, so a peer arriving later fails the
+ *   same call ("gave up") rather than folding them.  If a rank skipped a call altogether the peers report it ("gave up" /
+ *   "is ahead of this rank" / time-out); then all ranks attach again (same handles), barrier, and continue. */
 #define H2B_PEER_HANDLE_BYTES 64
 int h2b_peer_export(h2b_ctx* ctx, void* handle64_out, void** local_ptr_out);
 int h2b_peer_attach(h2b_ctx* ctx, int rank, int world, const void* handles, void* const* local_ptrs_or_null);

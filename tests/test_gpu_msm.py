@@ -455,6 +455,135 @@ def test_msm_sharded_reports_a_missing_peer():
         c.close()
 
 
+def _peer_group(world, options=()):
+    """`world` single-GPU contexts in this process, dealt over the visible devices, exported and attached to each other."""
+    import h2b200
+    ndev = h2b200.load().h2b_device_count()
+    ctxs = [h2b200.Context([r % ndev]) for r in range(world)]
+    for c in ctxs:
+        for name, value in options:
+            c.set_option(name, value)
+    engs = [h2b200.B200Engine(c) for c in ctxs]
+    for e in engs:
+        e.peer_export()
+    _attach_all(engs)
+    return ctxs, engs
+
+
+def _attach_all(engs):
+    world = len(engs)
+    for r, e in enumerate(engs):
+        e.peer_attach(r, world, None, {q: engs[q] for q in range(world) if q != r})
+
+
+def test_msm_sharded_after_reattach_ignores_the_old_groups_mailbox():
+    """h2b_peer_attach restarts the epoch at 0.  The flags, tags and slots three earlier calls left in the mailboxes
+    must not satisfy the new group's epochs 1..3 (they would be folded as if they were this call's terms): attach clears them,
+    and the wait accepts exactly its own epoch."""
+    world, n = 2, 6000
+    ctxs, engs = _peer_group(world)
+    per = n // world
+    b = C.gen_bases(n, 21)
+    descs = [engs[r].get_base_descriptor(np.ascontiguousarray(b[r * per:(r + 1) * per])) for r in range(world)]
+    for session in range(3):
+        if session:
+            _attach_all(engs)                # the same mailboxes, a new group
+        for rep in range(3):
+            s = C.random_fr(n, 500 + 10 * session + rep)          # different scalars every call: stale terms give a wrong point
+            exp = oracle_affine(s, b)
+            outs = _run_ranks(lambda r: engs[r].msm_sharded(np.ascontiguousarray(s[r * per:(r + 1) * per]), descs[r], n), world)
+            for o in outs:
+                check(o, exp)
+    for d in descs:
+        d.release()
+    for c in ctxs:
+        c.close()
+
+
+def test_msm_sharded_recovers_after_a_one_sided_failure():
+    """The recovery contract of include/h2b200.h: every h2b_msm_sharded call counts, failed ones too.  Rank 0's call is refused
+    (unknown handle) while rank 1 publishes and times out; the next call of both ranks is in step again and correct.  A rank that
+    SKIPS a call gets an error on its next one (the peer's terms for the skipped call are marked "gave up"), never a silently
+    wrong point; attaching again repairs the group."""
+    import h2b200
+    world, n = 2, 4000
+    ctxs, engs = _peer_group(world, [("peer_timeout_ms", 400)])
+    per = n // world
+    b = C.gen_bases(n, 22)
+    descs = [engs[r].get_base_descriptor(np.ascontiguousarray(b[r * per:(r + 1) * per])) for r in range(world)]
+    shard = lambda s, r: np.ascontiguousarray(s[r * per:(r + 1) * per])
+
+    def run(seed, broken_rank=None):
+        s = C.random_fr(n, seed)
+        errs = [None] * world
+
+        def call(r):
+            try:
+                if r == broken_rank:
+                    bogus = h2b200.BaseDescriptor.__new__(h2b200.BaseDescriptor)
+                    bogus.ctx, bogus.n, bogus.handle = ctxs[r], per, 0xDEAD
+                    return engs[r].msm_sharded(shard(s, r), bogus, n)
+                return engs[r].msm_sharded(shard(s, r), descs[r], n)
+            except h2b200.H2bError as e:
+                errs[r] = str(e)
+                return None
+        outs = _run_ranks(call, world)
+        return s, outs, errs
+
+    s, outs, errs = run(700)
+    assert not any(errs)
+    s, outs, errs = run(701, broken_rank=0)
+    assert "unknown bases handle" in errs[0] and "timed out" in errs[1] and "rank 0" in errs[1]
+    for seed in (702, 703):                  # both parities after the failure
+        s, outs, errs = run(seed)
+        assert not any(errs), errs
+        for o in outs:
+            check(o, oracle_affine(s, b))
+    # rank 1 skips a call altogether: rank 0 times out; on the next call rank 0 is one epoch ahead and both ranks fail loudly
+    s = C.random_fr(n, 704)
+    with pytest.raises(h2b200.H2bError) as e:
+        engs[0].msm_sharded(shard(s, 0), descs[0], n)
+    assert "timed out" in str(e.value)
+    s, outs, errs = run(705)
+    assert errs[1] and "rank 0 gave up" in errs[1], errs      # the terms rank 0 published for the call rank 1 skipped are marked
+    assert errs[0] and "timed out" in errs[0], errs             # rank 1 never reaches rank 0's epoch
+    _attach_all(engs)
+    s, outs, errs = run(706)
+    assert not any(errs), errs
+    for o in outs:
+        check(o, oracle_affine(s, b))
+    for d in descs:
+        d.release()
+    for c in ctxs:
+        c.close()
+
+
+def test_msm_sharded_without_window_multiples_at_2p20():
+    """bases registered without the precomputed multiples (msm_precompute=0, or skipped for lack of memory) reduce one
+    bucket set per window; at n_total = 2^20 (c = 16, 2^15 buckets) the low-latency reduction would leave 16 x 17 terms, more
+    than a mailbox slot holds.  The sharded path then takes the classic reduction (one term per window) instead of failing."""
+    import h2b200
+    world, n = 2, 1 << 20
+    C.use_all_host_cores()
+    ctxs, engs = _peer_group(world, [("msm_precompute", 0)])
+    per = n // world
+    t0 = C.bench_t0()
+    d_b = h2b200.synth.device_bases(ctxs[0], n, t0 + 5)
+    d_s = h2b200.synth.chacha_scalars_device(ctxs[0], n)
+    s, b = d_s.cpu().numpy().view(np.uint64), d_b.cpu().numpy().view(np.uint64)
+    descs = [engs[r].get_base_descriptor(np.ascontiguousarray(b[r * per:(r + 1) * per])) for r in range(world)]
+    assert all(d.info()[0] == 0 for d in descs)
+    exp = oracle_affine(s, b)
+    for rep in range(2):
+        outs = _run_ranks(lambda r: engs[r].msm_sharded(np.ascontiguousarray(s[r * per:(r + 1) * per]), descs[r], n), world)
+        for o in outs:
+            check(o, exp)
+    for d in descs:
+        d.release()
+    for c in ctxs:
+        c.close()
+
+
 def test_seeded_inputs_match_the_oracle(ctx, engine):
     """the bench inputs come from ChaCha20 seeds so that CPU oracle and GPU agree: device generator
     (h2b_fr_random_chacha20_device / h2b_synth_bases) == oracle/cref.py's own ChaCha20 and base generator."""

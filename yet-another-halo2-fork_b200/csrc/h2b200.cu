@@ -99,6 +99,7 @@ struct Dev {
     std::map<std::string, NttPlanDev> plans;
     bool prof = false;
     bool peer_attr = false;
+    bool bin_attr = false;             // function attributes are per device: the tiled binning kernels' shared-memory opt-in was made here
     std::vector<ProfRec> recs;
     std::vector<cudaEvent_t> ev_pool;
     uint64_t launches = 0;
@@ -474,8 +475,10 @@ int msm_stage_sort(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan& pl, 
         // two-level binning, shared-memory atomics only (msm_bin.cuh): digits + coarse totals, scan of the totals, partition into
         // coarse bins, one block per coarse bin for offsets / ends / placement / population histogram
         static const MsmBinKernelTable& BK = msm_bin_kernel_table();
-        static const int prepared = BK.prepare();
-        if (prepared != 0) { d.launch_stream = d.stream; return ctx->fail(H2B_E_CUDA, "msm: cannot reserve the shared memory of the binning kernel"); }
+        if (!d.bin_attr) {          // (this device is current: every caller of the sort stage has set it)
+            if (BK.prepare() != 0) { cudaGetLastError(); d.launch_stream = d.stream; return ctx->fail(H2B_E_CUDA, "msm: cannot reserve the shared memory of the binning kernel"); }
+            d.bin_attr = true;
+        }
         const uint32_t lb = msm_bin_low_bits(nkeys), ncoarse = (nkeys + (1u << lb) - 1u) >> lb;
         uint32_t* cursor = S.coarse.as<uint32_t>();                       // [0, ncoarse]: totals -> exclusive scan -> run cursors
         uint32_t* start = cursor + MSM_BIN_MAX_COARSE + 4;                // [0, ncoarse]: the scan, kept; start[ncoarse] = total
@@ -552,8 +555,11 @@ int msm_stage_accumulate(h2b_ctx* ctx, Dev& d, MsmSortSet& S, const MsmChunkPlan
     return H2B_OK;
 }
 
+// max_terms_total: upper bound on sets x terms the caller can take (the peer mailbox slot holds MSM_PEER_SLOT_POINTS); 0 = no bound.
+// Beyond it the classic reduction (one term per bucket set) is used -- a pure function of the geometry, so every rank of a
+// sharded MSM decides alike.
 int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmLaunchInfo* info, uint32_t batch_sets = 0,
-                     bool copy_back = true) {
+                     bool copy_back = true, uint32_t max_terms_total = 0) {
     MsmShape sp = msm_shape(0, c, pre_stride, 0);
     const MsmGeom& g = sp.g;
     const uint32_t kw = batch_sets ? batch_sets : sp.kw;      // a batch of MSMs: one shared-window bucket set per column
@@ -569,7 +575,8 @@ int msm_stage_reduce(h2b_ctx* ctx, Dev& d, uint32_t c, uint32_t pre_stride, MsmL
     Xyzz* set_sums = nullptr;
     MsmGeom gr = g;
     gr.windows = kw;
-    const bool lines_path = g.nb >= (1u << 14) && !ctx->tune.msm_reduce_classic;
+    const bool lines_fit = !max_terms_total || (uint64_t)kw * (lg_nb + 1) <= max_terms_total;
+    const bool lines_path = g.nb >= (1u << 14) && !ctx->tune.msm_reduce_classic && lines_fit;
     info->n_terms = 1;
     info->exps[0] = 0;
     if (lines_path) {
@@ -727,7 +734,7 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
             S.consumed_pending = true;
         }
         if (rc) return rc;
-        rc = msm_stage_reduce(ctx, d, use_c, stride, &infos[di], 0, !peer_exchange);
+        rc = msm_stage_reduce(ctx, d, use_c, stride, &infos[di], 0, !peer_exchange, peer_exchange ? (uint32_t)MSM_PEER_SLOT_POINTS : 0u);
         if (rc) return rc;
         if (peer_exchange) { rc = msm_peer_epilogue(ctx, d, infos[di]); if (rc) return rc; }
         H2B_CK(cudaEventRecord(d.ev_last, d.stream));
@@ -769,7 +776,9 @@ int msm_run(h2b_ctx* ctx, const Bases& B, const void* scalars, bool on_device, s
         max_ms = std::max(max_ms, (double)ms);
         if (peer_exchange && *ctx->peer.status != 0) {
             const uint32_t st = *ctx->peer.status;
-            return ctx->fail(H2B_E_CUDA, st >= 0x100 ? "msm_sharded: rank " + std::to_string(st - 0x100) + " reduced with a different window geometry (register equal shard sizes)"
+            return ctx->fail(H2B_E_CUDA, st >= 0x300 ? "msm_sharded: rank " + std::to_string(st - 0x300) + " gave up on this call (it timed out or failed in its exchange)"
+                                         : st >= 0x200 ? "msm_sharded: rank " + std::to_string(st - 0x200) + " is ahead of this rank (the ranks have not made the same number of calls): every rank must h2b_peer_attach again"
+                                         : st >= 0x100 ? "msm_sharded: rank " + std::to_string(st - 0x100) + " reduced with a different window geometry (register equal shard sizes)"
                                                      : "msm_sharded: timed out waiting for the terms of rank " + std::to_string(st - 1));
         }
         msm_fold_terms(d, infos[di], windows_out);
@@ -789,7 +798,7 @@ int msm_peer_epilogue(h2b_ctx* ctx, Dev& d, const MsmLaunchInfo& info) {
     const size_t smem = (size_t)nt * (size_t)P.world * sizeof(Xyzz);
     if (smem > ((size_t)200 << 10)) return ctx->fail(H2B_E_INVALID, "msm_sharded: terms x ranks exceed the shared memory of the fold");
     if (!d.peer_attr) { H2B_CK(cudaFuncSetAttribute((const void*)MK.peer_exchange, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 << 10)); d.peer_attr = true; }
-    const uint64_t epoch = ++P.epoch;
+    const uint64_t epoch = P.epoch;          // bumped by h2b_msm_sharded on entry, so that a call failing before this point still counts
     // geometry tag: every rank must have reduced to the same terms with the same weights
     uint64_t tag = ((uint64_t)info.c << 48) | ((uint64_t)info.windows << 32) | ((uint64_t)info.n_terms << 16) | (info.pre ? 1u : 0u);
     *P.status = 0xffffffffu;
@@ -804,11 +813,26 @@ int msm_peer_epilogue(h2b_ctx* ctx, Dev& d, const MsmLaunchInfo& info) {
 // column k is "chunk" k of the two-stream pipeline with its own bucket set, and ONE reduction launch handles every set, so the
 // binning of column k+1 hides behind the accumulation of column k and the reduction latency is paid once.
 // Needs the precomputed-window layout (one bucket set per MSM) on a single device; callers fall back to a loop otherwise.
+int msm_run_batch_enqueue(h2b_ctx* ctx, const Bases& B, const void* const* cols, bool on_device, size_t m, size_t n, Xyzz* sums_out,
+                          uint32_t* c_out);
 int msm_run_batch(h2b_ctx* ctx, const Bases& B, const void* const* cols, bool on_device, size_t m, size_t n, Xyzz* sums_out,
                   uint32_t* c_out) {
     const BasesShard& sh = B.shard[0];
     Dev& d = ctx->devs[0];
     H2B_CK(cudaSetDevice(d.id));
+    int rc = msm_run_batch_enqueue(ctx, B, cols, on_device, m, n, sums_out, c_out);
+    if (rc) {          // copies / kernels may be in flight on three streams and `consumed` events pending: start the next call clean
+        cudaStreamSynchronize(d.copy_stream); cudaStreamSynchronize(d.sort_stream); cudaStreamSynchronize(d.stream);
+        d.ms[0].consumed_pending = d.ms[1].consumed_pending = false;
+        d.launch_stream = d.stream;
+        cudaGetLastError();
+    }
+    return rc;
+}
+int msm_run_batch_enqueue(h2b_ctx* ctx, const Bases& B, const void* const* cols, bool on_device, size_t m, size_t n, Xyzz* sums_out,
+                          uint32_t* c_out) {
+    const BasesShard& sh = B.shard[0];
+    Dev& d = ctx->devs[0];
     begin_call(d);
     const Affine* dev_bases = reinterpret_cast<const Affine*>(sh.pre);
     const uint32_t use_c = sh.pre_c, stride = (uint32_t)sh.count;
@@ -1363,6 +1387,11 @@ int h2b_peer_attach(h2b_ctx* ctx, int rank, int world, const void* handles, void
         P.opened.push_back(q);
         P.table.mailbox[r] = q;
     }
+    // A fresh group starts at epoch 0 with an empty mailbox: flags, tags and slots left by an earlier group (or by calls that
+    // failed half way) must not be taken for this group's.  Peers write into this mailbox as soon as THEY are attached and call
+    // h2b_msm_sharded, hence the rule in the header: every rank finishes h2b_peer_attach before any rank calls h2b_msm_sharded.
+    H2B_CK(cudaMemset(P.mailbox, 0, msm_peer_mailbox_bytes()));
+    H2B_CK(cudaDeviceSynchronize());
     P.rank = rank; P.world = world; P.epoch = 0;
     // ranks attached through IPC handles are other processes on this host, each with a copy pool of its own for pageable host
     // buffers: share the host threads between them (at N = 8, eight full-size pools oversubscribe the cores and the staging
@@ -1372,8 +1401,11 @@ int h2b_peer_attach(h2b_ctx* ctx, int rank, int world, const void* handles, void
 }
 int h2b_msm_sharded(h2b_ctx* ctx, uint64_t handle, const void* scalars, int scalars_on_device, size_t n, size_t n_total, void* out96) {
     if (!ctx) return H2B_E_INVALID;
-    if (!out96 || (!scalars && n)) return ctx->fail(H2B_E_INVALID, "msm_sharded: null argument");
     std::lock_guard<std::mutex> lk(ctx->mu);
+    // Every call counts, also one that is refused below or fails before its exchange: the epoch is what keeps the ranks' mailbox
+    // slots in step, and a rank that skipped one would take a peer's previous terms for the current ones.
+    if (ctx->peer.world > 0) ++ctx->peer.epoch;
+    if (!out96 || (!scalars && n)) return ctx->fail(H2B_E_INVALID, "msm_sharded: null argument");
     auto it = ctx->bases.find(handle);
     if (it == ctx->bases.end()) return ctx->fail(H2B_E_INVALID, "msm_sharded: unknown bases handle");
     if (n == 0) return ctx->fail(H2B_E_INVALID, "msm_sharded: every rank needs a non-empty point range");

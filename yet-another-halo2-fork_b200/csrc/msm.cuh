@@ -598,6 +598,7 @@ msm_reduce_masked_kernel(const Xyzz* __restrict__ lines, uint32_t h, uint32_t w,
 // ONE kernel publishes this rank's reduced terms into every peer's mailbox over NVLink (plain peer stores + a release flag),
 // waits for the same epoch from every peer, and folds the `world` contributions per term; the sums go straight into page-locked
 // host memory.  No NCCL call, no host staging: the exchange is the epilogue of the reduction on the compute stream.
+constexpr unsigned long long MSM_PEER_GAVE_UP = 1ull << 63;      // flag bit: "published for this epoch, then failed the call"
 H2B_D void st_release_sys_u64(unsigned long long* p, unsigned long long v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
@@ -642,7 +643,13 @@ msm_peer_exchange_kernel(const Xyzz* __restrict__ my_terms, uint32_t n_terms, Ms
         const unsigned long long* flag = reinterpret_cast<const unsigned long long*>(
             static_cast<unsigned char*>(peers.mailbox[rank]) + msm_peer_flags_offset()) + parity * MSM_PEER_MAX_RANKS + t;
         const unsigned long long t0 = global_timer_ns();
-        while (ld_acquire_sys_u64(flag) < epoch) {
+        // exactly this epoch: a smaller value is the peer's previous use of this slot (or the cleared mailbox), a larger one means
+        // the peer has made more calls than this rank and the slot no longer holds the terms of this call
+        // (bit 63 set: the peer published for that epoch but then gave up on the call -- see the failure path below)
+        for (;;) {
+            const unsigned long long f = ld_acquire_sys_u64(flag), fe = f & ~MSM_PEER_GAVE_UP;
+            if (fe == epoch) { if (f & MSM_PEER_GAVE_UP) atomicExch(&failed, 0x300u + t); break; }
+            if (fe > epoch) { atomicExch(&failed, 0x200u + t); break; }
             if (global_timer_ns() - t0 > timeout_ns) { atomicExch(&failed, 1u + t); break; }
             __nanosleep(200);
         }
@@ -651,7 +658,17 @@ msm_peer_exchange_kernel(const Xyzz* __restrict__ my_terms, uint32_t n_terms, Ms
         if (!failed && __ldcg(tags + t) != tag) atomicExch(&failed, 0x100u + t);
     }
     __syncthreads();
-    if (failed) { if (t == 0) *status = failed; return; }
+    if (failed) {
+        // This rank will report an error for this call.  A peer that has not looked yet must not fold the terms published above as
+        // if the call had gone through everywhere (it might be a call this rank's group has already abandoned): mark them.
+        if (t < world) {
+            unsigned long long* flag = reinterpret_cast<unsigned long long*>(static_cast<unsigned char*>(peers.mailbox[t]) +
+                                                                             msm_peer_flags_offset()) + parity * MSM_PEER_MAX_RANKS + rank;
+            st_release_sys_u64(flag, epoch | MSM_PEER_GAVE_UP);
+        }
+        if (t == 0) *status = failed;
+        return;
+    }
     // 3. fold over the ranks, per term (tree through shared memory)
     const unsigned char* mine = static_cast<const unsigned char*>(peers.mailbox[rank]) + (size_t)parity * MSM_PEER_MAX_RANKS * msm_peer_slot_bytes();
     for (uint32_t i = t; i < n_terms * world; i += nt) {

@@ -254,7 +254,8 @@ class B200Engine:
     def peer_attach(self, rank: int, world: int, all_gather_bytes=None, local_peers=None):
         """Join a group of `world` single-GPU contexts that shard MSMs by point range.  `all_gather_bytes(b)` must return the
         list of every rank's 64-byte blob in rank order (torch.distributed plumbing: see `dist_all_gather_bytes`);
-        `local_peers` = {rank: B200Engine} for peers living in this process (each already `peer_export`ed)."""
+        `local_peers` = {rank: B200Engine} for peers living in this process (each already `peer_export`ed).
+        Attaching clears this rank's mailbox and call counter: barrier after it, before the first `msm_sharded` of any rank."""
         blob = self.peer_export()
         blobs = all_gather_bytes(blob) if all_gather_bytes is not None else [blob] * world
         assert len(blobs) == world and all(len(b) == _lib.PEER_HANDLE_BYTES for b in blobs)
