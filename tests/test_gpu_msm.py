@@ -436,6 +436,22 @@ def test_msm_sharded_peer_exchange(world, n):
         c.close()
 
 
+@pytest.mark.parametrize("n", [6000, 1 << 18])
+def test_msm_sharded_across_processes_over_ipc(n):
+    """The deployment shape of bench.py --gpus N: one PROCESS per rank, mailboxes opened through CUDA IPC handles (the in-process
+    tests above hand raw pointers over).  Two gloo ranks (tests/_dist_gpu_worker.py); equal shard sizes so that both ranks reduce
+    with the same window geometry."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29541")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29541", os.path.join(root, "tests", "_dist_gpu_worker.py"), str(n)]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 def test_msm_sharded_reports_a_missing_peer():
     import h2b200
     ctxs = [h2b200.Context([0]) for _ in range(2)]
@@ -628,6 +644,53 @@ def test_full_size_msm_matches_the_oracle_directly(ctx, engine):
     s, b = d_s.cpu().numpy().view(np.uint64), d_b.cpu().numpy().view(np.uint64)
     assert np.array_equal(s[:1000], C.random_fr_chacha20(1000, C.SEED_SCALARS))
     check(got, oracle_affine(s, b))
+
+
+@pytest.mark.parametrize("k", [20, 22, 26])
+def test_sweep_sizes_match_the_oracle_directly(ctx, engine, k):
+    """BASELINE configs[1] names a sweep 2^16 .. 2^26: the sizes between the small cases above and the 2^24 headline, and the top of
+    the sweep (2^26: 4 GiB of bases, ~56 GB of window multiples, ~40 s of CPU), each compared with the C port itself."""
+    import torch
+    import h2b200
+    n = 1 << k
+    C.use_all_host_cores()
+    d_b = h2b200.synth.device_bases(ctx, n, C.bench_t0() + 1000 * k)
+    d_s = h2b200.synth.chacha_scalars_device(ctx, n, bytes([k]) * 32)
+    desc = engine.get_base_descriptor(d_b)
+    got = engine.msm_with_cached_base(d_s, desc)
+    desc.release()
+    s, b = d_s.cpu().numpy().view(np.uint64), d_b.cpu().numpy().view(np.uint64)
+    del d_s, d_b
+    torch.cuda.empty_cache()
+    check(got, oracle_affine(s, b))
+
+
+@pytest.mark.parametrize("kind", ["mostly_zero_or_one", "below_2p16"])
+def test_non_uniform_scalars_at_2p22(ctx, engine, kind):
+    """SURVEY.md 8(d)'s two non-uniform scalar sets at scale (the shapes real witnesses have: selector-like columns that are 90 % zeros
+    and ones; small range-checked values): a handful of buckets take nearly every point (the long-bucket path), most windows are empty."""
+    import torch
+    import h2b200
+    n = 1 << 22
+    C.use_all_host_cores()
+    rng = np.random.default_rng(5)
+    if kind == "mostly_zero_or_one":
+        s = C.random_fr_chacha20(n, bytes([9]) * 32)
+        u = rng.random(n)
+        s[u < 0.45] = 0
+        s[(u >= 0.45) & (u < 0.90)] = C.mont_from_int(1, R.R_MOD)
+    else:
+        table = C.fr_array_from_ints(list(range(1 << 16)), R.R_MOD)
+        s = np.ascontiguousarray(table[rng.integers(0, 1 << 16, size=n)])
+    d_b = h2b200.synth.device_bases(ctx, n, C.bench_t0() + 77)
+    b = d_b.cpu().numpy().view(np.uint64)
+    desc = engine.get_base_descriptor(d_b)
+    got_host = engine.msm_with_cached_base(s, desc)                                               # pageable host scalars, chunked
+    got_dev = engine.msm_with_cached_base(torch.from_numpy(s.view(np.int64)).cuda(), desc)       # device-resident scalars
+    desc.release()
+    exp = oracle_affine(s, b)
+    check(got_host, exp)
+    check(got_dev, exp)
 
 
 def test_release_after_destroy_is_harmless():

@@ -210,6 +210,23 @@ def test_round_trip_largest_bench_size(ctx, k):
     assert torch.equal(d, orig)
 
 
+def test_largest_bench_size_matches_the_oracle_directly(ctx):
+    """The top of BASELINE's NTT sweep, 2^26 elements (2 GiB), forward transform against the C port itself (~15 s of CPU), not only
+    a round trip."""
+    import torch
+    import h2b200
+    k = 26
+    C.use_all_host_cores()
+    dom = h2b200.EvaluationDomain(1, k, ctx)
+    d = h2b200.synth.chacha_scalars_device(ctx, 1 << k, bytes([26]) * 32)
+    exp = C.best_fft(d.cpu().numpy().view(np.uint64), m(omega_for(k)), k)
+    dom.coeff_to_lagrange(d)
+    got = d.cpu().numpy().view(np.uint64)
+    del d
+    torch.cuda.empty_cache()
+    assert np.array_equal(got, exp)
+
+
 @pytest.mark.parametrize("k,split", [(20, "5,5,5,5"), (22, "6,6,5,5"), (21, "9,3,3,6")])
 def test_four_pass_splits_at_real_sizes(ctx, k, split, knob):
     """The 4-pass plan is the default only from k = 28; forced here at sizes the oracle checks in a second."""
