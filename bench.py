@@ -284,7 +284,7 @@ def proof_sequence_resident(ctx, eng):
     return ms, ctx.launch_count() - l0
 
 
-def k20_proof(ctx, eng, k: int = SEQ_K, reps: int = 3):
+def k20_proof(ctx, eng, k: int = SEQ_K, reps: int = 3, circuit: str = "MyCircuit", threads: int = 16):
     """A real proof: the reference's frontend_backend_split circuit (gate with rotation, lookup, shuffle, copy constraints,
     second-phase column, instance) at 2^k rows, through the prover mirror (plonk.create_proof = keygen'd pk + ProverSingle +
     SHPLONK + Blake2b transcript) with every vector on the device.  tests/test_gpu_plonk.py checks the same path byte for byte
@@ -297,7 +297,7 @@ def k20_proof(ctx, eng, k: int = SEQ_K, reps: int = 3):
     from h2b200.plonk import example, rng as RNG
     from h2b200.plonk.ops import DeviceOps
     t0 = time.perf_counter()
-    circ = example.MyCircuit(k, 42)
+    circ = example.MyCircuit(k, 42) if circuit == "MyCircuit" else example.StandardPlonk(k, 7, 5)
     cc = circ.compile()
     cs = plonk.circuit.ConstraintSystemBack(cc.cs)
     params = h2b200.ParamsKZG.setup(k, 0x1234567, eng)
@@ -311,19 +311,85 @@ def k20_proof(ctx, eng, k: int = SEQ_K, reps: int = 3):
         l0 = ctx.launch_count()
         torch.cuda.synchronize()
         t = time.perf_counter()
-        plonk.create_proof(ops, pk, circ.instances(), circ.witness, RNG.OneNg(), tr, num_threads=16)
+        plonk.create_proof(ops, pk, circ.instances(), circ.witness, RNG.OneNg(), tr, num_threads=threads)
         torch.cuda.synchronize()
         if rep:
             times.append((time.perf_counter() - t) * 1e3)
         launches = ctx.launch_count() - l0
         proof = tr.finalize()
     d = ops.domain
-    return {"what": f"create_proof of the frontend_backend_split circuit at k = {k} (KZG / SHPLONK / Blake2b; degree {cs.degree()}, "
-                    f"extended_k = {d.extended_k}, {circ.units} units of 51 rows), host witness columns in, proof bytes out",
+    # the same proof written by the independent python-int oracle (tests/golden/make_golden_large.py; same circuit, SRS secret, RNG and
+    # thread count): the bytes must be identical.  None = no stored proof for this k.
+    gold_name = f"frontend_backend_split_k{k}_oneng_t{threads}" if circuit == "MyCircuit" else f"standard_plonk_k{k}_mindeg5_oneng_t{threads}"
+    gold_path = os.path.join(ROOT, "tests", "golden", "large", gold_name + ".json")
+    matches = (json.load(open(gold_path))["sha256"] == hashlib.sha256(proof).hexdigest()) if os.path.exists(gold_path) else None
+    if matches is False:
+        raise SystemExit(f"bench: the k = {k} proof differs from the oracle's stored proof ({gold_path})")
+    return {"matches_oracle_sha": matches,
+            "what": (f"create_proof of the frontend_backend_split circuit at k = {k} (KZG / SHPLONK / Blake2b; degree {cs.degree()}, "
+                     f"extended_k = {d.extended_k}, {circ.units} units of 51 rows), host witness columns in, proof bytes out") if circuit == "MyCircuit" else
+                    (f"create_proof of the simple example circuit of halo2_proofs/benches/plonk.rs (StandardPlonk, minimum_degree 5) at k = {k} "
+                     f"(KZG / SHPLONK / Blake2b; extended_k = {d.extended_k}): BASELINE.json configs[0]; launch / latency bound at this size"),
             "value": min(times), "unit": "ms", "runs_ms": times, "gpu_launches": launches, "proof_bytes": len(proof),
-            "proof_sha256": hashlib.sha256(proof).hexdigest(), "rng": "OneNg, num_threads = 16",
+            "proof_sha256": hashlib.sha256(proof).hexdigest(), "rng": f"OneNg, num_threads = {threads}",
             "h2d_bytes_per_proof": 4 * 32 * (1 << k), "d2h_bytes_per_proof": len(proof),
             "setup_keygen_s": setup_s, "verified": "tests/test_gpu_plonk.py (verify_proof restatement, and proof bytes == CPU restatement)"}
+
+
+def msm_raw_bench(ctx, eng):
+    """What an unmodified caller gets: ParamsKZG::commit_lagrange calls plain `engine.msm(&scalars, &bases)` (kzg/commitment.rs:305-317 ->
+    zal.rs:58), i.e. h2b_msm_raw: the bases cross PCIe for this call only and no window multiples exist (one bucket set per window)."""
+    out = {"what": "h2b_msm_raw (MsmAccel::msm): pageable host scalars AND pageable host bases in, nothing registered or cached; "
+                   "best of 3 after one warm-up call", "unit": "ms", "sizes": {}}
+    import torch
+    import h2b200
+    for k in (20, 24):
+        n = 1 << k
+        b = h2b200.synth.device_bases(ctx, n, h2b200.synth.bench_t0()).cpu().numpy().view(np.uint64)
+        s = h2b200.synth.chacha_scalars_device(ctx, n).cpu().numpy().view(np.uint64)
+        torch.cuda.empty_cache()
+        ts, res = [], None
+        for rep in range(4):
+            t = time.perf_counter()
+            res = eng.msm(s, b)
+            if rep:
+                ts.append((time.perf_counter() - t) * 1e3)
+        out["sizes"][f"2^{k}"] = {"value": min(ts), "runs_ms": ts, "h2d_bytes": 96 * n, "result_sha256": point_sha256(res)}
+        gold = json.load(open(os.path.join(ROOT, "tests", "golden", "msm_results.json"))).get(str(k))
+        if gold:          # the seeded problem of the headline bench: same committed result, through the uncached path
+            out["sizes"][f"2^{k}"]["result_matches_golden_sha"] = point_sha256(res) == gold["affine_sha256"]
+            if not out["sizes"][f"2^{k}"]["result_matches_golden_sha"]:
+                raise SystemExit(f"bench: h2b_msm_raw at 2^{k} differs from the committed oracle result")
+    return out
+
+
+def multi_gpu_proof(world: int, timeout_s: int = 420):
+    """BASELINE.json configs[4] under the driver's eyes: after the ranks of the sharded bench have released their GPUs, rank 0 runs ONE
+    process with one context over all N devices (scripts/prove_k.py, H2B_COSETS=1: MSMs sharded by point range inside the library, the
+    quotient evaluated coset by coset over the devices, plonk/evaluation.rs:344-361) -- k = 24 on 8 GPUs, 22 on 4, 21 on 2 -- one
+    warm-up proof and two timed ones, verified by the verify_proof restatement.  Any failure is reported, never fatal to the line."""
+    k = {2: 21, 4: 22, 8: 24}.get(world)
+    if k is None:
+        return {"skipped": f"no multi-GPU proof size is defined for {world} GPUs"}
+    env = dict(os.environ, H2B_DEVICES=",".join(str(i) for i in range(world)), H2B_COSETS="1", H2B_VERIFY="1")
+    for var in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS"):
+        env.pop(var, None)
+    t0 = time.perf_counter()
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "prove_k.py"), str(k), "3"], env=env, capture_output=True,
+                           text=True, timeout=timeout_s)
+    except subprocess.TimeoutExpired:
+        return {"k": k, "skipped": f"scripts/prove_k.py did not finish within {timeout_s} s"}
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    if r.returncode != 0 or not lines:
+        return {"k": k, "failed": (r.stderr or r.stdout)[-600:]}
+    out = json.loads(lines[-1])
+    runs = [x["ms"] for x in out["runs"]]
+    return {"what": f"create_proof of the frontend_backend_split circuit at k = {k}, one process, one context over {world} GPUs, quotient by cosets "
+                    "(configs[4] shape); host witness columns in, proof bytes out; first run (warm-up: tables, key cosets) excluded",
+            "k": k, "devices": out["devices"], "value": min(runs[1:]), "unit": "ms", "runs_ms": runs, "gpu_launches_device0_context": out["runs"][-1]["launches"],
+            "proof_sha256": out["proof_sha256"], "verified": out.get("verified"), "per_device_used_gib": out.get("per_device_used_gib"),
+            "script_wall_s": time.perf_counter() - t0}
 
 
 def proof_sequence_cpu():
@@ -698,6 +764,8 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
                     "quotient folds over 2^23 rows and the opening helpers (SURVEY 8f N1-N3) on the device; witness upload included",
             "extra_counts": RES_COUNTS, "value": res_ms, "unit": "ms", "gpu_launches": res_launches}
         line["k20_proof"] = k20_proof(ctx, eng)
+        line["k12_proof"] = k20_proof(ctx, eng, k=12, reps=5, circuit="StandardPlonk", threads=2)
+        line["msm_raw"] = msm_raw_bench(ctx, eng)
         if not args.no_cpu:
             cpu_total, cpu_parts, thr = proof_sequence_cpu()
             line["k20_kernel_sequence"]["cpu_baseline"] = {"value": cpu_total, "unit": "ms", "cores": thr, "kind": "port",
@@ -708,6 +776,9 @@ def run_gpu(args, rank: int, world: int, local_rank: int):
     ctx.close()
     if world > 1:
         dist.destroy_process_group()
+        if not args.no_seq:
+            torch.cuda.empty_cache()
+            line["proof_multi_gpu"] = multi_gpu_proof(world)
     if world == 1 and not args.no_cpu:
         # the CPU port beside it, on the SAME inputs at the SAME size (one full 2^24 MSM, ~10 s; one full 2^24 NTT, ~3 s), and the
         # one check of the GPU result against the oracle at the headline size
